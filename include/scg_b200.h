@@ -1,0 +1,269 @@
+/*
+ * scg_b200.h -- C ABI of the B200-native batched env-step library (libscg_b200.so).
+ *
+ * Drop-in boundary for ONE hot path of ekumenlabs/safe-control-gym: the per-control-step
+ * work of Quadrotor.step()/reset() with physics=DYN (and the CartPole symbolic step), run
+ * in lock-step over N independent environments on one GPU.  The reference has no FFI for
+ * this path (it is pure Python); each entry point below names the reference interface it
+ * replaces (paths under safe_control_gym/).  The Python binding a maintainer would add is
+ * a ctypes stub; safe_control_gym_b200/_lib.py is that stub.
+ *
+ * Conventions
+ *  - plain C types only; every function returns an int status (SCG_OK = 0, negative =
+ *    error; scg_last_error() gives the text); nothing throws, nothing aborts.
+ *  - all batch memory is owned by the CALLER (device pointers, e.g. torch tensors);
+ *    the library owns only a small per-handle constant block.
+ *  - work is enqueued on the given CUDA stream (cudaStream_t passed as void*), no hidden
+ *    synchronisation.  One handle is used from one host thread at a time.
+ *  - batch tensors are struct-of-arrays "[field][n]" of the handle's real type
+ *    (float for precision 32, double for 64) unless stated; actions are env-major
+ *    "[n][nu]" (one 16-byte vector load per 3D env).
+ */
+#ifndef SCG_B200_H
+#define SCG_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SCG_OK 0
+#define SCG_ERR_BAD_CONFIG (-1)
+#define SCG_ERR_NULL (-2)
+#define SCG_ERR_SHAPE (-3)
+#define SCG_ERR_STATE (-4)   /* e.g. step before reset (benchmark_env.py:268-275) */
+#define SCG_ERR_CUDA (-100)  /* -100 - cudaError_t */
+
+#define SCG_MAX_NX 12
+#define SCG_MAX_NU 4
+#define SCG_MAX_CONSTRAINTS 8   /* constraint objects (YAML entries) */
+#define SCG_MAX_CON_ROWS 24     /* values per object: bounded = 2 * 12 */
+#define SCG_MAX_ROWS 64         /* total constraint values */
+#define SCG_MAX_DIST 4          /* disturbances per channel */
+#define SCG_MAX_GATES 8
+#define SCG_MAX_OBSTACLES 8
+#define SCG_STATS_LEN 16
+
+/* env_kind: QuadType (quadrotor_utils.py:11-18) or the cart-pole */
+enum { SCG_QUAD_1D = 1, SCG_QUAD_2D = 2, SCG_QUAD_3D = 3, SCG_CARTPOLE = 10 };
+/* Task / Cost (benchmark_env.py:19-33) */
+enum { SCG_TASK_STABILIZATION = 0, SCG_TASK_TRAJ_TRACKING = 1 };
+enum { SCG_COST_RL_REWARD = 0, SCG_COST_QUADRATIC = 1, SCG_COST_COMPETITION = 2 };
+/* constraint_form (constraints.py:586-591, 371-415) */
+enum { SCG_CON_BOUNDED = 0, SCG_CON_LINEAR = 1, SCG_CON_QUADRATIC = 2, SCG_CON_SYMMETRIC = 3 };
+enum { SCG_VAR_STATE = 0, SCG_VAR_INPUT = 1 };
+/* disturbance_func (disturbances.py:307-312) and channel (quadrotor.py:808-813) */
+enum { SCG_DIST_IMPULSE = 0, SCG_DIST_STEP = 1, SCG_DIST_UNIFORM = 2, SCG_DIST_WHITE = 3, SCG_DIST_PERIODIC = 4 };
+enum { SCG_CH_OBSERVATION = 0, SCG_CH_ACTION = 1, SCG_CH_DYNAMICS = 2 };
+/* distribution of a randomised reset value (benchmark_env.py:277-308) */
+enum { SCG_RAND_NONE = 0, SCG_RAND_UNIFORM = 1, SCG_RAND_NORMAL = 2 };
+/* attitude update: literal PyBullet quaternion round trip, or the equivalent wrap with
+ * the round trip kept only outside the identity region */
+enum { SCG_ATT_ROUNDTRIP = 0, SCG_ATT_FAST = 1 };
+/* scg_symbolic_eval ops (symbolic_systems.py:63-123) */
+enum { SCG_SYM_FC = 0, SCG_SYM_FD_RK4 = 1, SCG_SYM_DF = 2, SCG_SYM_LOSS = 3, SCG_SYM_FD_EULER = 4 };
+
+/* info bits written per env by scg_step (quadrotor.py:1004-1134, benchmark_env.py:437-461) */
+#define SCG_INFO_VIOLATION   0x01u  /* info["constraint_violation"] */
+#define SCG_INFO_TRUNCATED   0x02u  /* info["TimeLimit.truncated"]  */
+#define SCG_INFO_COLLISION   0x04u  /* info["collision"][1]          */
+#define SCG_INFO_GATE_PASSED 0x08u  /* stepped_through_gate          */
+#define SCG_INFO_AT_GOAL     0x10u  /* info["at_goal_position"]      */
+#define SCG_INFO_COMPLETED   0x20u  /* info["task_completed"]        */
+#define SCG_INFO_GOAL_REACHED 0x40u /* info["goal_reached"]          */
+#define SCG_INFO_OUT_OF_BOUND 0x80u /* out-of-bound termination      */
+
+/* layout of the per-env packed "flags" word kept between steps */
+#define SCG_FLAG_CNSTR_VIOLATION 0x1u  /* previous step's violation (benchmark_env.py:438-449, F8) */
+#define SCG_FLAG_AT_GOAL         0x2u
+#define SCG_FLAG_FLIPPED         0x4u  /* 2D: Euler fold left roll = yaw = pi */
+#define SCG_FLAG_COMPLETED       0x8u
+#define SCG_FLAG_GATE_SHIFT 8          /* bits 8..15  current_gate       */
+#define SCG_FLAG_HOLD_SHIFT 16         /* bits 16..31 steps_at_goal_pos  */
+
+/* indices into the float64[SCG_STATS_LEN] episode-statistics vector (record_episode_statistics.py:142-169) */
+enum { SCG_STAT_EPISODES = 0, SCG_STAT_RETURN = 1, SCG_STAT_LENGTH = 2, SCG_STAT_VIOLATION_STEPS = 3,
+       SCG_STAT_MSE = 4, SCG_STAT_GATES = 5, SCG_STAT_COLLISIONS = 6, SCG_STAT_TRUNCATED = 7,
+       SCG_STAT_COMPLETED = 8, SCG_STAT_ENV_STEPS = 9, SCG_STAT_VIOLATED_EPISODES = 10 };
+
+/* one YAML constraint entry (constraints.py:21-415) */
+typedef struct {
+    int32_t form;                          /* SCG_CON_*  */
+    int32_t var;                           /* SCG_VAR_*  */
+    int32_t strict;                        /* constraints.py:137-140 */
+    int32_t n_rows;                        /* num_constraints */
+    int32_t n_active;                      /* filtered input dim */
+    int32_t active_dims[SCG_MAX_NX];       /* rows of the filter eye(dim)[active_dims] (:77) */
+    double lower[SCG_MAX_NX];              /* bounded / default / symmetric(-bound) */
+    double upper[SCG_MAX_NX];
+    double A[SCG_MAX_NX * SCG_MAX_NX];     /* linear: n_rows x n_active row-major; quadratic: P */
+    double b[SCG_MAX_CON_ROWS];            /* linear rows / quadratic b[0] */
+    int32_t has_tolerance;                 /* is_almost_active (:143-158) */
+    double tolerance[SCG_MAX_CON_ROWS];
+} scg_constraint;
+
+/* one YAML disturbance entry (disturbances.py:89-288) */
+typedef struct {
+    int32_t kind;                          /* SCG_DIST_* */
+    int32_t slot;                          /* row in dist_offset / Philox randint slot: running index
+                                              over all disturbances in YAML order (DisturbanceList.reset) */
+    int32_t has_mask;
+    double mask[SCG_MAX_NX];
+    double magnitude;                      /* impulse / step */
+    int32_t step_offset;                   /* >= 0 fixed, -1 = randint(max_step) at reset */
+    int32_t max_step;                      /* int(EPISODE_LEN_SEC / CTRL_TIMESTEP) */
+    double duration, decay_rate;           /* impulse */
+    double low[SCG_MAX_NX], high[SCG_MAX_NX]; /* uniform */
+    double std[SCG_MAX_NX];                /* white noise */
+    double scale, frequency;               /* periodic */
+    /* optional injected draws, device pointer [dim][n] for the NEXT step/reset call (raw
+     * values as numpy would return them: U(low,high), N(0,std), phase); NULL = Philox */
+    const void* inject;
+} scg_disturbance;
+
+typedef struct {
+    int32_t distrib;                       /* SCG_RAND_* */
+    double a, b;                           /* uniform: low, high; normal: loc, scale */
+} scg_rand;
+
+/* everything Quadrotor.__init__ / BenchmarkEnv.__init__ derive from the YAML kwargs */
+typedef struct {
+    int32_t env_kind, precision, attitude_mode;
+    int32_t substeps;                      /* PYB_STEPS_PER_CTRL (benchmark_env.py:156) */
+    int32_t ctrl_steps;                    /* CTRL_STEPS (:161) */
+    int32_t ctrl_freq, pyb_freq;
+    double pyb_dt;                         /* PYB_TIMESTEP == the DYN integrator step (F3) */
+    /* physical constants (base_aviary.py:104-147, cf2x.urdf) */
+    double mass, gravity_acc, gravity_force, J[3], J_inv[3], kf, km, arm;
+    double pwm2rpm_scale, pwm2rpm_const, pwm_min, pwm_max;
+    /* cart-pole (A13): effective pole half-length, pole mass, cart mass */
+    double cp_length, cp_pole_mass, cp_cart_mass;
+    /* action map (quadrotor.py:699-733, 815-842) */
+    int32_t normalized_action;
+    double norm_act_scale, hover_thrust;
+    double act_low[SCG_MAX_NU], act_high[SCG_MAX_NU];
+    /* state space (quadrotor.py:735-806) */
+    double state_low[SCG_MAX_NX], state_high[SCG_MAX_NX];
+    int32_t done_on_out_of_bound;
+    /* task / cost */
+    int32_t task, cost, rew_exponential, obs_goal_horizon;
+    double rew_state_weight[SCG_MAX_NX], rew_act_weight[SCG_MAX_NU];
+    double Q[SCG_MAX_NX * SCG_MAX_NX], R[SCG_MAX_NU * SCG_MAX_NU];
+    double u_goal[SCG_MAX_NU], mse_weight[SCG_MAX_NX], goal_tolerance;
+    int32_t n_goal_rows;                   /* 1 (stabilisation) or T (trajectory) */
+    const double* x_goal;                  /* HOST pointer, n_goal_rows x nx row-major (copied) */
+    /* termination (benchmark_env.py:422-463, quadrotor.py:956-1002) */
+    int32_t done_on_violation, done_on_collision, done_on_completion;
+    int32_t use_constraint_penalty;
+    double constraint_penalty;
+    /* constraints */
+    int32_t n_constraints;
+    scg_constraint constraints[SCG_MAX_CONSTRAINTS];
+    /* disturbances: [channel][k] */
+    int32_t n_dist[3];
+    scg_disturbance dist[3][SCG_MAX_DIST];
+    int32_t adversary_channel;             /* -1 none, SCG_CH_ACTION, SCG_CH_DYNAMICS */
+    /* reset (quadrotor.py:356-504) */
+    double init_state[SCG_MAX_NX + 1];     /* nominal INIT_*, state order; 3D/1D unused tail = 0 */
+    scg_rand init_rand[SCG_MAX_NX];
+    double inertia_nominal[4];             /* M, Ixx, Iyy, Izz after inertial_prop override */
+    scg_rand inertia_rand[4];
+    int32_t reseed_on_reset;               /* every episode replays episode 0's draws */
+    /* gates / obstacles (quadrotor.py:371-434, 1060-1130) */
+    int32_t n_gates, n_obstacles;
+    double gates[SCG_MAX_GATES][7];
+    double obstacles[SCG_MAX_OBSTACLES][6];
+    scg_rand gate_rand, obstacle_rand;
+    /* RNG contract (oracle/philox.py): key = (seed, env_id_base + i) */
+    uint32_t seed;
+    int64_t env_id_base;
+    /* extensions beyond the reference's DYN behaviour (off = parity mode) */
+    int32_t dyn_uses_episode_inertia;      /* F9 */
+    int32_t dyn_applies_force;             /* F5 */
+    int32_t gate_geometry;                 /* analytic gate-pass / collision tests */
+    int32_t auto_reset;                    /* DummyVecEnv.step_wait semantics (dummy_vec_env.py:38-49) */
+} scg_config;
+
+/* caller-owned batch memory (device pointers; NULL = not wanted where marked optional) */
+typedef struct {
+    int64_t n;
+    /* persistent per-env state */
+    void* state;              /* [nx][n] real, reference state order; angles are the pre-round-trip Euler
+                                 angles, rate slots hold rpy_rates (base_aviary.py:576) */
+    int32_t* ctrl_step;       /* [n] ctrl_step_counter */
+    int32_t* episode;         /* [n] episodes started (Philox counter word) */
+    uint32_t* flags;          /* [n] SCG_FLAG_* */
+    int32_t* dist_offset;     /* [sum n_dist][n] impulse / step offsets, optional if none */
+    void* inertia;            /* [4][n] real episode M, Ixx, Iyy, Izz, optional */
+    /* per-step outputs */
+    void* obs;                /* [obs_dim][n] */
+    void* env_state;          /* [nx][n] env.state (optional) */
+    void* reward;             /* [n] */
+    uint8_t* done;            /* [n] */
+    uint8_t* info;            /* [n] SCG_INFO_* */
+    void* mse;                /* [n] optional */
+    void* c_values;           /* [rows][n] optional, info["constraint_values"] */
+    void* terminal_obs;       /* [obs_dim][n] optional (auto_reset) */
+    /* episode statistics (optional) */
+    void* ep_return;          /* [n] real running return */
+    int32_t* ep_length;       /* [n] */
+    int32_t* ep_violations;   /* [n] */
+    double* stats;            /* [SCG_STATS_LEN] device accumulators */
+    /* adversary action for the next step, [n][dim] env-major (optional) */
+    const void* adv_action;
+} scg_buffers;
+
+/* K-step fused rollout (state stays in registers for all K * substeps integrator steps) */
+typedef struct {
+    const void* actions;      /* [K][n][nu] real, device */
+    int32_t k_steps;
+    void* reward_out;         /* [K][n] optional */
+    uint8_t* done_out;        /* [K][n] optional */
+    void* log_out;            /* [K][16][n] optional: pos3 vel3 rpy3 ang_vel3 rpm4 (Logger.py:50-66) */
+    int32_t log_stride;       /* log every log_stride-th ctrl step (>= 1) */
+} scg_rollout_args;
+
+typedef struct scg_env scg_env;
+
+/* Quadrotor.__init__ (quadrotor.py:148-354) / make() (utils/registration.py:145-149) */
+int scg_create(const scg_config* cfg, scg_env** out);
+/* close() (base_aviary.py:198-206) */
+int scg_destroy(scg_env* env);
+/* (re)bind the batch tensors; validates n and required pointers */
+int scg_bind_buffers(scg_env* env, const scg_buffers* buf);
+/* update injected-draw pointers / adversary pointer between calls (cheap, host only) */
+int scg_set_injection(scg_env* env, int channel, int k, const void* dev_ptr);
+/* Quadrotor.reset() (quadrotor.py:356-504): mask = NULL resets every env, else envs with
+ * mask[i] != 0.  inject_* optional device tensors of pre-drawn additive offsets:
+ * init [nx][n], inertia [4][n], dist offsets [slots][n]. */
+int scg_reset(scg_env* env, const uint8_t* mask, const void* inject_init, const void* inject_inertia,
+              const int32_t* inject_offsets, void* stream);
+/* Quadrotor.step(action) (quadrotor.py:507-558) for all n envs; action [n][nu] device */
+int scg_step(scg_env* env, const void* action, void* stream);
+/* K fused ctrl steps with auto-reset; the batched analogue of the PPO rollout loop
+ * (controllers/ppo/ppo.py:247-273) driving DummyVecEnv.step_wait */
+int scg_rollout(scg_env* env, const scg_rollout_args* args, void* stream);
+/* same, actions in pinned HOST memory [K][n][nu]; copies are chunked and overlapped
+ * with compute on an internal copy stream; final obs / reward sums land in the bound buffers */
+int scg_rollout_host(scg_env* env, const void* host_actions, int32_t k_steps, int32_t chunk_steps, void* stream);
+/* zero / read the float64[SCG_STATS_LEN] statistics vector (async copy to host_out) */
+int scg_stats_reset(scg_env* env, void* stream);
+int scg_stats_read(scg_env* env, double* host_out, void* stream);
+/* ConstraintList.get_values / is_violated (constraints.py:503-563) on caller-given
+ * state [nx][n] and raw action [n][nu]; out_values [rows][n], out_flags [n] */
+int scg_constraints_eval(scg_env* env, const void* state, const void* action, int64_t n,
+                         void* out_values, uint8_t* out_flags, void* stream);
+/* SymbolicModel.fc_func / fd (RK4, mpc_utils.py:79-101) / df_func / loss
+ * (symbolic_systems.py:63-123): x [nx][n], u [nu][n]; out layout per op */
+int scg_symbolic_eval(scg_env* env, int op, const void* x, const void* u, int64_t n, double dt,
+                      void* out0, void* out1, void* stream);
+/* number of kernels this handle has launched (bench.py "gpu_launches") */
+int64_t scg_launch_count(const scg_env* env);
+const char* scg_last_error(void);
+const char* scg_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SCG_B200_H */

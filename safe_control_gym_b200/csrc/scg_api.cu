@@ -1,0 +1,492 @@
+// scg_api.cu -- host side of libscg_b200.so: the extern "C" ABI declared in include/scg_b200.h.
+// Builds the device parameter blocks from scg_config, validates shapes, and launches the fused
+// kernels of scg_step.cuh / scg_cartpole.cuh / scg_symbolic.cuh on the caller's stream.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <new>
+#include <string>
+
+#include "scg_step.cuh"
+#include "scg_cartpole.cuh"
+#include "scg_symbolic.cuh"
+
+using namespace scg;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+static int cuda_fail(cudaError_t e, const char* what) {
+    g_err = std::string(what) + ": " + cudaGetErrorString(e);
+    return SCG_ERR_CUDA - int(e);
+}
+#define CU(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return cuda_fail(_e, #x); } while (0)
+
+struct scg_env {
+    scg_config cfg;
+    int nx, nu, obs_dim, n_rows, n_slots;
+    Hot<float> hf;
+    Hot<double> hd;
+    void* cold_dev = nullptr;      // Cold<float> or Cold<double>
+    void* cold_host = nullptr;     // host mirror (for injection pointer updates)
+    void* x_goal_dev = nullptr;
+    scg_buffers buf;
+    bool bound = false, did_reset = false;
+    int64_t launches = 0;
+    // scg_rollout_host staging
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};
+    void* stage[2] = {nullptr, nullptr};
+    size_t stage_bytes = 0;
+};
+
+static int kind_dims(int kind, int* nx, int* nu) {
+    switch (kind) {
+        case SCG_QUAD_1D: *nx = 2; *nu = 1; return 0;
+        case SCG_QUAD_2D: *nx = 6; *nu = 2; return 0;
+        case SCG_QUAD_3D: *nx = 12; *nu = 4; return 0;
+        case SCG_CARTPOLE: *nx = 4; *nu = 1; return 0;
+    }
+    return -1;
+}
+
+template <typename real>
+static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<real>& k, int* n_rows_out, int* n_slots_out) {
+    std::memset(&h, 0, sizeof(h));
+    std::memset(&k, 0, sizeof(k));
+    const real INF = std::numeric_limits<real>::infinity();
+    h.substeps = c.substeps; h.ctrl_steps = c.ctrl_steps; h.ctrl_freq = c.ctrl_freq; h.pyb_freq = c.pyb_freq;
+    h.dt = real(c.pyb_dt);
+    h.kf = real(c.kf); h.km = real(c.km); h.arm_s2 = real(c.arm / std::sqrt(2.0));
+    h.inv_mass = real(1.0 / c.mass); h.gravity_force = real(c.gravity_force);
+    for (int j = 0; j < 3; ++j) { h.J[j] = real(c.J[j]); h.J_inv[j] = real(c.J_inv[j]); }
+    h.pwm_scale = real(c.pwm2rpm_scale); h.pwm_const = real(c.pwm2rpm_const);
+    h.pwm_min = real(c.pwm_min); h.pwm_max = real(c.pwm_max); h.inv_pwm_scale = real(1.0 / c.pwm2rpm_scale);
+    if (c.env_kind != SCG_CARTPOLE) h.inv_nkf = real(1.0 / ((4 / nu) * c.kf));
+    h.normalized_action = c.normalized_action; h.norm_act_scale = real(c.norm_act_scale); h.hover_thrust = real(c.hover_thrust);
+    for (int j = 0; j < nu; ++j) { h.act_low[j] = real(c.act_low[j]); h.act_high[j] = real(c.act_high[j]); }
+    for (int d = 0; d < nx; ++d) {
+        h.state_low[d] = real(c.state_low[d]); h.state_high[d] = real(c.state_high[d]);
+        h.rew_state_weight[d] = real(c.rew_state_weight[d]); h.mse_weight[d] = real(c.mse_weight[d]);
+        h.x_goal0[d] = c.x_goal ? real(c.x_goal[d]) : real(0);
+        h.init_state[d] = real(c.init_state[d]);
+    }
+    for (int j = 0; j < nu; ++j) { h.rew_act_weight[j] = real(c.rew_act_weight[j]); h.u_goal[j] = real(c.u_goal[j]); }
+    h.done_on_out_of_bound = c.done_on_out_of_bound; h.done_on_violation = c.done_on_violation;
+    h.done_on_collision = c.done_on_collision; h.done_on_completion = c.done_on_completion;
+    h.task = c.task; h.cost = c.cost; h.rew_exponential = c.rew_exponential; h.obs_goal_horizon = c.obs_goal_horizon;
+    h.n_goal_rows = c.n_goal_rows; h.goal_tol = real(c.goal_tolerance);
+    h.use_constraint_penalty = c.use_constraint_penalty; h.constraint_penalty = real(c.constraint_penalty);
+    // quadratic cost: diagonal fast path
+    bool diag = true;
+    for (int a = 0; a < nx; ++a) for (int b = 0; b < nx; ++b) {
+        k.Q[a * SCG_MAX_NX + b] = real(c.Q[a * SCG_MAX_NX + b]);
+        if (a != b && c.Q[a * SCG_MAX_NX + b] != 0.0) diag = false;
+    }
+    for (int a = 0; a < nu; ++a) for (int b = 0; b < nu; ++b) {
+        k.R[a * SCG_MAX_NU + b] = real(c.R[a * SCG_MAX_NU + b]);
+        if (a != b && c.R[a * SCG_MAX_NU + b] != 0.0) diag = false;
+    }
+    h.quadratic_diag = diag ? 1 : 0;
+    for (int a = 0; a < nx; ++a) h.q_diag[a] = real(c.Q[a * SCG_MAX_NX + a]);
+    for (int a = 0; a < nu; ++a) h.r_diag[a] = real(c.R[a * SCG_MAX_NU + a]);
+    // ---- constraints: bounded objects -> per-dim tables (hot), everything else -> dense rows (cold)
+    int row = 0, nb = 0, nd = 0, np = 0;
+    if (c.n_constraints < 0 || c.n_constraints > SCG_MAX_CONSTRAINTS) return fail(SCG_ERR_BAD_CONFIG, "n_constraints out of range");
+    for (int ci = 0; ci < c.n_constraints; ++ci) {
+        const scg_constraint& s = c.constraints[ci];
+        const int full = s.var == SCG_VAR_STATE ? nx : nu;
+        if (s.var != SCG_VAR_STATE && s.var != SCG_VAR_INPUT) return fail(SCG_ERR_BAD_CONFIG, "constraint var must be state or input");
+        if (s.n_active < 1 || s.n_active > full) return fail(SCG_ERR_BAD_CONFIG, "constraint n_active out of range");
+        for (int j = 0; j < s.n_active; ++j)
+            if (s.active_dims[j] < 0 || s.active_dims[j] >= full) return fail(SCG_ERR_BAD_CONFIG, "active_dim not strictly smaller than dim");
+        if (s.form == SCG_CON_BOUNDED || s.form == SCG_CON_SYMMETRIC) {
+            if (nb >= MAX_BOUNDED) return fail(SCG_ERR_BAD_CONFIG, "too many bounded constraints");
+            BoundedCon<real>& bc = h.bounded[nb];
+            for (int d = 0; d < SCG_MAX_NX; ++d) { bc.lo[d] = -INF; bc.hi[d] = INF; bc.row_lo[d] = bc.row_hi[d] = -1; }
+            for (int d = 0; d < 2 * SCG_MAX_NX; ++d) k.bounded_tol[nb][d] = -INF;
+            bc.var = int8_t(s.var); bc.strict = int8_t(s.strict); bc.has_tol = int8_t(s.has_tolerance);
+            bc.symmetric = s.form == SCG_CON_SYMMETRIC;
+            const int nrows = bc.symmetric ? s.n_active : 2 * s.n_active;
+            if (s.n_rows != nrows) return fail(SCG_ERR_BAD_CONFIG, "bounded constraint n_rows mismatch");
+            for (int j = 0; j < s.n_active; ++j) {
+                const int d = s.active_dims[j];
+                if (bc.row_lo[d] >= 0) return fail(SCG_ERR_BAD_CONFIG, "duplicates in active_dims");
+                bc.lo[d] = real(s.lower[j]); bc.hi[d] = real(s.upper[j]);
+                bc.row_lo[d] = int8_t(row + j);
+                if (!bc.symmetric) bc.row_hi[d] = int8_t(row + s.n_active + j);
+                if (s.has_tolerance) {
+                    k.bounded_tol[nb][d] = real(s.tolerance[j]);
+                    if (!bc.symmetric) k.bounded_tol[nb][SCG_MAX_NX + d] = real(s.tolerance[s.n_active + j]);
+                }
+            }
+            if (s.has_tolerance) h.any_tolerance = 1;
+            row += nrows; ++nb;
+        } else if (s.form == SCG_CON_LINEAR) {
+            if (s.n_rows < 1 || s.n_rows > SCG_MAX_CON_ROWS) return fail(SCG_ERR_BAD_CONFIG, "linear constraint n_rows out of range");
+            for (int r = 0; r < s.n_rows; ++r) {
+                if (nd >= MAX_DENSE_ROWS) return fail(SCG_ERR_BAD_CONFIG, "too many dense constraint rows");
+                DenseRow<real>& dr = k.dense[nd++];
+                for (int j = 0; j < s.n_active; ++j) dr.a[s.active_dims[j]] += real(s.A[r * s.n_active + j]);
+                dr.b = real(s.b[r]); dr.var = int8_t(s.var); dr.strict = int8_t(s.strict);
+                dr.has_tol = int8_t(s.has_tolerance); dr.tol = s.has_tolerance ? real(s.tolerance[r]) : real(0);
+                dr.quadratic = 0; dr.out_row = row + r;
+            }
+            if (s.has_tolerance) h.any_tolerance = 1;
+            row += s.n_rows;
+        } else if (s.form == SCG_CON_QUADRATIC) {
+            if (nd >= MAX_DENSE_ROWS || np >= 2) return fail(SCG_ERR_BAD_CONFIG, "too many quadratic constraints");
+            DenseRow<real>& dr = k.dense[nd++];
+            for (int a = 0; a < s.n_active; ++a) for (int b = 0; b < s.n_active; ++b)   // P_full = F' P F
+                k.P[np][s.active_dims[a] * SCG_MAX_NX + s.active_dims[b]] += real(s.A[a * s.n_active + b]);
+            dr.b = real(s.b[0]); dr.var = int8_t(s.var); dr.strict = int8_t(s.strict);
+            dr.has_tol = int8_t(s.has_tolerance); dr.tol = s.has_tolerance ? real(s.tolerance[0]) : real(0);
+            dr.quadratic = 1; dr.p_index = np++; dr.out_row = row;
+            if (s.has_tolerance) h.any_tolerance = 1;
+            row += 1;
+        } else return fail(SCG_ERR_BAD_CONFIG, "unknown constraint form");
+    }
+    if (row > SCG_MAX_ROWS) return fail(SCG_ERR_BAD_CONFIG, "too many constraint rows");
+    h.n_bounded = nb; h.n_dense_rows = nd; h.n_rows = row;
+    *n_rows_out = row;
+    // ---- disturbances
+    int slots = 0;
+    const int dims[3] = {nx, nu, c.env_kind == SCG_CARTPOLE ? 2 : c.env_kind};
+    for (int ch = 0; ch < 3; ++ch) {
+        if (c.n_dist[ch] < 0 || c.n_dist[ch] > SCG_MAX_DIST) return fail(SCG_ERR_BAD_CONFIG, "n_dist out of range");
+        for (int q = 0; q < c.n_dist[ch]; ++q) {
+            const scg_disturbance& s = c.dist[ch][q];
+            DistP<real>& D = k.dist[ch][q];
+            if (s.kind < SCG_DIST_IMPULSE || s.kind > SCG_DIST_PERIODIC) return fail(SCG_ERR_BAD_CONFIG, "unknown disturbance kind");
+            D.kind = s.kind; D.has_mask = s.has_mask; D.step_offset = s.step_offset; D.max_step = s.max_step;
+            D.slot = s.slot; D.dim = dims[ch];
+            if (s.slot + 1 > slots) slots = s.slot + 1;
+            for (int d = 0; d < SCG_MAX_NX; ++d) {
+                D.mask[d] = real(s.mask[d]); D.low[d] = real(s.low[d]); D.span[d] = real(s.high[d] - s.low[d]); D.std[d] = real(s.std[d]);
+            }
+            D.magnitude = real(s.magnitude); D.duration = real(s.duration); D.half_duration = real(s.duration / 2.0);
+            D.decay_rate = real(s.decay_rate); D.scale = real(s.scale); D.omega = real(2.0 * M_PI * s.frequency);
+            D.inject = static_cast<const real*>(s.inject);
+        }
+    }
+    *n_slots_out = slots;
+    h.n_dist_obs = c.n_dist[0]; h.n_dist_act = c.n_dist[1]; h.n_dist_dyn = c.n_dist[2];
+    h.adversary_channel = c.adversary_channel;
+    h.n_gates = c.n_gates; h.gate_geometry = c.gate_geometry;
+    h.dyn_uses_episode_inertia = c.dyn_uses_episode_inertia; h.dyn_applies_force = c.dyn_applies_force;
+    h.auto_reset = c.auto_reset; h.reseed_on_reset = c.reseed_on_reset;
+    for (int d = 0; d < nx; ++d) {
+        k.init_rand[d].distrib = c.init_rand[d].distrib; k.init_rand[d].a = real(c.init_rand[d].a); k.init_rand[d].b = real(c.init_rand[d].b);
+        if (c.init_rand[d].distrib != SCG_RAND_NONE) h.any_init_rand = 1;
+    }
+    for (int j = 0; j < 4; ++j) {
+        h.inertia_nominal[j] = real(c.inertia_nominal[j]);
+        k.inertia_rand[j].distrib = c.inertia_rand[j].distrib; k.inertia_rand[j].a = real(c.inertia_rand[j].a); k.inertia_rand[j].b = real(c.inertia_rand[j].b);
+        if (c.inertia_rand[j].distrib != SCG_RAND_NONE) h.any_inertia_rand = 1;
+    }
+    k.gate_rand.distrib = c.gate_rand.distrib; k.gate_rand.a = real(c.gate_rand.a); k.gate_rand.b = real(c.gate_rand.b);
+    k.obstacle_rand.distrib = c.obstacle_rand.distrib; k.obstacle_rand.a = real(c.obstacle_rand.a); k.obstacle_rand.b = real(c.obstacle_rand.b);
+    h.any_gate_rand = (c.gate_rand.distrib != SCG_RAND_NONE || c.obstacle_rand.distrib != SCG_RAND_NONE) ? 1 : 0;
+    if (c.n_gates < 0 || c.n_gates > SCG_MAX_GATES || c.n_obstacles < 0 || c.n_obstacles > SCG_MAX_OBSTACLES)
+        return fail(SCG_ERR_BAD_CONFIG, "too many gates / obstacles");
+    for (int g = 0; g < c.n_gates; ++g) for (int j = 0; j < 7; ++j) k.gates[g][j] = real(c.gates[g][j]);
+    for (int g = 0; g < c.n_obstacles; ++g) for (int j = 0; j < 6; ++j) k.obstacles[g][j] = real(c.obstacles[g][j]);
+    k.n_obstacles = c.n_obstacles;
+    h.seed = c.seed; h.env_id_base_lo = uint32_t(c.env_id_base & 0xFFFFFFFFll);
+    h.viol_thr = real(5e-9);
+    return SCG_OK;
+}
+
+extern "C" const char* scg_last_error(void) { return g_err.c_str(); }
+extern "C" const char* scg_version(void) { return "scg_b200 0.1 (sm_100a)"; }
+extern "C" int64_t scg_launch_count(const scg_env* env) { return env ? env->launches : 0; }
+
+template <typename real> static int upload_params(scg_env* e) {
+    Cold<real>* k = new (std::nothrow) Cold<real>;
+    if (!k) return fail(SCG_ERR_BAD_CONFIG, "out of host memory");
+    Hot<real>& h = *reinterpret_cast<Hot<real>*>(sizeof(real) == 4 ? (void*)&e->hf : (void*)&e->hd);
+    int rc = build_params<real>(e->cfg, e->nx, e->nu, h, *k, &e->n_rows, &e->n_slots);
+    if (rc != SCG_OK) { delete k; return rc; }
+    const int rows = e->cfg.n_goal_rows > 0 ? e->cfg.n_goal_rows : 1;
+    real* goal_host = new real[size_t(rows) * e->nx];
+    for (int r = 0; r < rows; ++r) for (int d = 0; d < e->nx; ++d)
+        goal_host[size_t(r) * e->nx + d] = e->cfg.x_goal ? real(e->cfg.x_goal[size_t(r) * e->nx + d]) : real(0);
+    cudaError_t ce = cudaMalloc(&e->x_goal_dev, sizeof(real) * rows * e->nx);
+    if (ce == cudaSuccess) ce = cudaMemcpy(e->x_goal_dev, goal_host, sizeof(real) * rows * e->nx, cudaMemcpyHostToDevice);
+    delete[] goal_host;
+    if (ce != cudaSuccess) { delete k; return cuda_fail(ce, "x_goal upload"); }
+    k->x_goal = static_cast<const real*>(e->x_goal_dev);
+    ce = cudaMalloc(&e->cold_dev, sizeof(Cold<real>));
+    if (ce == cudaSuccess) ce = cudaMemcpy(e->cold_dev, k, sizeof(Cold<real>), cudaMemcpyHostToDevice);
+    if (ce != cudaSuccess) { delete k; return cuda_fail(ce, "cold block upload"); }
+    e->cold_host = k;
+    return SCG_OK;
+}
+
+extern "C" int scg_create(const scg_config* cfg, scg_env** out) {
+    if (!cfg || !out) return fail(SCG_ERR_NULL, "scg_create: null argument");
+    int nx, nu;
+    if (kind_dims(cfg->env_kind, &nx, &nu)) return fail(SCG_ERR_BAD_CONFIG, "unknown env_kind");
+    if (cfg->precision != 32 && cfg->precision != 64) return fail(SCG_ERR_BAD_CONFIG, "precision must be 32 or 64");
+    if (cfg->attitude_mode != SCG_ATT_ROUNDTRIP && cfg->attitude_mode != SCG_ATT_FAST) return fail(SCG_ERR_BAD_CONFIG, "bad attitude_mode");
+    if (cfg->substeps < 1 || cfg->pyb_freq < 1 || cfg->ctrl_freq < 1 || cfg->pyb_freq % cfg->ctrl_freq != 0)
+        return fail(SCG_ERR_BAD_CONFIG, "[ERROR] in BenchmarkEnv.__init__(), pyb_freq is not divisible by env_freq.");
+    if (cfg->substeps != cfg->pyb_freq / cfg->ctrl_freq) return fail(SCG_ERR_BAD_CONFIG, "substeps != pyb_freq / ctrl_freq");
+    if (cfg->n_goal_rows < 1 || !cfg->x_goal) return fail(SCG_ERR_BAD_CONFIG, "x_goal table missing");
+    if (cfg->obs_goal_horizon < 0) return fail(SCG_ERR_BAD_CONFIG, "negative obs_goal_horizon");
+    if (!(cfg->mass > 0.0)) return fail(SCG_ERR_BAD_CONFIG, "mass must be positive");
+    scg_env* e = new (std::nothrow) scg_env;
+    if (!e) return fail(SCG_ERR_BAD_CONFIG, "out of host memory");
+    e->cfg = *cfg; e->nx = nx; e->nu = nu;
+    int mul = 1;
+    if (cfg->cost == SCG_COST_RL_REWARD && cfg->obs_goal_horizon > 0)
+        mul = cfg->task == SCG_TASK_TRAJ_TRACKING ? 1 + cfg->obs_goal_horizon : 2;
+    e->obs_dim = nx * mul;
+    std::memset(&e->buf, 0, sizeof(e->buf));
+    int rc = cfg->precision == 32 ? upload_params<float>(e) : upload_params<double>(e);
+    if (rc != SCG_OK) { scg_destroy(e); return rc; }
+    e->cfg.x_goal = nullptr;   // host table was copied; do not keep the caller's pointer
+    *out = e;
+    return SCG_OK;
+}
+
+extern "C" int scg_destroy(scg_env* e) {
+    if (!e) return SCG_OK;
+    if (e->cold_dev) cudaFree(e->cold_dev);
+    if (e->x_goal_dev) cudaFree(e->x_goal_dev);
+    for (int j = 0; j < 2; ++j) {
+        if (e->stage[j]) cudaFree(e->stage[j]);
+        if (e->ev_copied[j]) cudaEventDestroy(e->ev_copied[j]);
+        if (e->ev_consumed[j]) cudaEventDestroy(e->ev_consumed[j]);
+    }
+    if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
+    if (e->cold_host) { if (e->cfg.precision == 32) delete static_cast<Cold<float>*>(e->cold_host); else delete static_cast<Cold<double>*>(e->cold_host); }
+    delete e;
+    return SCG_OK;
+}
+
+extern "C" int scg_bind_buffers(scg_env* e, const scg_buffers* b) {
+    if (!e || !b) return fail(SCG_ERR_NULL, "scg_bind_buffers: null argument");
+    if (b->n < 1 || b->n > (int64_t(1) << 31) - 1024) return fail(SCG_ERR_SHAPE, "n out of range");
+    if (!b->state || !b->ctrl_step || !b->episode || !b->flags || !b->obs || !b->reward || !b->done || !b->info)
+        return fail(SCG_ERR_NULL, "scg_bind_buffers: state, ctrl_step, episode, flags, obs, reward, done, info are required");
+    if (e->n_slots > 0 && !b->dist_offset) return fail(SCG_ERR_NULL, "dist_offset required when disturbances carry step offsets");
+    if (e->cfg.dyn_uses_episode_inertia && !b->inertia) return fail(SCG_ERR_NULL, "inertia buffer required for dyn_uses_episode_inertia");
+    if (e->cfg.adversary_channel >= 0 && e->cfg.adversary_channel != SCG_CH_ACTION && e->cfg.adversary_channel != SCG_CH_DYNAMICS)
+        return fail(SCG_ERR_BAD_CONFIG, "adversary channel must be action or dynamics");
+    e->buf = *b;
+    e->bound = true;
+    return SCG_OK;
+}
+
+extern "C" int scg_set_injection(scg_env* e, int channel, int k, const void* dev_ptr) {
+    if (!e) return fail(SCG_ERR_NULL, "scg_set_injection: null env");
+    if (channel == -1) { e->buf.adv_action = dev_ptr; return SCG_OK; }   // adversary action for the next step
+    if (channel < 0 || channel > 2 || k < 0 || k >= e->cfg.n_dist[channel]) return fail(SCG_ERR_SHAPE, "no such disturbance");
+    if (e->cfg.precision == 32) {
+        Cold<float>* c = static_cast<Cold<float>*>(e->cold_host);
+        c->dist[channel][k].inject = static_cast<const float*>(dev_ptr);
+        const size_t off = reinterpret_cast<char*>(&c->dist[channel][k].inject) - reinterpret_cast<char*>(c);
+        CU(cudaMemcpy(static_cast<char*>(e->cold_dev) + off, &c->dist[channel][k].inject, sizeof(void*), cudaMemcpyHostToDevice));
+    } else {
+        Cold<double>* c = static_cast<Cold<double>*>(e->cold_host);
+        c->dist[channel][k].inject = static_cast<const double*>(dev_ptr);
+        const size_t off = reinterpret_cast<char*>(&c->dist[channel][k].inject) - reinterpret_cast<char*>(c);
+        CU(cudaMemcpy(static_cast<char*>(e->cold_dev) + off, &c->dist[channel][k].inject, sizeof(void*), cudaMemcpyHostToDevice));
+    }
+    return SCG_OK;
+}
+
+template <typename real> static Buf<real> typed_buf(const scg_buffers& b) {
+    Buf<real> t;
+    t.n = b.n; t.state = (real*)b.state; t.ctrl_step = b.ctrl_step; t.episode = b.episode; t.flags = b.flags;
+    t.dist_offset = b.dist_offset; t.inertia = (real*)b.inertia; t.obs = (real*)b.obs; t.env_state = (real*)b.env_state;
+    t.reward = (real*)b.reward; t.done = b.done; t.info = b.info; t.mse = (real*)b.mse; t.c_values = (real*)b.c_values;
+    t.terminal_obs = (real*)b.terminal_obs; t.ep_return = (real*)b.ep_return; t.ep_length = b.ep_length;
+    t.ep_violations = b.ep_violations; t.stats = b.stats; t.adv_action = (const real*)b.adv_action;
+    return t;
+}
+
+template <int KIND, typename real, int MODE>
+static int launch_att(scg_env* e, const Hot<real>& h, const Roll<real>& ro, const ResetInject<real>& inj,
+                      const uint8_t* mask, cudaStream_t st) {
+    const Buf<real> b = typed_buf<real>(e->buf);
+    const int threads = 128;
+    const unsigned blocks = unsigned((b.n + threads - 1) / threads);
+    const Cold<real>* cold = static_cast<const Cold<real>*>(e->cold_dev);
+    if constexpr (KIND == SCG_CARTPOLE) {
+        k_cartpole<real, MODE><<<blocks, threads, 0, st>>>(h, cold, b, ro, inj, mask);
+    } else {
+        if (e->cfg.attitude_mode == SCG_ATT_FAST) k_env<KIND, real, SCG_ATT_FAST, MODE><<<blocks, threads, 0, st>>>(h, cold, b, ro, inj, mask);
+        else k_env<KIND, real, SCG_ATT_ROUNDTRIP, MODE><<<blocks, threads, 0, st>>>(h, cold, b, ro, inj, mask);
+    }
+    e->launches += 1;
+    CU(cudaGetLastError());
+    return SCG_OK;
+}
+
+template <typename real, int MODE>
+static int launch_kind(scg_env* e, const Roll<real>& ro, const ResetInject<real>& inj, const uint8_t* mask, cudaStream_t st) {
+    const Hot<real>& h = *reinterpret_cast<const Hot<real>*>(sizeof(real) == 4 ? (const void*)&e->hf : (const void*)&e->hd);
+    switch (e->cfg.env_kind) {
+        case SCG_QUAD_1D: return launch_att<SCG_QUAD_1D, real, MODE>(e, h, ro, inj, mask, st);
+        case SCG_QUAD_2D: return launch_att<SCG_QUAD_2D, real, MODE>(e, h, ro, inj, mask, st);
+        case SCG_QUAD_3D: return launch_att<SCG_QUAD_3D, real, MODE>(e, h, ro, inj, mask, st);
+        case SCG_CARTPOLE: return launch_att<SCG_CARTPOLE, real, MODE>(e, h, ro, inj, mask, st);
+    }
+    return fail(SCG_ERR_BAD_CONFIG, "unknown env_kind");
+}
+
+extern "C" int scg_reset(scg_env* e, const uint8_t* mask, const void* inject_init, const void* inject_inertia,
+                         const int32_t* inject_offsets, void* stream) {
+    if (!e) return fail(SCG_ERR_NULL, "scg_reset: null env");
+    if (!e->bound) return fail(SCG_ERR_STATE, "scg_reset: buffers not bound");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int rc;
+    if (e->cfg.precision == 32) {
+        Roll<float> ro{}; ResetInject<float> inj{(const float*)inject_init, (const float*)inject_inertia, inject_offsets};
+        rc = launch_kind<float, 0>(e, ro, inj, mask, st);
+    } else {
+        Roll<double> ro{}; ResetInject<double> inj{(const double*)inject_init, (const double*)inject_inertia, inject_offsets};
+        rc = launch_kind<double, 0>(e, ro, inj, mask, st);
+    }
+    if (rc == SCG_OK) e->did_reset = true;
+    return rc;
+}
+
+static int run_steps(scg_env* e, const void* actions, int k_steps, void* reward_out, uint8_t* done_out, void* log_out,
+                     int log_stride, int step_outputs, cudaStream_t st) {
+    if (e->cfg.precision == 32) {
+        Roll<float> ro{(const float*)actions, k_steps, (float*)reward_out, done_out, (float*)log_out, log_stride, step_outputs};
+        ResetInject<float> inj{nullptr, nullptr, nullptr};
+        return launch_kind<float, 1>(e, ro, inj, nullptr, st);
+    }
+    Roll<double> ro{(const double*)actions, k_steps, (double*)reward_out, done_out, (double*)log_out, log_stride, step_outputs};
+    ResetInject<double> inj{nullptr, nullptr, nullptr};
+    return launch_kind<double, 1>(e, ro, inj, nullptr, st);
+}
+
+extern "C" int scg_step(scg_env* e, const void* action, void* stream) {
+    if (!e || !action) return fail(SCG_ERR_NULL, "scg_step: null argument");
+    if (!e->bound) return fail(SCG_ERR_STATE, "scg_step: buffers not bound");
+    if (!e->did_reset) return fail(SCG_ERR_STATE, "[ERROR] You must call env.reset() at least once before using env.step().");
+    return run_steps(e, action, 1, nullptr, nullptr, nullptr, 1, 1, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int scg_rollout(scg_env* e, const scg_rollout_args* a, void* stream) {
+    if (!e || !a || !a->actions) return fail(SCG_ERR_NULL, "scg_rollout: null argument");
+    if (!e->bound) return fail(SCG_ERR_STATE, "scg_rollout: buffers not bound");
+    if (!e->did_reset) return fail(SCG_ERR_STATE, "[ERROR] You must call env.reset() at least once before using env.step().");
+    if (a->k_steps < 1) return fail(SCG_ERR_SHAPE, "k_steps must be >= 1");
+    if (a->log_out && a->log_stride < 1) return fail(SCG_ERR_SHAPE, "log_stride must be >= 1");
+    return run_steps(e, a->actions, a->k_steps, a->reward_out, a->done_out, a->log_out, a->log_stride > 0 ? a->log_stride : 1,
+                     0, static_cast<cudaStream_t>(stream));
+}
+
+// Actions in pinned host memory: chunked H2D copies on a private stream, double-buffered against
+// the rollout launches on the caller's stream.
+extern "C" int scg_rollout_host(scg_env* e, const void* host_actions, int32_t k_steps, int32_t chunk_steps, void* stream) {
+    if (!e || !host_actions) return fail(SCG_ERR_NULL, "scg_rollout_host: null argument");
+    if (!e->bound) return fail(SCG_ERR_STATE, "scg_rollout_host: buffers not bound");
+    if (!e->did_reset) return fail(SCG_ERR_STATE, "[ERROR] You must call env.reset() at least once before using env.step().");
+    if (k_steps < 1 || chunk_steps < 1) return fail(SCG_ERR_SHAPE, "k_steps and chunk_steps must be >= 1");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const size_t real_bytes = e->cfg.precision == 32 ? 4 : 8;
+    const size_t step_bytes = size_t(e->buf.n) * e->nu * real_bytes;
+    const size_t need = step_bytes * chunk_steps;
+    if (!e->copy_stream) {
+        CU(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
+        for (int j = 0; j < 2; ++j) {
+            CU(cudaEventCreateWithFlags(&e->ev_copied[j], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&e->ev_consumed[j], cudaEventDisableTiming));
+        }
+    }
+    if (need > e->stage_bytes) {
+        CU(cudaStreamSynchronize(e->copy_stream));
+        for (int j = 0; j < 2; ++j) { if (e->stage[j]) CU(cudaFree(e->stage[j])); CU(cudaMalloc(&e->stage[j], need)); }
+        e->stage_bytes = need;
+    }
+    const char* src = static_cast<const char*>(host_actions);
+    int chunk = 0;
+    for (int k0 = 0; k0 < k_steps; k0 += chunk_steps, ++chunk) {
+        const int ks = k_steps - k0 < chunk_steps ? k_steps - k0 : chunk_steps;
+        const int s = chunk & 1;
+        if (chunk >= 2) CU(cudaStreamWaitEvent(e->copy_stream, e->ev_consumed[s], 0));
+        CU(cudaMemcpyAsync(e->stage[s], src + size_t(k0) * step_bytes, step_bytes * ks, cudaMemcpyHostToDevice, e->copy_stream));
+        CU(cudaEventRecord(e->ev_copied[s], e->copy_stream));
+        CU(cudaStreamWaitEvent(st, e->ev_copied[s], 0));
+        int rc = run_steps(e, e->stage[s], ks, nullptr, nullptr, nullptr, 1, 0, st);
+        if (rc != SCG_OK) return rc;
+        CU(cudaEventRecord(e->ev_consumed[s], st));
+    }
+    return SCG_OK;
+}
+
+extern "C" int scg_stats_reset(scg_env* e, void* stream) {
+    if (!e || !e->bound || !e->buf.stats) return fail(SCG_ERR_NULL, "scg_stats_reset: no stats buffer bound");
+    CU(cudaMemsetAsync(e->buf.stats, 0, sizeof(double) * SCG_STATS_LEN, static_cast<cudaStream_t>(stream)));
+    return SCG_OK;
+}
+
+extern "C" int scg_stats_read(scg_env* e, double* host_out, void* stream) {
+    if (!e || !host_out || !e->bound || !e->buf.stats) return fail(SCG_ERR_NULL, "scg_stats_read: no stats buffer bound");
+    CU(cudaMemcpyAsync(host_out, e->buf.stats, sizeof(double) * SCG_STATS_LEN, cudaMemcpyDeviceToHost, static_cast<cudaStream_t>(stream)));
+    return SCG_OK;
+}
+
+template <int KIND, typename real>
+__global__ void __launch_bounds__(128)
+k_constraints(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, const real* __restrict__ state,
+              const real* __restrict__ action, int64_t n, real* __restrict__ out_values, uint8_t* __restrict__ out_flags) {
+    constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
+    const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    real st[NX], raw[NU];
+#pragma unroll
+    for (int d = 0; d < NX; ++d) st[d] = state[int64_t(d) * n + i];
+#pragma unroll
+    for (int j = 0; j < NU; ++j) raw[j] = action ? action[i * NU + j] : real(0);
+    bool violated, almost;
+    eval_constraints<KIND, real>(h, cold, st, raw, action == nullptr, out_values, n, i, violated, almost);
+    if (out_flags) out_flags[i] = (violated ? 1 : 0) | (almost ? 2 : 0);
+}
+
+template <typename real> static int constraints_eval_t(scg_env* e, const void* state, const void* action, int64_t n,
+                                                       void* out_values, uint8_t* out_flags, cudaStream_t st) {
+    const Hot<real>& h = *reinterpret_cast<const Hot<real>*>(sizeof(real) == 4 ? (const void*)&e->hf : (const void*)&e->hd);
+    const Cold<real>* cold = static_cast<const Cold<real>*>(e->cold_dev);
+    const unsigned blocks = unsigned((n + 127) / 128);
+    switch (e->cfg.env_kind) {
+        case SCG_QUAD_1D: k_constraints<SCG_QUAD_1D, real><<<blocks, 128, 0, st>>>(h, cold, (const real*)state, (const real*)action, n, (real*)out_values, out_flags); break;
+        case SCG_QUAD_2D: k_constraints<SCG_QUAD_2D, real><<<blocks, 128, 0, st>>>(h, cold, (const real*)state, (const real*)action, n, (real*)out_values, out_flags); break;
+        case SCG_QUAD_3D: k_constraints<SCG_QUAD_3D, real><<<blocks, 128, 0, st>>>(h, cold, (const real*)state, (const real*)action, n, (real*)out_values, out_flags); break;
+        case SCG_CARTPOLE: k_constraints<SCG_CARTPOLE, real><<<blocks, 128, 0, st>>>(h, cold, (const real*)state, (const real*)action, n, (real*)out_values, out_flags); break;
+    }
+    e->launches += 1;
+    CU(cudaGetLastError());
+    return SCG_OK;
+}
+
+extern "C" int scg_constraints_eval(scg_env* e, const void* state, const void* action, int64_t n, void* out_values,
+                                    uint8_t* out_flags, void* stream) {
+    if (!e || !state) return fail(SCG_ERR_NULL, "scg_constraints_eval: null argument");
+    if (n < 1) return fail(SCG_ERR_SHAPE, "n must be >= 1");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    return e->cfg.precision == 32 ? constraints_eval_t<float>(e, state, action, n, out_values, out_flags, st)
+                                  : constraints_eval_t<double>(e, state, action, n, out_values, out_flags, st);
+}
+
+extern "C" int scg_symbolic_eval(scg_env* e, int op, const void* x, const void* u, int64_t n, double dt, void* out0,
+                                 void* out1, void* stream) {
+    if (!e || !x || !u || !out0) return fail(SCG_ERR_NULL, "scg_symbolic_eval: null argument");
+    if (n < 1) return fail(SCG_ERR_SHAPE, "n must be >= 1");
+    if (op < SCG_SYM_FC || op > SCG_SYM_FD_EULER) return fail(SCG_ERR_BAD_CONFIG, "unknown symbolic op");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int rc = e->cfg.precision == 32
+                 ? symbolic_launch<float>(e->cfg, e->hf, static_cast<const Cold<float>*>(e->cold_dev), op, (const float*)x, (const float*)u, n, float(dt), (float*)out0, (float*)out1, st)
+                 : symbolic_launch<double>(e->cfg, e->hd, static_cast<const Cold<double>*>(e->cold_dev), op, (const double*)x, (const double*)u, n, dt, (double*)out0, (double*)out1, st);
+    if (rc != 0) return fail(SCG_ERR_BAD_CONFIG, "symbolic op not available for this env kind");
+    e->launches += 1;
+    CU(cudaGetLastError());
+    return SCG_OK;
+}

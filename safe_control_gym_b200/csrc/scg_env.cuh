@@ -1,0 +1,281 @@
+// scg_env.cuh -- per-env device functions of the fused step: one thread owns one env, the
+// state and motor commands live in registers for all PYB_FREQ / CTRL_FREQ substeps.
+// Reference line numbers are under safe_control_gym/ (see SURVEY.md section 8a rows A1-A11).
+#pragma once
+#include "scg_params.cuh"
+
+namespace scg {
+
+// ------------------------------------------------------------------ attitude (row A3)
+// The reference stores the attitude in PyBullet as quatFromEuler(rpy + dt * rates) and reads it
+// back as eulerFromQuat(quat) before every use (base_aviary.py:565-574, 281-285, 322, 362-374).
+// Inside the identity region of that round trip (|pitch| < asin(0.99999), roll and yaw in
+// (-pi, pi)) the read-back equals the input, so SCG_ATT_FAST skips the quaternion and builds the
+// rotation from sin/cos of the Euler angles; outside it (fold, wrap, gimbal branch) -- and always
+// with SCG_ATT_ROUNDTRIP -- the literal bullet3 arithmetic is executed.
+template <typename real> struct Att3 {
+    real rpy[3];   // wrapped angles == self.rpy after _update_and_store_kinematic_information
+    real R[9];     // getMatrixFromQuaternion(self.quat), row-major
+};
+
+template <typename real, int ATT, bool FULL>
+SCG_DEV void attitude3(const real (&pre)[3], Att3<real>& a) {
+    const bool fast = (ATT == SCG_ATT_FAST) && m_abs(pre[1]) < real(1.5663) && m_abs(pre[0]) < real(3.1415) &&
+                      m_abs(pre[2]) < real(3.1415);
+    if (fast) {
+        real sph, cph, sth, cth, sps, cps;
+        m_sincos(pre[0], &sph, &cph);
+        m_sincos(pre[1], &sth, &cth);
+        m_sincos(pre[2], &sps, &cps);
+        a.rpy[0] = pre[0]; a.rpy[1] = pre[1]; a.rpy[2] = pre[2];
+        a.R[2] = cps * sth * cph + sps * sph;
+        a.R[5] = sps * sth * cph - cps * sph;
+        a.R[8] = cth * cph;
+        if (FULL) {
+            a.R[0] = cps * cth; a.R[1] = cps * sth * sph - sps * cph;
+            a.R[3] = sps * cth; a.R[4] = sps * sth * sph + cps * cph;
+            a.R[6] = -sth;      a.R[7] = cth * sph;
+        }
+        return;
+    }
+    // pybullet getQuaternionFromEuler
+    real sph, cph, sth, cth, sps, cps;
+    m_sincos(pre[0] * real(0.5), &sph, &cph);
+    m_sincos(pre[1] * real(0.5), &sth, &cth);
+    m_sincos(pre[2] * real(0.5), &sps, &cps);
+    real x = sph * cth * cps - cph * sth * sps;
+    real y = cph * sth * cps + sph * cth * sps;
+    real z = cph * cth * sps - sph * sth * cps;
+    real w = cph * cth * cps + sph * sth * sps;
+    const real len = m_sqrt(x * x + y * y + z * z + w * w);
+    x /= len; y /= len; z /= len; w /= len;
+    // pybullet getEulerFromQuaternion
+    const real sqx = x * x, sqy = y * y, sqz = z * z, squ = w * w;
+    const real sarg = real(-2) * (x * z - w * y);
+    if (sarg <= real(-0.99999)) {
+        a.rpy[0] = real(0); a.rpy[1] = -Consts<real>::half_pi; a.rpy[2] = real(2) * m_atan2(x, -y);
+    } else if (sarg >= real(0.99999)) {
+        a.rpy[0] = real(0); a.rpy[1] = Consts<real>::half_pi; a.rpy[2] = real(2) * m_atan2(-x, y);
+    } else {
+        a.rpy[0] = m_atan2(real(2) * (y * z + w * x), squ - sqx - sqy + sqz);
+        a.rpy[1] = m_asin(sarg);
+        a.rpy[2] = m_atan2(real(2) * (x * y + w * z), squ + sqx - sqy - sqz);
+    }
+    // pybullet getMatrixFromQuaternion
+    const real s = real(2) / (sqx + sqy + sqz + squ);
+    const real xs = x * s, ys = y * s, zs = z * s;
+    const real wx = w * xs, wy = w * ys, wz = w * zs;
+    const real xx = x * xs, xy = x * ys, xz = x * zs;
+    const real yy = y * ys, yz = y * zs, zz = z * zs;
+    a.R[2] = xz + wy; a.R[5] = yz - wx; a.R[8] = real(1) - (xx + yy);
+    if (FULL) {
+        a.R[0] = real(1) - (yy + zz); a.R[1] = xy - wz;
+        a.R[3] = xy + wz;             a.R[4] = real(1) - (xx + zz);
+        a.R[6] = xz - wy;             a.R[7] = yz + wx;
+    }
+}
+
+// Planar (2D) attitude: pitch alpha as the reference reports it plus the "flipped" bit that
+// records roll = yaw = pi after the asin fold.  r3 = third column of R = (sin, 0, cos) of the
+// physical pitch.
+template <typename real> struct Att2 { real theta; real r3x, r3z; uint32_t flipped; };
+
+template <typename real>
+SCG_DEV void attitude2(real alpha_pre, uint32_t flipped_in, Att2<real>& a) {
+    if (!flipped_in && m_abs(alpha_pre) < real(1.5663)) {
+        m_sincos(alpha_pre, &a.r3x, &a.r3z);
+        a.theta = alpha_pre; a.flipped = 0u;
+        return;
+    }
+    const real phys = flipped_in ? Consts<real>::pi - alpha_pre : alpha_pre;
+    real s, c;
+    m_sincos(phys, &s, &c);
+    a.r3x = s; a.r3z = c;
+    if (s <= real(-0.99999)) { a.theta = -Consts<real>::half_pi; a.flipped = 0u; }
+    else if (s >= real(0.99999)) { a.theta = Consts<real>::half_pi; a.flipped = 0u; }
+    else { a.theta = m_asin(s); a.flipped = (c < real(0)) ? 1u : 0u; }
+}
+
+// ------------------------------------------------------------------ motors (rows A1-A2)
+template <typename real> struct Motors {
+    real T;            // sum of the four rotor forces
+    real tx, ty, tz;   // body torques before the gyroscopic term
+    real rpm[4];
+};
+
+// quadrotor.py:815-842, quadrotor_utils.py:21-67, base_aviary.py:538-551.
+// thrust[] is the (possibly disturbed) commanded thrust per input.
+template <int KIND, typename real>
+SCG_DEV void motors_from_thrust(const Hot<real>& h, const real (&thrust)[Dims<KIND>::NU], Motors<real>& m) {
+    constexpr int NU = Dims<KIND>::NU;
+    real rp[NU];
+#pragma unroll
+    for (int j = 0; j < NU; ++j) {
+        const real t = m_max(thrust[j], real(0));
+        real pwm = (m_sqrt(t * h.inv_nkf) - h.pwm_const) * h.inv_pwm_scale;
+        pwm = m_clip(pwm, h.pwm_min, h.pwm_max);
+        rp[j] = h.pwm_scale * pwm + h.pwm_const;
+    }
+    if (KIND == SCG_QUAD_1D) { m.rpm[0] = m.rpm[1] = m.rpm[2] = m.rpm[3] = rp[0]; }
+    else if (KIND == SCG_QUAD_2D) { m.rpm[0] = rp[0]; m.rpm[1] = rp[NU - 1]; m.rpm[2] = rp[NU - 1]; m.rpm[3] = rp[0]; }
+    else { m.rpm[0] = rp[0]; m.rpm[1] = rp[1 % NU]; m.rpm[2] = rp[2 % NU]; m.rpm[3] = rp[3 % NU]; }
+    real f[4], zt[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { const real r2 = m.rpm[j] * m.rpm[j]; f[j] = r2 * h.kf; zt[j] = r2 * h.km; }
+    m.T = ((f[0] + f[1]) + f[2]) + f[3];
+    m.tz = ((zt[0] - zt[1]) + zt[2]) - zt[3];
+    m.tx = (((f[0] + f[1]) - f[2]) - f[3]) * h.arm_s2;
+    m.ty = (((-f[0] + f[1]) + f[2]) - f[3]) * h.arm_s2;
+}
+
+// per-episode inertial constants (nominal in parity mode, F9)
+template <typename real> struct Inertia { real inv_mass, g_over_m, J[3], J_inv[3]; };
+
+// ------------------------------------------------------------------ constraints (row A6)
+// c = g(x) rounded to 8 decimals (constraints.py:119); violated = any(c > 0) (or >= 0 if strict).
+// round(c, 8) > 0  <=>  rint(c * 1e8) > 0  <=>  c * 1e8 > 0.5 (ties go to even = 0), and
+// round(c, 8) >= 0 <=>  c * 1e8 >= -0.5, so the flags need no rounding instruction.
+template <typename real> SCG_DEV real round8(real c) { return m_rint(c * real(1e8)) / real(1e8); }
+template <> SCG_DEV float round8<float>(float c) {
+    // fp32 carries fewer than 8 decimals above |c| ~ 0.08: rounding is then the identity
+    return m_abs(c) < 0.08f ? m_rint(c * 1e8f) / 1e8f : c;
+}
+template <typename real> SCG_DEV bool viol_test(real c, int strict) {
+    const real y = c * real(1e8);
+    return strict ? (y >= real(-0.5)) : (y > real(0.5));
+}
+
+template <int KIND, typename real>
+SCG_DEV void eval_constraints(const Hot<real>& h, const Cold<real>* __restrict__ cold,
+                              const real (&st)[Dims<KIND>::NX], const real (&raw)[Dims<KIND>::NU],
+                              bool state_only, real* __restrict__ c_out, int64_t n, int64_t i,
+                              bool& violated, bool& almost) {
+    constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
+    violated = false; almost = false;
+    for (int k = 0; k < h.n_bounded; ++k) {
+        const BoundedCon<real>& bc = h.bounded[k];
+        if (bc.var == SCG_VAR_STATE) {
+#pragma unroll
+            for (int d = 0; d < NX; ++d) {
+                real clo, chi;
+                if (bc.symmetric) { clo = m_abs(st[d]) - bc.hi[d]; chi = -INFINITY; }   // constraints.py:404-406 (unrounded)
+                else { clo = bc.lo[d] - st[d]; chi = st[d] - bc.hi[d]; }
+                if (bc.symmetric) violated |= bc.strict ? (clo >= real(0)) : (clo > real(0));
+                else violated |= viol_test(clo, bc.strict) | viol_test(chi, bc.strict);
+                if (c_out || bc.has_tol) {
+                    const real rlo = bc.symmetric ? clo : round8(clo), rhi = round8(chi);
+                    if (c_out && bc.row_lo[d] >= 0) c_out[int64_t(bc.row_lo[d]) * n + i] = rlo;
+                    if (c_out && bc.row_hi[d] >= 0) c_out[int64_t(bc.row_hi[d]) * n + i] = rhi;
+                    if (bc.has_tol) almost |= (rlo + cold->bounded_tol[k][d] > real(0)) | (rhi + cold->bounded_tol[k][NX + d] > real(0));
+                }
+            }
+        } else if (!state_only) {
+#pragma unroll
+            for (int d = 0; d < NU; ++d) {
+                const real clo = bc.lo[d] - raw[d], chi = raw[d] - bc.hi[d];
+                violated |= viol_test(clo, bc.strict) | viol_test(chi, bc.strict);
+                if (c_out || bc.has_tol) {
+                    const real rlo = round8(clo), rhi = round8(chi);
+                    if (c_out && bc.row_lo[d] >= 0) c_out[int64_t(bc.row_lo[d]) * n + i] = rlo;
+                    if (c_out && bc.row_hi[d] >= 0) c_out[int64_t(bc.row_hi[d]) * n + i] = rhi;
+                    if (bc.has_tol) almost |= (rlo + cold->bounded_tol[k][d] > real(0)) | (rhi + cold->bounded_tol[k][NX + d] > real(0));
+                }
+            }
+        }
+    }
+    for (int r = 0; r < h.n_dense_rows; ++r) {   // linear / quadratic rows (uniform loads)
+        const DenseRow<real>& dr = cold->dense[r];
+        if (dr.var == SCG_VAR_INPUT && state_only) continue;
+        real c = real(0);
+        if (dr.quadratic) {
+            const real* P = cold->P[dr.p_index];
+            if (dr.var == SCG_VAR_STATE) {
+#pragma unroll
+                for (int a = 0; a < NX; ++a) {
+                    real row = real(0);
+#pragma unroll
+                    for (int b = 0; b < NX; ++b) row += P[a * SCG_MAX_NX + b] * st[b];
+                    c += st[a] * row;
+                }
+            } else {
+#pragma unroll
+                for (int a = 0; a < NU; ++a) {
+                    real row = real(0);
+#pragma unroll
+                    for (int b = 0; b < NU; ++b) row += P[a * SCG_MAX_NX + b] * raw[b];
+                    c += raw[a] * row;
+                }
+            }
+        } else if (dr.var == SCG_VAR_STATE) {
+#pragma unroll
+            for (int d = 0; d < NX; ++d) c += dr.a[d] * st[d];
+        } else {
+#pragma unroll
+            for (int d = 0; d < NU; ++d) c += dr.a[d] * raw[d];
+        }
+        c -= dr.b;
+        const real rc = round8(c);
+        violated |= dr.strict ? (rc >= real(0)) : (rc > real(0));
+        if (dr.has_tol) almost |= (rc + dr.tol > real(0));
+        if (c_out) c_out[int64_t(dr.out_row) * n + i] = rc;
+    }
+}
+
+// ------------------------------------------------------------------ disturbances (row A5)
+// Additive, applied in YAML order (DisturbanceList.apply, disturbances.py:69-79).
+// t = ctrl_step_counter (pre-increment); index = Philox counter word 0 for this call.
+template <typename real, int DIM>
+SCG_DEV void apply_channel(const Cold<real>* __restrict__ cold, int ch, int n_dist, real (&v)[DIM],
+                           int32_t t, real t_sim, const RngKey& key, uint32_t index, uint32_t episode,
+                           const int32_t* __restrict__ offsets, int64_t n, int64_t i) {
+    for (int k = 0; k < n_dist; ++k) {
+        const DistP<real>& D = cold->dist[ch][k];
+        real noise[DIM];
+        if (D.kind == SCG_DIST_IMPULSE || D.kind == SCG_DIST_STEP) {
+            const int32_t off = D.step_offset >= 0 ? D.step_offset : offsets[int64_t(D.slot) * n + i];
+            real s = real(0);
+            if (t >= off) {
+                if (D.kind == SCG_DIST_STEP) s = D.magnitude;
+                else {
+                    const int32_t peak = static_cast<int32_t>(real(off) + D.half_duration);  // int(offset + duration / 2)
+                    const int32_t kk = t >= peak ? t - peak : peak - t;
+                    s = (real(kk) < D.half_duration) ? D.magnitude * m_pow(D.decay_rate, real(kk)) : real(0);
+                }
+            }
+#pragma unroll
+            for (int d = 0; d < DIM; ++d) noise[d] = s;
+        } else if (D.inject) {
+#pragma unroll
+            for (int d = 0; d < DIM; ++d) noise[d] = D.inject[int64_t(d) * n + i];
+            if (D.kind == SCG_DIST_PERIODIC) {
+#pragma unroll
+                for (int d = 0; d < DIM; ++d) noise[d] = D.scale * m_sin(D.omega * t_sim + noise[d]);
+            }
+        } else {
+            const uint32_t stream = STREAM_DISTURB_BASE + 8u * ch + k;
+            if (D.kind == SCG_DIST_WHITE) {
+                draw_normals<real, DIM>(key, index, episode, stream, noise);
+#pragma unroll
+                for (int d = 0; d < DIM; ++d) noise[d] *= D.std[d];
+            } else {
+                draw_uniforms<real, DIM>(key, index, episode, stream, noise);
+                if (D.kind == SCG_DIST_UNIFORM) {
+#pragma unroll
+                    for (int d = 0; d < DIM; ++d) noise[d] = D.low[d] + D.span[d] * noise[d];
+                } else {
+#pragma unroll
+                    for (int d = 0; d < DIM; ++d)
+                        noise[d] = D.scale * m_sin(D.omega * t_sim + (-Consts<real>::pi + Consts<real>::two_pi * noise[d]));
+                }
+            }
+        }
+        if (D.has_mask) {
+#pragma unroll
+            for (int d = 0; d < DIM; ++d) noise[d] *= D.mask[d];
+        }
+#pragma unroll
+        for (int d = 0; d < DIM; ++d) v[d] += noise[d];
+    }
+}
+
+}  // namespace scg

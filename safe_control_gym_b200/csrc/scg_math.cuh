@@ -1,0 +1,114 @@
+// scg_math.cuh -- precision-generic math wrappers and the Philox4x32-10 draw contract.
+// The draw contract (key = (seed, env id), counter = (index, episode, stream, block),
+// u01 / Box-Muller / randint transforms) is specified in oracle/philox.py; the stream ids
+// below must stay in sync with it.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace scg {
+
+#define SCG_DEV __device__ __forceinline__
+
+SCG_DEV float  m_sqrt(float x)  { return sqrtf(x); }
+SCG_DEV double m_sqrt(double x) { return sqrt(x); }
+SCG_DEV float  m_rsqrt(float x)  { return rsqrtf(x); }
+SCG_DEV double m_rsqrt(double x) { return 1.0 / sqrt(x); }
+SCG_DEV void m_sincos(float x, float* s, float* c)   { sincosf(x, s, c); }
+SCG_DEV void m_sincos(double x, double* s, double* c) { sincos(x, s, c); }
+SCG_DEV float  m_sin(float x)  { return sinf(x); }
+SCG_DEV double m_sin(double x) { return sin(x); }
+SCG_DEV float  m_atan2(float y, float x)   { return atan2f(y, x); }
+SCG_DEV double m_atan2(double y, double x) { return atan2(y, x); }
+SCG_DEV float  m_asin(float x)  { return asinf(x); }
+SCG_DEV double m_asin(double x) { return asin(x); }
+SCG_DEV float  m_exp(float x)  { return expf(x); }
+SCG_DEV double m_exp(double x) { return exp(x); }
+SCG_DEV float  m_log(float x)  { return logf(x); }
+SCG_DEV double m_log(double x) { return log(x); }
+SCG_DEV float  m_pow(float x, float y)   { return powf(x, y); }
+SCG_DEV double m_pow(double x, double y) { return pow(x, y); }
+SCG_DEV float  m_abs(float x)  { return fabsf(x); }
+SCG_DEV double m_abs(double x) { return fabs(x); }
+SCG_DEV float  m_max(float a, float b)   { return fmaxf(a, b); }
+SCG_DEV double m_max(double a, double b) { return fmax(a, b); }
+SCG_DEV float  m_min(float a, float b)   { return fminf(a, b); }
+SCG_DEV double m_min(double a, double b) { return fmin(a, b); }
+SCG_DEV float  m_rint(float x)  { return rintf(x); }
+SCG_DEV double m_rint(double x) { return rint(x); }
+// np.clip(x, lo, hi) == minimum(maximum(x, lo), hi)
+template <typename real> SCG_DEV real m_clip(real x, real lo, real hi) { return m_min(m_max(x, lo), hi); }
+
+template <typename real> struct Consts;
+template <> struct Consts<float> {
+    static constexpr float pi = 3.14159265358979323846f;
+    static constexpr float two_pi = 6.28318530717958647692f;
+    static constexpr float half_pi = 1.57079632679489661923f;
+};
+template <> struct Consts<double> {
+    static constexpr double pi = 3.14159265358979323846;
+    static constexpr double two_pi = 6.28318530717958647692;
+    static constexpr double half_pi = 1.57079632679489661923;
+};
+
+// ---------------------------------------------------------------- Philox4x32-10
+constexpr uint32_t STREAM_RESET_INIT = 0, STREAM_RESET_INERTIA = 1, STREAM_RESET_OFFSETS = 2,
+                   STREAM_RESET_GATES = 3, STREAM_RESET_OBSTACLES = 4, STREAM_DISTURB_BASE = 16;
+
+struct U4 { uint32_t x, y, z, w; };
+
+SCG_DEV U4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1) {
+    constexpr uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(M0, c0), lo0 = M0 * c0;
+        const uint32_t hi1 = __umulhi(M1, c2), lo1 = M1 * c2;
+        const uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+        k0 += W0; k1 += W1;
+    }
+    return U4{c0, c1, c2, c3};
+}
+
+template <typename real> SCG_DEV real u01(uint32_t w) {
+    return (static_cast<real>(w >> 8) + real(0.5)) * real(5.9604644775390625e-08);  // 2^-24
+}
+template <typename real> SCG_DEV void normal_pair(uint32_t w0, uint32_t w1, real* n0, real* n1) {
+    const real r = m_sqrt(real(-2) * m_log(u01<real>(w0)));
+    real s, c;
+    m_sincos(Consts<real>::two_pi * u01<real>(w1), &s, &c);
+    *n0 = r * c;
+    *n1 = r * s;
+}
+SCG_DEV int32_t randint(uint32_t w, int32_t n) { return static_cast<int32_t>(__umulhi(w, static_cast<uint32_t>(n))); }
+
+// value i (of a vector draw) lives in word i % 4 of block i / 4
+SCG_DEV uint32_t word_of(const U4& b, int i) { return (i & 3) == 0 ? b.x : (i & 3) == 1 ? b.y : (i & 3) == 2 ? b.z : b.w; }
+
+struct RngKey { uint32_t seed, env; };
+
+template <typename real, int DIM> SCG_DEV void draw_uniforms(const RngKey& k, uint32_t index, uint32_t episode,
+                                                              uint32_t stream, real (&u)[DIM]) {
+#pragma unroll
+    for (int b = 0; b < (DIM + 3) / 4; ++b) {
+        const U4 w = philox4x32_10(index, episode, stream, b, k.seed, k.env);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (4 * b + j < DIM) u[4 * b + j] = u01<real>(word_of(w, j));
+    }
+}
+template <typename real, int DIM> SCG_DEV void draw_normals(const RngKey& k, uint32_t index, uint32_t episode,
+                                                             uint32_t stream, real (&z)[DIM]) {
+#pragma unroll
+    for (int b = 0; b < (DIM + 3) / 4; ++b) {
+        const U4 w = philox4x32_10(index, episode, stream, b, k.seed, k.env);
+        real n[4];
+        normal_pair<real>(w.x, w.y, &n[0], &n[1]);
+        normal_pair<real>(w.z, w.w, &n[2], &n[3]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (4 * b + j < DIM) z[4 * b + j] = n[j];
+    }
+}
+
+}  // namespace scg

@@ -1,0 +1,113 @@
+// scg_params.cuh -- device-side parameter blocks built once by scg_create() from scg_config.
+//
+// Hot<real>  : passed BY VALUE as a __grid_constant__ kernel parameter, so every field is a
+//              constant-bank operand (no load instruction, no register) in the substep loop.
+// Cold<real> : library-owned device memory; read with uniform loads only when a feature
+//              that needs it is enabled (dense constraint rows, disturbances, goal table, gates).
+#pragma once
+#include "scg_math.cuh"
+#include "../../include/scg_b200.h"
+
+namespace scg {
+
+constexpr int MAX_BOUNDED = 4;   // bounded/default constraint objects kept in the hot block
+constexpr int MAX_DENSE_ROWS = 24;
+
+template <typename real> struct BoundedCon {
+    real lo[SCG_MAX_NX], hi[SCG_MAX_NX];       // per FULL dim; inactive dims: -inf / +inf
+    int8_t row_lo[SCG_MAX_NX], row_hi[SCG_MAX_NX];  // output row (YAML order) or -1
+    int8_t var, strict, has_tol, symmetric;
+};
+
+template <typename real> struct Hot {
+    // timing
+    int32_t substeps, ctrl_steps, ctrl_freq, pyb_freq;
+    real dt;
+    // physics (base_aviary.py:522-576)
+    real kf, km, arm_s2;            // arm_s2 = L / sqrt(2)
+    real inv_mass, gravity_force;   // nominal (parity mode)
+    real J[3], J_inv[3];
+    real pwm_scale, pwm_const, pwm_min, pwm_max, inv_pwm_scale;
+    real inv_nkf;                   // 1 / (n_motor * KF)
+    // action map
+    int32_t normalized_action;
+    real norm_act_scale, hover_thrust;
+    real act_low[SCG_MAX_NU], act_high[SCG_MAX_NU];
+    // state space / termination
+    real state_low[SCG_MAX_NX], state_high[SCG_MAX_NX];
+    int32_t done_on_out_of_bound, done_on_violation, done_on_collision, done_on_completion;
+    // task / cost
+    int32_t task, cost, rew_exponential, obs_goal_horizon, n_goal_rows;
+    real rew_state_weight[SCG_MAX_NX], rew_act_weight[SCG_MAX_NU], u_goal[SCG_MAX_NU];
+    real x_goal0[SCG_MAX_NX];       // stabilisation goal (row 0)
+    real mse_weight[SCG_MAX_NX];
+    real goal_tol;
+    int32_t quadratic_diag;         // Q, R diagonal -> hot path, else dense from Cold
+    real q_diag[SCG_MAX_NX], r_diag[SCG_MAX_NU];
+    int32_t use_constraint_penalty;
+    real constraint_penalty;
+    // constraints
+    int32_t n_bounded, n_dense_rows, n_rows, any_tolerance;
+    BoundedCon<real> bounded[MAX_BOUNDED];
+    real viol_thr;                  // fp32: 5e-9 (== round(c, 8) > 0 in exact arithmetic)
+    // feature switches (uniform branches)
+    int32_t n_dist_obs, n_dist_act, n_dist_dyn, adversary_channel;
+    int32_t n_gates, gate_geometry, dyn_uses_episode_inertia, dyn_applies_force, auto_reset;
+    int32_t reseed_on_reset, any_init_rand, any_inertia_rand, any_gate_rand;
+    real init_state[SCG_MAX_NX + 1];
+    real inertia_nominal[4];
+    uint32_t seed;
+    uint32_t env_id_base_lo;
+};
+
+template <typename real> struct DenseRow {     // linear: c = a . x - b ; quadratic: c = x' P x - b
+    real a[SCG_MAX_NX];
+    real b, tol;
+    int8_t var, strict, has_tol, quadratic;    // quadratic rows index Cold::P[p_index]
+    int32_t out_row, p_index;
+};
+
+template <typename real> struct DistP {
+    int32_t kind, has_mask, step_offset, max_step, slot, dim;
+    real mask[SCG_MAX_NX];
+    real magnitude, duration, half_duration, decay_rate;
+    real low[SCG_MAX_NX], span[SCG_MAX_NX], std[SCG_MAX_NX];
+    real scale, omega;              // omega = 2 pi frequency
+    const real* inject;             // [dim][n] or nullptr
+};
+
+template <typename real> struct RandP { int32_t distrib; real a, b; };
+
+template <typename real> struct Cold {
+    DenseRow<real> dense[MAX_DENSE_ROWS];
+    real P[2][SCG_MAX_NX * SCG_MAX_NX];
+    real bounded_tol[MAX_BOUNDED][2 * SCG_MAX_NX];   // per (object, lo/hi dim)
+    real Q[SCG_MAX_NX * SCG_MAX_NX], R[SCG_MAX_NU * SCG_MAX_NU];
+    DistP<real> dist[3][SCG_MAX_DIST];
+    RandP<real> init_rand[SCG_MAX_NX], inertia_rand[4], gate_rand, obstacle_rand;
+    real gates[SCG_MAX_GATES][7], obstacles[SCG_MAX_OBSTACLES][6];
+    int32_t n_obstacles;
+    const real* x_goal;             // [n_goal_rows][nx] device
+};
+
+// caller-owned batch memory, typed
+template <typename real> struct Buf {
+    int64_t n;
+    real* state; int32_t* ctrl_step; int32_t* episode; uint32_t* flags; int32_t* dist_offset; real* inertia;
+    real* obs; real* env_state; real* reward; uint8_t* done; uint8_t* info; real* mse; real* c_values;
+    real* terminal_obs; real* ep_return; int32_t* ep_length; int32_t* ep_violations; double* stats;
+    const real* adv_action;
+};
+
+template <typename real> struct Roll {
+    const real* actions; int32_t k_steps; real* reward_out; uint8_t* done_out; real* log_out; int32_t log_stride;
+    int32_t step_outputs;           // 1: write the per-step outputs of Buf (scg_step), 0: only final obs/state
+};
+
+template <int KIND> struct Dims;
+template <> struct Dims<SCG_QUAD_1D> { static constexpr int NX = 2, NU = 1, NF = 1; };
+template <> struct Dims<SCG_QUAD_2D> { static constexpr int NX = 6, NU = 2, NF = 2; };
+template <> struct Dims<SCG_QUAD_3D> { static constexpr int NX = 12, NU = 4, NF = 3; };
+template <> struct Dims<SCG_CARTPOLE> { static constexpr int NX = 4, NU = 1, NF = 2; };
+
+}  // namespace scg

@@ -1,0 +1,538 @@
+// scg_step.cuh -- the fused reset / step / K-step rollout kernel for the quadrotor envs.
+// One thread = one env.  Everything Quadrotor.step() does per control step (rows A1-A11 of
+// SURVEY.md section 8a) plus DummyVecEnv's auto-reset (A14) happens between one load and one
+// store of the env's state; the substep loop touches registers and constant-bank operands only.
+#pragma once
+#include "scg_env.cuh"
+
+namespace scg {
+
+template <typename real> struct ResetInject { const real* init; const real* inertia; const int32_t* offsets; };
+
+template <int KIND, typename real> struct EnvRegs {
+    static constexpr int NX = Dims<KIND>::NX;
+    real x[NX];          // internal state, reference order; 3D angles pre-round-trip, rates = rpy_rates
+    int32_t t;           // ctrl_step_counter
+    int32_t resets;      // number of resets so far (episode index = resets - 1)
+    uint32_t flags;      // SCG_FLAG_*
+    Inertia<real> in;
+    Att3<real> a3;       // 3D
+    Att2<real> a2;       // 2D
+};
+
+template <typename real> SCG_DEV void load_inertia(const Hot<real>& h, const real* __restrict__ inertia, int64_t n, int64_t i,
+                                                   Inertia<real>& in) {
+    if (h.dyn_uses_episode_inertia && inertia) {   // extension (F9)
+        const real m = inertia[i];
+        in.inv_mass = real(1) / m;
+        in.g_over_m = h.gravity_force * h.inv_mass;   // g * m_env / m_env == GRAVITY_ACC
+#pragma unroll
+        for (int j = 0; j < 3; ++j) { in.J[j] = inertia[int64_t(j + 1) * n + i]; in.J_inv[j] = real(1) / in.J[j]; }
+    } else {
+        in.inv_mass = h.inv_mass;
+        in.g_over_m = h.gravity_force * h.inv_mass;
+#pragma unroll
+        for (int j = 0; j < 3; ++j) { in.J[j] = h.J[j]; in.J_inv[j] = h.J_inv[j]; }
+    }
+}
+
+template <int KIND, typename real, int ATT> SCG_DEV void derive_attitude(EnvRegs<KIND, real>& e) {
+    if constexpr (KIND == SCG_QUAD_3D) {
+        const real pre[3] = {e.x[6], e.x[7], e.x[8]};
+        attitude3<real, ATT, true>(pre, e.a3);
+    } else if constexpr (KIND == SCG_QUAD_2D) {
+        attitude2<real>(e.x[4], (e.flags & SCG_FLAG_FLIPPED) ? 1u : 0u, e.a2);
+        e.x[4] = e.a2.theta;
+        e.flags = (e.flags & ~SCG_FLAG_FLIPPED) | (e.a2.flipped ? SCG_FLAG_FLIPPED : 0u);
+    }
+}
+
+// env.state (quadrotor.py:853-869) from the registers; ang = the angular-velocity vector
+// PyBullet holds (rpy_rates after a step, INIT_ANG_VEL right after reset).
+template <int KIND, typename real>
+SCG_DEV void make_state(const EnvRegs<KIND, real>& e, const real (&ang)[3], real (&st)[Dims<KIND>::NX]) {
+    if constexpr (KIND == SCG_QUAD_3D) {
+#pragma unroll
+        for (int d = 0; d < 6; ++d) st[d] = e.x[d];
+        st[6] = e.a3.rpy[0]; st[7] = e.a3.rpy[1]; st[8] = e.a3.rpy[2];
+        const real* R = e.a3.R;   // pqr = R^T ang_v (quadrotor.py:862-864)
+        st[9] = (R[0] * ang[0] + R[3] * ang[1]) + R[6] * ang[2];
+        st[10] = (R[1] * ang[0] + R[4] * ang[1]) + R[7] * ang[2];
+        st[11] = (R[2] * ang[0] + R[5] * ang[1]) + R[8] * ang[2];
+    } else if constexpr (KIND == SCG_QUAD_2D) {
+#pragma unroll
+        for (int d = 0; d < 4; ++d) st[d] = e.x[d];
+        st[4] = e.a2.theta; st[5] = ang[1];
+    } else {
+        st[0] = e.x[0]; st[1] = e.x[1];
+    }
+}
+
+// goal row for step index idx (X_GOAL or X_GOAL[idx])
+template <int KIND, typename real>
+SCG_DEV void goal_row(const Hot<real>& h, const Cold<real>* __restrict__ cold, int32_t idx, real (&g)[Dims<KIND>::NX]) {
+    constexpr int NX = Dims<KIND>::NX;
+    if (h.task == SCG_TASK_STABILIZATION) {
+#pragma unroll
+        for (int d = 0; d < NX; ++d) g[d] = h.x_goal0[d];
+    } else {
+        const real* row = cold->x_goal + int64_t(idx) * NX;
+#pragma unroll
+        for (int d = 0; d < NX; ++d) g[d] = row[d];
+    }
+}
+
+// obs = state + observation disturbances, then extend_obs (quadrotor.py:878-884, benchmark_env.py:406-420)
+template <int KIND, typename real>
+SCG_DEV void write_obs(const Hot<real>& h, const Cold<real>* __restrict__ cold, const Buf<real>& b, real* __restrict__ dst,
+                       const real (&st)[Dims<KIND>::NX], int32_t t_pre, uint32_t obs_index, const RngKey& key,
+                       uint32_t episode, int64_t n, int64_t i) {
+    constexpr int NX = Dims<KIND>::NX;
+    real o[NX];
+#pragma unroll
+    for (int d = 0; d < NX; ++d) o[d] = st[d];
+    if (h.n_dist_obs)
+        apply_channel<real, NX>(cold, SCG_CH_OBSERVATION, h.n_dist_obs, o, t_pre, real(t_pre * h.substeps) * h.dt, key,
+                                obs_index, episode, b.dist_offset, n, i);
+#pragma unroll
+    for (int d = 0; d < NX; ++d) dst[int64_t(d) * n + i] = o[d];
+    if (h.cost == SCG_COST_RL_REWARD && h.obs_goal_horizon > 0) {
+        const int rows = h.task == SCG_TASK_TRAJ_TRACKING ? h.obs_goal_horizon : 1;
+        for (int r = 0; r < rows; ++r) {
+            int32_t idx = t_pre + 1 + r;
+            idx = idx < h.n_goal_rows - 1 ? idx : h.n_goal_rows - 1;
+            real g[NX];
+            goal_row<KIND, real>(h, cold, idx, g);
+#pragma unroll
+            for (int d = 0; d < NX; ++d) dst[int64_t((r + 1) * NX + d) * n + i] = g[d];
+        }
+    }
+}
+
+template <typename real> SCG_DEV real rand_value(const RandP<real>& rp, real u, real z) {
+    if (rp.distrib == SCG_RAND_UNIFORM) return rp.a + (rp.b - rp.a) * u;
+    if (rp.distrib == SCG_RAND_NORMAL) return rp.a + rp.b * z;
+    return real(0);
+}
+
+// Quadrotor.reset() (quadrotor.py:356-504) for one env.  Leaves e ready for the next step and
+// returns env.state of the fresh episode in st.
+template <int KIND, typename real, int ATT>
+SCG_DEV void reset_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, const Buf<real>& b,
+                       const ResetInject<real>& inj, const RngKey& key, int64_t n, int64_t i,
+                       EnvRegs<KIND, real>& e, real (&st)[Dims<KIND>::NX]) {
+    constexpr int NX = Dims<KIND>::NX;
+    const uint32_t ep = h.reseed_on_reset ? 0u : uint32_t(e.resets);
+    e.resets += 1;
+    e.t = 0;
+    e.flags &= SCG_FLAG_CNSTR_VIOLATION;   // cnstr_violation survives reset (benchmark_env.py:218)
+    // disturbance offsets (DisturbanceList.reset -> randint(max_step), disturbances.py:122-126,169-172)
+    for (int ch = 0; ch < 3; ++ch) {
+        const int nd = ch == 0 ? h.n_dist_obs : ch == 1 ? h.n_dist_act : h.n_dist_dyn;
+        for (int k = 0; k < nd; ++k) {
+            const DistP<real>& D = cold->dist[ch][k];
+            if ((D.kind == SCG_DIST_IMPULSE || D.kind == SCG_DIST_STEP) && D.step_offset < 0) {
+                int32_t off;
+                if (inj.offsets) off = inj.offsets[int64_t(D.slot) * n + i];
+                else {
+                    const U4 w = philox4x32_10(0u, ep, STREAM_RESET_OFFSETS, uint32_t(D.slot >> 2), key.seed, key.env);
+                    off = randint(word_of(w, D.slot & 3), D.max_step);
+                }
+                b.dist_offset[int64_t(D.slot) * n + i] = off;
+            }
+        }
+    }
+    // inertial properties (quadrotor.py:447-467): value += distrib(...)
+    if (b.inertia) {
+        real u[4], z[4];
+        if (h.any_inertia_rand && !inj.inertia) {
+            draw_uniforms<real, 4>(key, 0u, ep, STREAM_RESET_INERTIA, u);
+            draw_normals<real, 4>(key, 0u, ep, STREAM_RESET_INERTIA, z);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            real v = h.inertia_nominal[j];
+            if (inj.inertia) v += inj.inertia[int64_t(j) * n + i];
+            else if (h.any_inertia_rand) v += rand_value(cold->inertia_rand[j], u[j], z[j]);
+            b.inertia[int64_t(j) * n + i] = v;
+        }
+    }
+    load_inertia(h, b.inertia, n, i, e.in);
+    // initial state (quadrotor.py:477-493), label order == state order
+    real init[NX];
+#pragma unroll
+    for (int d = 0; d < NX; ++d) init[d] = h.init_state[d];
+    if (inj.init) {
+#pragma unroll
+        for (int d = 0; d < NX; ++d) init[d] += inj.init[int64_t(d) * n + i];
+    } else if (h.any_init_rand) {
+        real u[NX], z[NX];
+        draw_uniforms<real, NX>(key, 0u, ep, STREAM_RESET_INIT, u);
+        draw_normals<real, NX>(key, 0u, ep, STREAM_RESET_INIT, z);
+#pragma unroll
+        for (int d = 0; d < NX; ++d) init[d] += rand_value(cold->init_rand[d], u[d], z[d]);
+    }
+    real ang[3] = {real(0), real(0), real(0)};
+    if constexpr (KIND == SCG_QUAD_3D) {
+#pragma unroll
+        for (int d = 0; d < 9; ++d) e.x[d] = init[d];
+        e.x[9] = e.x[10] = e.x[11] = real(0);          // rpy_rates restart at 0 (base_aviary.py:232-233)
+        ang[0] = init[9]; ang[1] = init[10]; ang[2] = init[11];   // INIT_ANG_VEL lives in PyBullet only
+    } else if constexpr (KIND == SCG_QUAD_2D) {
+#pragma unroll
+        for (int d = 0; d < 5; ++d) e.x[d] = init[d];
+        e.x[5] = real(0);
+        ang[1] = init[5];
+    } else {
+        // 1D labels are init_x / init_x_dot (quadrotor.py:208): they set the unobserved x axis;
+        // z and z_dot always start at 0.
+        e.x[0] = real(0); e.x[1] = real(0);
+    }
+    derive_attitude<KIND, real, ATT>(e);
+    make_state<KIND, real>(e, ang, st);
+}
+
+// One Quadrotor.step(): returns reward / done / info bits, leaves env.state in st.
+template <int KIND, typename real, int ATT>
+SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, const Buf<real>& b,
+                      const RngKey& key, int64_t n, int64_t i, EnvRegs<KIND, real>& e,
+                      const real (&raw)[Dims<KIND>::NU], real (&st)[Dims<KIND>::NX], real& reward, bool& done,
+                      uint32_t& info, real& mse, Motors<real>& mot, real* __restrict__ c_out) {
+    constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
+    const uint32_t ep = h.reseed_on_reset ? 0u : uint32_t(e.resets - 1);
+    const int32_t t = e.t;
+    const real t_sim = real(t * h.substeps) * h.dt;
+    info = 0u;
+    // ---- before_step / _preprocess_control (quadrotor.py:815-842)
+    real thr[NU], pre[NU];
+#pragma unroll
+    for (int j = 0; j < NU; ++j) {
+        const real c = m_clip(raw[j], h.act_low[j], h.act_high[j]);
+        pre[j] = h.normalized_action ? (real(1) + h.norm_act_scale * c) * h.hover_thrust : c;
+        thr[j] = pre[j];
+    }
+    if (h.n_dist_act)
+        apply_channel<real, NU>(cold, SCG_CH_ACTION, h.n_dist_act, thr, t, t_sim, key, uint32_t(t), ep, b.dist_offset, n, i);
+    if (h.adversary_channel == SCG_CH_ACTION && b.adv_action) {
+#pragma unroll
+        for (int j = 0; j < NU; ++j) thr[j] += b.adv_action[i * NU + j];
+    }
+    motors_from_thrust<KIND, real>(h, thr, mot);
+    // ---- external force (extension, F5: the reference never integrates it in DYN)
+    real fx = real(0), fy = real(0), fz = real(0);
+    if (h.dyn_applies_force && (h.n_dist_dyn || h.adversary_channel == SCG_CH_DYNAMICS)) {
+        constexpr int NF = Dims<KIND>::NF;
+        real f[NF];
+#pragma unroll
+        for (int d = 0; d < NF; ++d) f[d] = real(0);
+        if (h.n_dist_dyn)
+            apply_channel<real, NF>(cold, SCG_CH_DYNAMICS, h.n_dist_dyn, f, t, t_sim, key, uint32_t(t), ep, b.dist_offset, n, i);
+        if (h.adversary_channel == SCG_CH_DYNAMICS && b.adv_action) {
+#pragma unroll
+            for (int d = 0; d < NF; ++d) f[d] += b.adv_action[i * NF + d];
+        }
+        if constexpr (KIND == SCG_QUAD_1D) { fz = f[0]; }
+        else if constexpr (KIND == SCG_QUAD_2D) { fx = f[0]; fz = f[1]; }
+        else { fx = f[0]; fy = f[1]; fz = f[2]; }
+    }
+    // ---- _advance_simulation: S explicit substeps (base_aviary.py:266-322, 522-576)
+    const real Tm = mot.T * e.in.inv_mass;
+    const real dt = h.dt;
+    if constexpr (KIND == SCG_QUAD_3D) {
+        const real axf = fx * e.in.inv_mass, ayf = fy * e.in.inv_mass, azf = fz * e.in.inv_mass - e.in.g_over_m;
+        for (int s = 0; s < h.substeps; ++s) {
+            const real ax = e.a3.R[2] * Tm + axf, ay = e.a3.R[5] * Tm + ayf, az = e.a3.R[8] * Tm + azf;
+            const real w0 = e.x[9], w1 = e.x[10], w2 = e.x[11];
+            const real jw0 = e.in.J[0] * w0, jw1 = e.in.J[1] * w1, jw2 = e.in.J[2] * w2;
+            const real d0 = e.in.J_inv[0] * (mot.tx - (w1 * jw2 - w2 * jw1));
+            const real d1 = e.in.J_inv[1] * (mot.ty - (w2 * jw0 - w0 * jw2));
+            const real d2 = e.in.J_inv[2] * (mot.tz - (w0 * jw1 - w1 * jw0));
+            e.x[1] += dt * ax; e.x[3] += dt * ay; e.x[5] += dt * az;          // vel first
+            e.x[9] += dt * d0; e.x[10] += dt * d1; e.x[11] += dt * d2;         // then rates
+            e.x[0] += dt * e.x[1]; e.x[2] += dt * e.x[3]; e.x[4] += dt * e.x[5];   // pos uses NEW vel
+            const real pre3[3] = {e.a3.rpy[0] + dt * e.x[9], e.a3.rpy[1] + dt * e.x[10], e.a3.rpy[2] + dt * e.x[11]};
+            e.x[6] = pre3[0]; e.x[7] = pre3[1]; e.x[8] = pre3[2];
+            if (s + 1 < h.substeps) attitude3<real, ATT, false>(pre3, e.a3);
+            else attitude3<real, ATT, true>(pre3, e.a3);
+        }
+    } else if constexpr (KIND == SCG_QUAD_2D) {
+        const real axf = fx * e.in.inv_mass, azf = fz * e.in.inv_mass - e.in.g_over_m;
+        for (int s = 0; s < h.substeps; ++s) {
+            const real ax = e.a2.r3x * Tm + axf, az = e.a2.r3z * Tm + azf;
+            const real dw = e.in.J_inv[1] * mot.ty;
+            e.x[1] += dt * ax; e.x[3] += dt * az;
+            e.x[5] += dt * dw;
+            e.x[0] += dt * e.x[1]; e.x[2] += dt * e.x[3];
+            attitude2<real>(e.a2.theta + dt * e.x[5], e.a2.flipped, e.a2);
+            e.x[4] = e.a2.theta;
+        }
+        e.flags = (e.flags & ~SCG_FLAG_FLIPPED) | (e.a2.flipped ? SCG_FLAG_FLIPPED : 0u);
+    } else {
+        const real az = Tm + (fz * e.in.inv_mass - e.in.g_over_m);
+        for (int s = 0; s < h.substeps; ++s) { e.x[1] += dt * az; e.x[0] += dt * e.x[1]; }
+    }
+    // ---- _get_observation: env.state (obs itself is written by the caller, it may be replaced on reset)
+    real ang[3];
+    if constexpr (KIND == SCG_QUAD_3D) { ang[0] = e.x[9]; ang[1] = e.x[10]; ang[2] = e.x[11]; }
+    else if constexpr (KIND == SCG_QUAD_2D) { ang[0] = real(0); ang[1] = e.x[5]; ang[2] = real(0); }
+    else { ang[0] = ang[1] = ang[2] = real(0); }
+    make_state<KIND, real>(e, ang, st);
+    // ---- _get_info (quadrotor.py:1004-1134): mse, goal hold (collision scan is dead in DYN, F5)
+    real goal[NX];
+    {
+        const int32_t gi = t < h.n_goal_rows - 1 ? t : h.n_goal_rows - 1;
+        goal_row<KIND, real>(h, cold, gi, goal);
+    }
+    mse = real(0);
+#pragma unroll
+    for (int d = 0; d < NX; ++d) { const real er = (st[d] - goal[d]) * h.mse_weight[d]; mse += er * er; }
+    bool gate_passed = false, at_goal = false, completed = (e.flags & SCG_FLAG_COMPLETED) != 0u;
+    uint32_t cur_gate = (e.flags >> SCG_FLAG_GATE_SHIFT) & 0xFFu;
+    if constexpr (KIND == SCG_QUAD_3D) {
+        if (cur_gate == uint32_t(h.n_gates) && h.task == SCG_TASK_STABILIZATION) {   // quadrotor.py:1117-1130
+            uint32_t hold = e.flags >> SCG_FLAG_HOLD_SHIFT;
+            const real dx = st[0] - h.x_goal0[0], dy = st[2] - h.x_goal0[2], dz = st[4] - h.x_goal0[4];
+            if (m_sqrt(dx * dx + dy * dy + dz * dz) < h.goal_tol) { at_goal = true; hold = hold < 0xFFFFu ? hold + 1u : hold; }
+            else hold = 0u;
+            if (hold > uint32_t(2 * h.ctrl_freq)) completed = true;
+            e.flags = (e.flags & 0xFFFFu) | (hold << SCG_FLAG_HOLD_SHIFT);
+        }
+    }
+    e.flags = (e.flags & ~(SCG_FLAG_AT_GOAL | SCG_FLAG_COMPLETED)) | (at_goal ? SCG_FLAG_AT_GOAL : 0u) |
+              (completed ? SCG_FLAG_COMPLETED : 0u);
+    if (at_goal) info |= SCG_INFO_AT_GOAL;
+    if (completed) info |= SCG_INFO_COMPLETED;
+    if (gate_passed) info |= SCG_INFO_GATE_PASSED;
+    // ---- _get_done (quadrotor.py:956-1002)
+    done = false;
+    if (h.task == SCG_TASK_STABILIZATION && h.cost == SCG_COST_QUADRATIC) {
+        real nn = real(0);
+#pragma unroll
+        for (int d = 0; d < NX; ++d) { const real er = st[d] - h.x_goal0[d]; nn += er * er; }
+        if (m_sqrt(nn) < h.goal_tol) { done = true; info |= SCG_INFO_GOAL_REACHED; }
+    }
+    if (h.done_on_out_of_bound) {
+        bool oob = false;
+#pragma unroll
+        for (int d = 0; d < NX; ++d) {
+            const bool masked = KIND == SCG_QUAD_3D ? (d == 0 || d == 2 || d == 4 || d == 6 || d == 7 || d == 8)
+                                                   : ((d & 1) == 0);
+            if (masked) oob |= (st[d] < h.state_low[d]) | (st[d] > h.state_high[d]);
+        }
+        if (oob) { done = true; info |= SCG_INFO_OUT_OF_BOUND; }
+    }
+    if (h.done_on_completion && completed) done = true;
+    // ---- _get_reward (quadrotor.py:886-954); t is still the pre-increment counter
+    if (h.cost == SCG_COST_RL_REWARD) {
+        real dist = real(0), dact = real(0);
+#pragma unroll
+        for (int d = 0; d < NX; ++d) { const real er = st[d] - goal[d]; dist += h.rew_state_weight[d] * er * er; }
+#pragma unroll
+        for (int j = 0; j < NU; ++j) { const real er = pre[j] - h.u_goal[j]; dact += h.rew_act_weight[j] * er * er; }
+        reward = -(dist + dact);
+        if (h.rew_exponential) reward = m_exp(reward);
+    } else if (h.cost == SCG_COST_QUADRATIC) {
+        real gq[NX];   // traj tracking uses X_GOAL[t] un-clamped (quadrotor.py:924-926)
+        goal_row<KIND, real>(h, cold, t, gq);
+        real lx = real(0), lu = real(0);
+        if (h.quadratic_diag) {
+#pragma unroll
+            for (int d = 0; d < NX; ++d) { const real er = st[d] - gq[d]; lx += h.q_diag[d] * er * er; }
+#pragma unroll
+            for (int j = 0; j < NU; ++j) { const real er = pre[j] - h.u_goal[j]; lu += h.r_diag[j] * er * er; }
+        } else {
+#pragma unroll
+            for (int a = 0; a < NX; ++a) {
+                real row = real(0);
+#pragma unroll
+                for (int c = 0; c < NX; ++c) row += cold->Q[a * SCG_MAX_NX + c] * (st[c] - gq[c]);
+                lx += (st[a] - gq[a]) * row;
+            }
+#pragma unroll
+            for (int a = 0; a < NU; ++a) {
+                real row = real(0);
+#pragma unroll
+                for (int c = 0; c < NU; ++c) row += cold->R[a * SCG_MAX_NU + c] * (pre[c] - h.u_goal[c]);
+                lu += (pre[a] - h.u_goal[a]) * row;
+            }
+        }
+        reward = -(real(0.5) * lx + real(0.5) * lu);
+    } else {
+        reward = real(0);
+        if (gate_passed) reward += real(100);
+        if (at_goal) reward += real(100);
+        if (e.flags & SCG_FLAG_CNSTR_VIOLATION) reward -= real(100);   // previous step's flag (F8)
+    }
+    // ---- after_step (benchmark_env.py:422-463)
+    e.t = t + 1;
+    if (h.n_rows > 0) {
+        bool violated, almost;
+        eval_constraints<KIND, real>(h, cold, st, raw, false, c_out, n, i, violated, almost);
+        if (violated) {
+            e.flags |= SCG_FLAG_CNSTR_VIOLATION; info |= SCG_INFO_VIOLATION;
+            if (h.done_on_violation) done = true;
+        } else e.flags &= ~SCG_FLAG_CNSTR_VIOLATION;
+        if (h.cost == SCG_COST_RL_REWARD && h.use_constraint_penalty && almost) reward += h.constraint_penalty;
+    }
+    if (e.t >= h.ctrl_steps) {
+        if (!done) info |= SCG_INFO_TRUNCATED;
+        done = true;
+    }
+}
+
+template <typename T> SCG_DEV T warp_sum(T v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// MODE 0: reset (mask optional)   MODE 1: K fused control steps (scg_step is K = 1 with outputs)
+template <int KIND, typename real, int ATT, int MODE>
+__global__ void __launch_bounds__(128)
+k_env(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, const Buf<real> b,
+      const Roll<real> ro, const ResetInject<real> inj, const uint8_t* __restrict__ mask) {
+    constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
+    const int64_t n = b.n;
+    const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    const bool valid = i < n;
+    const int64_t ii = valid ? i : n - 1;   // out-of-range lanes shadow the last env, never store
+    const RngKey key{h.seed, h.env_id_base_lo + uint32_t(ii)};
+    EnvRegs<KIND, real> e;
+#pragma unroll
+    for (int d = 0; d < NX; ++d) e.x[d] = b.state[int64_t(d) * n + ii];
+    e.t = b.ctrl_step[ii];
+    e.resets = b.episode[ii];
+    e.flags = b.flags[ii];
+    real st[NX];
+    if constexpr (MODE == 0) {
+        const bool sel = valid && (mask == nullptr || mask[ii] != 0);
+        if (!sel) return;
+        reset_env<KIND, real, ATT>(h, cold, b, inj, key, n, ii, e, st);
+#pragma unroll
+        for (int d = 0; d < NX; ++d) b.state[int64_t(d) * n + ii] = e.x[d];
+        b.ctrl_step[ii] = e.t; b.episode[ii] = e.resets; b.flags[ii] = e.flags;
+        if (b.env_state) {
+#pragma unroll
+            for (int d = 0; d < NX; ++d) b.env_state[int64_t(d) * n + ii] = st[d];
+        }
+        write_obs<KIND, real>(h, cold, b, b.obs, st, 0, 0u, key, h.reseed_on_reset ? 0u : uint32_t(e.resets - 1), n, ii);
+        if (b.ep_return) b.ep_return[ii] = real(0);
+        if (b.ep_length) b.ep_length[ii] = 0;
+        if (b.ep_violations) b.ep_violations[ii] = 0;
+        if (h.n_rows > 0 && b.c_values) {   // after_reset: state constraints only (benchmark_env.py:376-383)
+            bool v, a;
+            real raw0[NU];
+#pragma unroll
+            for (int j = 0; j < NU; ++j) raw0[j] = real(0);
+            eval_constraints<KIND, real>(h, cold, st, raw0, true, b.c_values, n, ii, v, a);
+        }
+        return;
+    } else {
+        load_inertia(h, b.inertia, n, ii, e.in);
+        derive_attitude<KIND, real, ATT>(e);
+        real ep_ret = b.ep_return ? b.ep_return[ii] : real(0);
+        int32_t ep_len = b.ep_length ? b.ep_length[ii] : 0;
+        int32_t ep_viol = b.ep_violations ? b.ep_violations[ii] : 0;
+        // per-thread statistics (reduced once at the end)
+        float s_eps = 0.f, s_ret = 0.f, s_len = 0.f, s_viol = 0.f, s_mse = 0.f, s_trunc = 0.f, s_compl = 0.f, s_vep = 0.f;
+        real reward = real(0), mse = real(0);
+        bool done = false;
+        uint32_t info = 0u;
+        Motors<real> mot;
+        // software prefetch of the next action (one 16-byte load per 3D env per step)
+        real raw[NU], nxt[NU];
+        const real* ap = ro.actions + ii * NU;
+#pragma unroll
+        for (int j = 0; j < NU; ++j) nxt[j] = ap[j];
+        bool fresh = false;   // obs must come from a reset this step
+        for (int k = 0; k < ro.k_steps; ++k) {
+#pragma unroll
+            for (int j = 0; j < NU; ++j) raw[j] = nxt[j];
+            if (k + 1 < ro.k_steps) {
+                const real* an = ro.actions + (int64_t(k + 1) * n + ii) * NU;
+#pragma unroll
+                for (int j = 0; j < NU; ++j) nxt[j] = an[j];
+            }
+            real* c_out = (ro.step_outputs && valid) ? b.c_values : nullptr;
+            step_env<KIND, real, ATT>(h, cold, b, key, n, ii, e, raw, st, reward, done, info, mse, mot, c_out);
+            ep_ret += reward; ep_len += 1; ep_viol += (info & SCG_INFO_VIOLATION) ? 1 : 0;
+            s_viol += (info & SCG_INFO_VIOLATION) ? 1.f : 0.f;
+            s_mse += float(mse);
+            if (valid) {
+                if (ro.reward_out) ro.reward_out[int64_t(k) * n + ii] = reward;
+                if (ro.done_out) ro.done_out[int64_t(k) * n + ii] = done ? 1 : 0;
+                if (ro.log_out && (k % ro.log_stride) == 0) {   // Logger.py:50-66 record
+                    real* L = ro.log_out + int64_t(k / ro.log_stride) * 16 * n + ii;
+                    real rec[16];
+                    if constexpr (KIND == SCG_QUAD_3D) {
+                        rec[0] = e.x[0]; rec[1] = e.x[2]; rec[2] = e.x[4]; rec[3] = e.x[1]; rec[4] = e.x[3]; rec[5] = e.x[5];
+                        rec[6] = e.a3.rpy[0]; rec[7] = e.a3.rpy[1]; rec[8] = e.a3.rpy[2];
+                        rec[9] = e.x[9]; rec[10] = e.x[10]; rec[11] = e.x[11];
+                    } else if constexpr (KIND == SCG_QUAD_2D) {
+                        rec[0] = e.x[0]; rec[1] = 0; rec[2] = e.x[2]; rec[3] = e.x[1]; rec[4] = 0; rec[5] = e.x[3];
+                        rec[6] = 0; rec[7] = e.a2.theta; rec[8] = 0; rec[9] = 0; rec[10] = e.x[5]; rec[11] = 0;
+                    } else {
+                        rec[0] = 0; rec[1] = 0; rec[2] = e.x[0]; rec[3] = 0; rec[4] = 0; rec[5] = e.x[1];
+                        rec[6] = rec[7] = rec[8] = rec[9] = rec[10] = rec[11] = 0;
+                    }
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) rec[12 + j] = mot.rpm[j];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) L[int64_t(j) * n] = rec[j];
+                }
+            }
+            fresh = false;
+            if (done) {
+                s_eps += 1.f; s_ret += float(ep_ret); s_len += float(ep_len);
+                s_trunc += (info & SCG_INFO_TRUNCATED) ? 1.f : 0.f;
+                s_compl += (info & SCG_INFO_COMPLETED) ? 1.f : 0.f;
+                s_vep += ep_viol > 0 ? 1.f : 0.f;
+                if (h.auto_reset) {   // DummyVecEnv.step_wait (dummy_vec_env.py:38-49)
+                    if (ro.step_outputs && valid && b.terminal_obs)
+                        write_obs<KIND, real>(h, cold, b, b.terminal_obs, st, e.t - 1, uint32_t(e.t), key,
+                                              h.reseed_on_reset ? 0u : uint32_t(e.resets - 1), n, ii);
+                    const ResetInject<real> none{nullptr, nullptr, nullptr};
+                    reset_env<KIND, real, ATT>(h, cold, b, none, key, n, ii, e, st);
+                    ep_ret = real(0); ep_len = 0; ep_viol = 0;
+                    fresh = true;
+                }
+            }
+        }
+        if (valid) {
+#pragma unroll
+            for (int d = 0; d < NX; ++d) b.state[int64_t(d) * n + ii] = e.x[d];
+            b.ctrl_step[ii] = e.t; b.episode[ii] = e.resets; b.flags[ii] = e.flags;
+            if (b.env_state) {
+#pragma unroll
+                for (int d = 0; d < NX; ++d) b.env_state[int64_t(d) * n + ii] = st[d];
+            }
+            const uint32_t ep = h.reseed_on_reset ? 0u : uint32_t(e.resets - 1);
+            if (fresh) write_obs<KIND, real>(h, cold, b, b.obs, st, 0, 0u, key, ep, n, ii);
+            else write_obs<KIND, real>(h, cold, b, b.obs, st, e.t - 1, uint32_t(e.t), key, ep, n, ii);
+            b.reward[ii] = reward; b.done[ii] = done ? 1 : 0; b.info[ii] = uint8_t(info);
+            if (b.mse) b.mse[ii] = mse;
+            if (b.ep_return) b.ep_return[ii] = ep_ret;
+            if (b.ep_length) b.ep_length[ii] = ep_len;
+            if (b.ep_violations) b.ep_violations[ii] = ep_viol;
+        }
+        if (b.stats) {   // warp-shuffle reduction, one atomic per warp per statistic
+            const float steps = valid ? float(ro.k_steps) : 0.f;
+            float v[8] = {s_eps, s_ret, s_len, s_viol, s_mse, s_trunc, s_compl, s_vep};
+            if (!valid) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] = 0.f;
+            }
+            const int slot[8] = {SCG_STAT_EPISODES, SCG_STAT_RETURN, SCG_STAT_LENGTH, SCG_STAT_VIOLATION_STEPS,
+                                 SCG_STAT_MSE, SCG_STAT_TRUNCATED, SCG_STAT_COMPLETED, SCG_STAT_VIOLATED_EPISODES};
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const double r = warp_sum<double>(double(v[j]));
+                if ((threadIdx.x & 31) == 0 && r != 0.0) atomicAdd(b.stats + slot[j], r);
+            }
+            const double rs = warp_sum<double>(double(steps));
+            if ((threadIdx.x & 31) == 0) atomicAdd(b.stats + SCG_STAT_ENV_STEPS, rs);
+        }
+    }
+}
+
+}  // namespace scg

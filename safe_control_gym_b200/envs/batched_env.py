@@ -1,0 +1,250 @@
+"""Common host logic of the batched envs: buffer ownership, the C-ABI calls, and the
+``BenchmarkEnv`` reset()/step() surface (safe_control_gym/envs/benchmark_env.py:63-463) in
+VecEnv form (vec_env.py:16-163): ``reset() -> (obs[N, obs_dim], info)``,
+``step(actions[N, nu]) -> (obs, rew[N], done[N], info)`` with ``info`` a dict of device tensors
+carrying the reference's keys.  ``num_envs == 1`` with ``squeeze=True`` returns the reference's
+scalar signatures (numpy obs, float reward, bool done, dict info).
+
+torch is used as the zero-copy container for the batch memory and for streams; every
+computation of the path happens in libscg_b200.so.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from .. import _lib as L
+
+
+class BatchedEnvBase:
+    NAME = "base"
+
+    # ------------------------------------------------------------------ construction
+    def _init_batch(self, cfg, num_envs, device, dtype, nx, nu, obs_dim, n_rows, n_slots, squeeze):
+        if not torch.cuda.is_available():
+            raise RuntimeError("safe_control_gym_b200 needs a CUDA device: there is no CPU fallback for the env step")
+        self.lib = L.load()
+        self.num_envs = int(num_envs)
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("device must be a CUDA device")
+        self.dtype = dtype
+        self._squeeze = bool(squeeze) and self.num_envs == 1
+        self._cfg = cfg
+        self._np_real = np.float32 if dtype == torch.float32 else np.float64
+        n = self.num_envs
+        dev = self.device
+        with torch.cuda.device(dev):
+            handle = C.c_void_p()
+            L.check(self.lib.scg_create(C.byref(cfg), C.byref(handle)))
+        self._h = handle
+
+        def z(*shape, dt=dtype):
+            return torch.zeros(*shape, dtype=dt, device=dev)
+        self.buf_state = z(nx, n)
+        self.buf_ctrl_step = z(n, dt=torch.int32)
+        self.buf_episode = z(n, dt=torch.int32)
+        self.buf_flags = z(n, dt=torch.int32)
+        self.buf_dist_offset = z(max(n_slots, 1), n, dt=torch.int32)
+        self.buf_inertia = z(4, n)
+        self.buf_obs = z(obs_dim, n)
+        self.buf_env_state = z(nx, n)
+        self.buf_reward = z(n)
+        self.buf_done = z(n, dt=torch.uint8)
+        self.buf_info = z(n, dt=torch.uint8)
+        self.buf_mse = z(n)
+        self.buf_c_values = z(max(n_rows, 1), n)
+        self.buf_terminal_obs = z(obs_dim, n)
+        self.buf_ep_return = z(n)
+        self.buf_ep_length = z(n, dt=torch.int32)
+        self.buf_ep_violations = z(n, dt=torch.int32)
+        self.buf_stats = z(L.STATS_LEN, dt=torch.float64)
+        self._adv = None
+        self._bind()
+        self.initial_reset = False
+        self._keep = []   # tensors referenced by in-flight launches (injection buffers)
+
+    def _bind(self, with_step_outputs=True):
+        b = L.Buffers()
+        b.n = self.num_envs
+        b.state, b.ctrl_step, b.episode = self.buf_state.data_ptr(), self.buf_ctrl_step.data_ptr(), self.buf_episode.data_ptr()
+        b.flags, b.dist_offset, b.inertia = self.buf_flags.data_ptr(), self.buf_dist_offset.data_ptr(), self.buf_inertia.data_ptr()
+        b.obs, b.env_state, b.reward = self.buf_obs.data_ptr(), self.buf_env_state.data_ptr(), self.buf_reward.data_ptr()
+        b.done, b.info = self.buf_done.data_ptr(), self.buf_info.data_ptr()
+        if with_step_outputs:
+            b.mse, b.c_values, b.terminal_obs = self.buf_mse.data_ptr(), self.buf_c_values.data_ptr(), self.buf_terminal_obs.data_ptr()
+            b.ep_return, b.ep_length, b.ep_violations = (self.buf_ep_return.data_ptr(), self.buf_ep_length.data_ptr(),
+                                                         self.buf_ep_violations.data_ptr())
+        b.stats = self.buf_stats.data_ptr()
+        b.adv_action = self._adv.data_ptr() if self._adv is not None else None
+        self._buffers = b
+        L.check(self.lib.scg_bind_buffers(self._h, C.byref(b)))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self.lib.scg_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ helpers
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _as_real(self, x, shape=None):
+        t = torch.as_tensor(x, dtype=self.dtype, device=self.device)
+        if shape is not None:
+            t = t.reshape(shape)
+        return t.contiguous()
+
+    @property
+    def launch_count(self):
+        return int(self.lib.scg_launch_count(self._h))
+
+    def set_injection(self, channel, k, tensor):
+        """Feed pre-drawn noise for disturbance ``k`` of ``channel`` ([dim, N]); None = Philox."""
+        ch = {"observation": L.CH_OBSERVATION, "action": L.CH_ACTION, "dynamics": L.CH_DYNAMICS}[channel]
+        if tensor is None:
+            L.check(self.lib.scg_set_injection(self._h, ch, k, None))
+            return
+        t = self._as_real(tensor)
+        self._keep.append(t)
+        L.check(self.lib.scg_set_injection(self._h, ch, k, C.c_void_p(t.data_ptr())))
+
+    # ------------------------------------------------------------------ reset / step
+    def _info_from_buffers(self, reset=False):
+        bits = self.buf_info
+        if reset:   # after_reset: state constraints only, in YAML order (benchmark_env.py:376-383)
+            return {"constraint_values": self.buf_c_values[self._state_row_idx].t()}
+        info = {"constraint_values": self.buf_c_values[:self._n_rows].t()}
+        info.update({
+            "constraint_violation": (bits & L.INFO_VIOLATION).ne(0).to(torch.int32),
+            "TimeLimit.truncated": (bits & L.INFO_TRUNCATED).ne(0),
+            "mse": self.buf_mse,
+            "collision": (bits & L.INFO_COLLISION).ne(0),
+            "stepped_through_gate": (bits & L.INFO_GATE_PASSED).ne(0),
+            "at_goal_position": (bits & L.INFO_AT_GOAL).ne(0),
+            "task_completed": (bits & L.INFO_COMPLETED).ne(0),
+            "goal_reached": (bits & L.INFO_GOAL_REACHED).ne(0),
+            "out_of_bound": (bits & L.INFO_OUT_OF_BOUND).ne(0),
+            "current_target_gate_id": (self.buf_flags >> L.FLAG_GATE_SHIFT) & 0xFF,
+            "terminal_observation": self.buf_terminal_obs.t(),
+            "state": self.buf_env_state.t(),
+        })
+        return info
+
+    def reset(self, mask=None, inject_init=None, inject_inertia=None, inject_offsets=None):
+        """Quadrotor.reset() for every env (or those with ``mask[i] != 0``)."""
+        self.before_reset()
+        keep = []
+        def ptr(t, dt):
+            if t is None:
+                return None
+            t = torch.as_tensor(t, dtype=dt, device=self.device).contiguous()
+            keep.append(t)
+            return C.c_void_p(t.data_ptr())
+        m = ptr(mask, torch.uint8)
+        with torch.cuda.device(self.device):
+            L.check(self.lib.scg_reset(self._h, m, ptr(inject_init, self.dtype), ptr(inject_inertia, self.dtype),
+                                       ptr(inject_offsets, torch.int32), self._stream()))
+        self._keep = keep
+        obs = self.buf_obs.t()
+        info = self._info_from_buffers(reset=True)
+        info.update(self._reset_info())
+        if self._squeeze:
+            obs = obs[0].cpu().numpy().astype(np.float64)
+            info = dict(info)
+            info["constraint_values"] = info["constraint_values"][0].cpu().numpy().astype(np.float64)
+            return (obs, info) if self.INFO_IN_RESET else obs
+        return (obs, info) if self.INFO_IN_RESET else obs
+
+    def before_reset(self):
+        self.initial_reset = True
+
+    def _reset_info(self):
+        return {}
+
+    def step(self, action):
+        """Quadrotor.step(action) for the whole batch: ONE kernel launch."""
+        if not self.initial_reset:
+            raise RuntimeError("[ERROR] You must call env.reset() at least once before using env.step().")
+        a = self._as_real(action, (self.num_envs, self.action_dim))
+        self.current_raw_input_action = a
+        with torch.cuda.device(self.device):
+            L.check(self.lib.scg_step(self._h, C.c_void_p(a.data_ptr()), self._stream()))
+        self._adv_consumed()
+        obs, rew, done = self.buf_obs.t(), self.buf_reward, self.buf_done.ne(0)
+        info = self._info_from_buffers()
+        if self._squeeze:
+            i = {k: (v[0].cpu().numpy() if v.dim() > 1 else v[0].item()) for k, v in info.items()}
+            i["constraint_values"] = np.asarray(i["constraint_values"], dtype=np.float64)
+            return obs[0].cpu().numpy().astype(np.float64), float(rew[0].item()), bool(done[0].item()), i
+        return obs, rew, done, info
+
+    def _adv_consumed(self):
+        pass
+
+    def rollout(self, actions, reward_out=None, done_out=None, log_out=None, log_stride=1):
+        """K fused control steps with auto-reset; ``actions`` is a device tensor [K, N, nu].
+        Returns the final observation view; per-episode statistics accumulate in ``stats()``."""
+        if not self.initial_reset:
+            raise RuntimeError("[ERROR] You must call env.reset() at least once before using env.step().")
+        a = torch.as_tensor(actions, dtype=self.dtype, device=self.device).contiguous()
+        k = a.shape[0]
+        assert a.shape[1:] == (self.num_envs, self.action_dim), "actions must be [K, N, nu]"
+        args = L.RolloutArgs()
+        args.actions, args.k_steps, args.log_stride = a.data_ptr(), k, int(log_stride)
+        args.reward_out = reward_out.data_ptr() if reward_out is not None else None
+        args.done_out = done_out.data_ptr() if done_out is not None else None
+        args.log_out = log_out.data_ptr() if log_out is not None else None
+        with torch.cuda.device(self.device):
+            L.check(self.lib.scg_rollout(self._h, C.byref(args), self._stream()))
+        return self.buf_obs.t()
+
+    def rollout_host(self, host_actions, chunk_steps=50):
+        """Same as ``rollout`` with the action table in pinned HOST memory [K, N, nu]; the
+        library pipelines the host->device copies against the kernel launches."""
+        if not self.initial_reset:
+            raise RuntimeError("[ERROR] You must call env.reset() at least once before using env.step().")
+        assert host_actions.dtype == self.dtype and host_actions.is_contiguous() and not host_actions.is_cuda
+        k = host_actions.shape[0]
+        with torch.cuda.device(self.device):
+            L.check(self.lib.scg_rollout_host(self._h, C.c_void_p(host_actions.data_ptr()), k, int(chunk_steps), self._stream()))
+        return self.buf_obs.t()
+
+    def stats(self, reset=False):
+        """Episode statistics accumulated on the device (VecRecordEpisodeStatistics semantics)."""
+        out = self.buf_stats.cpu().numpy().copy()
+        if reset:
+            self.buf_stats.zero_()
+        return {name: float(out[i]) for i, name in enumerate(L.STAT_NAMES)}
+
+    # ------------------------------------------------------------------ state access
+    @property
+    def state(self):
+        s = self.buf_env_state.t()
+        return s[0].cpu().numpy().astype(np.float64) if self._squeeze else s
+
+    @property
+    def ctrl_step_counter(self):
+        return int(self.buf_ctrl_step[0].item()) if self._squeeze else self.buf_ctrl_step
+
+    @property
+    def pyb_step_counter(self):
+        c = self.ctrl_step_counter
+        return c * self.PYB_STEPS_PER_CTRL
+
+    def state_dict(self):
+        """Checkpoint of the batch: a handful of tensors."""
+        names = ["state", "ctrl_step", "episode", "flags", "dist_offset", "inertia", "ep_return", "ep_length",
+                 "ep_violations", "stats", "obs", "env_state"]
+        return {k: getattr(self, "buf_" + k).clone() for k in names}
+
+    def load_state_dict(self, sd):
+        for k, v in sd.items():
+            getattr(self, "buf_" + k).copy_(v)
+        self.initial_reset = True
