@@ -1,0 +1,297 @@
+"""bench.py -- Quadrotor-3D DYN env-steps/sec (BASELINE.json metric) on N B200s.
+
+Workload (BASELINE.json configs[1]): 65,536 envs per GPU x 1,000
+control steps, quad_type 3, physics = dyn, 60 / 240 Hz (S = 4 substeps), level0's state/input bound
+constraints (14 values), cost = competition, done_on_violation with auto-reset, randomised initial
+state (Philox).  One bench "step" = one fused K = 1000 rollout launch over the whole batch
+(65.5 M env-steps, 262 M integrator substeps).  Actions are a [1000, N, 4] fp32 table (1.05 GB, larger
+than the 126 MB L2) that is re-streamed from HBM every step.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Prints ONE JSON line (see the task contract).  `value` = device-timed throughput with inputs resident
+in HBM; `e2e` = the same metric through the public API with the action table in pinned HOST memory
+(chunked H2D copies inside the timed region, final observations + statistics read back);
+`roofline` = the rollout kernel against the live-measured FP32 FMA peak (the kernel is compute-bound:
+16 B of HBM traffic per env-step against 632 algorithmic flops) with the HBM view alongside;
+`cpu_baseline` = the C/OpenMP oracle (oracle/scg_oracle.c) on the host cores over a bounded sample.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_ENVS = 65536
+K_CTRL = 1000
+SUBSTEPS = 4
+FLOPS_PER_STEP = 200 + 108 * SUBSTEPS        # SURVEY.md section 8d accounting (FMA = 2), frozen
+BYTES_PER_STEP_FUSED = 16                    # one float4 action per env-step (state amortised over K)
+METRIC = "quadrotor3d_dyn_env_steps_per_sec"
+
+INIT_RAND = {"init_x": dict(distrib="uniform", low=-0.1, high=0.1), "init_y": dict(distrib="uniform", low=-0.1, high=0.1),
+             "init_z": dict(distrib="uniform", low=0.47, high=1.47), "init_phi": dict(distrib="uniform", low=-0.1, high=0.1),
+             "init_theta": dict(distrib="uniform", low=-0.1, high=0.1), "init_psi": dict(distrib="uniform", low=-0.1, high=0.1)}
+
+
+def env_kwargs():
+    """level0.yaml's quadrotor_config (competition/level0.yaml:16-182) with physics=dyn at 60/240 Hz."""
+    return dict(quad_type=3, ctrl_freq=60, pyb_freq=240, episode_len_sec=33, cost="competition", task="stabilization",
+                task_info=dict(stabilization_goal=[-0.5, 2.9, 0.75], stabilization_goal_tolerance=0.15),
+                init_state=dict(init_x=-0.9, init_x_dot=0, init_y=-2.9, init_y_dot=0, init_z=0.03, init_z_dot=0,
+                                init_phi=0, init_theta=0, init_psi=0, init_p=0, init_q=0, init_r=0),
+                randomized_init=True, init_state_randomization_info=INIT_RAND,
+                gates=[[0.5, -2.5, 0, 0, 0, -1.57, 0], [2, -1.5, 0, 0, 0, 0, 1], [0, 0.2, 0, 0, 0, 1.57, 1], [-0.5, 1.5, 0, 0, 0, 0, 0]],
+                obstacles=[[1.5, -2.5, 0, 0, 0, 0], [0.5, -1, 0, 0, 0, 0], [1.5, 0, 0, 0, 0, 0], [-1, 0, 0, 0, 0, 0]],
+                constraints=[dict(constraint_form="default_constraint", constrained_variable="input"),
+                             dict(constraint_form="bounded_constraint", constrained_variable="state", active_dims=[0, 2, 4],
+                                  upper_bounds=[3, 3, 2], lower_bounds=[-3, -3, -0.1])],
+                done_on_violation=True, done_on_completion=True, done_on_collision=True, done_on_out_of_bound=False,
+                normalized_rl_action_space=False, seed=1337)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, gpu_index):
+        self.q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+                  "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        self.idx, self.rows, self.stop = gpu_index, [], threading.Event()
+        self.th = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self.stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.q}", "--format=csv,noheader,nounits", "-i", str(self.idx)],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.split(",")])
+            except Exception:
+                pass
+            self.stop.wait(0.2)
+
+    def __enter__(self):
+        self.th.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop.set()
+        self.th.join(timeout=6)
+
+    def summary(self):
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[j] for r in self.rows for j in range(4) if len(r) > 2 + j and r[2 + j].lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+def make_actions(torch, n, k, device, seed, std=0.005):
+    """hover + N(0, 0.005^2) per motor, clipped to the action bounds."""
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    a = torch.empty(k, n, 4, dtype=torch.float32, device=device)
+    a.normal_(mean=0.03454 * 9.8 / 4, std=std, generator=g) if std > 0 else a.fill_(0.03454 * 9.8 / 4)
+    return a.clamp_(0.0281616878, 0.1483414471)
+
+
+def cpu_reference(sample_envs, sample_steps, repeats, threads=0):
+    """Times the C/OpenMP oracle on the host cores: env-steps/s over `repeats` rollouts of a bounded
+    sample (sample_envs envs x sample_steps control steps) of the same workload."""
+    import numpy as np
+    from oracle.c_oracle import COracle3D
+    from oracle.quad_oracle import QuadOracle
+    kw = env_kwargs()
+    kw.pop("seed")
+    co = COracle3D(QuadOracle(**kw), n=sample_envs, seed=1337, init_rand=INIT_RAND, auto_reset=True, threads=threads)
+    rng = np.random.default_rng(1337)
+    acts = np.clip(0.03454 * 9.8 / 4 + rng.normal(0, 0.005, size=(sample_steps, sample_envs, 4)), 0.0281616878, 0.1483414471)
+    co.reset()
+    co.rollout(acts[:max(1, sample_steps // 10)])   # warm-up
+    times = []
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        co.rollout(acts)
+        times.append(time.perf_counter() - t0)
+    return sample_envs * sample_steps / (sum(times) / len(times)), co.num_threads(), times
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path.  The reference itself cannot be
+    imported on this image (pybullet / gym / casadi absent) and its DYN path does not run as
+    shipped (F3), so the arm times the oracle port (C + OpenMP, all host threads) on a bounded sample."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sample_envs, sample_steps = 4096, 200
+    t0 = time.perf_counter()
+    vals = []
+    for _ in range(args.warmup):
+        cpu_reference(sample_envs, sample_steps, 1)
+    v, cores, times = cpu_reference(sample_envs, sample_steps, max(args.steps, 1))
+    line = {"metric": METRIC, "value": v, "unit": "env-steps/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * sum(times) / len(times), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "impl": "reference",
+            "config": {"workload": "quadrotor3d_dyn_65536x1000_level0_constraints", "substeps": SUBSTEPS,
+                       "sample": f"{sample_envs} envs x {sample_steps} ctrl steps per step"},
+            "cpu_baseline": {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port",
+                             "sample": f"{sample_envs} envs x {sample_steps} ctrl steps, C/OpenMP oracle (oracle/scg_oracle.c), fp64"},
+            "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0, "wall_s": time.perf_counter() - t0}
+    print(json.dumps(line))
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+    from safe_control_gym_b200 import _lib as L
+    from safe_control_gym_b200.envs.quadrotor import BatchedQuadrotor
+    import ctypes as C
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    n, k = args.envs, args.ctrl_steps
+    kw = env_kwargs()
+    env = BatchedQuadrotor(num_envs=n, device=dev, dtype=torch.float32, attitude=args.attitude, auto_reset=True,
+                           seed_offset=rank * n, **kw)   # Philox keyed by GLOBAL env id: shard-independent results
+    actions = make_actions(torch, n, k, dev, 1337 + rank, args.action_std)
+    stats_all = torch.zeros(L.STATS_LEN, dtype=torch.float64, device=dev)
+
+    def one_step():
+        env.rollout(actions)
+        if world > 1:   # the only collective of the path: merge the episode statistics
+            stats_all.copy_(env.buf_stats)
+            dist.all_reduce(stats_all)
+
+    env.reset()
+    env.buf_stats.zero_()
+    for _ in range(args.warmup):
+        one_step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    launches0 = env.launch_count
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    with ClockSampler(local) as clk:
+        torch.cuda.synchronize()
+        ev[0].record()
+        for s in range(args.steps):
+            one_step()
+            ev[s + 1].record()
+        torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    total_ms = ev[0].elapsed_time(ev[-1])
+    per = [ev[s].elapsed_time(ev[s + 1]) for s in range(args.steps)]
+    launches = env.launch_count - launches0
+    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t.item())
+    value = world * n * k * args.steps / (total_ms * 1e-3)
+    stats = env.stats()
+
+    # ---- end to end through the public API: host action table -> rollout_host -> obs + stats on the host
+    host_actions = torch.empty(k, n, 4, dtype=torch.float32, pin_memory=True)
+    host_actions.copy_(actions)
+    obs_host = torch.empty(12, n, dtype=torch.float32, pin_memory=True)
+    e2e_steps = max(1, min(args.steps, 5))
+
+    def one_e2e():
+        env.rollout_host(host_actions, chunk_steps=args.chunk)
+        obs_host.copy_(env.buf_obs, non_blocking=True)
+        st = env.buf_stats.cpu()
+        torch.cuda.synchronize()
+        return st
+    one_e2e()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        one_e2e()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * n * k * e2e_steps / float(t.item())
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    # ---- roofline of the dominant kernel (k_env<3, float, FAST, rollout>): one launch per step
+    peak = C.c_double()
+    L.check(L.load().scg_measure_fp32_peak(C.byref(peak)))
+    kernel_ms = sum(per) / len(per)   # one launch per step; stats all-reduce excluded at N = 1
+    flops = float(n) * k * FLOPS_PER_STEP
+    achieved_tf = flops / (kernel_ms * 1e-3) / 1e12
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        hbm_peak, hbm_src = float(peaks["hbm_gbs"]), "MEASURED_PEAKS.json"
+    except Exception:
+        hbm_peak, hbm_src = 6650.0, "fallback (B200_PROFILING.md)"
+    hbm_bytes = float(n) * k * BYTES_PER_STEP_FUSED + n * (12 * 4 * 3 + 24)
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tp):
+        try:
+            traffic = json.load(open(tp)).get("k_env_rollout_dram_bytes_per_launch")
+        except Exception:
+            traffic = None
+    cpu_v, cores, _ = cpu_reference(4096, 200, 3)
+    line = {
+        "metric": METRIC, "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "quadrotor3d_dyn_65536x1000_level0_constraints", "envs_per_gpu": n, "ctrl_steps_per_step": k,
+                   "substeps": SUBSTEPS, "env_substeps_per_sec": value * SUBSTEPS, "mode": "fused rollout, auto-reset, Philox init", "attitude": args.attitude, "action_std": args.action_std,
+                   "l2_policy": "inputs larger than L2 (1.05 GB action table re-streamed each step)"},
+        "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": peak.value, "unit": "TFLOP/s", "frac": achieved_tf / peak.value,
+                     "traffic": traffic, "kernel": "scg::k_env<3,float,FAST,rollout>", "kernel_ms": kernel_ms,
+                     "flops_per_env_step": FLOPS_PER_STEP,
+                     "peak_source": "measured live: register-only FFMA kernel (scg_measure_fp32_peak); MEASURED_PEAKS.json has no non-tensor fp32 figure",
+                     "hbm": {"bound": "hbm", "achieved": hbm_bytes / (kernel_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                             "frac": hbm_bytes / (kernel_ms * 1e-3) / 1e9 / hbm_peak, "peak_source": hbm_src,
+                             "bytes_per_env_step": BYTES_PER_STEP_FUSED}},
+        "cpu_baseline": {"value": cpu_v, "unit": "env-steps/s", "cores": cores, "kind": "port",
+                         "sample": "4096 envs x 200 ctrl steps x 3, C/OpenMP oracle (oracle/scg_oracle.c), fp64"},
+        "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": int(host_actions.numel() * 4),
+                "d2h_bytes_per_step": int(obs_host.numel() * 4 + L.STATS_LEN * 8), "steps": e2e_steps, "chunk_ctrl_steps": args.chunk},
+        "gpu_launches": launches, "clocks": clk.summary(),
+        "episode_stats": {kk: stats[kk] for kk in ("episodes", "return", "length", "violation_steps", "env_steps")},
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--envs", type=int, default=N_ENVS)
+    ap.add_argument("--ctrl-steps", type=int, default=K_CTRL)
+    ap.add_argument("--chunk", type=int, default=50)
+    ap.add_argument("--attitude", default="fast")
+    ap.add_argument("--action-std", type=float, default=0.005)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

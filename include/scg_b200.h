@@ -60,7 +60,7 @@ enum { SCG_CH_OBSERVATION = 0, SCG_CH_ACTION = 1, SCG_CH_DYNAMICS = 2 };
 enum { SCG_RAND_NONE = 0, SCG_RAND_UNIFORM = 1, SCG_RAND_NORMAL = 2 };
 /* attitude update: literal PyBullet quaternion round trip, or the equivalent wrap with
  * the round trip kept only outside the identity region */
-enum { SCG_ATT_ROUNDTRIP = 0, SCG_ATT_FAST = 1 };
+enum { SCG_ATT_ROUNDTRIP = 0, SCG_ATT_FAST = 1, SCG_ATT_FAST_INTRINSIC = 2 /* fp32: sin/cos on the SFU */ };
 /* scg_symbolic_eval ops (symbolic_systems.py:63-123) */
 enum { SCG_SYM_FC = 0, SCG_SYM_FD_RK4 = 1, SCG_SYM_DF = 2, SCG_SYM_LOSS = 3, SCG_SYM_FD_EULER = 4 };
 
@@ -258,6 +258,10 @@ int scg_constraints_eval(scg_env* env, const void* state, const void* action, in
  * (symbolic_systems.py:63-123): x [nx][n], u [nu][n]; out layout per op */
 int scg_symbolic_eval(scg_env* env, int op, const void* x, const void* u, int64_t n, double dt,
                       void* out0, void* out1, void* stream);
+/* FP32 FMA microbenchmark (measurement aid, not on the path): runs a register-only FFMA kernel on the
+ * current device and returns the achieved TFLOP/s (FMA = 2 flop) -- the roofline denominator for the
+ * compute-bound fused rollout, since MEASURED_PEAKS.json carries no non-tensor fp32 figure. */
+int scg_measure_fp32_peak(double* tflops_out);
 /* number of kernels this handle has launched (bench.py "gpu_launches") */
 int64_t scg_launch_count(const scg_env* env);
 const char* scg_last_error(void);

@@ -21,7 +21,7 @@ VAR_STATE, VAR_INPUT = 0, 1
 DIST_IMPULSE, DIST_STEP, DIST_UNIFORM, DIST_WHITE, DIST_PERIODIC = 0, 1, 2, 3, 4
 CH_OBSERVATION, CH_ACTION, CH_DYNAMICS = 0, 1, 2
 RAND_NONE, RAND_UNIFORM, RAND_NORMAL = 0, 1, 2
-ATT_ROUNDTRIP, ATT_FAST = 0, 1
+ATT_ROUNDTRIP, ATT_FAST, ATT_FAST_INTRINSIC = 0, 1, 2
 SYM_FC, SYM_FD_RK4, SYM_DF, SYM_LOSS, SYM_FD_EULER = 0, 1, 2, 3, 4
 
 INFO_VIOLATION, INFO_TRUNCATED, INFO_COLLISION, INFO_GATE_PASSED = 0x01, 0x02, 0x04, 0x08
@@ -33,7 +33,7 @@ STAT_NAMES = ["episodes", "return", "length", "violation_steps", "mse", "gates",
 
 EXPORTS = ["scg_create", "scg_destroy", "scg_bind_buffers", "scg_set_injection", "scg_reset", "scg_step",
            "scg_rollout", "scg_rollout_host", "scg_stats_reset", "scg_stats_read", "scg_constraints_eval",
-           "scg_symbolic_eval", "scg_launch_count", "scg_last_error", "scg_version"]
+           "scg_symbolic_eval", "scg_measure_fp32_peak", "scg_launch_count", "scg_last_error", "scg_version"]
 
 
 class Constraint(C.Structure):
@@ -129,6 +129,7 @@ def load():
     lib.scg_stats_read.argtypes = [vp, C.POINTER(C.c_double), vp]
     lib.scg_constraints_eval.argtypes = [vp, vp, vp, i64, vp, vp, vp]
     lib.scg_symbolic_eval.argtypes = [vp, C.c_int, vp, vp, i64, C.c_double, vp, vp, vp]
+    lib.scg_measure_fp32_peak.argtypes = [C.POINTER(C.c_double)]
     lib.scg_launch_count.argtypes = [vp]
     lib.scg_launch_count.restype = i64
     lib.scg_last_error.restype = C.c_char_p

@@ -1,6 +1,6 @@
 // scg_api.cu -- host side of libscg_b200.so: the extern "C" ABI declared in include/scg_b200.h.
 // Builds the device parameter blocks from scg_config, validates shapes, and launches the fused
-// kernels of scg_step.cuh / scg_cartpole.cuh / scg_symbolic.cuh on the caller's stream.
+// kernels of scg_step.cuh / scg_symbolic.cuh on the caller's stream.
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -9,7 +9,6 @@
 #include <string>
 
 #include "scg_step.cuh"
-#include "scg_cartpole.cuh"
 #include "scg_symbolic.cuh"
 
 using namespace scg;
@@ -63,6 +62,7 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
     h.pwm_scale = real(c.pwm2rpm_scale); h.pwm_const = real(c.pwm2rpm_const);
     h.pwm_min = real(c.pwm_min); h.pwm_max = real(c.pwm_max); h.inv_pwm_scale = real(1.0 / c.pwm2rpm_scale);
     if (c.env_kind != SCG_CARTPOLE) h.inv_nkf = real(1.0 / ((4 / nu) * c.kf));
+    h.gravity_acc = real(c.gravity_acc); h.cp_length = real(c.cp_length); h.cp_pole_mass = real(c.cp_pole_mass); h.cp_cart_mass = real(c.cp_cart_mass);
     h.normalized_action = c.normalized_action; h.norm_act_scale = real(c.norm_act_scale); h.hover_thrust = real(c.hover_thrust);
     for (int j = 0; j < nu; ++j) { h.act_low[j] = real(c.act_low[j]); h.act_high[j] = real(c.act_high[j]); }
     for (int d = 0; d < nx; ++d) {
@@ -177,12 +177,14 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
     h.auto_reset = c.auto_reset; h.reseed_on_reset = c.reseed_on_reset;
     for (int d = 0; d < nx; ++d) {
         k.init_rand[d].distrib = c.init_rand[d].distrib; k.init_rand[d].a = real(c.init_rand[d].a); k.init_rand[d].b = real(c.init_rand[d].b);
-        if (c.init_rand[d].distrib != SCG_RAND_NONE) h.any_init_rand = 1;
+        if (c.init_rand[d].distrib == SCG_RAND_UNIFORM) h.any_init_rand |= 1;
+        if (c.init_rand[d].distrib == SCG_RAND_NORMAL) h.any_init_rand |= 2;
     }
     for (int j = 0; j < 4; ++j) {
         h.inertia_nominal[j] = real(c.inertia_nominal[j]);
         k.inertia_rand[j].distrib = c.inertia_rand[j].distrib; k.inertia_rand[j].a = real(c.inertia_rand[j].a); k.inertia_rand[j].b = real(c.inertia_rand[j].b);
-        if (c.inertia_rand[j].distrib != SCG_RAND_NONE) h.any_inertia_rand = 1;
+        if (c.inertia_rand[j].distrib == SCG_RAND_UNIFORM) h.any_inertia_rand |= 1;
+        if (c.inertia_rand[j].distrib == SCG_RAND_NORMAL) h.any_inertia_rand |= 2;
     }
     k.gate_rand.distrib = c.gate_rand.distrib; k.gate_rand.a = real(c.gate_rand.a); k.gate_rand.b = real(c.gate_rand.b);
     k.obstacle_rand.distrib = c.obstacle_rand.distrib; k.obstacle_rand.a = real(c.obstacle_rand.a); k.obstacle_rand.b = real(c.obstacle_rand.b);
@@ -228,7 +230,8 @@ extern "C" int scg_create(const scg_config* cfg, scg_env** out) {
     int nx, nu;
     if (kind_dims(cfg->env_kind, &nx, &nu)) return fail(SCG_ERR_BAD_CONFIG, "unknown env_kind");
     if (cfg->precision != 32 && cfg->precision != 64) return fail(SCG_ERR_BAD_CONFIG, "precision must be 32 or 64");
-    if (cfg->attitude_mode != SCG_ATT_ROUNDTRIP && cfg->attitude_mode != SCG_ATT_FAST) return fail(SCG_ERR_BAD_CONFIG, "bad attitude_mode");
+    if (cfg->attitude_mode < SCG_ATT_ROUNDTRIP || cfg->attitude_mode > SCG_ATT_FAST_INTRINSIC) return fail(SCG_ERR_BAD_CONFIG, "bad attitude_mode");
+    if (cfg->attitude_mode == SCG_ATT_FAST_INTRINSIC && cfg->precision != 32) return fail(SCG_ERR_BAD_CONFIG, "SCG_ATT_FAST_INTRINSIC is fp32 only");
     if (cfg->substeps < 1 || cfg->pyb_freq < 1 || cfg->ctrl_freq < 1 || cfg->pyb_freq % cfg->ctrl_freq != 0)
         return fail(SCG_ERR_BAD_CONFIG, "[ERROR] in BenchmarkEnv.__init__(), pyb_freq is not divisible by env_freq.");
     if (cfg->substeps != cfg->pyb_freq / cfg->ctrl_freq) return fail(SCG_ERR_BAD_CONFIG, "substeps != pyb_freq / ctrl_freq");
@@ -315,10 +318,13 @@ static int launch_att(scg_env* e, const Hot<real>& h, const Roll<real>& ro, cons
     const unsigned blocks = unsigned((b.n + threads - 1) / threads);
     const Cold<real>* cold = static_cast<const Cold<real>*>(e->cold_dev);
     if constexpr (KIND == SCG_CARTPOLE) {
-        k_cartpole<real, MODE><<<blocks, threads, 0, st>>>(h, cold, b, ro, inj, mask);
+        k_env<KIND, real, SCG_ATT_FAST, MODE><<<blocks, threads, 0, st>>>(h, cold, b, ro, inj, mask);
     } else {
         if (e->cfg.attitude_mode == SCG_ATT_FAST) k_env<KIND, real, SCG_ATT_FAST, MODE><<<blocks, threads, 0, st>>>(h, cold, b, ro, inj, mask);
-        else k_env<KIND, real, SCG_ATT_ROUNDTRIP, MODE><<<blocks, threads, 0, st>>>(h, cold, b, ro, inj, mask);
+        else if (e->cfg.attitude_mode == SCG_ATT_FAST_INTRINSIC) {
+            if constexpr (sizeof(real) == 4 && KIND == SCG_QUAD_3D) k_env<KIND, real, SCG_ATT_FAST_INTRINSIC, MODE><<<blocks, threads, 0, st>>>(h, cold, b, ro, inj, mask);
+            else k_env<KIND, real, SCG_ATT_FAST, MODE><<<blocks, threads, 0, st>>>(h, cold, b, ro, inj, mask);
+        } else k_env<KIND, real, SCG_ATT_ROUNDTRIP, MODE><<<blocks, threads, 0, st>>>(h, cold, b, ro, inj, mask);
     }
     e->launches += 1;
     CU(cudaGetLastError());
@@ -488,5 +494,50 @@ extern "C" int scg_symbolic_eval(scg_env* e, int op, const void* x, const void* 
     if (rc != 0) return fail(SCG_ERR_BAD_CONFIG, "symbolic op not available for this env kind");
     e->launches += 1;
     CU(cudaGetLastError());
+    return SCG_OK;
+}
+
+// ---------------------------------------------------------------- fp32 peak microbenchmark
+__global__ void __launch_bounds__(256) k_fma_peak(float* out, int iters, float a, float b) {
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = float(threadIdx.x + j) * 1e-3f;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = fmaf(v[j], a, b);
+        }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += v[j];
+    if (s == 12345.678f) out[0] = s;   // never true; keeps the chain alive
+}
+
+extern "C" int scg_measure_fp32_peak(double* tflops_out) {
+    if (!tflops_out) return fail(SCG_ERR_NULL, "scg_measure_fp32_peak: null argument");
+    int dev = 0, sms = 0;
+    CU(cudaGetDevice(&dev));
+    CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    float* out = nullptr;
+    CU(cudaMalloc(&out, sizeof(float)));
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
+    const int blocks = sms * 8, threads = 256, iters = 4096;
+    double best = 0.0;
+    for (int rep = 0; rep < 5; ++rep) {
+        CU(cudaEventRecord(e0));
+        k_fma_peak<<<blocks, threads>>>(out, iters, 0.999f, 1e-3f);
+        CU(cudaEventRecord(e1));
+        CU(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, e0, e1));
+        const double flops = 2.0 * 8 * 16 * double(iters) * blocks * threads;
+        const double tf = flops / (ms * 1e-3) / 1e12;
+        if (rep > 0 && tf > best) best = tf;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(out);
+    *tflops_out = best;
     return SCG_OK;
 }

@@ -9,34 +9,60 @@ namespace scg {
 // ------------------------------------------------------------------ attitude (row A3)
 // The reference stores the attitude in PyBullet as quatFromEuler(rpy + dt * rates) and reads it
 // back as eulerFromQuat(quat) before every use (base_aviary.py:565-574, 281-285, 322, 362-374).
-// Inside the identity region of that round trip (|pitch| < asin(0.99999), roll and yaw in
-// (-pi, pi)) the read-back equals the input, so SCG_ATT_FAST skips the quaternion and builds the
-// rotation from sin/cos of the Euler angles; outside it (fold, wrap, gimbal branch) -- and always
-// with SCG_ATT_ROUNDTRIP -- the literal bullet3 arithmetic is executed.
+// That round trip returns the canonical Euler angles of the same rotation, so SCG_ATT_FAST computes
+// them by wrap / fold arithmetic and builds the rotation from sin/cos of the angles; only inside the
+// gimbal band (|sin(pitch)| >= 0.99999, where bullet snaps the pitch) -- and always with
+// SCG_ATT_ROUNDTRIP -- the literal bullet3 arithmetic is executed.  SCG_ATT_FAST_INTRINSIC (fp32
+// only) additionally evaluates sin/cos on the SFU (MUFU.SIN / MUFU.COS).
 template <typename real> struct Att3 {
     real rpy[3];   // wrapped angles == self.rpy after _update_and_store_kinematic_information
     real R[9];     // getMatrixFromQuaternion(self.quat), row-major
 };
 
+// x - 2 pi * rint(x / 2 pi): the identity (bit-exact) for x already in [-pi, pi]
+SCG_DEV double wrap_pi(double x) {
+    const double k = rint(x * 0.15915494309189535);
+    return fma(-k, 2.4492935982947064e-16, fma(-k, 6.283185307179586, x));
+}
+SCG_DEV float wrap_pi(float x) {
+    const float k = rintf(x * 0.15915494309189535f);
+    return fmaf(-k, -1.7484555e-07f, fmaf(-k, 6.2831855f, x));   // 2 pi = 6.2831855f - 1.7484555e-07f
+}
+template <int ATT> SCG_DEV void att_sincos(float x, float* s, float* c) {
+    if (ATT == SCG_ATT_FAST_INTRINSIC) __sincosf(x, s, c);   // MUFU.SIN/COS, |err| <= 2^-21.4 on [-pi, pi]
+    else sincosf(x, s, c);
+}
+template <int ATT> SCG_DEV void att_sincos(double x, double* s, double* c) { sincos(x, s, c); }
+
 template <typename real, int ATT, bool FULL>
 SCG_DEV void attitude3(const real (&pre)[3], Att3<real>& a) {
-    const bool fast = (ATT == SCG_ATT_FAST) && m_abs(pre[1]) < real(1.5663) && m_abs(pre[0]) < real(3.1415) &&
-                      m_abs(pre[2]) < real(3.1415);
-    if (fast) {
-        real sph, cph, sth, cth, sps, cps;
-        m_sincos(pre[0], &sph, &cph);
-        m_sincos(pre[1], &sth, &cth);
-        m_sincos(pre[2], &sps, &cps);
-        a.rpy[0] = pre[0]; a.rpy[1] = pre[1]; a.rpy[2] = pre[2];
-        a.R[2] = cps * sth * cph + sps * sph;
-        a.R[5] = sps * sth * cph - cps * sph;
-        a.R[8] = cth * cph;
-        if (FULL) {
-            a.R[0] = cps * cth; a.R[1] = cps * sth * sph - sps * cph;
-            a.R[3] = sps * cth; a.R[4] = sps * sth * sph + cps * cph;
-            a.R[6] = -sth;      a.R[7] = cth * sph;
+    if (ATT != SCG_ATT_ROUNDTRIP) {
+        // Canonical Euler angles of the same rotation by arithmetic only: wrap into [-pi, pi], fold a
+        // pitch beyond +-pi/2 (Rz(psi+pi) Ry(pi-theta) Rx(phi+pi) == Rz(psi) Ry(theta) Rx(phi)), which is
+        // what eulerFromQuat(quatFromEuler(.)) returns outside its gimbal band |sin(pitch)| >= 0.99999.
+        real th = wrap_pi(pre[1]), ph = pre[0], ps = pre[2];
+        if (m_abs(th) > Consts<real>::half_pi) {
+            th = (th > real(0) ? Consts<real>::pi : -Consts<real>::pi) - th;
+            ph += Consts<real>::pi; ps += Consts<real>::pi;
         }
-        return;
+        ph = wrap_pi(ph); ps = wrap_pi(ps);
+        real sth, cth;
+        att_sincos<ATT>(th, &sth, &cth);
+        if (m_abs(sth) < real(0.99998)) {
+            real sph, cph, sps, cps;
+            att_sincos<ATT>(ph, &sph, &cph);
+            att_sincos<ATT>(ps, &sps, &cps);
+            a.rpy[0] = ph; a.rpy[1] = th; a.rpy[2] = ps;
+            a.R[2] = cps * sth * cph + sps * sph;
+            a.R[5] = sps * sth * cph - cps * sph;
+            a.R[8] = cth * cph;
+            if (FULL) {
+                a.R[0] = cps * cth; a.R[1] = cps * sth * sph - sps * cph;
+                a.R[3] = sps * cth; a.R[4] = sps * sth * sph + cps * cph;
+                a.R[6] = -sth;      a.R[7] = cth * sph;
+            }
+            return;
+        }
     }
     // pybullet getQuaternionFromEuler
     real sph, cph, sth, cth, sps, cps;
@@ -129,7 +155,37 @@ SCG_DEV void motors_from_thrust(const Hot<real>& h, const real (&thrust)[Dims<KI
 }
 
 // per-episode inertial constants (nominal in parity mode, F9)
-template <typename real> struct Inertia { real inv_mass, g_over_m, J[3], J_inv[3]; };
+template <typename real> struct Inertia { real inv_mass, g_over_m, J[3], J_inv[3]; real cp_l, cp_mp, cp_mc; };
+
+// ------------------------------------------------------------------ cart-pole ODE (row A13)
+// Frictionless cart-pole (Barto et al.), x = [x, x_dot, theta, theta_dot], theta = 0 upright,
+// l = effective (half) pole length.  The env is absent from the reference fork:
+// contract inferred from tests/scripts/verbose_api.yaml:1-91 -- parity unpinned.
+template <typename real>
+SCG_DEV void cartpole_f(const Inertia<real>& in, real g, const real (&x)[4], real F, real (&dx)[4]) {
+    real s, c;
+    m_sincos(x[2], &s, &c);
+    const real Mm = in.cp_mc + in.cp_mp, ml = in.cp_mp * in.cp_l;
+    const real tmp = (F + ml * x[3] * x[3] * s) / Mm;
+    const real thdd = (g * s - c * tmp) / (in.cp_l * (real(4.0 / 3.0) - in.cp_mp * c * c / Mm));
+    dx[0] = x[1]; dx[1] = tmp - ml * thdd * c / Mm; dx[2] = x[3]; dx[3] = thdd;
+}
+template <typename real>
+SCG_DEV void cartpole_rk4(const Inertia<real>& in, real g, real (&x)[4], real F, real dt) {   // mpc_utils.py:79-101
+    real k1[4], k2[4], k3[4], k4[4], y[4];
+    cartpole_f(in, g, x, F, k1);
+#pragma unroll
+    for (int d = 0; d < 4; ++d) y[d] = x[d] + dt * real(0.5) * k1[d];
+    cartpole_f(in, g, y, F, k2);
+#pragma unroll
+    for (int d = 0; d < 4; ++d) y[d] = x[d] + dt * real(0.5) * k2[d];
+    cartpole_f(in, g, y, F, k3);
+#pragma unroll
+    for (int d = 0; d < 4; ++d) y[d] = x[d] + dt * k3[d];
+    cartpole_f(in, g, y, F, k4);
+#pragma unroll
+    for (int d = 0; d < 4; ++d) x[d] += dt / real(6) * (k1[d] + real(2) * k2[d] + real(2) * k3[d] + k4[d]);
+}
 
 // ------------------------------------------------------------------ constraints (row A6)
 // c = g(x) rounded to 8 decimals (constraints.py:119); violated = any(c > 0) (or >= 0 if strict).
@@ -166,7 +222,7 @@ SCG_DEV void eval_constraints(const Hot<real>& h, const Cold<real>* __restrict__
                     const real rlo = bc.symmetric ? clo : round8(clo), rhi = round8(chi);
                     if (c_out && bc.row_lo[d] >= 0) c_out[int64_t(bc.row_lo[d]) * n + i] = rlo;
                     if (c_out && bc.row_hi[d] >= 0) c_out[int64_t(bc.row_hi[d]) * n + i] = rhi;
-                    if (bc.has_tol) almost |= (rlo + cold->bounded_tol[k][d] > real(0)) | (rhi + cold->bounded_tol[k][NX + d] > real(0));
+                    if (bc.has_tol) almost |= (rlo + cold->bounded_tol[k][d] > real(0)) | (rhi + cold->bounded_tol[k][SCG_MAX_NX + d] > real(0));
                 }
             }
         } else if (!state_only) {
@@ -178,7 +234,7 @@ SCG_DEV void eval_constraints(const Hot<real>& h, const Cold<real>* __restrict__
                     const real rlo = round8(clo), rhi = round8(chi);
                     if (c_out && bc.row_lo[d] >= 0) c_out[int64_t(bc.row_lo[d]) * n + i] = rlo;
                     if (c_out && bc.row_hi[d] >= 0) c_out[int64_t(bc.row_hi[d]) * n + i] = rhi;
-                    if (bc.has_tol) almost |= (rlo + cold->bounded_tol[k][d] > real(0)) | (rhi + cold->bounded_tol[k][NX + d] > real(0));
+                    if (bc.has_tol) almost |= (rlo + cold->bounded_tol[k][d] > real(0)) | (rhi + cold->bounded_tol[k][SCG_MAX_NX + d] > real(0));
                 }
             }
         }

@@ -36,6 +36,22 @@ SCG_DEV float  m_min(float a, float b)   { return fminf(a, b); }
 SCG_DEV double m_min(double a, double b) { return fmin(a, b); }
 SCG_DEV float  m_rint(float x)  { return rintf(x); }
 SCG_DEV double m_rint(double x) { return rint(x); }
+// sin/cos for |x| <= pi + small (the attitude angles after wrap_pi): quadrant reduction with a two-term
+// pi/2 and the cephes single-precision minimax polynomials on [-pi/4, pi/4] (about 1 ulp).  Compact:
+// no large-argument (Payne-Hanek) path, so the substep loop stays small in the instruction cache.
+SCG_DEV void sincos_pi(float x, float* s, float* c) {
+    const float k = rintf(x * 0.63661977236758134f);
+    const float r = fmaf(-k, -4.371139000186243e-08f, fmaf(-k, 1.5707963705062866f, x));
+    const float z = r * r;
+    const float sp = fmaf(r * z, fmaf(z, fmaf(z, -1.9515295891e-4f, 8.3321608736e-3f), -1.6666654611e-1f), r);
+    const float cp = fmaf(z * z, fmaf(z, fmaf(z, 2.443315711809948e-5f, -1.388731625493765e-3f), 4.166664568298827e-2f),
+                          fmaf(z, -0.5f, 1.0f));
+    const int q = static_cast<int>(k) & 3;
+    const float ss = (q & 1) ? cp : sp, cc = (q & 1) ? sp : cp;
+    *s = (q & 2) ? -ss : ss;
+    *c = ((q + 1) & 2) ? -cc : cc;
+}
+SCG_DEV void sincos_pi(double x, double* s, double* c) { sincos(x, s, c); }
 // np.clip(x, lo, hi) == minimum(maximum(x, lo), hi)
 template <typename real> SCG_DEV real m_clip(real x, real lo, real hi) { return m_min(m_max(x, lo), hi); }
 

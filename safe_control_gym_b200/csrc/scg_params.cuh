@@ -29,6 +29,7 @@ template <typename real> struct Hot {
     real J[3], J_inv[3];
     real pwm_scale, pwm_const, pwm_min, pwm_max, inv_pwm_scale;
     real inv_nkf;                   // 1 / (n_motor * KF)
+    real gravity_acc, cp_length, cp_pole_mass, cp_cart_mass;   // cart-pole (A13): effective (half) pole length, masses
     // action map
     int32_t normalized_action;
     real norm_act_scale, hover_thrust;
@@ -53,7 +54,7 @@ template <typename real> struct Hot {
     // feature switches (uniform branches)
     int32_t n_dist_obs, n_dist_act, n_dist_dyn, adversary_channel;
     int32_t n_gates, gate_geometry, dyn_uses_episode_inertia, dyn_applies_force, auto_reset;
-    int32_t reseed_on_reset, any_init_rand, any_inertia_rand, any_gate_rand;
+    int32_t reseed_on_reset, any_init_rand, any_inertia_rand, any_gate_rand;   // *_rand: bit 0 uniform, bit 1 normal draws needed
     real init_state[SCG_MAX_NX + 1];
     real inertia_nominal[4];
     uint32_t seed;

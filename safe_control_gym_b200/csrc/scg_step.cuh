@@ -20,9 +20,13 @@ template <int KIND, typename real> struct EnvRegs {
     Att2<real> a2;       // 2D
 };
 
-template <typename real> SCG_DEV void load_inertia(const Hot<real>& h, const real* __restrict__ inertia, int64_t n, int64_t i,
+template <int KIND, typename real> SCG_DEV void load_inertia(const Hot<real>& h, const real* __restrict__ inertia, int64_t n, int64_t i,
                                                    Inertia<real>& in) {
-    if (h.dyn_uses_episode_inertia && inertia) {   // extension (F9)
+    in.cp_l = h.cp_length; in.cp_mp = h.cp_pole_mass; in.cp_mc = h.cp_cart_mass;
+    if constexpr (KIND == SCG_CARTPOLE) {   // per-episode pole length / masses always reach the cart-pole ODE
+        if (inertia && h.any_inertia_rand) { in.cp_l = inertia[i]; in.cp_mp = inertia[n + i]; in.cp_mc = inertia[2 * n + i]; }
+    }
+    if (KIND != SCG_CARTPOLE && h.dyn_uses_episode_inertia && inertia) {   // extension (F9)
         const real m = inertia[i];
         in.inv_mass = real(1) / m;
         in.g_over_m = h.gravity_force * h.inv_mass;   // g * m_env / m_env == GRAVITY_ACC
@@ -63,6 +67,9 @@ SCG_DEV void make_state(const EnvRegs<KIND, real>& e, const real (&ang)[3], real
 #pragma unroll
         for (int d = 0; d < 4; ++d) st[d] = e.x[d];
         st[4] = e.a2.theta; st[5] = ang[1];
+    } else if constexpr (KIND == SCG_CARTPOLE) {
+#pragma unroll
+        for (int d = 0; d < 4; ++d) st[d] = e.x[d];
     } else {
         st[0] = e.x[0]; st[1] = e.x[1];
     }
@@ -144,10 +151,10 @@ SCG_DEV void reset_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, 
     }
     // inertial properties (quadrotor.py:447-467): value += distrib(...)
     if (b.inertia) {
-        real u[4], z[4];
-        if (h.any_inertia_rand && !inj.inertia) {
-            draw_uniforms<real, 4>(key, 0u, ep, STREAM_RESET_INERTIA, u);
-            draw_normals<real, 4>(key, 0u, ep, STREAM_RESET_INERTIA, z);
+        real u[4] = {real(0), real(0), real(0), real(0)}, z[4] = {real(0), real(0), real(0), real(0)};
+        if (!inj.inertia) {
+            if (h.any_inertia_rand & 1) draw_uniforms<real, 4>(key, 0u, ep, STREAM_RESET_INERTIA, u);
+            if (h.any_inertia_rand & 2) draw_normals<real, 4>(key, 0u, ep, STREAM_RESET_INERTIA, z);
         }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -157,7 +164,7 @@ SCG_DEV void reset_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, 
             b.inertia[int64_t(j) * n + i] = v;
         }
     }
-    load_inertia(h, b.inertia, n, i, e.in);
+    load_inertia<KIND, real>(h, b.inertia, n, i, e.in);
     // initial state (quadrotor.py:477-493), label order == state order
     real init[NX];
 #pragma unroll
@@ -167,8 +174,10 @@ SCG_DEV void reset_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, 
         for (int d = 0; d < NX; ++d) init[d] += inj.init[int64_t(d) * n + i];
     } else if (h.any_init_rand) {
         real u[NX], z[NX];
-        draw_uniforms<real, NX>(key, 0u, ep, STREAM_RESET_INIT, u);
-        draw_normals<real, NX>(key, 0u, ep, STREAM_RESET_INIT, z);
+#pragma unroll
+        for (int d = 0; d < NX; ++d) { u[d] = real(0); z[d] = real(0); }
+        if (h.any_init_rand & 1) draw_uniforms<real, NX>(key, 0u, ep, STREAM_RESET_INIT, u);
+        if (h.any_init_rand & 2) draw_normals<real, NX>(key, 0u, ep, STREAM_RESET_INIT, z);
 #pragma unroll
         for (int d = 0; d < NX; ++d) init[d] += rand_value(cold->init_rand[d], u[d], z[d]);
     }
@@ -183,6 +192,9 @@ SCG_DEV void reset_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, 
         for (int d = 0; d < 5; ++d) e.x[d] = init[d];
         e.x[5] = real(0);
         ang[1] = init[5];
+    } else if constexpr (KIND == SCG_CARTPOLE) {
+#pragma unroll
+        for (int d = 0; d < 4; ++d) e.x[d] = init[d];
     } else {
         // 1D labels are init_x / init_x_dot (quadrotor.py:208): they set the unobserved x axis;
         // z and z_dot always start at 0.
@@ -208,7 +220,8 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
 #pragma unroll
     for (int j = 0; j < NU; ++j) {
         const real c = m_clip(raw[j], h.act_low[j], h.act_high[j]);
-        pre[j] = h.normalized_action ? (real(1) + h.norm_act_scale * c) * h.hover_thrust : c;
+        if constexpr (KIND == SCG_CARTPOLE) pre[j] = h.normalized_action ? c * h.hover_thrust : c;   // force = action_scale * a
+        else pre[j] = h.normalized_action ? (real(1) + h.norm_act_scale * c) * h.hover_thrust : c;
         thr[j] = pre[j];
     }
     if (h.n_dist_act)
@@ -217,7 +230,8 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
 #pragma unroll
         for (int j = 0; j < NU; ++j) thr[j] += b.adv_action[i * NU + j];
     }
-    motors_from_thrust<KIND, real>(h, thr, mot);
+    if constexpr (KIND != SCG_CARTPOLE) motors_from_thrust<KIND, real>(h, thr, mot);
+    else { mot.T = mot.tx = mot.ty = mot.tz = real(0); mot.rpm[0] = mot.rpm[1] = mot.rpm[2] = mot.rpm[3] = real(0); }
     // ---- external force (extension, F5: the reference never integrates it in DYN)
     real fx = real(0), fy = real(0), fz = real(0);
     if (h.dyn_applies_force && (h.n_dist_dyn || h.adversary_channel == SCG_CH_DYNAMICS)) {
@@ -232,7 +246,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             for (int d = 0; d < NF; ++d) f[d] += b.adv_action[i * NF + d];
         }
         if constexpr (KIND == SCG_QUAD_1D) { fz = f[0]; }
-        else if constexpr (KIND == SCG_QUAD_2D) { fx = f[0]; fz = f[1]; }
+        else if constexpr (KIND == SCG_QUAD_2D || KIND == SCG_CARTPOLE) { fx = f[0]; fz = f[1]; }
         else { fx = f[0]; fy = f[1]; fz = f[2]; }
     }
     // ---- _advance_simulation: S explicit substeps (base_aviary.py:266-322, 522-576)
@@ -267,6 +281,12 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             e.x[4] = e.a2.theta;
         }
         e.flags = (e.flags & ~SCG_FLAG_FLIPPED) | (e.a2.flipped ? SCG_FLAG_FLIPPED : 0u);
+    } else if constexpr (KIND == SCG_CARTPOLE) {
+        // RK4 over the cart-pole ODE at the simulation rate; a dynamics-channel disturbance acts as an
+        // extra horizontal force on the cart when dyn_applies_force is on.
+        const real F = thr[0] + fx;
+        (void)fy; (void)fz; (void)Tm;
+        for (int s = 0; s < h.substeps; ++s) cartpole_rk4<real>(e.in, h.gravity_acc, e.x, F, dt);
     } else {
         const real az = Tm + (fz * e.in.inv_mass - e.in.g_over_m);
         for (int s = 0; s < h.substeps; ++s) { e.x[1] += dt * az; e.x[0] += dt * e.x[1]; }
@@ -428,7 +448,7 @@ k_env(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, 
         }
         return;
     } else {
-        load_inertia(h, b.inertia, n, ii, e.in);
+        load_inertia<KIND, real>(h, b.inertia, n, ii, e.in);
         derive_attitude<KIND, real, ATT>(e);
         real ep_ret = b.ep_return ? b.ep_return[ii] : real(0);
         int32_t ep_len = b.ep_length ? b.ep_length[ii] : 0;
@@ -471,6 +491,9 @@ k_env(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, 
                     } else if constexpr (KIND == SCG_QUAD_2D) {
                         rec[0] = e.x[0]; rec[1] = 0; rec[2] = e.x[2]; rec[3] = e.x[1]; rec[4] = 0; rec[5] = e.x[3];
                         rec[6] = 0; rec[7] = e.a2.theta; rec[8] = 0; rec[9] = 0; rec[10] = e.x[5]; rec[11] = 0;
+                    } else if constexpr (KIND == SCG_CARTPOLE) {
+                        rec[0] = e.x[0]; rec[1] = 0; rec[2] = 0; rec[3] = e.x[1]; rec[4] = 0; rec[5] = 0;
+                        rec[6] = 0; rec[7] = e.x[2]; rec[8] = 0; rec[9] = 0; rec[10] = e.x[3]; rec[11] = 0;
                     } else {
                         rec[0] = 0; rec[1] = 0; rec[2] = e.x[0]; rec[3] = 0; rec[4] = 0; rec[5] = e.x[1];
                         rec[6] = rec[7] = rec[8] = rec[9] = rec[10] = rec[11] = 0;

@@ -264,7 +264,9 @@ class BatchedQuadrotor(BatchedEnvBase):
         self._dyn_applies_force = bool(dyn_applies_force)
         self._gate_geometry = bool(gate_geometry)
         self._auto_reset = bool(auto_reset)
-        self._attitude = {"fast": L.ATT_FAST, "roundtrip": L.ATT_ROUNDTRIP}[attitude]
+        self._attitude = {"fast": L.ATT_FAST, "roundtrip": L.ATT_ROUNDTRIP, "fast_intrinsic": L.ATT_FAST_INTRINSIC}[attitude]
+        if self._attitude == L.ATT_FAST_INTRINSIC and dtype != torch.float32:
+            raise ValueError("attitude='fast_intrinsic' is an fp32-only mode")
         self._seed_offset = int(seed_offset)
         cfg = self._make_config(32 if dtype == torch.float32 else 64)
         rows = 0 if self.constraints is None else self.constraints.num_constraints

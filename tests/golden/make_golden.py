@@ -50,10 +50,13 @@ def scenarios():
     out["level0_dyn_s4"] = dict(cfg=level0(ctrl_freq=60, pyb_freq=240), actions=a)
     out["level0_dyn_s1"] = dict(cfg=level0(ctrl_freq=500, pyb_freq=500),
                                 actions=hover_actions(rng, 80, 4, lo=0.03, hi=0.145))
-    # 3: aggressive 3D attitude -- differential thrust drives pitch/roll through the asin
-    #    fold and the gimbal branch of getEulerFromQuaternion.
-    a = np.tile(np.array([0.14, 0.03, 0.03, 0.14]), (150, 1)) + rng.normal(0, 0.002, size=(150, 4))
-    a[60:] = np.array([0.05, 0.12, 0.06, 0.13])
+    # 3: 3D tumbling -- short differential-thrust pulses spin the body up to ~15 rad/s in pitch (plus
+    #    slower roll / yaw), then equal thrust: the attitude keeps running through the asin fold, the
+    #    +-pi wraps and the gimbal band of getEulerFromQuaternion for 2.5 s.
+    a = np.tile(np.array([0.085, 0.085, 0.085, 0.085]), (150, 1)) + rng.normal(0, 0.0005, size=(150, 4))
+    a[0:6] = np.array([0.12, 0.05, 0.05, 0.12])     # pitch torque
+    a[6:9] = np.array([0.11, 0.11, 0.06, 0.06])     # roll torque
+    a[9:14] = np.array([0.13, 0.04, 0.13, 0.04])    # yaw torque
     out["quad3d_tumble"] = dict(cfg=dict(physics="dyn", quad_type=3, ctrl_freq=60, pyb_freq=240, seed=7,
                                          episode_len_sec=5, cost="rl_reward", task="stabilization",
                                          task_info=dict(stabilization_goal=[0, 0, 1], stabilization_goal_tolerance=0.05),

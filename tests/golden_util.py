@@ -58,3 +58,85 @@ def replay_oracle(g):
         if done:
             do_reset()
     return ev, env
+
+
+# ----------------------------------------------------------------------------------------
+# Replay through the CUDA path (C ABI via the BatchedQuadrotor facade) with injected draws.
+class DrawCursor:
+    def __init__(self, draws):
+        self.draws, self.pos = draws, 0
+
+    def take(self):
+        v = self.draws[self.pos]
+        self.pos += 1
+        return np.asarray(v, dtype=np.float64).reshape(-1)
+
+
+def _needs_draw(d):
+    from safe_control_gym_b200 import _lib as L
+    return d.kind in (L.DIST_UNIFORM, L.DIST_WHITE, L.DIST_PERIODIC)
+
+
+def _inject_channel(env, mode, cur, n):
+    """Consume this call's draws of one channel (in list order) and hand them to the kernel."""
+    if mode not in env.disturbances:
+        return
+    for k, d in enumerate(env.disturbances[mode].disturbances):
+        if _needs_draw(d):
+            v = cur.take()
+            if mode == "dynamics" and not env._dyn_applies_force:
+                continue   # consumed by the reference, never reaches the DYN integrator (F5)
+            env.set_injection(mode, k, np.repeat(v[:, None], n, axis=1))
+
+
+def cuda_reset(env, cur):
+    """Quadrotor.reset() draw order: disturbance offsets -> (gates/obstacles) -> inertia -> init
+    -> observation noise of the first _get_observation."""
+    from safe_control_gym_b200 import _lib as L
+    n = env.num_envs
+    slots = max(sum(len(v.disturbances) for v in env.disturbances.values()), 1)
+    offsets = np.zeros((slots, n), dtype=np.int32)
+    for mode in env.disturbances:
+        for d in env.disturbances[mode].disturbances:
+            if d.kind in (L.DIST_IMPULSE, L.DIST_STEP) and d.step_offset is None:
+                offsets[d.slot, :] = int(cur.take()[0])
+    inertia = np.zeros((4, n))
+    if env.RANDOMIZED_INERTIAL_PROP:
+        for j, key in enumerate(["M", "Ixx", "Iyy", "Izz"]):
+            if key in env.INERTIAL_PROP_RAND_INFO:
+                inertia[j, :] = cur.take()[0]
+    labels = env.INIT_STATE_LABELS[env.QUAD_TYPE]
+    init = np.zeros((len(labels), n))
+    if env.RANDOMIZED_INIT:
+        for j, name in enumerate(labels):
+            if name in env.INIT_STATE_RAND_INFO:
+                init[j, :] = cur.take()[0]
+    _inject_channel(env, "observation", cur, n)
+    return env.reset(inject_init=init, inject_inertia=inertia, inject_offsets=offsets)
+
+
+def cuda_step(env, cur, action, adv=None):
+    n = env.num_envs
+    _inject_channel(env, "action", cur, n)
+    _inject_channel(env, "dynamics", cur, n)
+    _inject_channel(env, "observation", cur, n)
+    if adv is not None:
+        env.set_adversary_control(np.repeat(np.asarray(adv)[None, :], n, axis=0))
+    return env.step(np.repeat(np.asarray(action, dtype=np.float64)[None, :], n, axis=0))
+
+
+def force_state(env, kin, ctrl_step, prev_violation, n_resets):
+    """Teacher forcing: overwrite the kernel's internal state with the golden kinematics
+    (pos3, vel3, rpy3, rpy_rates3) of the previous event."""
+    import torch
+    pos, vel, rpy, rates = kin[0:3], kin[3:6], kin[6:9], kin[9:12]
+    if env.QUAD_TYPE == 3:
+        x = [pos[0], vel[0], pos[1], vel[1], pos[2], vel[2], rpy[0], rpy[1], rpy[2], rates[0], rates[1], rates[2]]
+    elif env.QUAD_TYPE == 2:
+        x = [pos[0], vel[0], pos[2], vel[2], rpy[1], rates[1]]
+    else:
+        x = [pos[2], vel[2]]
+    env.buf_state.copy_(torch.tensor(x, dtype=env.dtype, device=env.device)[:, None].expand(-1, env.num_envs))
+    env.buf_ctrl_step.fill_(int(ctrl_step))
+    env.buf_flags.fill_(1 if prev_violation else 0)
+    env.buf_episode.fill_(int(n_resets))

@@ -1,0 +1,128 @@
+"""CUDA path (through the C ABI) against the golden vectors recorded from the reference's own
+code.  fp64 build: free-running, <= 1e-12 relative (unit floor) on every float of every event,
+flags bit-exact.  fp32 build: per-step (teacher-forced from the golden state) <= 1e-5 relative
+(unit floor), flags bit-exact, plus free-running trajectory agreement over the first 100 steps
+of the level0 scenarios."""
+import numpy as np
+import pytest
+import torch
+
+from golden_util import SCENARIOS, DrawCursor, cuda_reset, cuda_step, force_state, load
+
+pytestmark = pytest.mark.gpu
+N_ENVS = 37   # replicas of the same env: exercises partial warps and the SoA indexing
+
+
+def _make(g, dtype, attitude):
+    from safe_control_gym_b200.envs.quadrotor import BatchedQuadrotor
+    cfg = dict(g["cfg"])
+    cfg["info_in_reset"] = True
+    return BatchedQuadrotor(num_envs=N_ENVS, dtype=dtype, attitude=attitude, auto_reset=False, **cfg)
+
+
+def _cmp(name, got, want, tol, what):
+    got = np.asarray(got, dtype=np.float64)
+    want = np.asarray(want, dtype=np.float64)
+    m = np.isfinite(want)
+    err = np.abs(got[..., m] - want[m]) / np.maximum(1.0, np.abs(want[m]))
+    assert err.size == 0 or err.max() <= tol, f"{name} {what}: rel err {err.max():.3e} > {tol}"
+    return 0.0 if err.size == 0 else float(err.max())
+
+
+def _check_event(name, e, g, env, out, tol, is_reset):
+    worst = 0.0
+    if is_reset:
+        obs, info = out
+    else:
+        obs, rew, done, info = out
+        worst = max(worst, _cmp(name, rew.cpu().numpy(), np.full(N_ENVS, g["ev_rew"][e]), tol, f"ev{e} rew"))
+        assert (done.cpu().numpy().astype(int) == g["ev_done"][e]).all(), f"{name} ev{e} done"
+        if g["ev_viol"][e] >= 0:
+            assert (info["constraint_violation"].cpu().numpy() == g["ev_viol"][e]).all(), f"{name} ev{e} violation"
+        if g["ev_trunc"][e] >= 0:
+            assert (info["TimeLimit.truncated"].cpu().numpy().astype(int) == g["ev_trunc"][e]).all(), f"{name} ev{e} trunc"
+        worst = max(worst, _cmp(name, info["mse"].cpu().numpy(), np.full(N_ENVS, g["ev_mse"][e]), tol, f"ev{e} mse"))
+    worst = max(worst, _cmp(name, obs.cpu().numpy(), g["ev_obs"][e], tol, f"ev{e} obs"))
+    worst = max(worst, _cmp(name, env.buf_env_state.t().cpu().numpy(), g["ev_state"][e], tol, f"ev{e} state"))
+    want_c = g["ev_cvals"][e]
+    k = int(np.isfinite(want_c).sum())
+    if k:
+        c = info["constraint_values"].cpu().numpy()[:, :k]
+        big = np.abs(want_c[:k]) > 1e30   # +-float32.max bounds: compare loosely
+        worst = max(worst, _cmp(name, c[:, ~big], want_c[:k][~big], tol, f"ev{e} constraint_values"))
+    return worst
+
+
+@pytest.mark.parametrize("attitude", ["roundtrip", "fast"])
+@pytest.mark.parametrize("name", SCENARIOS)
+def test_fp64_free_running(name, attitude):
+    g = load(name)
+    env = _make(g, torch.float64, attitude)
+    cur = DrawCursor(g["draws"])
+    worst, t = 0.0, 0
+    for e, kind in enumerate(g["ev_type"]):
+        if kind == 0:
+            out = cuda_reset(env, cur)
+        else:
+            out = cuda_step(env, cur, g["actions"][t], g["adv"][t] if "adv" in g else None)
+            t += 1
+        # the tumble scenario spins at > 300 rad/s: rounding differences grow chaotically in a
+        # free run, so its bar here is looser; its per-step 1e-12 bar is test_fp64_per_step.
+        worst = max(worst, _check_event(name, e, g, env, out, 1e-8 if name == "quad3d_tumble" else 1e-12, kind == 0))
+    assert cur.pos == len(g["draws"])
+    print(f"{name}[{attitude}] fp64 worst rel err {worst:.2e} over {len(g['ev_type'])} events")
+
+
+def _per_step(name, attitude, dtype, tol):
+    g = load(name)
+    env = _make(g, dtype, attitude)
+    cur = DrawCursor(g["draws"])
+    worst, t, resets, steps_in_ep = 0.0, 0, 0, 0
+    for e, kind in enumerate(g["ev_type"]):
+        if kind == 0:
+            out = cuda_reset(env, cur)
+            resets += 1
+            steps_in_ep = 0
+        else:
+            prev_viol = g["ev_viol"][e - 1] == 1 if g["ev_type"][e - 1] == 1 else bool(env.buf_flags[0].item() & 1)
+            if g["ev_type"][e - 1] == 1:   # the reset event leaves INIT_ANG_VEL only in the obs: keep the kernel's own state there
+                force_state(env, g["ev_kin"][e - 1], steps_in_ep, prev_viol, resets)
+            out = cuda_step(env, cur, g["actions"][t], g["adv"][t] if "adv" in g else None)
+            t += 1
+            steps_in_ep += 1
+        worst = max(worst, _check_event(name, e, g, env, out, tol, kind == 0))
+    print(f"{name}[{attitude}] {dtype} per-step worst rel err {worst:.2e}")
+
+
+@pytest.mark.parametrize("attitude", ["roundtrip", "fast", "fast_intrinsic"])
+@pytest.mark.parametrize("name", SCENARIOS)
+def test_fp32_per_step(name, attitude):
+    _per_step(name, attitude, torch.float32, 1e-5)
+
+
+@pytest.mark.parametrize("attitude", ["roundtrip", "fast"])
+@pytest.mark.parametrize("name", SCENARIOS)
+def test_fp64_per_step(name, attitude):
+    _per_step(name, attitude, torch.float64, 1e-12)
+
+
+@pytest.mark.parametrize("attitude", ["fast", "fast_intrinsic"])
+@pytest.mark.parametrize("name", ["level0_dyn_s4", "level0_dyn_s1"])
+def test_fp32_trajectory_100_steps(name, attitude):
+    """Free-running fp32 vs the fp64 reference over 100 control steps (reported, loose bound)."""
+    g = load(name)
+    env = _make(g, torch.float32, attitude)
+    cur = DrawCursor(g["draws"])
+    t, worst = 0, 0.0
+    for e, kind in enumerate(g["ev_type"]):
+        if t >= 100 or (kind == 0 and e > 0):
+            break
+        if kind == 0:
+            cuda_reset(env, cur)
+            continue
+        cuda_step(env, cur, g["actions"][t])
+        t += 1
+        got = env.buf_env_state.t().cpu().numpy()[0].astype(np.float64)
+        worst = max(worst, float(np.max(np.abs(got - g["ev_state"][e]) / np.maximum(1.0, np.abs(g["ev_state"][e])))))
+    print(f"{name}[{attitude}]: fp32 free-running drift after {t} steps: {worst:.2e}")
+    assert worst < 1e-3
