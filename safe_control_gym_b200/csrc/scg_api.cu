@@ -8,36 +8,20 @@
 #include <new>
 #include <string>
 
-#include "scg_step.cuh"
+#include "scg_host.cuh"
 #include "scg_symbolic.cuh"
 
 using namespace scg;
 
 static thread_local std::string g_err;
-static int fail(int code, const std::string& msg) { g_err = msg; return code; }
-static int cuda_fail(cudaError_t e, const char* what) {
+int scg_fail(int code, const std::string& msg) { g_err = msg; return code; }
+int scg_cuda_fail(cudaError_t e, const char* what) {
     g_err = std::string(what) + ": " + cudaGetErrorString(e);
     return SCG_ERR_CUDA - int(e);
 }
-#define CU(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return cuda_fail(_e, #x); } while (0)
-
-struct scg_env {
-    scg_config cfg;
-    int nx, nu, obs_dim, n_rows, n_slots;
-    Hot<float> hf;
-    Hot<double> hd;
-    void* cold_dev = nullptr;      // Cold<float> or Cold<double>
-    void* cold_host = nullptr;     // host mirror (for injection pointer updates)
-    void* x_goal_dev = nullptr;
-    scg_buffers buf;
-    bool bound = false, did_reset = false;
-    int64_t launches = 0;
-    // scg_rollout_host staging
-    cudaStream_t copy_stream = nullptr;
-    cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};
-    void* stage[2] = {nullptr, nullptr};
-    size_t stage_bytes = 0;
-};
+static int fail(int code, const std::string& msg) { return scg_fail(code, msg); }
+static int cuda_fail(cudaError_t e, const char* what) { return scg_cuda_fail(e, what); }
+#define CU(x) SCG_CU(x)
 
 static int kind_dims(int kind, int* nx, int* nu) {
     switch (kind) {
@@ -50,7 +34,7 @@ static int kind_dims(int kind, int* nx, int* nu) {
 }
 
 template <typename real>
-static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<real>& k, int* n_rows_out, int* n_slots_out) {
+static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<real>& k, int* n_rows_out, int* n_slots_out, bool* lean_out) {
     std::memset(&h, 0, sizeof(h));
     std::memset(&k, 0, sizeof(k));
     const real INF = std::numeric_limits<real>::infinity();
@@ -68,6 +52,7 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
     for (int d = 0; d < nx; ++d) {
         h.state_low[d] = real(c.state_low[d]); h.state_high[d] = real(c.state_high[d]);
         h.rew_state_weight[d] = real(c.rew_state_weight[d]); h.mse_weight[d] = real(c.mse_weight[d]);
+        if (c.mse_weight[d] != 0.0) h.mse_mask |= 1u << d;
         h.x_goal0[d] = c.x_goal ? real(c.x_goal[d]) : real(0);
         h.init_state[d] = real(c.init_state[d]);
     }
@@ -107,12 +92,14 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
             for (int d = 0; d < 2 * SCG_MAX_NX; ++d) k.bounded_tol[nb][d] = -INF;
             bc.var = int8_t(s.var); bc.strict = int8_t(s.strict); bc.has_tol = int8_t(s.has_tolerance);
             bc.symmetric = s.form == SCG_CON_SYMMETRIC;
+            bc.mask = 0u;
             const int nrows = bc.symmetric ? s.n_active : 2 * s.n_active;
             if (s.n_rows != nrows) return fail(SCG_ERR_BAD_CONFIG, "bounded constraint n_rows mismatch");
             for (int j = 0; j < s.n_active; ++j) {
                 const int d = s.active_dims[j];
                 if (bc.row_lo[d] >= 0) return fail(SCG_ERR_BAD_CONFIG, "duplicates in active_dims");
                 bc.lo[d] = real(s.lower[j]); bc.hi[d] = real(s.upper[j]);
+                bc.mask |= 1u << d;
                 bc.row_lo[d] = int8_t(row + j);
                 if (!bc.symmetric) bc.row_hi[d] = int8_t(row + s.n_active + j);
                 if (s.has_tolerance) {
@@ -176,13 +163,15 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
     h.dyn_uses_episode_inertia = c.dyn_uses_episode_inertia; h.dyn_applies_force = c.dyn_applies_force;
     h.auto_reset = c.auto_reset; h.reseed_on_reset = c.reseed_on_reset;
     for (int d = 0; d < nx; ++d) {
-        k.init_rand[d].distrib = c.init_rand[d].distrib; k.init_rand[d].a = real(c.init_rand[d].a); k.init_rand[d].b = real(c.init_rand[d].b);
+        h.init_rand[d].distrib = c.init_rand[d].distrib; h.init_rand[d].a = real(c.init_rand[d].a); h.init_rand[d].b = real(c.init_rand[d].b);
+        if (c.init_rand[d].distrib == SCG_RAND_NONE) h.init_rand[d].a = h.init_rand[d].b = real(0);
+        else h.init_block_mask |= 1u << (d / 4);
         if (c.init_rand[d].distrib == SCG_RAND_UNIFORM) h.any_init_rand |= 1;
         if (c.init_rand[d].distrib == SCG_RAND_NORMAL) h.any_init_rand |= 2;
     }
     for (int j = 0; j < 4; ++j) {
         h.inertia_nominal[j] = real(c.inertia_nominal[j]);
-        k.inertia_rand[j].distrib = c.inertia_rand[j].distrib; k.inertia_rand[j].a = real(c.inertia_rand[j].a); k.inertia_rand[j].b = real(c.inertia_rand[j].b);
+        h.inertia_rand[j].distrib = c.inertia_rand[j].distrib; h.inertia_rand[j].a = real(c.inertia_rand[j].a); h.inertia_rand[j].b = real(c.inertia_rand[j].b);
         if (c.inertia_rand[j].distrib == SCG_RAND_UNIFORM) h.any_inertia_rand |= 1;
         if (c.inertia_rand[j].distrib == SCG_RAND_NORMAL) h.any_inertia_rand |= 2;
     }
@@ -196,6 +185,26 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
     k.n_obstacles = c.n_obstacles;
     h.seed = c.seed; h.env_id_base_lo = uint32_t(c.env_id_base & 0xFFFFFFFFll);
     h.viol_thr = real(5e-9);
+    // ---- which per-step consumers read the 3D body rates p, q, r (they need the whole rotation matrix)
+    bool rates = c.env_kind != SCG_QUAD_3D;
+    if (c.env_kind == SCG_QUAD_3D) {
+        constexpr uint32_t RATE_BITS = 0xE00u;
+        if (h.mse_mask & RATE_BITS) rates = true;
+        for (int q = 0; q < nb; ++q) if (h.bounded[q].var == SCG_VAR_STATE && (h.bounded[q].mask & RATE_BITS)) rates = true;
+        for (int q = 0; q < nd; ++q) if (k.dense[q].var == SCG_VAR_STATE) rates = true;
+        if (c.cost == SCG_COST_RL_REWARD) for (int d = 9; d < 12; ++d) if (c.rew_state_weight[d] != 0.0) rates = true;
+        if (c.cost == SCG_COST_QUADRATIC) rates = true;   // Q weighs the rates (identity by default); goal_reached norms the full state
+    }
+    h.need_full_state = rates ? 1 : 0;
+    // ---- LEAN kernel specialisation (scg_step.cuh): none of the rare features is configured
+    bool symmetric = false;
+    for (int q = 0; q < nb; ++q) symmetric |= h.bounded[q].symmetric != 0;
+    h.need_cold_constraints = (nd > 0 || h.any_tolerance || symmetric) ? 1 : 0;
+    // (the extended observation lives in write_obs, outside the loop)
+    *lean_out = c.n_dist[0] == 0 && c.n_dist[1] == 0 && c.n_dist[2] == 0 && c.adversary_channel < 0 && !c.dyn_applies_force &&
+                !(h.any_init_rand & 2) && !h.any_inertia_rand &&
+                !c.dyn_uses_episode_inertia && nd == 0 && !h.any_tolerance && !symmetric && h.quadratic_diag && !c.gate_geometry &&
+                !(c.env_kind == SCG_CARTPOLE && (h.any_inertia_rand != 0));
     return SCG_OK;
 }
 
@@ -207,7 +216,7 @@ template <typename real> static int upload_params(scg_env* e) {
     Cold<real>* k = new (std::nothrow) Cold<real>;
     if (!k) return fail(SCG_ERR_BAD_CONFIG, "out of host memory");
     Hot<real>& h = *reinterpret_cast<Hot<real>*>(sizeof(real) == 4 ? (void*)&e->hf : (void*)&e->hd);
-    int rc = build_params<real>(e->cfg, e->nx, e->nu, h, *k, &e->n_rows, &e->n_slots);
+    int rc = build_params<real>(e->cfg, e->nx, e->nu, h, *k, &e->n_rows, &e->n_slots, &e->lean);
     if (rc != SCG_OK) { delete k; return rc; }
     const int rows = e->cfg.n_goal_rows > 0 ? e->cfg.n_goal_rows : 1;
     real* goal_host = new real[size_t(rows) * e->nx];
@@ -300,45 +309,24 @@ extern "C" int scg_set_injection(scg_env* e, int channel, int k, const void* dev
     return SCG_OK;
 }
 
-template <typename real> static Buf<real> typed_buf(const scg_buffers& b) {
-    Buf<real> t;
-    t.n = b.n; t.state = (real*)b.state; t.ctrl_step = b.ctrl_step; t.episode = b.episode; t.flags = b.flags;
-    t.dist_offset = b.dist_offset; t.inertia = (real*)b.inertia; t.obs = (real*)b.obs; t.env_state = (real*)b.env_state;
-    t.reward = (real*)b.reward; t.done = b.done; t.info = b.info; t.mse = (real*)b.mse; t.c_values = (real*)b.c_values;
-    t.terminal_obs = (real*)b.terminal_obs; t.ep_return = (real*)b.ep_return; t.ep_length = b.ep_length;
-    t.ep_violations = b.ep_violations; t.stats = b.stats; t.adv_action = (const real*)b.adv_action;
-    return t;
-}
-
-template <int KIND, typename real, int MODE>
-static int launch_att(scg_env* e, const Hot<real>& h, const Roll<real>& ro, const ResetInject<real>& inj,
-                      const uint8_t* mask, cudaStream_t st) {
-    const Buf<real> b = typed_buf<real>(e->buf);
-    const int threads = 128;
-    const unsigned blocks = unsigned((b.n + threads - 1) / threads);
-    const Cold<real>* cold = static_cast<const Cold<real>*>(e->cold_dev);
-    if constexpr (KIND == SCG_CARTPOLE) {
-        k_env<KIND, real, SCG_ATT_FAST, MODE><<<blocks, threads, 0, st>>>(h, cold, b, ro, inj, mask);
-    } else {
-        if (e->cfg.attitude_mode == SCG_ATT_FAST) k_env<KIND, real, SCG_ATT_FAST, MODE><<<blocks, threads, 0, st>>>(h, cold, b, ro, inj, mask);
-        else if (e->cfg.attitude_mode == SCG_ATT_FAST_INTRINSIC) {
-            if constexpr (sizeof(real) == 4 && KIND == SCG_QUAD_3D) k_env<KIND, real, SCG_ATT_FAST_INTRINSIC, MODE><<<blocks, threads, 0, st>>>(h, cold, b, ro, inj, mask);
-            else k_env<KIND, real, SCG_ATT_FAST, MODE><<<blocks, threads, 0, st>>>(h, cold, b, ro, inj, mask);
-        } else k_env<KIND, real, SCG_ATT_ROUNDTRIP, MODE><<<blocks, threads, 0, st>>>(h, cold, b, ro, inj, mask);
-    }
-    e->launches += 1;
-    CU(cudaGetLastError());
-    return SCG_OK;
-}
-
-template <typename real, int MODE>
-static int launch_kind(scg_env* e, const Roll<real>& ro, const ResetInject<real>& inj, const uint8_t* mask, cudaStream_t st) {
-    const Hot<real>& h = *reinterpret_cast<const Hot<real>*>(sizeof(real) == 4 ? (const void*)&e->hf : (const void*)&e->hd);
+template <typename real>
+static int dispatch_reset(scg_env* e, const ResetInject<real>& inj, const uint8_t* mask, cudaStream_t st) {
     switch (e->cfg.env_kind) {
-        case SCG_QUAD_1D: return launch_att<SCG_QUAD_1D, real, MODE>(e, h, ro, inj, mask, st);
-        case SCG_QUAD_2D: return launch_att<SCG_QUAD_2D, real, MODE>(e, h, ro, inj, mask, st);
-        case SCG_QUAD_3D: return launch_att<SCG_QUAD_3D, real, MODE>(e, h, ro, inj, mask, st);
-        case SCG_CARTPOLE: return launch_att<SCG_CARTPOLE, real, MODE>(e, h, ro, inj, mask, st);
+        case SCG_QUAD_1D: return launch_reset<SCG_QUAD_1D, real>(e, inj, mask, st);
+        case SCG_QUAD_2D: return launch_reset<SCG_QUAD_2D, real>(e, inj, mask, st);
+        case SCG_QUAD_3D: return launch_reset<SCG_QUAD_3D, real>(e, inj, mask, st);
+        case SCG_CARTPOLE: return launch_reset<SCG_CARTPOLE, real>(e, inj, mask, st);
+    }
+    return fail(SCG_ERR_BAD_CONFIG, "unknown env_kind");
+}
+
+template <typename real>
+static int dispatch_rollout(scg_env* e, const Roll<real>& ro, cudaStream_t st) {
+    switch (e->cfg.env_kind) {
+        case SCG_QUAD_1D: return launch_rollout<SCG_QUAD_1D, real>(e, ro, st);
+        case SCG_QUAD_2D: return launch_rollout<SCG_QUAD_2D, real>(e, ro, st);
+        case SCG_QUAD_3D: return launch_rollout<SCG_QUAD_3D, real>(e, ro, st);
+        case SCG_CARTPOLE: return launch_rollout<SCG_CARTPOLE, real>(e, ro, st);
     }
     return fail(SCG_ERR_BAD_CONFIG, "unknown env_kind");
 }
@@ -350,11 +338,11 @@ extern "C" int scg_reset(scg_env* e, const uint8_t* mask, const void* inject_ini
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     int rc;
     if (e->cfg.precision == 32) {
-        Roll<float> ro{}; ResetInject<float> inj{(const float*)inject_init, (const float*)inject_inertia, inject_offsets};
-        rc = launch_kind<float, 0>(e, ro, inj, mask, st);
+        ResetInject<float> inj{(const float*)inject_init, (const float*)inject_inertia, inject_offsets};
+        rc = dispatch_reset<float>(e, inj, mask, st);
     } else {
-        Roll<double> ro{}; ResetInject<double> inj{(const double*)inject_init, (const double*)inject_inertia, inject_offsets};
-        rc = launch_kind<double, 0>(e, ro, inj, mask, st);
+        ResetInject<double> inj{(const double*)inject_init, (const double*)inject_inertia, inject_offsets};
+        rc = dispatch_reset<double>(e, inj, mask, st);
     }
     if (rc == SCG_OK) e->did_reset = true;
     return rc;
@@ -364,12 +352,10 @@ static int run_steps(scg_env* e, const void* actions, int k_steps, void* reward_
                      int log_stride, int step_outputs, cudaStream_t st) {
     if (e->cfg.precision == 32) {
         Roll<float> ro{(const float*)actions, k_steps, (float*)reward_out, done_out, (float*)log_out, log_stride, step_outputs};
-        ResetInject<float> inj{nullptr, nullptr, nullptr};
-        return launch_kind<float, 1>(e, ro, inj, nullptr, st);
+        return dispatch_rollout<float>(e, ro, st);
     }
     Roll<double> ro{(const double*)actions, k_steps, (double*)reward_out, done_out, (double*)log_out, log_stride, step_outputs};
-    ResetInject<double> inj{nullptr, nullptr, nullptr};
-    return launch_kind<double, 1>(e, ro, inj, nullptr, st);
+    return dispatch_rollout<double>(e, ro, st);
 }
 
 extern "C" int scg_step(scg_env* e, const void* action, void* stream) {
@@ -440,37 +426,16 @@ extern "C" int scg_stats_read(scg_env* e, double* host_out, void* stream) {
     return SCG_OK;
 }
 
-template <int KIND, typename real>
-__global__ void __launch_bounds__(128)
-k_constraints(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, const real* __restrict__ state,
-              const real* __restrict__ action, int64_t n, real* __restrict__ out_values, uint8_t* __restrict__ out_flags) {
-    constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
-    const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    real st[NX], raw[NU];
-#pragma unroll
-    for (int d = 0; d < NX; ++d) st[d] = state[int64_t(d) * n + i];
-#pragma unroll
-    for (int j = 0; j < NU; ++j) raw[j] = action ? action[i * NU + j] : real(0);
-    bool violated, almost;
-    eval_constraints<KIND, real>(h, cold, st, raw, action == nullptr, out_values, n, i, violated, almost);
-    if (out_flags) out_flags[i] = (violated ? 1 : 0) | (almost ? 2 : 0);
-}
-
 template <typename real> static int constraints_eval_t(scg_env* e, const void* state, const void* action, int64_t n,
                                                        void* out_values, uint8_t* out_flags, cudaStream_t st) {
-    const Hot<real>& h = *reinterpret_cast<const Hot<real>*>(sizeof(real) == 4 ? (const void*)&e->hf : (const void*)&e->hd);
-    const Cold<real>* cold = static_cast<const Cold<real>*>(e->cold_dev);
-    const unsigned blocks = unsigned((n + 127) / 128);
+    const real* s_ = (const real*)state; const real* a_ = (const real*)action; real* o_ = (real*)out_values;
     switch (e->cfg.env_kind) {
-        case SCG_QUAD_1D: k_constraints<SCG_QUAD_1D, real><<<blocks, 128, 0, st>>>(h, cold, (const real*)state, (const real*)action, n, (real*)out_values, out_flags); break;
-        case SCG_QUAD_2D: k_constraints<SCG_QUAD_2D, real><<<blocks, 128, 0, st>>>(h, cold, (const real*)state, (const real*)action, n, (real*)out_values, out_flags); break;
-        case SCG_QUAD_3D: k_constraints<SCG_QUAD_3D, real><<<blocks, 128, 0, st>>>(h, cold, (const real*)state, (const real*)action, n, (real*)out_values, out_flags); break;
-        case SCG_CARTPOLE: k_constraints<SCG_CARTPOLE, real><<<blocks, 128, 0, st>>>(h, cold, (const real*)state, (const real*)action, n, (real*)out_values, out_flags); break;
+        case SCG_QUAD_1D: return launch_constraints<SCG_QUAD_1D, real>(e, s_, a_, n, o_, out_flags, st);
+        case SCG_QUAD_2D: return launch_constraints<SCG_QUAD_2D, real>(e, s_, a_, n, o_, out_flags, st);
+        case SCG_QUAD_3D: return launch_constraints<SCG_QUAD_3D, real>(e, s_, a_, n, o_, out_flags, st);
+        case SCG_CARTPOLE: return launch_constraints<SCG_CARTPOLE, real>(e, s_, a_, n, o_, out_flags, st);
     }
-    e->launches += 1;
-    CU(cudaGetLastError());
-    return SCG_OK;
+    return fail(SCG_ERR_BAD_CONFIG, "unknown env_kind");
 }
 
 extern "C" int scg_constraints_eval(scg_env* e, const void* state, const void* action, int64_t n, void* out_values,

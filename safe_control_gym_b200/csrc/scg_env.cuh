@@ -16,7 +16,9 @@ namespace scg {
 // only) additionally evaluates sin/cos on the SFU (MUFU.SIN / MUFU.COS).
 template <typename real> struct Att3 {
     real rpy[3];   // wrapped angles == self.rpy after _update_and_store_kinematic_information
-    real R[9];     // getMatrixFromQuaternion(self.quat), row-major
+    real R[9];     // getMatrixFromQuaternion(self.quat), row-major; the substep loop keeps only column 2 current
+    real sc[6];    // sin/cos of roll, pitch, yaw that column 2 was built from (fast path)
+    int form;      // 0: all of R is current; 1: columns 0 and 1 still to be built from sc (attitude3_complete)
 };
 
 // x - 2 pi * rint(x / 2 pi): the identity (bit-exact) for x already in [-pi, pi]
@@ -25,50 +27,23 @@ SCG_DEV double wrap_pi(double x) {
     return fma(-k, 2.4492935982947064e-16, fma(-k, 6.283185307179586, x));
 }
 SCG_DEV float wrap_pi(float x) {
-    const float k = rintf(x * 0.15915494309189535f);
+    const float k = fast_rint(x * 0.15915494309189535f);
     return fmaf(-k, -1.7484555e-07f, fmaf(-k, 6.2831855f, x));   // 2 pi = 6.2831855f - 1.7484555e-07f
 }
 template <int ATT> SCG_DEV void att_sincos(float x, float* s, float* c) {
     if (ATT == SCG_ATT_FAST_INTRINSIC) __sincosf(x, s, c);   // MUFU.SIN/COS, |err| <= 2^-21.4 on [-pi, pi]
-    else sincosf(x, s, c);
+    else sincos_pi(x, s, c);                                  // |x| <= pi after wrap_pi
 }
 template <int ATT> SCG_DEV void att_sincos(double x, double* s, double* c) { sincos(x, s, c); }
 
-template <typename real, int ATT, bool FULL>
-SCG_DEV void attitude3(const real (&pre)[3], Att3<real>& a) {
-    if (ATT != SCG_ATT_ROUNDTRIP) {
-        // Canonical Euler angles of the same rotation by arithmetic only: wrap into [-pi, pi], fold a
-        // pitch beyond +-pi/2 (Rz(psi+pi) Ry(pi-theta) Rx(phi+pi) == Rz(psi) Ry(theta) Rx(phi)), which is
-        // what eulerFromQuat(quatFromEuler(.)) returns outside its gimbal band |sin(pitch)| >= 0.99999.
-        real th = wrap_pi(pre[1]), ph = pre[0], ps = pre[2];
-        if (m_abs(th) > Consts<real>::half_pi) {
-            th = (th > real(0) ? Consts<real>::pi : -Consts<real>::pi) - th;
-            ph += Consts<real>::pi; ps += Consts<real>::pi;
-        }
-        ph = wrap_pi(ph); ps = wrap_pi(ps);
-        real sth, cth;
-        att_sincos<ATT>(th, &sth, &cth);
-        if (m_abs(sth) < real(0.99998)) {
-            real sph, cph, sps, cps;
-            att_sincos<ATT>(ph, &sph, &cph);
-            att_sincos<ATT>(ps, &sps, &cps);
-            a.rpy[0] = ph; a.rpy[1] = th; a.rpy[2] = ps;
-            a.R[2] = cps * sth * cph + sps * sph;
-            a.R[5] = sps * sth * cph - cps * sph;
-            a.R[8] = cth * cph;
-            if (FULL) {
-                a.R[0] = cps * cth; a.R[1] = cps * sth * sph - sps * cph;
-                a.R[3] = sps * cth; a.R[4] = sps * sth * sph + cps * cph;
-                a.R[6] = -sth;      a.R[7] = cth * sph;
-            }
-            return;
-        }
-    }
-    // pybullet getQuaternionFromEuler
+// The literal bullet3 sequence: getQuaternionFromEuler -> getEulerFromQuaternion / getMatrixFromQuaternion.
+// Out of line: SCG_ATT_FAST reaches it only inside the gimbal band, and the hot loop must stay small.
+template <typename real>
+__device__ __noinline__ void attitude3_roundtrip(real p0, real p1, real p2, Att3<real>& a) {
     real sph, cph, sth, cth, sps, cps;
-    m_sincos(pre[0] * real(0.5), &sph, &cph);
-    m_sincos(pre[1] * real(0.5), &sth, &cth);
-    m_sincos(pre[2] * real(0.5), &sps, &cps);
+    m_sincos(p0 * real(0.5), &sph, &cph);
+    m_sincos(p1 * real(0.5), &sth, &cth);
+    m_sincos(p2 * real(0.5), &sps, &cps);
     real x = sph * cth * cps - cph * sth * sps;
     real y = cph * sth * cps + sph * cth * sps;
     real z = cph * cth * sps - sph * sth * cps;
@@ -93,12 +68,83 @@ SCG_DEV void attitude3(const real (&pre)[3], Att3<real>& a) {
     const real wx = w * xs, wy = w * ys, wz = w * zs;
     const real xx = x * xs, xy = x * ys, xz = x * zs;
     const real yy = y * ys, yz = y * zs, zz = z * zs;
-    a.R[2] = xz + wy; a.R[5] = yz - wx; a.R[8] = real(1) - (xx + yy);
-    if (FULL) {
-        a.R[0] = real(1) - (yy + zz); a.R[1] = xy - wz;
-        a.R[3] = xy + wz;             a.R[4] = real(1) - (xx + zz);
-        a.R[6] = xz - wy;             a.R[7] = yz + wx;
+    a.R[0] = real(1) - (yy + zz); a.R[1] = xy - wz; a.R[2] = xz + wy;
+    a.R[3] = xy + wz;             a.R[4] = real(1) - (xx + zz); a.R[5] = yz - wx;
+    a.R[6] = xz - wy;             a.R[7] = yz + wx; a.R[8] = real(1) - (xx + yy);
+    a.form = 0;
+}
+
+// rpy and column 2 of R (the thrust direction) from the pre-round-trip angles.
+//
+// SCG_ATT_FAST*: the round trip eulerFromQuat(quatFromEuler(pre)) returns the canonical Euler angles of
+// the same rotation, so they are computed by wrap / fold arithmetic and R from their sin / cos:
+//   outside the gimbal band: wrap into [-pi, pi], fold a pitch beyond +-pi/2
+//       (Rz(psi+pi) Ry(pi-theta) Rx(phi+pi) == Rz(psi) Ry(theta) Rx(phi));
+//   inside the band |sin(pitch)| >= 0.99999 bullet snaps roll = 0, pitch = +-pi/2 and
+//       yaw = 2 atan2(-+x, +-y) of the quaternion built from the RAW angles.  Expanding the half-angle
+//       products around pitch = +-pi/2 with r = (pitch -+ pi/2) / 2, |r| <= 2.3e-3, gives
+//         yaw = psi -+ phi + 2 r sin(phi) / (1 +- r cos(phi))        taken modulo 4 pi into (-2 pi, 2 pi]
+//       (tan r ~ r and atan u ~ u drop terms below 3e-9; checked against the literal sequence in
+//       tests/test_oracle_attitude.py).  The reference never leaves the band again while
+//       |pitch rate| dt stays below its half-width: envs that pitch over fall "stuck" at +-90 deg
+//       until a position bound ends the episode -- about 2 % of all substeps of the BASELINE workload,
+//       i.e. half of all warp-substeps see at least one such lane, so the band is handled by a few
+//       predicated instructions here and not by the literal sequence.
+//   fp64 keeps the literal sequence inside the band (validation build, 1e-12).
+template <typename real, int ATT>
+SCG_DEV void attitude3(const real (&pre)[3], Att3<real>& a) {
+    if (ATT != SCG_ATT_ROUNDTRIP) {
+        const real thw = wrap_pi(pre[1]);
+        real th = thw, ph = pre[0], ps = pre[2];
+        const bool folded = m_abs(th) > Consts<real>::half_pi;
+        if (folded) {
+            th = (th > real(0) ? Consts<real>::pi : -Consts<real>::pi) - th;
+            ph += Consts<real>::pi; ps += Consts<real>::pi;
+        }
+        ph = wrap_pi(ph); ps = wrap_pi(ps);
+        real sth, cth;
+        att_sincos<ATT>(th, &sth, &cth);
+        const bool band = !(m_abs(sth) < real(sizeof(real) == 4 ? 0.99999 : 0.99998));
+        if (!band || sizeof(real) == 4) {
+            real sph, cph, sps, cps;
+            att_sincos<ATT>(ph, &sph, &cph);
+            att_sincos<ATT>(ps, &sps, &cps);
+            a.rpy[0] = ph; a.rpy[1] = th; a.rpy[2] = ps;
+            a.sc[0] = sph; a.sc[1] = cph; a.sc[2] = sth; a.sc[3] = cth; a.sc[4] = sps; a.sc[5] = cps;
+            a.R[2] = cps * sth * cph + sps * sph;
+            a.R[5] = sps * sth * cph - cps * sph;
+            a.R[8] = cth * cph;
+            a.form = 1;
+            if (band) {   // fp32 only (see above)
+                const bool up = sth > real(0);
+                const real r = real(0.5) * (thw - (up ? Consts<real>::half_pi : -Consts<real>::half_pi));
+                const real sr = folded ? -sph : sph, cr = folded ? -cph : cph;   // sin / cos of the RAW roll
+                const real u = up ? r * cr : -(r * cr);
+                const real corr = real(2) * r * sr * (real(1) - u + u * u);       // 1 / (1 + u), |u| <= 2.3e-3
+                real yaw = (up ? pre[2] - pre[0] : pre[2] + pre[0]) + corr;
+                const real k = fast_rint(yaw * real(0.07957747154594767));        // modulo 4 pi
+                yaw = m_fma(-k, real(-3.4969110629390343e-07), m_fma(-k, real(12.566370964050293), yaw));
+                a.rpy[0] = real(0);
+                a.rpy[1] = up ? Consts<real>::half_pi : -Consts<real>::half_pi;
+                a.rpy[2] = yaw;
+            }
+            return;
+        }
     }
+    Att3<real> lit;   // a private copy: the out-of-line call must not pin the caller's registers to memory
+    attitude3_roundtrip<real>(pre[0], pre[1], pre[2], lit);
+    a = lit;
+}
+
+// columns 0 and 1 of R, needed only where the body rates p, q, r are read (quadrotor.py:862-864)
+template <typename real> SCG_DEV void attitude3_complete(Att3<real>& a) {
+    if (a.form == 1) {
+        const real sph = a.sc[0], cph = a.sc[1], sth = a.sc[2], cth = a.sc[3], sps = a.sc[4], cps = a.sc[5];
+        a.R[0] = cps * cth; a.R[1] = cps * sth * sph - sps * cph;
+        a.R[3] = sps * cth; a.R[4] = sps * sth * sph + cps * cph;
+        a.R[6] = -sth;      a.R[7] = cth * sph;
+    }
+    a.form = 0;
 }
 
 // Planar (2D) attitude: pitch alpha as the reference reports it plus the "flipped" bit that
@@ -131,14 +177,14 @@ template <typename real> struct Motors {
 
 // quadrotor.py:815-842, quadrotor_utils.py:21-67, base_aviary.py:538-551.
 // thrust[] is the (possibly disturbed) commanded thrust per input.
-template <int KIND, typename real>
+template <int KIND, typename real, bool FASTMATH>
 SCG_DEV void motors_from_thrust(const Hot<real>& h, const real (&thrust)[Dims<KIND>::NU], Motors<real>& m) {
     constexpr int NU = Dims<KIND>::NU;
     real rp[NU];
 #pragma unroll
     for (int j = 0; j < NU; ++j) {
         const real t = m_max(thrust[j], real(0));
-        real pwm = (m_sqrt(t * h.inv_nkf) - h.pwm_const) * h.inv_pwm_scale;
+        real pwm = ((FASTMATH ? sqrt_fast(t * h.inv_nkf) : m_sqrt(t * h.inv_nkf)) - h.pwm_const) * h.inv_pwm_scale;
         pwm = m_clip(pwm, h.pwm_min, h.pwm_max);
         rp[j] = h.pwm_scale * pwm + h.pwm_const;
     }
@@ -201,79 +247,119 @@ template <typename real> SCG_DEV bool viol_test(real c, int strict) {
     return strict ? (y >= real(-0.5)) : (y > real(0.5));
 }
 
+// linear / quadratic rows (uniform loads from the cold block); out of line, rare
 template <int KIND, typename real>
-SCG_DEV void eval_constraints(const Hot<real>& h, const Cold<real>* __restrict__ cold,
-                              const real (&st)[Dims<KIND>::NX], const real (&raw)[Dims<KIND>::NU],
-                              bool state_only, real* __restrict__ c_out, int64_t n, int64_t i,
-                              bool& violated, bool& almost) {
+__device__ __noinline__ void eval_dense_rows(int n_dense_rows, const Cold<real>* __restrict__ cold,
+                                             const real* __restrict__ st, const real* __restrict__ raw,
+                                             bool state_only, real* __restrict__ c_out, int64_t n, int64_t i,
+                                             bool* violated, bool* almost) {
     constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
-    violated = false; almost = false;
-    for (int k = 0; k < h.n_bounded; ++k) {
-        const BoundedCon<real>& bc = h.bounded[k];
-        if (bc.var == SCG_VAR_STATE) {
-#pragma unroll
-            for (int d = 0; d < NX; ++d) {
-                real clo, chi;
-                if (bc.symmetric) { clo = m_abs(st[d]) - bc.hi[d]; chi = -INFINITY; }   // constraints.py:404-406 (unrounded)
-                else { clo = bc.lo[d] - st[d]; chi = st[d] - bc.hi[d]; }
-                if (bc.symmetric) violated |= bc.strict ? (clo >= real(0)) : (clo > real(0));
-                else violated |= viol_test(clo, bc.strict) | viol_test(chi, bc.strict);
-                if (c_out || bc.has_tol) {
-                    const real rlo = bc.symmetric ? clo : round8(clo), rhi = round8(chi);
-                    if (c_out && bc.row_lo[d] >= 0) c_out[int64_t(bc.row_lo[d]) * n + i] = rlo;
-                    if (c_out && bc.row_hi[d] >= 0) c_out[int64_t(bc.row_hi[d]) * n + i] = rhi;
-                    if (bc.has_tol) almost |= (rlo + cold->bounded_tol[k][d] > real(0)) | (rhi + cold->bounded_tol[k][SCG_MAX_NX + d] > real(0));
-                }
-            }
-        } else if (!state_only) {
-#pragma unroll
-            for (int d = 0; d < NU; ++d) {
-                const real clo = bc.lo[d] - raw[d], chi = raw[d] - bc.hi[d];
-                violated |= viol_test(clo, bc.strict) | viol_test(chi, bc.strict);
-                if (c_out || bc.has_tol) {
-                    const real rlo = round8(clo), rhi = round8(chi);
-                    if (c_out && bc.row_lo[d] >= 0) c_out[int64_t(bc.row_lo[d]) * n + i] = rlo;
-                    if (c_out && bc.row_hi[d] >= 0) c_out[int64_t(bc.row_hi[d]) * n + i] = rhi;
-                    if (bc.has_tol) almost |= (rlo + cold->bounded_tol[k][d] > real(0)) | (rhi + cold->bounded_tol[k][SCG_MAX_NX + d] > real(0));
-                }
-            }
-        }
-    }
-    for (int r = 0; r < h.n_dense_rows; ++r) {   // linear / quadratic rows (uniform loads)
+    bool v = false, al = false;
+    for (int r = 0; r < n_dense_rows; ++r) {
         const DenseRow<real>& dr = cold->dense[r];
         if (dr.var == SCG_VAR_INPUT && state_only) continue;
         real c = real(0);
         if (dr.quadratic) {
             const real* P = cold->P[dr.p_index];
             if (dr.var == SCG_VAR_STATE) {
-#pragma unroll
                 for (int a = 0; a < NX; ++a) {
                     real row = real(0);
-#pragma unroll
                     for (int b = 0; b < NX; ++b) row += P[a * SCG_MAX_NX + b] * st[b];
                     c += st[a] * row;
                 }
             } else {
-#pragma unroll
                 for (int a = 0; a < NU; ++a) {
                     real row = real(0);
-#pragma unroll
                     for (int b = 0; b < NU; ++b) row += P[a * SCG_MAX_NX + b] * raw[b];
                     c += raw[a] * row;
                 }
             }
         } else if (dr.var == SCG_VAR_STATE) {
-#pragma unroll
             for (int d = 0; d < NX; ++d) c += dr.a[d] * st[d];
         } else {
-#pragma unroll
             for (int d = 0; d < NU; ++d) c += dr.a[d] * raw[d];
         }
         c -= dr.b;
         const real rc = round8(c);
-        violated |= dr.strict ? (rc >= real(0)) : (rc > real(0));
-        if (dr.has_tol) almost |= (rc + dr.tol > real(0));
+        v |= dr.strict ? (rc >= real(0)) : (rc > real(0));
+        if (dr.has_tol) al |= (rc + dr.tol > real(0));
         if (c_out) c_out[int64_t(dr.out_row) * n + i] = rc;
+    }
+    *violated = v; *almost = al;
+}
+
+// Everything beyond the violation flag of bounded constraints -- the rounded values
+// (info["constraint_values"]), tolerances (is_almost_active), symmetric and dense rows -- out of
+// line: per-step outputs only exist in the host-driven scg_step mode.
+template <int KIND, typename real>
+__device__ __noinline__ void constraint_values_cold(const Hot<real>& h, const Cold<real>* __restrict__ cold,
+                                                    const real* __restrict__ st, const real* __restrict__ raw,
+                                                    bool state_only, real* __restrict__ c_out, int64_t n, int64_t i,
+                                                    bool* violated_out, bool* almost_out) {
+    constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
+    bool violated = false, almost = false;
+    for (int k = 0; k < h.n_bounded; ++k) {
+        const BoundedCon<real>& bc = h.bounded[k];
+        const bool is_state = bc.var == SCG_VAR_STATE;
+        if (!is_state && state_only) continue;
+        const int nd = is_state ? NX : NU;
+        for (int d = 0; d < nd; ++d) {
+            if (!((bc.mask >> d) & 1u)) continue;
+            const real x = is_state ? st[d] : raw[d];
+            real clo, chi, rlo, rhi;
+            if (bc.symmetric) {   // constraints.py:404-406 (unrounded)
+                clo = m_abs(x) - bc.hi[d]; chi = -INFINITY; rlo = clo; rhi = chi;
+                violated |= bc.strict ? (clo >= real(0)) : (clo > real(0));
+            } else {
+                clo = bc.lo[d] - x; chi = x - bc.hi[d]; rlo = round8(clo); rhi = round8(chi);
+                violated |= viol_test(clo, bc.strict) | viol_test(chi, bc.strict);
+            }
+            if (c_out && bc.row_lo[d] >= 0) c_out[int64_t(bc.row_lo[d]) * n + i] = rlo;
+            if (c_out && bc.row_hi[d] >= 0) c_out[int64_t(bc.row_hi[d]) * n + i] = rhi;
+            if (bc.has_tol) almost |= (rlo + cold->bounded_tol[k][d] > real(0)) | (rhi + cold->bounded_tol[k][SCG_MAX_NX + d] > real(0));
+        }
+    }
+    if (h.n_dense_rows > 0) {
+        bool v, al;
+        eval_dense_rows<KIND, real>(h.n_dense_rows, cold, st, raw, state_only, c_out, n, i, &v, &al);
+        violated |= v; almost |= al;
+    }
+    *violated_out = violated; *almost_out = almost;
+}
+
+// The in-loop part: violation flags of the bounded / default constraints (the only kind a LEAN
+// config has); anything else is delegated to constraint_values_cold.
+template <int KIND, typename real, bool LEAN>
+SCG_DEV void eval_constraints(const Hot<real>& h, const Cold<real>* __restrict__ cold,
+                              const real (&st)[Dims<KIND>::NX], const real (&raw)[Dims<KIND>::NU],
+                              bool state_only, real* __restrict__ c_out, int64_t n, int64_t i,
+                              bool& violated, bool& almost) {
+    constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
+    violated = false; almost = false;
+    if (c_out != nullptr || (!LEAN && h.need_cold_constraints)) {
+        real sl[NX], rl[NU];   // the out-of-line call takes copies, the caller's registers stay registers
+#pragma unroll
+        for (int d = 0; d < NX; ++d) sl[d] = st[d];
+#pragma unroll
+        for (int d = 0; d < NU; ++d) rl[d] = raw[d];
+        constraint_values_cold<KIND, real>(h, cold, sl, rl, state_only, c_out, n, i, &violated, &almost);
+        return;
+    }
+    for (int k = 0; k < h.n_bounded; ++k) {
+        const BoundedCon<real>& bc = h.bounded[k];
+        if (bc.var == SCG_VAR_STATE) {
+#pragma unroll
+            for (int d = 0; d < NX; ++d) {
+                if (!((bc.mask >> d) & 1u)) continue;   // uniform
+                violated |= viol_test(bc.lo[d] - st[d], bc.strict) | viol_test(st[d] - bc.hi[d], bc.strict);
+            }
+        } else if (!state_only) {
+#pragma unroll
+            for (int d = 0; d < NU; ++d) {
+                if (!((bc.mask >> d) & 1u)) continue;
+                violated |= viol_test(bc.lo[d] - raw[d], bc.strict) | viol_test(raw[d] - bc.hi[d], bc.strict);
+            }
+        }
     }
 }
 
@@ -281,7 +367,7 @@ SCG_DEV void eval_constraints(const Hot<real>& h, const Cold<real>* __restrict__
 // Additive, applied in YAML order (DisturbanceList.apply, disturbances.py:69-79).
 // t = ctrl_step_counter (pre-increment); index = Philox counter word 0 for this call.
 template <typename real, int DIM>
-SCG_DEV void apply_channel(const Cold<real>* __restrict__ cold, int ch, int n_dist, real (&v)[DIM],
+__device__ __noinline__ void apply_channel(const Cold<real>* __restrict__ cold, int ch, int n_dist, real (&v)[DIM],
                            int32_t t, real t_sim, const RngKey& key, uint32_t index, uint32_t episode,
                            const int32_t* __restrict__ offsets, int64_t n, int64_t i) {
     for (int k = 0; k < n_dist; ++k) {

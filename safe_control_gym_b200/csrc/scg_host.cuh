@@ -1,0 +1,54 @@
+// scg_host.cuh -- host-side handle shared by the translation units of libscg_b200.so.
+// scg_api.cu owns the extern "C" ABI; the kernels are instantiated per (env kind, precision) in
+// scg_k_*.cu (compiled in parallel) behind the three launchers declared at the bottom.
+#pragma once
+#include <string>
+
+#include "scg_params.cuh"
+
+struct scg_env {
+    scg_config cfg;
+    int nx, nu, obs_dim, n_rows, n_slots;
+    bool lean = false;             // the LEAN kernel specialisation applies (scg_step.cuh)
+    scg::Hot<float> hf;
+    scg::Hot<double> hd;
+    void* cold_dev = nullptr;      // Cold<float> or Cold<double>
+    void* cold_host = nullptr;     // host mirror (for injection pointer updates)
+    void* x_goal_dev = nullptr;
+    scg_buffers buf;
+    bool bound = false, did_reset = false;
+    int64_t launches = 0;
+    // scg_rollout_host staging
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};
+    void* stage[2] = {nullptr, nullptr};
+    size_t stage_bytes = 0;
+};
+
+int scg_fail(int code, const std::string& msg);
+int scg_cuda_fail(cudaError_t e, const char* what);
+#define SCG_CU(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return scg_cuda_fail(_e, #x); } while (0)
+
+namespace scg {
+
+template <typename real> inline const Hot<real>& hot_of(const scg_env* e);
+template <> inline const Hot<float>& hot_of<float>(const scg_env* e) { return e->hf; }
+template <> inline const Hot<double>& hot_of<double>(const scg_env* e) { return e->hd; }
+
+template <typename real> inline Buf<real> typed_buf(const scg_buffers& b) {
+    Buf<real> t;
+    t.n = b.n; t.state = (real*)b.state; t.ctrl_step = b.ctrl_step; t.episode = b.episode; t.flags = b.flags;
+    t.dist_offset = b.dist_offset; t.inertia = (real*)b.inertia; t.obs = (real*)b.obs; t.env_state = (real*)b.env_state;
+    t.reward = (real*)b.reward; t.done = b.done; t.info = b.info; t.mse = (real*)b.mse; t.c_values = (real*)b.c_values;
+    t.terminal_obs = (real*)b.terminal_obs; t.ep_return = (real*)b.ep_return; t.ep_length = b.ep_length;
+    t.ep_violations = b.ep_violations; t.stats = b.stats; t.adv_action = (const real*)b.adv_action;
+    return t;
+}
+
+// defined (and explicitly instantiated) in scg_inst.cuh / scg_k_*.cu
+template <int KIND, typename real> int launch_reset(scg_env* e, const ResetInject<real>& inj, const uint8_t* mask, cudaStream_t st);
+template <int KIND, typename real> int launch_rollout(scg_env* e, const Roll<real>& ro, cudaStream_t st);
+template <int KIND, typename real> int launch_constraints(scg_env* e, const real* state, const real* action, int64_t n,
+                                                          real* out_values, uint8_t* out_flags, cudaStream_t st);
+
+}  // namespace scg

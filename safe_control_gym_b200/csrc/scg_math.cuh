@@ -34,24 +34,59 @@ SCG_DEV float  m_max(float a, float b)   { return fmaxf(a, b); }
 SCG_DEV double m_max(double a, double b) { return fmax(a, b); }
 SCG_DEV float  m_min(float a, float b)   { return fminf(a, b); }
 SCG_DEV double m_min(double a, double b) { return fmin(a, b); }
+SCG_DEV float  m_fma(float a, float b, float c)    { return fmaf(a, b, c); }
+SCG_DEV double m_fma(double a, double b, double c) { return fma(a, b, c); }
 SCG_DEV float  m_rint(float x)  { return rintf(x); }
 SCG_DEV double m_rint(double x) { return rint(x); }
+// rint() by the 1.5 * 2^23 magic constant: two fma-pipe adds instead of FRND, which issues on the
+// quarter-rate XU pipe (valid for |x| < 2^22; the kernels only feed it angles / (2 pi)).
+SCG_DEV float fast_rint(float x) { return (x + 12582912.f) - 12582912.f; }
+SCG_DEV double fast_rint(double x) { return rint(x); }
 // sin/cos for |x| <= pi + small (the attitude angles after wrap_pi): quadrant reduction with a two-term
 // pi/2 and the cephes single-precision minimax polynomials on [-pi/4, pi/4] (about 1 ulp).  Compact:
-// no large-argument (Payne-Hanek) path, so the substep loop stays small in the instruction cache.
+// no large-argument (Payne-Hanek) path, no F2I / FRND, so the substep loop stays small in the
+// instruction cache and on the fma pipe.
 SCG_DEV void sincos_pi(float x, float* s, float* c) {
-    const float k = rintf(x * 0.63661977236758134f);
+    const float kf = fmaf(x, 0.63661977236758134f, 12582912.f);
+    const int q = __float_as_int(kf);          // mantissa = 0x400000 + k: the low bits are k mod 4
+    const float k = kf - 12582912.f;
     const float r = fmaf(-k, -4.371139000186243e-08f, fmaf(-k, 1.5707963705062866f, x));
     const float z = r * r;
     const float sp = fmaf(r * z, fmaf(z, fmaf(z, -1.9515295891e-4f, 8.3321608736e-3f), -1.6666654611e-1f), r);
     const float cp = fmaf(z * z, fmaf(z, fmaf(z, 2.443315711809948e-5f, -1.388731625493765e-3f), 4.166664568298827e-2f),
                           fmaf(z, -0.5f, 1.0f));
-    const int q = static_cast<int>(k) & 3;
-    const float ss = (q & 1) ? cp : sp, cc = (q & 1) ? sp : cp;
-    *s = (q & 2) ? -ss : ss;
-    *c = ((q + 1) & 2) ? -cc : cc;
+    const bool swap = (q & 1) != 0;
+    const float ss = swap ? cp : sp, cc = swap ? sp : cp;
+    const uint32_t uq = static_cast<uint32_t>(q);
+    *s = __uint_as_float(__float_as_uint(ss) ^ ((uq & 2u) << 30));
+    *c = __uint_as_float(__float_as_uint(cc) ^ (((uq + 1u) & 2u) << 30));
 }
 SCG_DEV void sincos_pi(double x, double* s, double* c) { sincos(x, s, c); }
+// sqrt for the fp32 fast paths: MUFU.SQRT (about 1 ulp) instead of the IEEE sequence with its
+// denormal / special-case branch
+SCG_DEV float sqrt_fast(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+SCG_DEV double sqrt_fast(double x) { return sqrt(x); }
+// atan2 for the fp32 fast paths: a = min/max in [0, 1], odd polynomial a * P(a^2) (degree 15, fitted
+// to 1.2e-7 max abs error in fp32, tools/fit_atan.py), octant fix-ups by selects.  About 25
+// instructions, one MUFU.RCP, no branches (libdevice's atan2f is ~3x that with a division).
+SCG_DEV float atan2_fast(float y, float x) {
+    const float ax = fabsf(x), ay = fabsf(y);
+    const float mx = fmaxf(ax, ay), mn = fminf(ax, ay);
+    const float a = mx > 0.f ? __fdividef(mn, mx) : 0.f;
+    const float z = a * a;
+    float p = -4.3554287404e-03f;
+    p = fmaf(p, z, 2.3040225729e-02f);
+    p = fmaf(p, z, -5.7773731649e-02f);
+    p = fmaf(p, z, 9.7942464054e-02f);
+    p = fmaf(p, z, -1.3976587355e-01f);
+    p = fmaf(p, z, 1.9962705672e-01f);
+    p = fmaf(p, z, -3.3331659436e-01f);
+    float r = fmaf(p * z, a, a);
+    r = ay > ax ? 1.57079632679489661923f - r : r;
+    r = x < 0.f ? 3.14159265358979323846f - r : r;
+    return copysignf(r, y);
+}
+SCG_DEV double atan2_fast(double y, double x) { return atan2(y, x); }
 // np.clip(x, lo, hi) == minimum(maximum(x, lo), hi)
 template <typename real> SCG_DEV real m_clip(real x, real lo, real hi) { return m_min(m_max(x, lo), hi); }
 

@@ -17,7 +17,10 @@ template <typename real> struct BoundedCon {
     real lo[SCG_MAX_NX], hi[SCG_MAX_NX];       // per FULL dim; inactive dims: -inf / +inf
     int8_t row_lo[SCG_MAX_NX], row_hi[SCG_MAX_NX];  // output row (YAML order) or -1
     int8_t var, strict, has_tol, symmetric;
+    uint32_t mask;                             // bit d set: FULL dim d is constrained
 };
+
+template <typename real> struct RandP { int32_t distrib; real a, b; };
 
 template <typename real> struct Hot {
     // timing
@@ -42,6 +45,8 @@ template <typename real> struct Hot {
     real rew_state_weight[SCG_MAX_NX], rew_act_weight[SCG_MAX_NU], u_goal[SCG_MAX_NU];
     real x_goal0[SCG_MAX_NX];       // stabilisation goal (row 0)
     real mse_weight[SCG_MAX_NX];
+    uint32_t mse_mask;              // dims with a non-zero mse weight
+    int32_t need_full_state;        // some per-step consumer reads the body rates p, q, r (else only the final obs does)
     real goal_tol;
     int32_t quadratic_diag;         // Q, R diagonal -> hot path, else dense from Cold
     real q_diag[SCG_MAX_NX], r_diag[SCG_MAX_NU];
@@ -49,6 +54,7 @@ template <typename real> struct Hot {
     real constraint_penalty;
     // constraints
     int32_t n_bounded, n_dense_rows, n_rows, any_tolerance;
+    int32_t need_cold_constraints;  // tolerances, symmetric or dense rows: the flags alone need constraint_values_cold
     BoundedCon<real> bounded[MAX_BOUNDED];
     real viol_thr;                  // fp32: 5e-9 (== round(c, 8) > 0 in exact arithmetic)
     // feature switches (uniform branches)
@@ -57,6 +63,8 @@ template <typename real> struct Hot {
     int32_t reseed_on_reset, any_init_rand, any_inertia_rand, any_gate_rand;   // *_rand: bit 0 uniform, bit 1 normal draws needed
     real init_state[SCG_MAX_NX + 1];
     real inertia_nominal[4];
+    RandP<real> init_rand[SCG_MAX_NX], inertia_rand[4];   // distrib NONE: a = b = 0
+    uint32_t init_block_mask;       // Philox blocks (4 labels each) holding a randomised init label
     uint32_t seed;
     uint32_t env_id_base_lo;
 };
@@ -77,15 +85,13 @@ template <typename real> struct DistP {
     const real* inject;             // [dim][n] or nullptr
 };
 
-template <typename real> struct RandP { int32_t distrib; real a, b; };
-
 template <typename real> struct Cold {
     DenseRow<real> dense[MAX_DENSE_ROWS];
     real P[2][SCG_MAX_NX * SCG_MAX_NX];
     real bounded_tol[MAX_BOUNDED][2 * SCG_MAX_NX];   // per (object, lo/hi dim)
     real Q[SCG_MAX_NX * SCG_MAX_NX], R[SCG_MAX_NU * SCG_MAX_NU];
     DistP<real> dist[3][SCG_MAX_DIST];
-    RandP<real> init_rand[SCG_MAX_NX], inertia_rand[4], gate_rand, obstacle_rand;
+    RandP<real> gate_rand, obstacle_rand;
     real gates[SCG_MAX_GATES][7], obstacles[SCG_MAX_OBSTACLES][6];
     int32_t n_obstacles;
     const real* x_goal;             // [n_goal_rows][nx] device
@@ -104,6 +110,8 @@ template <typename real> struct Roll {
     const real* actions; int32_t k_steps; real* reward_out; uint8_t* done_out; real* log_out; int32_t log_stride;
     int32_t step_outputs;           // 1: write the per-step outputs of Buf (scg_step), 0: only final obs/state
 };
+
+template <typename real> struct ResetInject { const real* init; const real* inertia; const int32_t* offsets; };
 
 template <int KIND> struct Dims;
 template <> struct Dims<SCG_QUAD_1D> { static constexpr int NX = 2, NU = 1, NF = 1; };

@@ -1,13 +1,20 @@
-// scg_step.cuh -- the fused reset / step / K-step rollout kernel for the quadrotor envs.
+// scg_step.cuh -- the fused reset / step / K-step rollout kernel for the quadrotor and cart-pole envs.
 // One thread = one env.  Everything Quadrotor.step() does per control step (rows A1-A11 of
 // SURVEY.md section 8a) plus DummyVecEnv's auto-reset (A14) happens between one load and one
 // store of the env's state; the substep loop touches registers and constant-bank operands only.
+//
+// Code-size discipline (profiles/r1a_summary.md): the control-step loop must fit the 32 KB L1.5
+// instruction cache, because 65,536 envs are only 3.5 warps per scheduler and nothing hides an
+// instruction-fetch miss.  So (a) everything rare -- reset with its Philox draws, the literal
+// quaternion round trip, disturbance kinds, dense constraint rows, the extended observation -- lives
+// in __noinline__ functions outside the loop, and (b) the kernel is instantiated twice: LEAN (no
+// disturbances, no adversary, no external force, bounded constraints without tolerances, nominal
+// inertia, diagonal Q/R, plain observation: what scg_create() finds in e.g. level0.yaml) compiles
+// those features out, GENERAL keeps them behind uniform branches.
 #pragma once
 #include "scg_env.cuh"
 
 namespace scg {
-
-template <typename real> struct ResetInject { const real* init; const real* inertia; const int32_t* offsets; };
 
 template <int KIND, typename real> struct EnvRegs {
     static constexpr int NX = Dims<KIND>::NX;
@@ -43,7 +50,7 @@ template <int KIND, typename real> SCG_DEV void load_inertia(const Hot<real>& h,
 template <int KIND, typename real, int ATT> SCG_DEV void derive_attitude(EnvRegs<KIND, real>& e) {
     if constexpr (KIND == SCG_QUAD_3D) {
         const real pre[3] = {e.x[6], e.x[7], e.x[8]};
-        attitude3<real, ATT, true>(pre, e.a3);
+        attitude3<real, ATT>(pre, e.a3);
     } else if constexpr (KIND == SCG_QUAD_2D) {
         attitude2<real>(e.x[4], (e.flags & SCG_FLAG_FLIPPED) ? 1u : 0u, e.a2);
         e.x[4] = e.a2.theta;
@@ -52,17 +59,21 @@ template <int KIND, typename real, int ATT> SCG_DEV void derive_attitude(EnvRegs
 }
 
 // env.state (quadrotor.py:853-869) from the registers; ang = the angular-velocity vector
-// PyBullet holds (rpy_rates after a step, INIT_ANG_VEL right after reset).
-template <int KIND, typename real>
-SCG_DEV void make_state(const EnvRegs<KIND, real>& e, const real (&ang)[3], real (&st)[Dims<KIND>::NX]) {
+// PyBullet holds (rpy_rates after a step, INIT_ANG_VEL right after reset).  FULL = false leaves
+// the 3D body rates p, q, r (slots 9-11) untouched: they need the whole rotation matrix.
+template <int KIND, typename real, bool FULL = true>
+SCG_DEV void make_state(EnvRegs<KIND, real>& e, const real (&ang)[3], real (&st)[Dims<KIND>::NX]) {
     if constexpr (KIND == SCG_QUAD_3D) {
 #pragma unroll
         for (int d = 0; d < 6; ++d) st[d] = e.x[d];
         st[6] = e.a3.rpy[0]; st[7] = e.a3.rpy[1]; st[8] = e.a3.rpy[2];
-        const real* R = e.a3.R;   // pqr = R^T ang_v (quadrotor.py:862-864)
-        st[9] = (R[0] * ang[0] + R[3] * ang[1]) + R[6] * ang[2];
-        st[10] = (R[1] * ang[0] + R[4] * ang[1]) + R[7] * ang[2];
-        st[11] = (R[2] * ang[0] + R[5] * ang[1]) + R[8] * ang[2];
+        if (FULL) {
+            attitude3_complete<real>(e.a3);
+            const real* R = e.a3.R;   // pqr = R^T ang_v (quadrotor.py:862-864)
+            st[9] = (R[0] * ang[0] + R[3] * ang[1]) + R[6] * ang[2];
+            st[10] = (R[1] * ang[0] + R[4] * ang[1]) + R[7] * ang[2];
+            st[11] = (R[2] * ang[0] + R[5] * ang[1]) + R[8] * ang[2];
+        }
     } else if constexpr (KIND == SCG_QUAD_2D) {
 #pragma unroll
         for (int d = 0; d < 4; ++d) st[d] = e.x[d];
@@ -89,18 +100,19 @@ SCG_DEV void goal_row(const Hot<real>& h, const Cold<real>* __restrict__ cold, i
     }
 }
 
-// obs = state + observation disturbances, then extend_obs (quadrotor.py:878-884, benchmark_env.py:406-420)
+// obs = state + observation disturbances, then extend_obs (quadrotor.py:878-884, benchmark_env.py:406-420).
+// Out of line: called once per launch (final obs) or on done steps (terminal obs), never in the substep loop.
 template <int KIND, typename real>
-SCG_DEV void write_obs(const Hot<real>& h, const Cold<real>* __restrict__ cold, const Buf<real>& b, real* __restrict__ dst,
-                       const real (&st)[Dims<KIND>::NX], int32_t t_pre, uint32_t obs_index, const RngKey& key,
-                       uint32_t episode, int64_t n, int64_t i) {
+__device__ __noinline__ void write_obs(const Hot<real>& h, const Cold<real>* __restrict__ cold, const int32_t* __restrict__ dist_offset,
+                                       real* __restrict__ dst, const real* __restrict__ st, int32_t t_pre, uint32_t obs_index,
+                                       RngKey key, uint32_t episode, int64_t n, int64_t i) {
     constexpr int NX = Dims<KIND>::NX;
     real o[NX];
 #pragma unroll
     for (int d = 0; d < NX; ++d) o[d] = st[d];
     if (h.n_dist_obs)
         apply_channel<real, NX>(cold, SCG_CH_OBSERVATION, h.n_dist_obs, o, t_pre, real(t_pre * h.substeps) * h.dt, key,
-                                obs_index, episode, b.dist_offset, n, i);
+                                obs_index, episode, dist_offset, n, i);
 #pragma unroll
     for (int d = 0; d < NX; ++d) dst[int64_t(d) * n + i] = o[d];
     if (h.cost == SCG_COST_RL_REWARD && h.obs_goal_horizon > 0) {
@@ -125,9 +137,9 @@ template <typename real> SCG_DEV real rand_value(const RandP<real>& rp, real u, 
 // Quadrotor.reset() (quadrotor.py:356-504) for one env.  Leaves e ready for the next step and
 // returns env.state of the fresh episode in st.
 template <int KIND, typename real, int ATT>
-SCG_DEV void reset_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, const Buf<real>& b,
-                       const ResetInject<real>& inj, const RngKey& key, int64_t n, int64_t i,
-                       EnvRegs<KIND, real>& e, real (&st)[Dims<KIND>::NX]) {
+SCG_DEV void reset_env_body(const Hot<real>& h, const Cold<real>* __restrict__ cold, const Buf<real>& b,
+                            const ResetInject<real>& inj, const RngKey& key, int64_t n, int64_t i,
+                            EnvRegs<KIND, real>& e, real (&st)[Dims<KIND>::NX]) {
     constexpr int NX = Dims<KIND>::NX;
     const uint32_t ep = h.reseed_on_reset ? 0u : uint32_t(e.resets);
     e.resets += 1;
@@ -160,7 +172,7 @@ SCG_DEV void reset_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, 
         for (int j = 0; j < 4; ++j) {
             real v = h.inertia_nominal[j];
             if (inj.inertia) v += inj.inertia[int64_t(j) * n + i];
-            else if (h.any_inertia_rand) v += rand_value(cold->inertia_rand[j], u[j], z[j]);
+            else if (h.any_inertia_rand) v += rand_value(h.inertia_rand[j], u[j], z[j]);
             b.inertia[int64_t(j) * n + i] = v;
         }
     }
@@ -179,7 +191,7 @@ SCG_DEV void reset_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, 
         if (h.any_init_rand & 1) draw_uniforms<real, NX>(key, 0u, ep, STREAM_RESET_INIT, u);
         if (h.any_init_rand & 2) draw_normals<real, NX>(key, 0u, ep, STREAM_RESET_INIT, z);
 #pragma unroll
-        for (int d = 0; d < NX; ++d) init[d] += rand_value(cold->init_rand[d], u[d], z[d]);
+        for (int d = 0; d < NX; ++d) init[d] += rand_value(h.init_rand[d], u[d], z[d]);
     }
     real ang[3] = {real(0), real(0), real(0)};
     if constexpr (KIND == SCG_QUAD_3D) {
@@ -204,16 +216,78 @@ SCG_DEV void reset_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, 
     make_state<KIND, real>(e, ang, st);
 }
 
-// One Quadrotor.step(): returns reward / done / info bits, leaves env.state in st.
+// Auto-reset of a LEAN config, inline in the rollout loop: no disturbance offsets, no inertia draws,
+// uniform-only initial-state randomisation (host-checked in scg_create).  With short episodes a warp
+// enters this path on a large share of its steps (48 % at 2 % resets per env-step), so it is kept to
+// the Philox blocks that hold a randomised label plus one attitude evaluation.
 template <int KIND, typename real, int ATT>
+SCG_DEV void reset_env_lean(const Hot<real>& h, const RngKey& key, EnvRegs<KIND, real>& e, real (&st)[Dims<KIND>::NX]) {
+    constexpr int NX = Dims<KIND>::NX;
+    const uint32_t ep = h.reseed_on_reset ? 0u : uint32_t(e.resets);
+    e.resets += 1;
+    e.t = 0;
+    e.flags &= SCG_FLAG_CNSTR_VIOLATION;   // cnstr_violation survives reset (benchmark_env.py:218)
+    real init[NX];
+#pragma unroll
+    for (int d = 0; d < NX; ++d) init[d] = h.init_state[d];
+#pragma unroll
+    for (int blk = 0; blk < (NX + 3) / 4; ++blk) {
+        if (!((h.init_block_mask >> blk) & 1u)) continue;   // uniform: no randomised label in this block
+        const U4 w = philox4x32_10(0u, ep, STREAM_RESET_INIT, uint32_t(blk), key.seed, key.env);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int d = 4 * blk + j;
+            if (d < NX) init[d] += h.init_rand[d].a + (h.init_rand[d].b - h.init_rand[d].a) * u01<real>(word_of(w, j));
+        }
+    }
+    real ang[3] = {real(0), real(0), real(0)};
+    if constexpr (KIND == SCG_QUAD_3D) {
+#pragma unroll
+        for (int d = 0; d < 9; ++d) e.x[d] = init[d];
+        e.x[9] = e.x[10] = e.x[11] = real(0);          // rpy_rates restart at 0 (base_aviary.py:232-233)
+        ang[0] = init[9]; ang[1] = init[10]; ang[2] = init[11];   // INIT_ANG_VEL lives in PyBullet only
+    } else if constexpr (KIND == SCG_QUAD_2D) {
+#pragma unroll
+        for (int d = 0; d < 5; ++d) e.x[d] = init[d];
+        e.x[5] = real(0);
+        ang[1] = init[5];
+    } else if constexpr (KIND == SCG_CARTPOLE) {
+#pragma unroll
+        for (int d = 0; d < 4; ++d) e.x[d] = init[d];
+    } else {
+        e.x[0] = real(0); e.x[1] = real(0);
+    }
+    derive_attitude<KIND, real, ATT>(e);
+    make_state<KIND, real>(e, ang, st);
+}
+
+// The auto-reset inside the rollout loop: one out-of-line copy, entered by the lanes whose episode
+// ended this step (dummy_vec_env.py:38-49).  Works on private copies so that the loop's registers
+// are not pinned to local memory by the call.
+template <int KIND, typename real, int ATT>
+__device__ __noinline__ void reset_env_cold(const Hot<real>& h, const Cold<real>* __restrict__ cold, const Buf<real>& b,
+                                            RngKey key, int64_t n, int64_t i, EnvRegs<KIND, real>* e_io, real* __restrict__ st_out) {
+    constexpr int NX = Dims<KIND>::NX;
+    EnvRegs<KIND, real> e = *e_io;
+    real st[NX];
+    const ResetInject<real> none{nullptr, nullptr, nullptr};
+    reset_env_body<KIND, real, ATT>(h, cold, b, none, key, n, i, e, st);
+    *e_io = e;
+#pragma unroll
+    for (int d = 0; d < NX; ++d) st_out[d] = st[d];
+}
+
+// One Quadrotor.step(): returns reward / done / info bits, leaves env.state in st
+// (3D: p, q, r only when `full`).
+template <int KIND, typename real, int ATT, bool LEAN>
 SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, const Buf<real>& b,
                       const RngKey& key, int64_t n, int64_t i, EnvRegs<KIND, real>& e,
-                      const real (&raw)[Dims<KIND>::NU], real (&st)[Dims<KIND>::NX], real& reward, bool& done,
+                      const real (&raw)[Dims<KIND>::NU], bool full, real (&st)[Dims<KIND>::NX], real& reward, bool& done,
                       uint32_t& info, real& mse, Motors<real>& mot, real* __restrict__ c_out) {
     constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
+    constexpr bool FASTMATH = sizeof(real) == 4 && ATT != SCG_ATT_ROUNDTRIP;
     const uint32_t ep = h.reseed_on_reset ? 0u : uint32_t(e.resets - 1);
     const int32_t t = e.t;
-    const real t_sim = real(t * h.substeps) * h.dt;
     info = 0u;
     // ---- before_step / _preprocess_control (quadrotor.py:815-842)
     real thr[NU], pre[NU];
@@ -224,36 +298,46 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
         else pre[j] = h.normalized_action ? (real(1) + h.norm_act_scale * c) * h.hover_thrust : c;
         thr[j] = pre[j];
     }
-    if (h.n_dist_act)
-        apply_channel<real, NU>(cold, SCG_CH_ACTION, h.n_dist_act, thr, t, t_sim, key, uint32_t(t), ep, b.dist_offset, n, i);
-    if (h.adversary_channel == SCG_CH_ACTION && b.adv_action) {
-#pragma unroll
-        for (int j = 0; j < NU; ++j) thr[j] += b.adv_action[i * NU + j];
-    }
-    if constexpr (KIND != SCG_CARTPOLE) motors_from_thrust<KIND, real>(h, thr, mot);
-    else { mot.T = mot.tx = mot.ty = mot.tz = real(0); mot.rpm[0] = mot.rpm[1] = mot.rpm[2] = mot.rpm[3] = real(0); }
-    // ---- external force (extension, F5: the reference never integrates it in DYN)
     real fx = real(0), fy = real(0), fz = real(0);
-    if (h.dyn_applies_force && (h.n_dist_dyn || h.adversary_channel == SCG_CH_DYNAMICS)) {
-        constexpr int NF = Dims<KIND>::NF;
-        real f[NF];
+    if constexpr (!LEAN) {
+        const real t_sim = real(t * h.substeps) * h.dt;
+        if (h.n_dist_act) {
+            real tmp[NU];
 #pragma unroll
-        for (int d = 0; d < NF; ++d) f[d] = real(0);
-        if (h.n_dist_dyn)
-            apply_channel<real, NF>(cold, SCG_CH_DYNAMICS, h.n_dist_dyn, f, t, t_sim, key, uint32_t(t), ep, b.dist_offset, n, i);
-        if (h.adversary_channel == SCG_CH_DYNAMICS && b.adv_action) {
+            for (int j = 0; j < NU; ++j) tmp[j] = thr[j];
+            apply_channel<real, NU>(cold, SCG_CH_ACTION, h.n_dist_act, tmp, t, t_sim, key, uint32_t(t), ep, b.dist_offset, n, i);
 #pragma unroll
-            for (int d = 0; d < NF; ++d) f[d] += b.adv_action[i * NF + d];
+            for (int j = 0; j < NU; ++j) thr[j] = tmp[j];
         }
-        if constexpr (KIND == SCG_QUAD_1D) { fz = f[0]; }
-        else if constexpr (KIND == SCG_QUAD_2D || KIND == SCG_CARTPOLE) { fx = f[0]; fz = f[1]; }
-        else { fx = f[0]; fy = f[1]; fz = f[2]; }
+        if (h.adversary_channel == SCG_CH_ACTION && b.adv_action) {
+#pragma unroll
+            for (int j = 0; j < NU; ++j) thr[j] += b.adv_action[i * NU + j];
+        }
+        // ---- external force (extension, F5: the reference never integrates it in DYN)
+        if (h.dyn_applies_force && (h.n_dist_dyn || h.adversary_channel == SCG_CH_DYNAMICS)) {
+            constexpr int NF = Dims<KIND>::NF;
+            real f[NF];
+#pragma unroll
+            for (int d = 0; d < NF; ++d) f[d] = real(0);
+            if (h.n_dist_dyn)
+                apply_channel<real, NF>(cold, SCG_CH_DYNAMICS, h.n_dist_dyn, f, t, t_sim, key, uint32_t(t), ep, b.dist_offset, n, i);
+            if (h.adversary_channel == SCG_CH_DYNAMICS && b.adv_action) {
+#pragma unroll
+                for (int d = 0; d < NF; ++d) f[d] += b.adv_action[i * NF + d];
+            }
+            if constexpr (KIND == SCG_QUAD_1D) { fz = f[0]; }
+            else if constexpr (KIND == SCG_QUAD_2D || KIND == SCG_CARTPOLE) { fx = f[0]; fz = f[1]; }
+            else { fx = f[0]; fy = f[1]; fz = f[2]; }
+        }
     }
+    if constexpr (KIND != SCG_CARTPOLE) motors_from_thrust<KIND, real, FASTMATH>(h, thr, mot);
+    else { mot.T = mot.tx = mot.ty = mot.tz = real(0); mot.rpm[0] = mot.rpm[1] = mot.rpm[2] = mot.rpm[3] = real(0); }
     // ---- _advance_simulation: S explicit substeps (base_aviary.py:266-322, 522-576)
     const real Tm = mot.T * e.in.inv_mass;
     const real dt = h.dt;
     if constexpr (KIND == SCG_QUAD_3D) {
         const real axf = fx * e.in.inv_mass, ayf = fy * e.in.inv_mass, azf = fz * e.in.inv_mass - e.in.g_over_m;
+#pragma unroll 1
         for (int s = 0; s < h.substeps; ++s) {
             const real ax = e.a3.R[2] * Tm + axf, ay = e.a3.R[5] * Tm + ayf, az = e.a3.R[8] * Tm + azf;
             const real w0 = e.x[9], w1 = e.x[10], w2 = e.x[11];
@@ -266,11 +350,11 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             e.x[0] += dt * e.x[1]; e.x[2] += dt * e.x[3]; e.x[4] += dt * e.x[5];   // pos uses NEW vel
             const real pre3[3] = {e.a3.rpy[0] + dt * e.x[9], e.a3.rpy[1] + dt * e.x[10], e.a3.rpy[2] + dt * e.x[11]};
             e.x[6] = pre3[0]; e.x[7] = pre3[1]; e.x[8] = pre3[2];
-            if (s + 1 < h.substeps) attitude3<real, ATT, false>(pre3, e.a3);
-            else attitude3<real, ATT, true>(pre3, e.a3);
+            attitude3<real, ATT>(pre3, e.a3);
         }
     } else if constexpr (KIND == SCG_QUAD_2D) {
         const real axf = fx * e.in.inv_mass, azf = fz * e.in.inv_mass - e.in.g_over_m;
+#pragma unroll 1
         for (int s = 0; s < h.substeps; ++s) {
             const real ax = e.a2.r3x * Tm + axf, az = e.a2.r3z * Tm + azf;
             const real dw = e.in.J_inv[1] * mot.ty;
@@ -286,9 +370,11 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
         // extra horizontal force on the cart when dyn_applies_force is on.
         const real F = thr[0] + fx;
         (void)fy; (void)fz; (void)Tm;
+#pragma unroll 1
         for (int s = 0; s < h.substeps; ++s) cartpole_rk4<real>(e.in, h.gravity_acc, e.x, F, dt);
     } else {
         const real az = Tm + (fz * e.in.inv_mass - e.in.g_over_m);
+#pragma unroll 1
         for (int s = 0; s < h.substeps; ++s) { e.x[1] += dt * az; e.x[0] += dt * e.x[1]; }
     }
     // ---- _get_observation: env.state (obs itself is written by the caller, it may be replaced on reset)
@@ -296,7 +382,17 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
     if constexpr (KIND == SCG_QUAD_3D) { ang[0] = e.x[9]; ang[1] = e.x[10]; ang[2] = e.x[11]; }
     else if constexpr (KIND == SCG_QUAD_2D) { ang[0] = real(0); ang[1] = e.x[5]; ang[2] = real(0); }
     else { ang[0] = ang[1] = ang[2] = real(0); }
-    make_state<KIND, real>(e, ang, st);
+    if constexpr (KIND == SCG_QUAD_3D) {
+        make_state<KIND, real, false>(e, ang, st);
+        st[9] = st[10] = st[11] = real(0);
+        if (full) {   // uniform: h.need_full_state or per-step outputs
+            attitude3_complete<real>(e.a3);
+            const real* R = e.a3.R;
+            st[9] = (R[0] * ang[0] + R[3] * ang[1]) + R[6] * ang[2];
+            st[10] = (R[1] * ang[0] + R[4] * ang[1]) + R[7] * ang[2];
+            st[11] = (R[2] * ang[0] + R[5] * ang[1]) + R[8] * ang[2];
+        }
+    } else make_state<KIND, real>(e, ang, st);
     // ---- _get_info (quadrotor.py:1004-1134): mse, goal hold (collision scan is dead in DYN, F5)
     real goal[NX];
     {
@@ -305,14 +401,20 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
     }
     mse = real(0);
 #pragma unroll
-    for (int d = 0; d < NX; ++d) { const real er = (st[d] - goal[d]) * h.mse_weight[d]; mse += er * er; }
+    for (int d = 0; d < NX; ++d) {
+        if (!((h.mse_mask >> d) & 1u)) continue;   // uniform; a zero weight contributes exactly 0
+        const real er = (st[d] - goal[d]) * h.mse_weight[d]; mse += er * er;
+    }
     bool gate_passed = false, at_goal = false, completed = (e.flags & SCG_FLAG_COMPLETED) != 0u;
-    uint32_t cur_gate = (e.flags >> SCG_FLAG_GATE_SHIFT) & 0xFFu;
     if constexpr (KIND == SCG_QUAD_3D) {
+        const uint32_t cur_gate = (e.flags >> SCG_FLAG_GATE_SHIFT) & 0xFFu;
         if (cur_gate == uint32_t(h.n_gates) && h.task == SCG_TASK_STABILIZATION) {   // quadrotor.py:1117-1130
             uint32_t hold = e.flags >> SCG_FLAG_HOLD_SHIFT;
             const real dx = st[0] - h.x_goal0[0], dy = st[2] - h.x_goal0[2], dz = st[4] - h.x_goal0[4];
-            if (m_sqrt(dx * dx + dy * dy + dz * dz) < h.goal_tol) { at_goal = true; hold = hold < 0xFFFFu ? hold + 1u : hold; }
+            // sqrt(d2) < tol  <=>  d2 < tol^2 up to one rounding of the square; the literal modes keep the sqrt
+            const real d2 = dx * dx + dy * dy + dz * dz;
+            const bool inside = FASTMATH ? (d2 < h.goal_tol * h.goal_tol) : (m_sqrt(d2) < h.goal_tol);
+            if (inside) { at_goal = true; hold = hold < 0xFFFFu ? hold + 1u : hold; }
             else hold = 0u;
             if (hold > uint32_t(2 * h.ctrl_freq)) completed = true;
             e.flags = (e.flags & 0xFFFFu) | (hold << SCG_FLAG_HOLD_SHIFT);
@@ -355,25 +457,29 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
         real gq[NX];   // traj tracking uses X_GOAL[t] un-clamped (quadrotor.py:924-926)
         goal_row<KIND, real>(h, cold, t, gq);
         real lx = real(0), lu = real(0);
-        if (h.quadratic_diag) {
+        if (LEAN || h.quadratic_diag) {
 #pragma unroll
             for (int d = 0; d < NX; ++d) { const real er = st[d] - gq[d]; lx += h.q_diag[d] * er * er; }
 #pragma unroll
             for (int j = 0; j < NU; ++j) { const real er = pre[j] - h.u_goal[j]; lu += h.r_diag[j] * er * er; }
         } else {
-#pragma unroll
             for (int a = 0; a < NX; ++a) {
                 real row = real(0);
 #pragma unroll
                 for (int c = 0; c < NX; ++c) row += cold->Q[a * SCG_MAX_NX + c] * (st[c] - gq[c]);
-                lx += (st[a] - gq[a]) * row;
-            }
+                real ea = real(0);
 #pragma unroll
+                for (int c = 0; c < NX; ++c) ea = c == a ? st[c] - gq[c] : ea;
+                lx += ea * row;
+            }
             for (int a = 0; a < NU; ++a) {
                 real row = real(0);
 #pragma unroll
                 for (int c = 0; c < NU; ++c) row += cold->R[a * SCG_MAX_NU + c] * (pre[c] - h.u_goal[c]);
-                lu += (pre[a] - h.u_goal[a]) * row;
+                real ea = real(0);
+#pragma unroll
+                for (int c = 0; c < NU; ++c) ea = c == a ? pre[c] - h.u_goal[c] : ea;
+                lu += ea * row;
             }
         }
         reward = -(real(0.5) * lx + real(0.5) * lu);
@@ -387,12 +493,12 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
     e.t = t + 1;
     if (h.n_rows > 0) {
         bool violated, almost;
-        eval_constraints<KIND, real>(h, cold, st, raw, false, c_out, n, i, violated, almost);
+        eval_constraints<KIND, real, LEAN>(h, cold, st, raw, false, c_out, n, i, violated, almost);
         if (violated) {
             e.flags |= SCG_FLAG_CNSTR_VIOLATION; info |= SCG_INFO_VIOLATION;
             if (h.done_on_violation) done = true;
         } else e.flags &= ~SCG_FLAG_CNSTR_VIOLATION;
-        if (h.cost == SCG_COST_RL_REWARD && h.use_constraint_penalty && almost) reward += h.constraint_penalty;
+        if (!LEAN && h.cost == SCG_COST_RL_REWARD && h.use_constraint_penalty && almost) reward += h.constraint_penalty;
     }
     if (e.t >= h.ctrl_steps) {
         if (!done) info |= SCG_INFO_TRUNCATED;
@@ -400,22 +506,109 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
     }
 }
 
-template <typename T> SCG_DEV T warp_sum(T v) {
+SCG_DEV float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     return v;
 }
 
-// MODE 0: reset (mask optional)   MODE 1: K fused control steps (scg_step is K = 1 with outputs)
-template <int KIND, typename real, int ATT, int MODE>
-__global__ void __launch_bounds__(128)
-k_env(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, const Buf<real> b,
-      const Roll<real> ro, const ResetInject<real> inj, const uint8_t* __restrict__ mask) {
+// the Logger record (Logger.py:50-66): pos3 vel3 rpy3 ang_vel3 rpm4, [16][n] per logged step
+template <int KIND, typename real>
+SCG_DEV void write_log(const EnvRegs<KIND, real>& e, const Motors<real>& mot, real* __restrict__ L, int64_t n) {
+    real rec[16];
+    if constexpr (KIND == SCG_QUAD_3D) {
+        rec[0] = e.x[0]; rec[1] = e.x[2]; rec[2] = e.x[4]; rec[3] = e.x[1]; rec[4] = e.x[3]; rec[5] = e.x[5];
+        rec[6] = e.a3.rpy[0]; rec[7] = e.a3.rpy[1]; rec[8] = e.a3.rpy[2];
+        rec[9] = e.x[9]; rec[10] = e.x[10]; rec[11] = e.x[11];
+    } else if constexpr (KIND == SCG_QUAD_2D) {
+        rec[0] = e.x[0]; rec[1] = 0; rec[2] = e.x[2]; rec[3] = e.x[1]; rec[4] = 0; rec[5] = e.x[3];
+        rec[6] = 0; rec[7] = e.a2.theta; rec[8] = 0; rec[9] = 0; rec[10] = e.x[5]; rec[11] = 0;
+    } else if constexpr (KIND == SCG_CARTPOLE) {
+        rec[0] = e.x[0]; rec[1] = 0; rec[2] = 0; rec[3] = e.x[1]; rec[4] = 0; rec[5] = 0;
+        rec[6] = 0; rec[7] = e.x[2]; rec[8] = 0; rec[9] = 0; rec[10] = e.x[3]; rec[11] = 0;
+    } else {
+        rec[0] = 0; rec[1] = 0; rec[2] = e.x[0]; rec[3] = 0; rec[4] = 0; rec[5] = e.x[1];
+        rec[6] = rec[7] = rec[8] = rec[9] = rec[10] = rec[11] = 0;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) rec[12 + j] = mot.rpm[j];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) L[int64_t(j) * n] = rec[j];
+}
+
+template <int NU, typename real> struct ActVec;
+template <> struct ActVec<4, float> { using type = float4; };
+template <> struct ActVec<2, float> { using type = float2; };
+template <> struct ActVec<1, float> { using type = float; };
+template <> struct ActVec<4, double> { using type = double4; };
+template <> struct ActVec<2, double> { using type = double2; };
+template <> struct ActVec<1, double> { using type = double; };
+
+// one vector load per env-step: the action row of env i ([n][nu] env-major, 16 B for 3D fp32)
+template <int NU, typename real> SCG_DEV void load_action(const real* __restrict__ p, real (&a)[NU]) {
+    using V = typename ActVec<NU, real>::type;
+    if constexpr (NU == 4 && sizeof(real) == 8) {   // 32-byte rows: two 16-byte loads
+        const double2 lo = __ldg(reinterpret_cast<const double2*>(p)), hi = __ldg(reinterpret_cast<const double2*>(p) + 1);
+        a[0] = lo.x; a[1] = lo.y; a[2] = hi.x; a[3] = hi.y;
+    } else {
+        const V v = __ldg(reinterpret_cast<const V*>(p));
+        const real* q = reinterpret_cast<const real*>(&v);
+#pragma unroll
+        for (int j = 0; j < NU; ++j) a[j] = q[j];
+    }
+}
+
+constexpr int ENV_BLOCK = 64;   // 65,536 envs -> 1,024 blocks: 6.9 per SM, within 1.2 % of an even split over 148 SMs
+
+// MODE 0: reset (mask optional)
+template <int KIND, typename real, int ATT>
+__global__ void __launch_bounds__(ENV_BLOCK)
+k_reset(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, const Buf<real> b,
+        const ResetInject<real> inj, const uint8_t* __restrict__ mask) {
+    constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
+    const int64_t n = b.n;
+    const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n || (mask != nullptr && mask[i] == 0)) return;
+    const RngKey key{h.seed, h.env_id_base_lo + uint32_t(i)};
+    EnvRegs<KIND, real> e;
+#pragma unroll
+    for (int d = 0; d < NX; ++d) e.x[d] = b.state[int64_t(d) * n + i];
+    e.t = b.ctrl_step[i];
+    e.resets = b.episode[i];
+    e.flags = b.flags[i];
+    real st[NX];
+    reset_env_body<KIND, real, ATT>(h, cold, b, inj, key, n, i, e, st);
+#pragma unroll
+    for (int d = 0; d < NX; ++d) b.state[int64_t(d) * n + i] = e.x[d];
+    b.ctrl_step[i] = e.t; b.episode[i] = e.resets; b.flags[i] = e.flags;
+    if (b.env_state) {
+#pragma unroll
+        for (int d = 0; d < NX; ++d) b.env_state[int64_t(d) * n + i] = st[d];
+    }
+    write_obs<KIND, real>(h, cold, b.dist_offset, b.obs, st, 0, 0u, key, h.reseed_on_reset ? 0u : uint32_t(e.resets - 1), n, i);
+    if (b.ep_return) b.ep_return[i] = real(0);
+    if (b.ep_length) b.ep_length[i] = 0;
+    if (b.ep_violations) b.ep_violations[i] = 0;
+    if (h.n_rows > 0 && b.c_values) {   // after_reset: state constraints only (benchmark_env.py:376-383)
+        bool v, a;
+        real raw0[NU];
+#pragma unroll
+        for (int j = 0; j < NU; ++j) raw0[j] = real(0);
+        eval_constraints<KIND, real, false>(h, cold, st, raw0, true, b.c_values, n, i, v, a);
+    }
+}
+
+// K fused control steps (scg_step is K = 1 with the per-step outputs)
+template <int KIND, typename real, int ATT, bool LEAN>
+__global__ void __launch_bounds__(ENV_BLOCK)
+k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, const Buf<real> b, const Roll<real> ro) {
     constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
     const int64_t n = b.n;
     const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
     const bool valid = i < n;
-    const int64_t ii = valid ? i : n - 1;   // out-of-range lanes shadow the last env, never store
+    // out-of-range lanes shadow the last env: they compute and store the same values as its owner
+    // (benign duplicates) and only stay out of the statistics
+    const int64_t ii = valid ? i : n - 1;
     const RngKey key{h.seed, h.env_id_base_lo + uint32_t(ii)};
     EnvRegs<KIND, real> e;
 #pragma unroll
@@ -424,136 +617,103 @@ k_env(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, 
     e.resets = b.episode[ii];
     e.flags = b.flags[ii];
     real st[NX];
-    if constexpr (MODE == 0) {
-        const bool sel = valid && (mask == nullptr || mask[ii] != 0);
-        if (!sel) return;
-        reset_env<KIND, real, ATT>(h, cold, b, inj, key, n, ii, e, st);
+    load_inertia<KIND, real>(h, LEAN ? nullptr : b.inertia, n, ii, e.in);
+    derive_attitude<KIND, real, ATT>(e);
+    real ep_ret = b.ep_return ? b.ep_return[ii] : real(0);
+    int32_t ep_len = b.ep_length ? b.ep_length[ii] : 0;
+    int32_t ep_viol = b.ep_violations ? b.ep_violations[ii] : 0;
+    // per-thread statistics (reduced once at the end)
+    float s_eps = 0.f, s_ret = 0.f, s_len = 0.f, s_viol = 0.f, s_mse = 0.f, s_trunc = 0.f, s_compl = 0.f, s_vep = 0.f;
+    real reward = real(0), mse = real(0);
+    bool done = false;
+    uint32_t info = 0u;
+    Motors<real> mot;
+    const bool full = h.need_full_state != 0 || ro.step_outputs != 0;   // uniform
+    real* const c_out = ro.step_outputs ? b.c_values : nullptr;
+    // software prefetch of the next action (one 16-byte load per 3D env per step)
+    real raw[NU], nxt[NU];
+    load_action<NU, real>(ro.actions + ii * NU, nxt);
+    bool fresh = false;   // obs must come from a reset this step
+#pragma unroll 1
+    for (int k = 0; k < ro.k_steps; ++k) {
 #pragma unroll
-        for (int d = 0; d < NX; ++d) b.state[int64_t(d) * n + ii] = e.x[d];
-        b.ctrl_step[ii] = e.t; b.episode[ii] = e.resets; b.flags[ii] = e.flags;
-        if (b.env_state) {
+        for (int j = 0; j < NU; ++j) raw[j] = nxt[j];
+        if (k + 1 < ro.k_steps) load_action<NU, real>(ro.actions + (int64_t(k + 1) * n + ii) * NU, nxt);
+        step_env<KIND, real, ATT, LEAN>(h, cold, b, key, n, ii, e, raw, full, st, reward, done, info, mse, mot, c_out);
+        ep_ret += reward; ep_len += 1;
+        const bool viol = (info & SCG_INFO_VIOLATION) != 0u;
+        ep_viol += viol ? 1 : 0;
+        s_viol += viol ? 1.f : 0.f;
+        s_mse += float(mse);
+        if (ro.reward_out) ro.reward_out[int64_t(k) * n + ii] = reward;
+        if (ro.done_out) ro.done_out[int64_t(k) * n + ii] = done ? 1 : 0;
+        if (ro.log_out && (k % ro.log_stride) == 0)
+            write_log<KIND, real>(e, mot, ro.log_out + int64_t(k / ro.log_stride) * 16 * n + ii, n);
+        fresh = false;
+        if (done) {
+            s_eps += 1.f; s_ret += float(ep_ret); s_len += float(ep_len);
+            s_trunc += (info & SCG_INFO_TRUNCATED) ? 1.f : 0.f;
+            s_compl += (info & SCG_INFO_COMPLETED) ? 1.f : 0.f;
+            s_vep += ep_viol > 0 ? 1.f : 0.f;
+            if (h.auto_reset) {   // DummyVecEnv.step_wait (dummy_vec_env.py:38-49)
+                if (ro.step_outputs && b.terminal_obs) {
+                    real tl[NX];
 #pragma unroll
-            for (int d = 0; d < NX; ++d) b.env_state[int64_t(d) * n + ii] = st[d];
-        }
-        write_obs<KIND, real>(h, cold, b, b.obs, st, 0, 0u, key, h.reseed_on_reset ? 0u : uint32_t(e.resets - 1), n, ii);
-        if (b.ep_return) b.ep_return[ii] = real(0);
-        if (b.ep_length) b.ep_length[ii] = 0;
-        if (b.ep_violations) b.ep_violations[ii] = 0;
-        if (h.n_rows > 0 && b.c_values) {   // after_reset: state constraints only (benchmark_env.py:376-383)
-            bool v, a;
-            real raw0[NU];
-#pragma unroll
-            for (int j = 0; j < NU; ++j) raw0[j] = real(0);
-            eval_constraints<KIND, real>(h, cold, st, raw0, true, b.c_values, n, ii, v, a);
-        }
-        return;
-    } else {
-        load_inertia<KIND, real>(h, b.inertia, n, ii, e.in);
-        derive_attitude<KIND, real, ATT>(e);
-        real ep_ret = b.ep_return ? b.ep_return[ii] : real(0);
-        int32_t ep_len = b.ep_length ? b.ep_length[ii] : 0;
-        int32_t ep_viol = b.ep_violations ? b.ep_violations[ii] : 0;
-        // per-thread statistics (reduced once at the end)
-        float s_eps = 0.f, s_ret = 0.f, s_len = 0.f, s_viol = 0.f, s_mse = 0.f, s_trunc = 0.f, s_compl = 0.f, s_vep = 0.f;
-        real reward = real(0), mse = real(0);
-        bool done = false;
-        uint32_t info = 0u;
-        Motors<real> mot;
-        // software prefetch of the next action (one 16-byte load per 3D env per step)
-        real raw[NU], nxt[NU];
-        const real* ap = ro.actions + ii * NU;
-#pragma unroll
-        for (int j = 0; j < NU; ++j) nxt[j] = ap[j];
-        bool fresh = false;   // obs must come from a reset this step
-        for (int k = 0; k < ro.k_steps; ++k) {
-#pragma unroll
-            for (int j = 0; j < NU; ++j) raw[j] = nxt[j];
-            if (k + 1 < ro.k_steps) {
-                const real* an = ro.actions + (int64_t(k + 1) * n + ii) * NU;
-#pragma unroll
-                for (int j = 0; j < NU; ++j) nxt[j] = an[j];
-            }
-            real* c_out = (ro.step_outputs && valid) ? b.c_values : nullptr;
-            step_env<KIND, real, ATT>(h, cold, b, key, n, ii, e, raw, st, reward, done, info, mse, mot, c_out);
-            ep_ret += reward; ep_len += 1; ep_viol += (info & SCG_INFO_VIOLATION) ? 1 : 0;
-            s_viol += (info & SCG_INFO_VIOLATION) ? 1.f : 0.f;
-            s_mse += float(mse);
-            if (valid) {
-                if (ro.reward_out) ro.reward_out[int64_t(k) * n + ii] = reward;
-                if (ro.done_out) ro.done_out[int64_t(k) * n + ii] = done ? 1 : 0;
-                if (ro.log_out && (k % ro.log_stride) == 0) {   // Logger.py:50-66 record
-                    real* L = ro.log_out + int64_t(k / ro.log_stride) * 16 * n + ii;
-                    real rec[16];
-                    if constexpr (KIND == SCG_QUAD_3D) {
-                        rec[0] = e.x[0]; rec[1] = e.x[2]; rec[2] = e.x[4]; rec[3] = e.x[1]; rec[4] = e.x[3]; rec[5] = e.x[5];
-                        rec[6] = e.a3.rpy[0]; rec[7] = e.a3.rpy[1]; rec[8] = e.a3.rpy[2];
-                        rec[9] = e.x[9]; rec[10] = e.x[10]; rec[11] = e.x[11];
-                    } else if constexpr (KIND == SCG_QUAD_2D) {
-                        rec[0] = e.x[0]; rec[1] = 0; rec[2] = e.x[2]; rec[3] = e.x[1]; rec[4] = 0; rec[5] = e.x[3];
-                        rec[6] = 0; rec[7] = e.a2.theta; rec[8] = 0; rec[9] = 0; rec[10] = e.x[5]; rec[11] = 0;
-                    } else if constexpr (KIND == SCG_CARTPOLE) {
-                        rec[0] = e.x[0]; rec[1] = 0; rec[2] = 0; rec[3] = e.x[1]; rec[4] = 0; rec[5] = 0;
-                        rec[6] = 0; rec[7] = e.x[2]; rec[8] = 0; rec[9] = 0; rec[10] = e.x[3]; rec[11] = 0;
-                    } else {
-                        rec[0] = 0; rec[1] = 0; rec[2] = e.x[0]; rec[3] = 0; rec[4] = 0; rec[5] = e.x[1];
-                        rec[6] = rec[7] = rec[8] = rec[9] = rec[10] = rec[11] = 0;
-                    }
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) rec[12 + j] = mot.rpm[j];
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) L[int64_t(j) * n] = rec[j];
+                    for (int d = 0; d < NX; ++d) tl[d] = st[d];
+                    write_obs<KIND, real>(h, cold, b.dist_offset, b.terminal_obs, tl, e.t - 1, uint32_t(e.t), key,
+                                          h.reseed_on_reset ? 0u : uint32_t(e.resets - 1), n, ii);
                 }
-            }
-            fresh = false;
-            if (done) {
-                s_eps += 1.f; s_ret += float(ep_ret); s_len += float(ep_len);
-                s_trunc += (info & SCG_INFO_TRUNCATED) ? 1.f : 0.f;
-                s_compl += (info & SCG_INFO_COMPLETED) ? 1.f : 0.f;
-                s_vep += ep_viol > 0 ? 1.f : 0.f;
-                if (h.auto_reset) {   // DummyVecEnv.step_wait (dummy_vec_env.py:38-49)
-                    if (ro.step_outputs && valid && b.terminal_obs)
-                        write_obs<KIND, real>(h, cold, b, b.terminal_obs, st, e.t - 1, uint32_t(e.t), key,
-                                              h.reseed_on_reset ? 0u : uint32_t(e.resets - 1), n, ii);
-                    const ResetInject<real> none{nullptr, nullptr, nullptr};
-                    reset_env<KIND, real, ATT>(h, cold, b, none, key, n, ii, e, st);
-                    ep_ret = real(0); ep_len = 0; ep_viol = 0;
-                    fresh = true;
+                if constexpr (LEAN) reset_env_lean<KIND, real, ATT>(h, key, e, st);
+                else {
+                    EnvRegs<KIND, real> ec = e;
+                    real sn[NX];
+                    reset_env_cold<KIND, real, ATT>(h, cold, b, key, n, ii, &ec, sn);
+                    e = ec;
+#pragma unroll
+                    for (int d = 0; d < NX; ++d) st[d] = sn[d];
                 }
+                ep_ret = real(0); ep_len = 0; ep_viol = 0;
+                fresh = true;
             }
         }
-        if (valid) {
-#pragma unroll
-            for (int d = 0; d < NX; ++d) b.state[int64_t(d) * n + ii] = e.x[d];
-            b.ctrl_step[ii] = e.t; b.episode[ii] = e.resets; b.flags[ii] = e.flags;
-            if (b.env_state) {
-#pragma unroll
-                for (int d = 0; d < NX; ++d) b.env_state[int64_t(d) * n + ii] = st[d];
-            }
-            const uint32_t ep = h.reseed_on_reset ? 0u : uint32_t(e.resets - 1);
-            if (fresh) write_obs<KIND, real>(h, cold, b, b.obs, st, 0, 0u, key, ep, n, ii);
-            else write_obs<KIND, real>(h, cold, b, b.obs, st, e.t - 1, uint32_t(e.t), key, ep, n, ii);
-            b.reward[ii] = reward; b.done[ii] = done ? 1 : 0; b.info[ii] = uint8_t(info);
-            if (b.mse) b.mse[ii] = mse;
-            if (b.ep_return) b.ep_return[ii] = ep_ret;
-            if (b.ep_length) b.ep_length[ii] = ep_len;
-            if (b.ep_violations) b.ep_violations[ii] = ep_viol;
+    }
+    if constexpr (KIND == SCG_QUAD_3D) {
+        if (!full && !fresh) {   // the final observation needs p, q, r
+            attitude3_complete<real>(e.a3);
+            const real* R = e.a3.R;
+            st[9] = (R[0] * e.x[9] + R[3] * e.x[10]) + R[6] * e.x[11];
+            st[10] = (R[1] * e.x[9] + R[4] * e.x[10]) + R[7] * e.x[11];
+            st[11] = (R[2] * e.x[9] + R[5] * e.x[10]) + R[8] * e.x[11];
         }
-        if (b.stats) {   // warp-shuffle reduction, one atomic per warp per statistic
-            const float steps = valid ? float(ro.k_steps) : 0.f;
-            float v[8] = {s_eps, s_ret, s_len, s_viol, s_mse, s_trunc, s_compl, s_vep};
-            if (!valid) {
+    }
 #pragma unroll
-                for (int j = 0; j < 8; ++j) v[j] = 0.f;
-            }
-            const int slot[8] = {SCG_STAT_EPISODES, SCG_STAT_RETURN, SCG_STAT_LENGTH, SCG_STAT_VIOLATION_STEPS,
-                                 SCG_STAT_MSE, SCG_STAT_TRUNCATED, SCG_STAT_COMPLETED, SCG_STAT_VIOLATED_EPISODES};
+    for (int d = 0; d < NX; ++d) b.state[int64_t(d) * n + ii] = e.x[d];
+    b.ctrl_step[ii] = e.t; b.episode[ii] = e.resets; b.flags[ii] = e.flags;
+    if (b.env_state) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const double r = warp_sum<double>(double(v[j]));
-                if ((threadIdx.x & 31) == 0 && r != 0.0) atomicAdd(b.stats + slot[j], r);
-            }
-            const double rs = warp_sum<double>(double(steps));
-            if ((threadIdx.x & 31) == 0) atomicAdd(b.stats + SCG_STAT_ENV_STEPS, rs);
+        for (int d = 0; d < NX; ++d) b.env_state[int64_t(d) * n + ii] = st[d];
+    }
+    {
+        const uint32_t ep = h.reseed_on_reset ? 0u : uint32_t(e.resets - 1);
+        real fl[NX];
+#pragma unroll
+        for (int d = 0; d < NX; ++d) fl[d] = st[d];
+        write_obs<KIND, real>(h, cold, b.dist_offset, b.obs, fl, fresh ? 0 : e.t - 1, fresh ? 0u : uint32_t(e.t), key, ep, n, ii);
+    }
+    b.reward[ii] = reward; b.done[ii] = done ? 1 : 0; b.info[ii] = uint8_t(info);
+    if (b.mse) b.mse[ii] = mse;
+    if (b.ep_return) b.ep_return[ii] = ep_ret;
+    if (b.ep_length) b.ep_length[ii] = ep_len;
+    if (b.ep_violations) b.ep_violations[ii] = ep_viol;
+    if (b.stats) {   // warp-shuffle reduction, one atomic per warp per statistic
+        const float steps = valid ? float(ro.k_steps) : 0.f;
+        float v[9] = {s_eps, s_ret, s_len, s_viol, s_mse, s_trunc, s_compl, s_vep, steps};
+        const int slot[9] = {SCG_STAT_EPISODES, SCG_STAT_RETURN, SCG_STAT_LENGTH, SCG_STAT_VIOLATION_STEPS,
+                             SCG_STAT_MSE, SCG_STAT_TRUNCATED, SCG_STAT_COMPLETED, SCG_STAT_VIOLATED_EPISODES, SCG_STAT_ENV_STEPS};
+#pragma unroll
+        for (int j = 0; j < 9; ++j) {
+            const float r = warp_sum(valid ? v[j] : 0.f);
+            if ((threadIdx.x & 31) == 0 && r != 0.f) atomicAdd(b.stats + slot[j], double(r));
         }
     }
 }
