@@ -133,7 +133,7 @@ def run(name, spec, Quadrotor):
     kwargs = {k: v for k, v in cfg.items()}
     ref_stubs.DRAW_LOG.clear()
     env = Quadrotor(**kwargs)
-    ev = {k: [] for k in ["type", "obs", "rew", "done", "viol", "trunc", "mse", "cvals", "state", "kin", "ndraw"]}
+    ev = {k: [] for k in ["type", "obs", "rew", "done", "viol", "trunc", "mse", "cvals", "state", "kin", "quat", "ndraw"]}
     nc = env.num_constraints
 
     def record(kind, obs, rew, done, info):
@@ -151,6 +151,7 @@ def run(name, spec, Quadrotor):
         ev["cvals"].append(c)
         ev["state"].append(np.asarray(env.state, dtype=np.float64))
         ev["kin"].append(np.hstack([env.pos[0], env.vel[0], env.rpy[0], env.rpy_rates[0]]))
+        ev["quat"].append(np.array(env.quat[0], dtype=np.float64, copy=True))   # the attitude PyBullet holds (x, y, z, w)
         ev["ndraw"].append(len(ref_stubs.DRAW_LOG))
 
     def do_reset():

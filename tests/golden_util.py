@@ -125,11 +125,27 @@ def cuda_step(env, cur, action, adv=None):
     return env.step(np.repeat(np.asarray(action, dtype=np.float64)[None, :], n, axis=0))
 
 
-def force_state(env, kin, ctrl_step, prev_violation, n_resets):
+def _pre_angles_from_quat(q):
+    """Euler angles whose quatFromEuler() is the stored quaternion (x, y, z, w): the general
+    getEulerFromQuaternion formulas WITHOUT the gimbal-band snap.  The kernel keeps the
+    pre-round-trip angles as its attitude state, PyBullet keeps the quaternion; inside the band the
+    snapped rpy of the golden record no longer determines the rotation, the quaternion does."""
+    x, y, z, w = (float(v) for v in q)
+    sarg = max(-1.0, min(1.0, -2.0 * (x * z - w * y)))
+    roll = np.arctan2(2 * (y * z + w * x), w * w - x * x - y * y + z * z)
+    yaw = np.arctan2(2 * (x * y + w * z), w * w + x * x - y * y - z * z)
+    return roll, np.arcsin(sarg), yaw
+
+
+def force_state(env, kin, ctrl_step, prev_violation, n_resets, quat=None):
     """Teacher forcing: overwrite the kernel's internal state with the golden kinematics
-    (pos3, vel3, rpy3, rpy_rates3) of the previous event."""
+    (pos3, vel3, attitude, rpy_rates3) of the previous event."""
     import torch
     pos, vel, rpy, rates = kin[0:3], kin[3:6], kin[6:9], kin[9:12]
+    if quat is not None and env.QUAD_TYPE == 3:
+        rpy = _pre_angles_from_quat(quat)
+    elif quat is not None and env.QUAD_TYPE == 2:
+        rpy = (0.0, 2.0 * np.arctan2(float(quat[1]), float(quat[3])), 0.0)   # physical pitch, "flipped" bit clear
     if env.QUAD_TYPE == 3:
         x = [pos[0], vel[0], pos[1], vel[1], pos[2], vel[2], rpy[0], rpy[1], rpy[2], rates[0], rates[1], rates[2]]
     elif env.QUAD_TYPE == 2:
