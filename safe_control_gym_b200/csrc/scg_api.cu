@@ -200,10 +200,33 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
     bool symmetric = false;
     for (int q = 0; q < nb; ++q) symmetric |= h.bounded[q].symmetric != 0;
     h.need_cold_constraints = (nd > 0 || h.any_tolerance || symmetric) ? 1 : 0;
+    // merged violation box: any(c_k > thr) == (max_k c_k > thr) when every bounded constraint shares one strictness
+    bool same_strict = true;
+    for (int d = 0; d < SCG_MAX_NX; ++d) { h.box_lo[d] = -INF; h.box_hi[d] = INF; }
+    for (int d = 0; d < SCG_MAX_NU; ++d) { h.ubox_lo[d] = -INF; h.ubox_hi[d] = INF; }
+    for (int q = 0; q < nb; ++q) {
+        const BoundedCon<real>& bc = h.bounded[q];
+        if (bc.strict != h.bounded[0].strict) same_strict = false;
+        if (bc.symmetric) continue;
+        const int full = bc.var == SCG_VAR_STATE ? nx : nu;
+        for (int d = 0; d < full; ++d) {
+            if (!((bc.mask >> d) & 1u)) continue;
+            if (bc.var == SCG_VAR_STATE) {
+                h.box_mask |= 1u << d;
+                if (bc.lo[d] > h.box_lo[d]) h.box_lo[d] = bc.lo[d];
+                if (bc.hi[d] < h.box_hi[d]) h.box_hi[d] = bc.hi[d];
+            } else {
+                h.ubox_mask |= 1u << d;
+                if (bc.lo[d] > h.ubox_lo[d]) h.ubox_lo[d] = bc.lo[d];
+                if (bc.hi[d] < h.ubox_hi[d]) h.ubox_hi[d] = bc.hi[d];
+            }
+        }
+    }
+    h.box_thr = (nb > 0 && h.bounded[0].strict) ? std::nextafter(real(-0.5), -INF) : real(0.5);
     // (the extended observation lives in write_obs, outside the loop)
     *lean_out = c.n_dist[0] == 0 && c.n_dist[1] == 0 && c.n_dist[2] == 0 && c.adversary_channel < 0 && !c.dyn_applies_force &&
                 !(h.any_init_rand & 2) && !h.any_inertia_rand &&
-                !c.dyn_uses_episode_inertia && nd == 0 && !h.any_tolerance && !symmetric && h.quadratic_diag && !c.gate_geometry &&
+                !c.dyn_uses_episode_inertia && nd == 0 && !h.any_tolerance && !symmetric && same_strict && h.quadratic_diag && !c.gate_geometry &&
                 !(c.env_kind == SCG_CARTPOLE && (h.any_inertia_rand != 0));
     return SCG_OK;
 }

@@ -345,19 +345,37 @@ SCG_DEV void eval_constraints(const Hot<real>& h, const Cold<real>* __restrict__
         constraint_values_cold<KIND, real>(h, cold, sl, rl, state_only, c_out, n, i, &violated, &almost);
         return;
     }
-    for (int k = 0; k < h.n_bounded; ++k) {
-        const BoundedCon<real>& bc = h.bounded[k];
-        if (bc.var == SCG_VAR_STATE) {
+    if constexpr (LEAN) {
+        // one merged box: violated <=> the largest c = max(lo - x, x - hi) over all bounded dims rounds above 0
+        real worst = -INFINITY;
 #pragma unroll
-            for (int d = 0; d < NX; ++d) {
-                if (!((bc.mask >> d) & 1u)) continue;   // uniform
-                violated |= viol_test(bc.lo[d] - st[d], bc.strict) | viol_test(st[d] - bc.hi[d], bc.strict);
-            }
-        } else if (!state_only) {
+        for (int d = 0; d < NX; ++d) {
+            if (!((h.box_mask >> d) & 1u)) continue;   // uniform
+            worst = m_max(worst, m_max(h.box_lo[d] - st[d], st[d] - h.box_hi[d]));
+        }
+        if (!state_only) {
 #pragma unroll
             for (int d = 0; d < NU; ++d) {
-                if (!((bc.mask >> d) & 1u)) continue;
-                violated |= viol_test(bc.lo[d] - raw[d], bc.strict) | viol_test(raw[d] - bc.hi[d], bc.strict);
+                if (!((h.ubox_mask >> d) & 1u)) continue;
+                worst = m_max(worst, m_max(h.ubox_lo[d] - raw[d], raw[d] - h.ubox_hi[d]));
+            }
+        }
+        violated = worst * real(1e8) > h.box_thr;
+    } else {
+        for (int k = 0; k < h.n_bounded; ++k) {
+            const BoundedCon<real>& bc = h.bounded[k];
+            if (bc.var == SCG_VAR_STATE) {
+#pragma unroll
+                for (int d = 0; d < NX; ++d) {
+                    if (!((bc.mask >> d) & 1u)) continue;   // uniform
+                    violated |= viol_test(bc.lo[d] - st[d], bc.strict) | viol_test(st[d] - bc.hi[d], bc.strict);
+                }
+            } else if (!state_only) {
+#pragma unroll
+                for (int d = 0; d < NU; ++d) {
+                    if (!((bc.mask >> d) & 1u)) continue;
+                    violated |= viol_test(bc.lo[d] - raw[d], bc.strict) | viol_test(raw[d] - bc.hi[d], bc.strict);
+                }
             }
         }
     }

@@ -57,6 +57,10 @@ template <typename real> struct Hot {
     int32_t need_cold_constraints;  // tolerances, symmetric or dense rows: the flags alone need constraint_values_cold
     BoundedCon<real> bounded[MAX_BOUNDED];
     real viol_thr;                  // fp32: 5e-9 (== round(c, 8) > 0 in exact arithmetic)
+    // LEAN configs: all bounded constraints merged into one box per state / input dim (violation flag only)
+    real box_lo[SCG_MAX_NX], box_hi[SCG_MAX_NX], ubox_lo[SCG_MAX_NU], ubox_hi[SCG_MAX_NU];
+    uint32_t box_mask, ubox_mask;   // dims that carry a bound
+    real box_thr;                   // violated <=> max_k(c_k) * 1e8 > box_thr (0.5, or just below -0.5 when strict)
     // feature switches (uniform branches)
     int32_t n_dist_obs, n_dist_act, n_dist_dyn, adversary_channel;
     int32_t n_gates, gate_geometry, dyn_uses_episode_inertia, dyn_applies_force, auto_reset;

@@ -216,18 +216,17 @@ SCG_DEV void reset_env_body(const Hot<real>& h, const Cold<real>* __restrict__ c
     make_state<KIND, real>(e, ang, st);
 }
 
-// Auto-reset of a LEAN config, inline in the rollout loop: no disturbance offsets, no inertia draws,
-// uniform-only initial-state randomisation (host-checked in scg_create).  With short episodes a warp
-// enters this path on a large share of its steps (48 % at 2 % resets per env-step), so it is kept to
-// the Philox blocks that hold a randomised label plus one attitude evaluation.
-template <int KIND, typename real, int ATT>
-SCG_DEV void reset_env_lean(const Hot<real>& h, const RngKey& key, EnvRegs<KIND, real>& e, real (&st)[Dims<KIND>::NX]) {
+// Auto-reset of a LEAN config (no disturbance offsets, no inertia draws, uniform-only initial-state
+// randomisation: host-checked in scg_create) is split in two so that the Philox work does not run
+// one lane at a time.  With short episodes a warp sees a reset on a large share of its steps (48 %
+// at 2 % resets per env-step):
+//   draw_init_lean    the initial state of episode `ep` (counter-based: it can be drawn at any time),
+//                     executed by all lanes that miss a spare at a fixed cadence of the loop;
+//   reset_from_spare  what the finished lanes do on the spot: take the spare, restart counters,
+//                     evaluate the attitude (env.state is rebuilt later, only if it is observed).
+template <int KIND, typename real>
+SCG_DEV void draw_init_lean(const Hot<real>& h, const RngKey& key, uint32_t ep, real (&init)[Dims<KIND>::NX]) {
     constexpr int NX = Dims<KIND>::NX;
-    const uint32_t ep = h.reseed_on_reset ? 0u : uint32_t(e.resets);
-    e.resets += 1;
-    e.t = 0;
-    e.flags &= SCG_FLAG_CNSTR_VIOLATION;   // cnstr_violation survives reset (benchmark_env.py:218)
-    real init[NX];
 #pragma unroll
     for (int d = 0; d < NX; ++d) init[d] = h.init_state[d];
 #pragma unroll
@@ -240,17 +239,24 @@ SCG_DEV void reset_env_lean(const Hot<real>& h, const RngKey& key, EnvRegs<KIND,
             if (d < NX) init[d] += h.init_rand[d].a + (h.init_rand[d].b - h.init_rand[d].a) * u01<real>(word_of(w, j));
         }
     }
-    real ang[3] = {real(0), real(0), real(0)};
+}
+
+template <int KIND, typename real, int ATT>
+SCG_DEV void reset_from_spare(const real (&init)[Dims<KIND>::NX], EnvRegs<KIND, real>& e, real (&ang0)[3]) {
+    e.resets += 1;
+    e.t = 0;
+    e.flags &= SCG_FLAG_CNSTR_VIOLATION;   // cnstr_violation survives reset (benchmark_env.py:218)
+    ang0[0] = ang0[1] = ang0[2] = real(0);
     if constexpr (KIND == SCG_QUAD_3D) {
 #pragma unroll
         for (int d = 0; d < 9; ++d) e.x[d] = init[d];
         e.x[9] = e.x[10] = e.x[11] = real(0);          // rpy_rates restart at 0 (base_aviary.py:232-233)
-        ang[0] = init[9]; ang[1] = init[10]; ang[2] = init[11];   // INIT_ANG_VEL lives in PyBullet only
+        ang0[0] = init[9]; ang0[1] = init[10]; ang0[2] = init[11];   // INIT_ANG_VEL lives in PyBullet only
     } else if constexpr (KIND == SCG_QUAD_2D) {
 #pragma unroll
         for (int d = 0; d < 5; ++d) e.x[d] = init[d];
         e.x[5] = real(0);
-        ang[1] = init[5];
+        ang0[1] = init[5];
     } else if constexpr (KIND == SCG_CARTPOLE) {
 #pragma unroll
         for (int d = 0; d < 4; ++d) e.x[d] = init[d];
@@ -258,7 +264,6 @@ SCG_DEV void reset_env_lean(const Hot<real>& h, const RngKey& key, EnvRegs<KIND,
         e.x[0] = real(0); e.x[1] = real(0);
     }
     derive_attitude<KIND, real, ATT>(e);
-    make_state<KIND, real>(e, ang, st);
 }
 
 // The auto-reset inside the rollout loop: one out-of-line copy, entered by the lanes whose episode
@@ -634,6 +639,11 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     real raw[NU], nxt[NU];
     load_action<NU, real>(ro.actions + ii * NU, nxt);
     bool fresh = false;   // obs must come from a reset this step
+    // LEAN: spare initial state for the next episode (drawn ahead, see draw_init_lean) and the
+    // PyBullet-side INIT_ANG_VEL of the current one
+    real spare[LEAN ? NX : 1], ang0[3] = {real(0), real(0), real(0)};
+    bool spare_ok = false;
+    const bool ahead = ro.k_steps >= 16;   // uniform: host-driven single steps draw on demand only
 #pragma unroll 1
     for (int k = 0; k < ro.k_steps; ++k) {
 #pragma unroll
@@ -663,8 +673,7 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
                     write_obs<KIND, real>(h, cold, b.dist_offset, b.terminal_obs, tl, e.t - 1, uint32_t(e.t), key,
                                           h.reseed_on_reset ? 0u : uint32_t(e.resets - 1), n, ii);
                 }
-                if constexpr (LEAN) reset_env_lean<KIND, real, ATT>(h, key, e, st);
-                else {
+                if constexpr (!LEAN) {
                     EnvRegs<KIND, real> ec = e;
                     real sn[NX];
                     reset_env_cold<KIND, real, ATT>(h, cold, b, key, n, ii, &ec, sn);
@@ -676,6 +685,22 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
                 fresh = true;
             }
         }
+        if constexpr (LEAN) {
+            const bool restart = done && h.auto_reset != 0;
+            // one inline copy of the draw: at the cadence every lane that used its spare refills it together;
+            // a lane that ends two episodes inside one period draws on the spot
+            if (!spare_ok && (restart || (ahead && (k & 15) == 0))) {
+                draw_init_lean<KIND, real>(h, key, h.reseed_on_reset ? 0u : uint32_t(e.resets), spare);
+                spare_ok = true;
+            }
+            if (restart) {
+                reset_from_spare<KIND, real, ATT>(spare, e, ang0);
+                spare_ok = false;
+            }
+        }
+    }
+    if constexpr (LEAN) {
+        if (fresh) make_state<KIND, real>(e, ang0, st);   // env.state of the fresh episode, observed below
     }
     if constexpr (KIND == SCG_QUAD_3D) {
         if (!full && !fresh) {   // the final observation needs p, q, r
