@@ -229,7 +229,7 @@ def run_gpu(args):
         if world > 1:
             dist.destroy_process_group()
         return
-    # ---- roofline of the dominant kernel (k_env<3, float, FAST, rollout>): one launch per step
+    # ---- roofline of the dominant kernel (k_rollout<3, float, ATT, LEAN>): one launch per step
     peak = C.c_double()
     L.check(L.load().scg_measure_fp32_peak(C.byref(peak)))
     kernel_ms = sum(per) / len(per)   # one launch per step; stats all-reduce excluded at N = 1
@@ -257,7 +257,7 @@ def run_gpu(args):
                    "substeps": SUBSTEPS, "env_substeps_per_sec": value * SUBSTEPS, "mode": "fused rollout, auto-reset, Philox init", "attitude": args.attitude, "action_std": args.action_std,
                    "l2_policy": "inputs larger than L2 (1.05 GB action table re-streamed each step)"},
         "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": peak.value, "unit": "TFLOP/s", "frac": achieved_tf / peak.value,
-                     "traffic": traffic, "kernel": "scg::k_env<3,float,FAST,rollout>", "kernel_ms": kernel_ms,
+                     "traffic": traffic, "kernel": "scg::k_rollout<3,float,%s,LEAN>" % args.attitude, "kernel_ms": kernel_ms,
                      "flops_per_env_step": FLOPS_PER_STEP,
                      "peak_source": "measured live: register-only FFMA kernel (scg_measure_fp32_peak); MEASURED_PEAKS.json has no non-tensor fp32 figure",
                      "hbm": {"bound": "hbm", "achieved": hbm_bytes / (kernel_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
@@ -278,13 +278,13 @@ def run_gpu(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=300)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--envs", type=int, default=N_ENVS)
     ap.add_argument("--ctrl-steps", type=int, default=K_CTRL)
     ap.add_argument("--chunk", type=int, default=50)
-    ap.add_argument("--attitude", default="fast")
+    ap.add_argument("--attitude", default="fast_intrinsic", help="fast_intrinsic (MUFU sin/cos) | fast (polynomial sin/cos) | roundtrip (literal)")
     ap.add_argument("--action-std", type=float, default=0.005)
     args = ap.parse_args()
     if args.impl == "reference":

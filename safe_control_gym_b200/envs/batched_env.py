@@ -16,6 +16,44 @@ import torch
 from .. import _lib as L
 
 
+class LazyInfo(dict):
+    """The per-step ``info`` dict with the reference's keys.  The kernel writes one packed byte per env;
+    unpacking it into a dozen boolean tensors costs a dozen small launches, so each entry is built the
+    first time it is read (``info["constraint_violation"]``, ``.get``, ``.items()`` ...)."""
+
+    def __init__(self, makers):
+        super().__init__()
+        self._makers = makers
+
+    def __missing__(self, key):
+        if key not in self._makers:
+            raise KeyError(key)
+        v = self._makers[key]()
+        self[key] = v
+        return v
+
+    def __contains__(self, key):
+        return dict.__contains__(self, key) or key in self._makers
+
+    def get(self, key, default=None):
+        return self[key] if key in self else default
+
+    def keys(self):
+        return list(dict.fromkeys(list(dict.keys(self)) + list(self._makers)))
+
+    def __iter__(self):
+        return iter(self.keys())
+
+    def __len__(self):
+        return len(self.keys())
+
+    def items(self):
+        return [(k, self[k]) for k in self.keys()]
+
+    def values(self):
+        return [self[k] for k in self.keys()]
+
+
 class BatchedEnvBase:
     NAME = "base"
 
@@ -60,6 +98,7 @@ class BatchedEnvBase:
         self.buf_ep_violations = z(n, dt=torch.int32)
         self.buf_stats = z(L.STATS_LEN, dt=torch.float64)
         self._adv = None
+        self._obs_view = self.buf_obs.t()
         self._bind()
         self.initial_reset = False
         self._keep = []   # tensors referenced by in-flight launches (injection buffers)
@@ -120,22 +159,25 @@ class BatchedEnvBase:
         bits = self.buf_info
         if reset:   # after_reset: state constraints only, in YAML order (benchmark_env.py:376-383)
             return {"constraint_values": self.buf_c_values[self._state_row_idx].t()}
-        info = {"constraint_values": self.buf_c_values[:self._n_rows].t()}
-        info.update({
-            "constraint_violation": (bits & L.INFO_VIOLATION).ne(0).to(torch.int32),
-            "TimeLimit.truncated": (bits & L.INFO_TRUNCATED).ne(0),
-            "mse": self.buf_mse,
-            "collision": (bits & L.INFO_COLLISION).ne(0),
-            "stepped_through_gate": (bits & L.INFO_GATE_PASSED).ne(0),
-            "at_goal_position": (bits & L.INFO_AT_GOAL).ne(0),
-            "task_completed": (bits & L.INFO_COMPLETED).ne(0),
-            "goal_reached": (bits & L.INFO_GOAL_REACHED).ne(0),
-            "out_of_bound": (bits & L.INFO_OUT_OF_BOUND).ne(0),
-            "current_target_gate_id": (self.buf_flags >> L.FLAG_GATE_SHIFT) & 0xFF,
-            "terminal_observation": self.buf_terminal_obs.t(),
-            "state": self.buf_env_state.t(),
+
+        def bit(mask, as_int=False):
+            return (lambda: (bits & mask).ne(0).to(torch.int32)) if as_int else (lambda: (bits & mask).ne(0))
+        return LazyInfo({
+            "constraint_values": lambda: self.buf_c_values[:self._n_rows].t(),
+            "constraint_violation": bit(L.INFO_VIOLATION, True),
+            "TimeLimit.truncated": bit(L.INFO_TRUNCATED),
+            "mse": lambda: self.buf_mse,
+            "collision": bit(L.INFO_COLLISION),
+            "stepped_through_gate": bit(L.INFO_GATE_PASSED),
+            "at_goal_position": bit(L.INFO_AT_GOAL),
+            "task_completed": bit(L.INFO_COMPLETED),
+            "goal_reached": bit(L.INFO_GOAL_REACHED),
+            "out_of_bound": bit(L.INFO_OUT_OF_BOUND),
+            "current_target_gate_id": lambda: (self.buf_flags >> L.FLAG_GATE_SHIFT) & 0xFF,
+            "terminal_observation": lambda: self.buf_terminal_obs.t(),
+            "state": lambda: self.buf_env_state.t(),
+            "info_bits": lambda: bits,
         })
-        return info
 
     def reset(self, mask=None, inject_init=None, inject_inertia=None, inject_offsets=None):
         """Quadrotor.reset() for every env (or those with ``mask[i] != 0``)."""
@@ -172,12 +214,16 @@ class BatchedEnvBase:
         """Quadrotor.step(action) for the whole batch: ONE kernel launch."""
         if not self.initial_reset:
             raise RuntimeError("[ERROR] You must call env.reset() at least once before using env.step().")
-        a = self._as_real(action, (self.num_envs, self.action_dim))
+        if isinstance(action, torch.Tensor) and action.dtype == self.dtype and action.device == self.device \
+                and action.is_contiguous() and action.numel() == self.num_envs * self.action_dim:
+            a = action   # already the [N, nu] device tensor the kernel reads
+        else:
+            a = self._as_real(action, (self.num_envs, self.action_dim))
         self.current_raw_input_action = a
         with torch.cuda.device(self.device):
             L.check(self.lib.scg_step(self._h, C.c_void_p(a.data_ptr()), self._stream()))
         self._adv_consumed()
-        obs, rew, done = self.buf_obs.t(), self.buf_reward, self.buf_done.ne(0)
+        obs, rew, done = self._obs_view, self.buf_reward, self.buf_done.view(torch.bool)
         info = self._info_from_buffers()
         if self._squeeze:
             i = {k: (v[0].cpu().numpy() if v.dim() > 1 else v[0].item()) for k, v in info.items()}
