@@ -255,9 +255,18 @@ int scg_stats_read(scg_env* env, double* host_out, void* stream);
 int scg_constraints_eval(scg_env* env, const void* state, const void* action, int64_t n,
                          void* out_values, uint8_t* out_flags, void* stream);
 /* SymbolicModel.fc_func / fd (RK4, mpc_utils.py:79-101) / df_func / loss
- * (symbolic_systems.py:63-123): x [nx][n], u [nu][n]; out layout per op */
+ * (symbolic_systems.py:63-123): x [nx][n], u [nu][n].  out0 / out1 per op:
+ *   SCG_SYM_FC f [nx][n]; SCG_SYM_FD_RK4 / _EULER x_next [nx][n] over dt;
+ *   SCG_SYM_DF df/dx [nx*nx][n] (entry r*nx+c), df/du [nx*nu][n]; SCG_SYM_LOSS l [n], l_x [nx][n]
+ *   (handle's Q, R, U_GOAL, Xr = 0; scg_symbolic_loss takes them as arguments) */
 int scg_symbolic_eval(scg_env* env, int op, const void* x, const void* u, int64_t n, double dt,
                       void* out0, void* out1, void* stream);
+/* SymbolicModel.loss(x, u, Xr, Ur, Q, R) (symbolic_systems.py:114-123): xr [nx][n] / ur [nu][n] device or
+ * NULL (0 / U_GOAL); Q [nx*nx], R [nu*nu] HOST row-major or NULL (the handle's); out_l [n],
+ * out_lx [nx][n] and out_lu [nu][n] optional.  l_xx = (Q + Q')/2, l_uu = (R + R')/2, l_xu = 0 are
+ * constants the host forms itself. */
+int scg_symbolic_loss(scg_env* env, const void* x, const void* u, const void* xr, const void* ur, const double* Q,
+                      const double* R, int64_t n, void* out_l, void* out_lx, void* out_lu, void* stream);
 /* FP32 FMA microbenchmark (measurement aid, not on the path): runs a register-only FFMA kernel on the
  * current device and returns the achieved TFLOP/s (FMA = 2 flop) -- the roofline denominator for the
  * compute-bound fused rollout, since MEASURED_PEAKS.json carries no non-tensor fp32 figure. */

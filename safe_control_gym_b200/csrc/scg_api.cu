@@ -470,19 +470,36 @@ extern "C" int scg_constraints_eval(scg_env* e, const void* state, const void* a
                                   : constraints_eval_t<double>(e, state, action, n, out_values, out_flags, st);
 }
 
+static int symbolic_dispatch(scg_env* e, int op, const void* x, const void* u, const void* xr, const void* ur,
+                             const double* Q, const double* R, int64_t n, double dt, void* out0, void* out1, void* out2,
+                             cudaStream_t st) {
+    int rc = e->cfg.precision == 32
+                 ? symbolic_launch<float>(e->cfg, op, (const float*)x, (const float*)u, (const float*)xr, (const float*)ur, Q, R, n,
+                                          float(dt), (float*)out0, (float*)out1, (float*)out2, st)
+                 : symbolic_launch<double>(e->cfg, op, (const double*)x, (const double*)u, (const double*)xr, (const double*)ur, Q, R,
+                                           n, dt, (double*)out0, (double*)out1, (double*)out2, st);
+    if (rc == -2) return fail(SCG_ERR_NULL, "scg_symbolic_eval: SCG_SYM_DF needs out1 (df/du)");
+    if (rc != 0) return fail(SCG_ERR_BAD_CONFIG, "symbolic op not available for this env kind");
+    e->launches += 1;
+    CU(cudaGetLastError());
+    return SCG_OK;
+}
+
 extern "C" int scg_symbolic_eval(scg_env* e, int op, const void* x, const void* u, int64_t n, double dt, void* out0,
                                  void* out1, void* stream) {
     if (!e || !x || !u || !out0) return fail(SCG_ERR_NULL, "scg_symbolic_eval: null argument");
     if (n < 1) return fail(SCG_ERR_SHAPE, "n must be >= 1");
     if (op < SCG_SYM_FC || op > SCG_SYM_FD_EULER) return fail(SCG_ERR_BAD_CONFIG, "unknown symbolic op");
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    int rc = e->cfg.precision == 32
-                 ? symbolic_launch<float>(e->cfg, e->hf, static_cast<const Cold<float>*>(e->cold_dev), op, (const float*)x, (const float*)u, n, float(dt), (float*)out0, (float*)out1, st)
-                 : symbolic_launch<double>(e->cfg, e->hd, static_cast<const Cold<double>*>(e->cold_dev), op, (const double*)x, (const double*)u, n, dt, (double*)out0, (double*)out1, st);
-    if (rc != 0) return fail(SCG_ERR_BAD_CONFIG, "symbolic op not available for this env kind");
-    e->launches += 1;
-    CU(cudaGetLastError());
-    return SCG_OK;
+    // SCG_SYM_LOSS through this entry point: the handle's Q, R and U_GOAL, Xr = 0, out1 = l_x, no l_u
+    return symbolic_dispatch(e, op, x, u, nullptr, nullptr, nullptr, nullptr, n, dt, out0, out1, nullptr,
+                             static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int scg_symbolic_loss(scg_env* e, const void* x, const void* u, const void* xr, const void* ur, const double* Q,
+                                 const double* R, int64_t n, void* out_l, void* out_lx, void* out_lu, void* stream) {
+    if (!e || !x || !u || !out_l) return fail(SCG_ERR_NULL, "scg_symbolic_loss: null argument");
+    if (n < 1) return fail(SCG_ERR_SHAPE, "n must be >= 1");
+    return symbolic_dispatch(e, SCG_SYM_LOSS, x, u, xr, ur, Q, R, n, 0.0, out_l, out_lx, out_lu, static_cast<cudaStream_t>(stream));
 }
 
 // ---------------------------------------------------------------- fp32 peak microbenchmark

@@ -1,0 +1,149 @@
+"""Batch-level properties of the CUDA path that do not need a per-env reference: Philox-mode parity against
+the oracle on the same counter-based streams, fused rollout == host-driven stepping (bit-identical), shard
+equivalence (N envs on one GPU == two halves with global env ids), episode statistics, the Logger record, and
+determinism at BASELINE config-2 size."""
+import numpy as np
+import pytest
+import torch
+
+import bench
+from oracle.quad_oracle import PhiloxEnvDraws, QuadOracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _quad(n, dtype=torch.float32, attitude="fast", **over):
+    from safe_control_gym_b200.envs.quadrotor import BatchedQuadrotor
+    kw = bench.env_kwargs()
+    kw.update(over)
+    return BatchedQuadrotor(num_envs=n, dtype=dtype, attitude=attitude, **kw)
+
+
+def _actions(n, k, seed=3, std=0.005, dtype=torch.float32):
+    return bench.make_actions(torch, n, k, torch.device("cuda:0"), seed, std).to(dtype)
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float64, 1e-10), (torch.float32, 1e-3)])
+def test_philox_mode_matches_oracle(dtype, tol):
+    """BASELINE config 2 in small (level0 constraints, Philox init randomisation, auto-reset on violation):
+    the kernel and the numpy oracle draw from the same (seed, env id, episode) counters."""
+    n, steps, base = 64, 90, 7000
+    env = _quad(n, dtype, "fast", seed_offset=base, info_in_reset=True)
+    acts = _actions(n, steps, dtype=dtype).cpu().numpy().astype(np.float64)
+    lanes = [0, 1, 33, 63]
+    kw = bench.env_kwargs()
+    seed = kw.pop("seed")
+    refs = {i: QuadOracle(draws=PhiloxEnvDraws(seed, base + i), info_in_reset=True, **kw) for i in lanes}
+    obs, _ = env.reset()
+    for i in lanes:
+        o_obs, _ = refs[i].reset()
+        assert np.max(np.abs(obs[i].double().cpu().numpy() - o_obs)) <= tol
+    resets, worst = 0, 0.0
+    for t in range(steps):
+        obs, rew, done, info = env.step(acts[t])
+        term = info["terminal_observation"]
+        for i in lanes:
+            o_obs, o_rew, o_done, o_info = refs[i].step(acts[t, i])
+            assert bool(done[i]) == bool(o_done) and float(rew[i]) == float(o_rew), (t, i)
+            assert int(info["constraint_violation"][i]) == int(o_info["constraint_violation"])
+            got = (term if o_done else obs)[i].double().cpu().numpy()
+            err = float(np.max(np.abs(got - o_obs) / np.maximum(1.0, np.abs(o_obs))))
+            worst = max(worst, err)
+            assert err <= tol, (str(dtype), t, i, err)
+            if o_done:
+                resets += 1
+                r_obs, _ = refs[i].reset()
+                assert np.max(np.abs(obs[i].double().cpu().numpy() - r_obs)) <= tol
+    assert resets >= 2
+    print(f"philox parity {dtype}: worst {worst:.2e}, {resets} auto-resets")
+    env.close()
+
+
+@pytest.mark.parametrize("attitude", ["fast", "fast_intrinsic", "roundtrip"])
+def test_fused_rollout_equals_host_driven_steps(attitude):
+    """The K-step kernel (state in registers, spare initial states drawn ahead) and K single-step launches are
+    the same computation: bit-identical state, counters and statistics."""
+    n, k = 8192, 48
+    acts = _actions(n, k)
+    a, b = _quad(n, attitude=attitude), _quad(n, attitude=attitude)
+    a.reset(); b.reset()
+    rew = torch.empty(k, n, device="cuda"); dn = torch.empty(k, n, dtype=torch.uint8, device="cuda")
+    a.rollout(acts, reward_out=rew, done_out=dn)
+    for t in range(k):
+        _, r, d, _ = b.step(acts[t])
+        assert torch.equal(rew[t], r) and torch.equal(dn[t].bool(), d), t
+    torch.cuda.synchronize()
+    for name in ("state", "ctrl_step", "episode", "flags", "obs", "env_state", "ep_return", "ep_length"):
+        assert torch.equal(getattr(a, "buf_" + name), getattr(b, "buf_" + name)), name
+    sa, sb = a.stats(), b.stats()
+    # integer-valued statistics agree exactly; the mse sum is accumulated in fp32 per thread, so its rounding
+    # depends on how many steps one launch covers
+    assert all(sa[key] == sb[key] for key in sa if key != "mse") and abs(sa["mse"] - sb["mse"]) <= 1e-6 * sb["mse"]
+    assert sa["env_steps"] == n * k and sa["episodes"] > 0
+    # VecRecordEpisodeStatistics semantics: return / length of finished episodes
+    fin = dn.bool()
+    assert sa["episodes"] == int(fin.sum())
+    a.close(); b.close()
+
+
+def test_shard_equivalence():
+    """N envs on one GPU == N/2 + N/2 with seed_offset (global env ids): identical trajectories, summed stats."""
+    n, k = 4096, 64
+    acts = _actions(n, k)
+    whole = _quad(n)
+    lo, hi = _quad(n // 2, seed_offset=0), _quad(n // 2, seed_offset=n // 2)
+    for e in (whole, lo, hi):
+        e.reset()
+    whole.rollout(acts)
+    lo.rollout(acts[:, :n // 2].contiguous())
+    hi.rollout(acts[:, n // 2:].contiguous())
+    torch.cuda.synchronize()
+    assert torch.equal(whole.buf_state[:, :n // 2], lo.buf_state) and torch.equal(whole.buf_state[:, n // 2:], hi.buf_state)
+    assert torch.equal(whole.buf_episode[n // 2:], hi.buf_episode)
+    sw, sl, sh = whole.stats(), lo.stats(), hi.stats()
+    for key in ("episodes", "env_steps", "violation_steps", "length", "return"):
+        assert sw[key] == sl[key] + sh[key], key
+    for e in (whole, lo, hi):
+        e.close()
+
+
+def test_logged_rollout_record():
+    """log_out carries the Logger record [pos3 vel3 rpy3 ang_vel3 rpm4] (Logger.py:50-66) per env and step."""
+    n, k = 512, 20
+    acts = _actions(n, k)
+    a, b = _quad(n, auto_reset=False, done_on_violation=False), _quad(n, auto_reset=False, done_on_violation=False)
+    a.reset(); b.reset()
+    log = torch.zeros(k // 2, 16, n, device="cuda")
+    a.rollout(acts, log_out=log, log_stride=2)
+    for t in range(k):
+        b.step(acts[t])
+        if t % 2 == 0:
+            s = b.buf_env_state
+            rec = log[t // 2]
+            assert torch.equal(rec[0], s[0]) and torch.equal(rec[1], s[2]) and torch.equal(rec[2], s[4])   # pos
+            assert torch.equal(rec[3], s[1]) and torch.equal(rec[5], s[5])                                   # vel
+            assert torch.equal(rec[6:9], s[6:9])                                                             # rpy
+            assert torch.equal(rec[9:12], b.buf_state[9:12])                                                 # rpy_rates (ang_vel in DYN)
+            kf = 3.16e-10
+            thrust = kf * (rec[12:16] ** 2)                                                                  # rpm -> per-motor thrust
+            assert torch.allclose(thrust, acts[t].t().clamp(0.0281616878, 0.1483414471), rtol=2e-6)
+    a.close(); b.close()
+
+
+def test_config2_size_is_deterministic():
+    """BASELINE config 2 at full batch size (65,536 envs), 100 steps: two runs are bit-identical and every
+    env-step is accounted for."""
+    n, k = 65536, 100
+    acts = _actions(n, k)
+    out = []
+    for _ in range(2):
+        e = _quad(n, attitude="fast_intrinsic")
+        e.reset()
+        e.rollout(acts)
+        torch.cuda.synchronize()
+        out.append((e.buf_state.clone(), e.buf_episode.clone(), e.stats()))
+        e.close()
+    assert torch.equal(out[0][0], out[1][0]) and torch.equal(out[0][1], out[1][1]) and out[0][2] == out[1][2]
+    st = out[0][2]
+    assert st["env_steps"] == n * k and st["length"] <= st["env_steps"] and st["episodes"] == st["violated_episodes"] + st["truncated"] + st["completed"]
+    assert not torch.isnan(out[0][0]).any()

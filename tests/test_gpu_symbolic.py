@@ -1,0 +1,90 @@
+"""SymbolicModel facade -> scg_symbolic_eval / scg_symbolic_loss (csrc/scg_symbolic.cu) against
+oracle/symbolic_oracle.py: fc, RK4 / Euler discretisation, closed-form Jacobians (vs complex-step), loss.
+fp64 <= 1e-12, fp32 <= 1e-5 relative (unit floor)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import symbolic_oracle as so
+
+pytestmark = pytest.mark.gpu
+N = 257
+
+
+def _env(kind, dtype):
+    if kind == 10:
+        from safe_control_gym_b200.envs.cartpole import BatchedCartPole
+        env = BatchedCartPole(num_envs=4, dtype=dtype, prior_prop=dict(pole_length=0.4, pole_mass=0.12, cart_mass=0.9))
+        prm = dict(g=9.8, m=1.0, cp_l=0.4, cp_mp=0.12, cp_mc=0.9)
+    else:
+        from safe_control_gym_b200.envs.quadrotor import BatchedQuadrotor
+        ip = {1: [0.03], 2: [0.031, 1.5e-5], 3: [0.032, 1.3e-5, 1.5e-5, 2.2e-5]}[kind]
+        ti = dict(stabilization_goal=[0, 0, 1][:max(kind, 2)], stabilization_goal_tolerance=0.05)
+        env = BatchedQuadrotor(num_envs=4, dtype=dtype, quad_type=kind, inertial_prop=ip, task_info=ti)
+        prm = dict(m=env.MASS, g=env.GRAVITY_ACC, L=env.L, Ixx=env.J[0, 0], Iyy=env.J[1, 1], Izz=env.J[2, 2], KF=env.KF, KM=env.KM)
+    return env, prm
+
+
+def _rel(got, want):
+    got, want = np.asarray(got, dtype=np.float64), np.asarray(want, dtype=np.float64)
+    return float(np.max(np.abs(got - want) / np.maximum(1.0, np.abs(want))))
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float64, 1e-12), (torch.float32, 1e-5)])
+@pytest.mark.parametrize("kind", [1, 2, 3, 10])
+def test_fc_fd_df(kind, dtype, tol):
+    env, prm = _env(kind, dtype)
+    nx, nu = so.DIMS[kind]
+    rng = np.random.default_rng(kind)
+    x = rng.normal(0, 0.4, size=(N, nx))
+    u = rng.uniform(0.03, 0.12, size=(N, nu)) if kind != 10 else rng.normal(0, 3.0, size=(N, nu))
+    if dtype == torch.float32:   # give both sides the same representable inputs
+        x, u = x.astype(np.float32).astype(np.float64), u.astype(np.float32).astype(np.float64)
+    sym = env.symbolic
+    f = sym.fc_func(x, u)
+    xr = sym.fd_func(x0=x, p=u)["xf"]
+    xe = sym.fd_euler_func(x0=x, p=u)["xf"]
+    A, B = sym.df_func(x, u)
+    assert f.shape == (N, nx) and A.shape == (N, nx, nx) and B.shape == (N, nx, nu)
+    dt = env.CTRL_TIMESTEP
+    for i in range(0, N, 16):
+        assert _rel(f[i], so.fc(kind, prm, x[i], u[i])) <= tol
+        assert _rel(xr[i], so.fd_rk4(kind, prm, x[i], u[i], dt)) <= tol
+        assert _rel(xe[i], so.fd_euler(kind, prm, x[i], u[i], dt)) <= tol
+        Ao, Bo = so.df(kind, prm, x[i], u[i])
+        # the Jacobian entries scale with 1 / inertia (1e5): relative to the matrix scale
+        assert np.max(np.abs(A[i] - Ao)) <= tol * max(1.0, np.abs(Ao).max())
+        assert np.max(np.abs(B[i] - Bo)) <= tol * max(1.0, np.abs(Bo).max())
+    # single-sample call style of the reference: fc_func(x, u) with 1-D arrays
+    f1 = sym.fc_func(x[0], u[0])
+    assert f1.shape == (nx,) and _rel(f1, so.fc(kind, prm, x[0], u[0])) <= tol
+    env.close()
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float64, 1e-12), (torch.float32, 1e-5)])
+def test_loss(dtype, tol):
+    env, _ = _env(2, dtype)
+    rng = np.random.default_rng(0)
+    x, u = rng.normal(size=(N, 6)), rng.normal(size=(N, 2))
+    xr, ur = rng.normal(size=6), rng.normal(size=2)
+    Q, R = rng.normal(size=(6, 6)), rng.normal(size=(2, 2))
+    if dtype == torch.float32:
+        x, u, xr, ur = (a.astype(np.float32).astype(np.float64) for a in (x, u, xr, ur))
+        Q, R = Q.astype(np.float32).astype(np.float64), R.astype(np.float32).astype(np.float64)
+    out = env.symbolic.loss(x, u, xr, ur, Q, R)
+    for i in range(0, N, 32):
+        o = so.loss(x[i], u[i], xr, ur, Q, R)
+        scale = max(1.0, abs(o["l"]))
+        assert abs(out["l"][i] - o["l"]) <= 10 * tol * scale
+        assert _rel(out["l_x"][i], o["l_x"]) <= 10 * tol and _rel(out["l_u"][i], o["l_u"]) <= 10 * tol
+    assert np.allclose(out["l_xx"], 0.5 * (Q + Q.T)) and out["l_xu"].shape == (6, 2)
+    env.close()
+
+
+def test_device_tensors_stay_on_device():
+    env, _ = _env(3, torch.float32)
+    x = torch.zeros(8, 12, device="cuda")
+    u = torch.full((8, 4), float(env.MASS * 9.8 / 4), device="cuda")
+    f = env.symbolic.fc_func(x, u)
+    assert f.is_cuda and f.shape == (8, 12) and float(f.abs().max()) < 1e-5   # hover equilibrium
+    env.close()
