@@ -292,10 +292,9 @@ __device__ __noinline__ void eval_dense_rows(int n_dense_rows, const Cold<real>*
 // (info["constraint_values"]), tolerances (is_almost_active), symmetric and dense rows -- out of
 // line: per-step outputs only exist in the host-driven scg_step mode.
 template <int KIND, typename real>
-__device__ __noinline__ void constraint_values_cold(const Hot<real>& h, const Cold<real>* __restrict__ cold,
-                                                    const real* __restrict__ st, const real* __restrict__ raw,
-                                                    bool state_only, real* __restrict__ c_out, int64_t n, int64_t i,
-                                                    bool* violated_out, bool* almost_out) {
+__device__ __noinline__ uint32_t constraint_values_cold(const Hot<real>& h, const Cold<real>* __restrict__ cold,
+                                                        const real* __restrict__ st, const real* __restrict__ raw,
+                                                        bool state_only, real* __restrict__ c_out, int64_t n, int64_t i) {
     constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
     bool violated = false, almost = false;
     for (int k = 0; k < h.n_bounded; ++k) {
@@ -324,7 +323,7 @@ __device__ __noinline__ void constraint_values_cold(const Hot<real>& h, const Co
         eval_dense_rows<KIND, real>(h.n_dense_rows, cold, st, raw, state_only, c_out, n, i, &v, &al);
         violated |= v; almost |= al;
     }
-    *violated_out = violated; *almost_out = almost;
+    return (violated ? 1u : 0u) | (almost ? 2u : 0u);   // by value: the caller's flags stay in registers
 }
 
 // The in-loop part: violation flags of the bounded / default constraints (the only kind a LEAN
@@ -342,23 +341,24 @@ SCG_DEV void eval_constraints(const Hot<real>& h, const Cold<real>* __restrict__
         for (int d = 0; d < NX; ++d) sl[d] = st[d];
 #pragma unroll
         for (int d = 0; d < NU; ++d) rl[d] = raw[d];
-        constraint_values_cold<KIND, real>(h, cold, sl, rl, state_only, c_out, n, i, &violated, &almost);
+        const uint32_t bits = constraint_values_cold<KIND, real>(h, cold, sl, rl, state_only, c_out, n, i);
+        violated = (bits & 1u) != 0u; almost = (bits & 2u) != 0u;
         return;
     }
     if constexpr (LEAN) {
         // one merged box: violated <=> the largest c = max(lo - x, x - hi) over all bounded dims rounds above 0
+        // (unbounded dims carry lo = -inf, hi = +inf; whole groups of three dims without a bound are skipped
+        // by a uniform branch, inside a group every dim costs two subtractions and one three-way max)
         real worst = -INFINITY;
 #pragma unroll
-        for (int d = 0; d < NX; ++d) {
-            if (!((h.box_mask >> d) & 1u)) continue;   // uniform
-            worst = m_max(worst, m_max(h.box_lo[d] - st[d], st[d] - h.box_hi[d]));
-        }
-        if (!state_only) {
+        for (int g = 0; g < NX; g += 3) {
+            if (!((h.box_mask >> g) & 7u)) continue;   // uniform
 #pragma unroll
-            for (int d = 0; d < NU; ++d) {
-                if (!((h.ubox_mask >> d) & 1u)) continue;
-                worst = m_max(worst, m_max(h.ubox_lo[d] - raw[d], raw[d] - h.ubox_hi[d]));
-            }
+            for (int d = g; d < g + 3 && d < NX; ++d) worst = m_max3(worst, h.box_lo[d] - st[d], st[d] - h.box_hi[d]);
+        }
+        if (!state_only && h.ubox_mask) {
+#pragma unroll
+            for (int d = 0; d < NU; ++d) worst = m_max3(worst, h.ubox_lo[d] - raw[d], raw[d] - h.ubox_hi[d]);
         }
         violated = worst * real(1e8) > h.box_thr;
     } else {

@@ -32,6 +32,7 @@ SCG_DEV float  m_abs(float x)  { return fabsf(x); }
 SCG_DEV double m_abs(double x) { return fabs(x); }
 SCG_DEV float  m_max(float a, float b)   { return fmaxf(a, b); }
 SCG_DEV double m_max(double a, double b) { return fmax(a, b); }
+template <typename real> SCG_DEV real m_max3(real a, real b, real c) { return m_max(a, m_max(b, c)); }   // FMNMX3 in fp32
 SCG_DEV float  m_min(float a, float b)   { return fminf(a, b); }
 SCG_DEV double m_min(double a, double b) { return fmin(a, b); }
 SCG_DEV float  m_fma(float a, float b, float c)    { return fmaf(a, b, c); }

@@ -21,11 +21,29 @@ template <int KIND, typename real> struct EnvRegs {
     real x[NX];          // internal state, reference order; 3D angles pre-round-trip, rates = rpy_rates
     int32_t t;           // ctrl_step_counter
     int32_t resets;      // number of resets so far (episode index = resets - 1)
-    uint32_t flags;      // SCG_FLAG_*
+    // SCG_FLAG_* of the flags buffer, unpacked while the env lives in registers (2D's fold bit is a2.flipped)
+    bool viol, at_goal, completed;
+    uint32_t gate, hold;
     Inertia<real> in;
     Att3<real> a3;       // 3D
     Att2<real> a2;       // 2D
 };
+
+template <int KIND, typename real> SCG_DEV void unpack_flags(EnvRegs<KIND, real>& e, uint32_t f) {
+    e.viol = (f & SCG_FLAG_CNSTR_VIOLATION) != 0u;
+    e.at_goal = (f & SCG_FLAG_AT_GOAL) != 0u;
+    e.completed = (f & SCG_FLAG_COMPLETED) != 0u;
+    e.a2.flipped = (f & SCG_FLAG_FLIPPED) ? 1u : 0u;
+    e.gate = (f >> SCG_FLAG_GATE_SHIFT) & 0xFFu;
+    e.hold = f >> SCG_FLAG_HOLD_SHIFT;
+}
+
+template <int KIND, typename real> SCG_DEV uint32_t pack_flags(const EnvRegs<KIND, real>& e) {
+    uint32_t f = (e.viol ? SCG_FLAG_CNSTR_VIOLATION : 0u) | (e.at_goal ? SCG_FLAG_AT_GOAL : 0u) |
+                 (e.completed ? SCG_FLAG_COMPLETED : 0u) | (e.gate << SCG_FLAG_GATE_SHIFT) | (e.hold << SCG_FLAG_HOLD_SHIFT);
+    if (KIND == SCG_QUAD_2D && e.a2.flipped) f |= SCG_FLAG_FLIPPED;
+    return f;
+}
 
 template <int KIND, typename real> SCG_DEV void load_inertia(const Hot<real>& h, const real* __restrict__ inertia, int64_t n, int64_t i,
                                                    Inertia<real>& in) {
@@ -52,9 +70,8 @@ template <int KIND, typename real, int ATT> SCG_DEV void derive_attitude(EnvRegs
         const real pre[3] = {e.x[6], e.x[7], e.x[8]};
         attitude3<real, ATT>(pre, e.a3);
     } else if constexpr (KIND == SCG_QUAD_2D) {
-        attitude2<real>(e.x[4], (e.flags & SCG_FLAG_FLIPPED) ? 1u : 0u, e.a2);
+        attitude2<real>(e.x[4], e.a2.flipped, e.a2);
         e.x[4] = e.a2.theta;
-        e.flags = (e.flags & ~SCG_FLAG_FLIPPED) | (e.a2.flipped ? SCG_FLAG_FLIPPED : 0u);
     }
 }
 
@@ -144,7 +161,7 @@ SCG_DEV void reset_env_body(const Hot<real>& h, const Cold<real>* __restrict__ c
     const uint32_t ep = h.reseed_on_reset ? 0u : uint32_t(e.resets);
     e.resets += 1;
     e.t = 0;
-    e.flags &= SCG_FLAG_CNSTR_VIOLATION;   // cnstr_violation survives reset (benchmark_env.py:218)
+    e.at_goal = e.completed = false; e.gate = e.hold = 0u; e.a2.flipped = 0u;   // cnstr_violation survives reset (benchmark_env.py:218)
     // disturbance offsets (DisturbanceList.reset -> randint(max_step), disturbances.py:122-126,169-172)
     for (int ch = 0; ch < 3; ++ch) {
         const int nd = ch == 0 ? h.n_dist_obs : ch == 1 ? h.n_dist_act : h.n_dist_dyn;
@@ -245,7 +262,7 @@ template <int KIND, typename real, int ATT>
 SCG_DEV void reset_from_spare(const real (&init)[Dims<KIND>::NX], EnvRegs<KIND, real>& e, real (&ang0)[3]) {
     e.resets += 1;
     e.t = 0;
-    e.flags &= SCG_FLAG_CNSTR_VIOLATION;   // cnstr_violation survives reset (benchmark_env.py:218)
+    e.at_goal = e.completed = false; e.gate = e.hold = 0u; e.a2.flipped = 0u;   // cnstr_violation survives reset (benchmark_env.py:218)
     ang0[0] = ang0[1] = ang0[2] = real(0);
     if constexpr (KIND == SCG_QUAD_3D) {
 #pragma unroll
@@ -369,7 +386,6 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             attitude2<real>(e.a2.theta + dt * e.x[5], e.a2.flipped, e.a2);
             e.x[4] = e.a2.theta;
         }
-        e.flags = (e.flags & ~SCG_FLAG_FLIPPED) | (e.a2.flipped ? SCG_FLAG_FLIPPED : 0u);
     } else if constexpr (KIND == SCG_CARTPOLE) {
         // RK4 over the cart-pole ODE at the simulation rate; a dynamics-channel disturbance acts as an
         // extra horizontal force on the cart when dyn_applies_force is on.
@@ -398,38 +414,21 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             st[11] = (R[2] * ang[0] + R[5] * ang[1]) + R[8] * ang[2];
         }
     } else make_state<KIND, real>(e, ang, st);
-    // ---- _get_info (quadrotor.py:1004-1134): mse, goal hold (collision scan is dead in DYN, F5)
-    real goal[NX];
-    {
-        const int32_t gi = t < h.n_goal_rows - 1 ? t : h.n_goal_rows - 1;
-        goal_row<KIND, real>(h, cold, gi, goal);
-    }
-    mse = real(0);
-#pragma unroll
-    for (int d = 0; d < NX; ++d) {
-        if (!((h.mse_mask >> d) & 1u)) continue;   // uniform; a zero weight contributes exactly 0
-        const real er = (st[d] - goal[d]) * h.mse_weight[d]; mse += er * er;
-    }
-    bool gate_passed = false, at_goal = false, completed = (e.flags & SCG_FLAG_COMPLETED) != 0u;
+    // ---- _get_info (quadrotor.py:1004-1134): goal hold (collision scan is dead in DYN, F5)
+    const bool gate_passed = false;
+    e.at_goal = false;
     if constexpr (KIND == SCG_QUAD_3D) {
-        const uint32_t cur_gate = (e.flags >> SCG_FLAG_GATE_SHIFT) & 0xFFu;
-        if (cur_gate == uint32_t(h.n_gates) && h.task == SCG_TASK_STABILIZATION) {   // quadrotor.py:1117-1130
-            uint32_t hold = e.flags >> SCG_FLAG_HOLD_SHIFT;
+        if (e.gate == uint32_t(h.n_gates) && h.task == SCG_TASK_STABILIZATION) {   // quadrotor.py:1117-1130
             const real dx = st[0] - h.x_goal0[0], dy = st[2] - h.x_goal0[2], dz = st[4] - h.x_goal0[4];
             // sqrt(d2) < tol  <=>  d2 < tol^2 up to one rounding of the square; the literal modes keep the sqrt
             const real d2 = dx * dx + dy * dy + dz * dz;
             const bool inside = FASTMATH ? (d2 < h.goal_tol * h.goal_tol) : (m_sqrt(d2) < h.goal_tol);
-            if (inside) { at_goal = true; hold = hold < 0xFFFFu ? hold + 1u : hold; }
-            else hold = 0u;
-            if (hold > uint32_t(2 * h.ctrl_freq)) completed = true;
-            e.flags = (e.flags & 0xFFFFu) | (hold << SCG_FLAG_HOLD_SHIFT);
+            e.at_goal = inside;
+            e.hold = inside ? (e.hold < 0xFFFFu ? e.hold + 1u : e.hold) : 0u;
+            if (e.hold > uint32_t(2 * h.ctrl_freq)) e.completed = true;
         }
     }
-    e.flags = (e.flags & ~(SCG_FLAG_AT_GOAL | SCG_FLAG_COMPLETED)) | (at_goal ? SCG_FLAG_AT_GOAL : 0u) |
-              (completed ? SCG_FLAG_COMPLETED : 0u);
-    if (at_goal) info |= SCG_INFO_AT_GOAL;
-    if (completed) info |= SCG_INFO_COMPLETED;
-    if (gate_passed) info |= SCG_INFO_GATE_PASSED;
+    info = (e.at_goal ? SCG_INFO_AT_GOAL : 0u) | (e.completed ? SCG_INFO_COMPLETED : 0u) | (gate_passed ? SCG_INFO_GATE_PASSED : 0u);
     // ---- _get_done (quadrotor.py:956-1002)
     done = false;
     if (h.task == SCG_TASK_STABILIZATION && h.cost == SCG_COST_QUADRATIC) {
@@ -448,61 +447,80 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
         }
         if (oob) { done = true; info |= SCG_INFO_OUT_OF_BOUND; }
     }
-    if (h.done_on_completion && completed) done = true;
-    // ---- _get_reward (quadrotor.py:886-954); t is still the pre-increment counter
-    if (h.cost == SCG_COST_RL_REWARD) {
-        real dist = real(0), dact = real(0);
+    if (h.done_on_completion && e.completed) done = true;
+    // ---- info["mse"] (quadrotor.py:1016-1021) and _get_reward (quadrotor.py:886-954); t is still the
+    // pre-increment counter.  Written once against a goal accessor so that a stabilisation goal stays
+    // a constant-bank operand and only trajectory tracking loads a row into registers.
+    auto costs = [&](auto goal_at, auto goal_q_at) {
+        mse = real(0);
 #pragma unroll
-        for (int d = 0; d < NX; ++d) { const real er = st[d] - goal[d]; dist += h.rew_state_weight[d] * er * er; }
+        for (int g = 0; g < NX; g += 2) {
+            if (!((h.mse_mask >> g) & 3u)) continue;   // uniform; a zero weight contributes exactly 0
 #pragma unroll
-        for (int j = 0; j < NU; ++j) { const real er = pre[j] - h.u_goal[j]; dact += h.rew_act_weight[j] * er * er; }
-        reward = -(dist + dact);
-        if (h.rew_exponential) reward = m_exp(reward);
-    } else if (h.cost == SCG_COST_QUADRATIC) {
-        real gq[NX];   // traj tracking uses X_GOAL[t] un-clamped (quadrotor.py:924-926)
-        goal_row<KIND, real>(h, cold, t, gq);
-        real lx = real(0), lu = real(0);
-        if (LEAN || h.quadratic_diag) {
-#pragma unroll
-            for (int d = 0; d < NX; ++d) { const real er = st[d] - gq[d]; lx += h.q_diag[d] * er * er; }
-#pragma unroll
-            for (int j = 0; j < NU; ++j) { const real er = pre[j] - h.u_goal[j]; lu += h.r_diag[j] * er * er; }
-        } else {
-            for (int a = 0; a < NX; ++a) {
-                real row = real(0);
-#pragma unroll
-                for (int c = 0; c < NX; ++c) row += cold->Q[a * SCG_MAX_NX + c] * (st[c] - gq[c]);
-                real ea = real(0);
-#pragma unroll
-                for (int c = 0; c < NX; ++c) ea = c == a ? st[c] - gq[c] : ea;
-                lx += ea * row;
-            }
-            for (int a = 0; a < NU; ++a) {
-                real row = real(0);
-#pragma unroll
-                for (int c = 0; c < NU; ++c) row += cold->R[a * SCG_MAX_NU + c] * (pre[c] - h.u_goal[c]);
-                real ea = real(0);
-#pragma unroll
-                for (int c = 0; c < NU; ++c) ea = c == a ? pre[c] - h.u_goal[c] : ea;
-                lu += ea * row;
-            }
+            for (int d = g; d < g + 2 && d < NX; ++d) { const real er = (st[d] - goal_at(d)) * h.mse_weight[d]; mse += er * er; }
         }
-        reward = -(real(0.5) * lx + real(0.5) * lu);
+        if (h.cost == SCG_COST_RL_REWARD) {
+            real dist = real(0), dact = real(0);
+#pragma unroll
+            for (int d = 0; d < NX; ++d) { const real er = st[d] - goal_at(d); dist += h.rew_state_weight[d] * er * er; }
+#pragma unroll
+            for (int j = 0; j < NU; ++j) { const real er = pre[j] - h.u_goal[j]; dact += h.rew_act_weight[j] * er * er; }
+            reward = -(dist + dact);
+            if (h.rew_exponential) reward = m_exp(reward);
+        } else if (h.cost == SCG_COST_QUADRATIC) {
+            real lx = real(0), lu = real(0);
+            if (LEAN || h.quadratic_diag) {
+#pragma unroll
+                for (int d = 0; d < NX; ++d) { const real er = st[d] - goal_q_at(d); lx += h.q_diag[d] * er * er; }
+#pragma unroll
+                for (int j = 0; j < NU; ++j) { const real er = pre[j] - h.u_goal[j]; lu += h.r_diag[j] * er * er; }
+            } else {
+                real ex[NX], eu[NU];
+#pragma unroll
+                for (int c = 0; c < NX; ++c) ex[c] = st[c] - goal_q_at(c);
+#pragma unroll
+                for (int c = 0; c < NU; ++c) eu[c] = pre[c] - h.u_goal[c];
+                for (int a = 0; a < NX; ++a) {
+                    real row = real(0), ea = real(0);
+#pragma unroll
+                    for (int c = 0; c < NX; ++c) { row += cold->Q[a * SCG_MAX_NX + c] * ex[c]; ea = c == a ? ex[c] : ea; }
+                    lx += ea * row;
+                }
+                for (int a = 0; a < NU; ++a) {
+                    real row = real(0), ea = real(0);
+#pragma unroll
+                    for (int c = 0; c < NU; ++c) { row += cold->R[a * SCG_MAX_NU + c] * eu[c]; ea = c == a ? eu[c] : ea; }
+                    lu += ea * row;
+                }
+            }
+            reward = -(real(0.5) * lx + real(0.5) * lu);
+        } else {
+            reward = real(0);
+            if (gate_passed) reward += real(100);
+            if (e.at_goal) reward += real(100);
+            if (e.viol) reward -= real(100);   // previous step's flag (F8)
+        }
+    };
+    if (h.task == SCG_TASK_STABILIZATION) {
+        auto g0 = [&](int d) { return h.x_goal0[d]; };
+        costs(g0, g0);
     } else {
-        reward = real(0);
-        if (gate_passed) reward += real(100);
-        if (at_goal) reward += real(100);
-        if (e.flags & SCG_FLAG_CNSTR_VIOLATION) reward -= real(100);   // previous step's flag (F8)
+        // X_GOAL[t]; the index is clamped to the last row where the reference would raise an IndexError
+        // (t >= rows never happens inside an episode: rows == ctrl_steps, quadrotor.py:924-926, 1016-1021)
+        const int32_t gi = t < h.n_goal_rows - 1 ? t : h.n_goal_rows - 1;
+        real ga[NX];
+#pragma unroll
+        for (int d = 0; d < NX; ++d) ga[d] = cold->x_goal[int64_t(gi) * NX + d];
+        auto gt = [&](int d) { return ga[d]; };
+        costs(gt, gt);
     }
     // ---- after_step (benchmark_env.py:422-463)
     e.t = t + 1;
     if (h.n_rows > 0) {
         bool violated, almost;
         eval_constraints<KIND, real, LEAN>(h, cold, st, raw, false, c_out, n, i, violated, almost);
-        if (violated) {
-            e.flags |= SCG_FLAG_CNSTR_VIOLATION; info |= SCG_INFO_VIOLATION;
-            if (h.done_on_violation) done = true;
-        } else e.flags &= ~SCG_FLAG_CNSTR_VIOLATION;
+        e.viol = violated;
+        if (violated) { info |= SCG_INFO_VIOLATION; if (h.done_on_violation) done = true; }
         if (!LEAN && h.cost == SCG_COST_RL_REWARD && h.use_constraint_penalty && almost) reward += h.constraint_penalty;
     }
     if (e.t >= h.ctrl_steps) {
@@ -580,12 +598,12 @@ k_reset(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold
     for (int d = 0; d < NX; ++d) e.x[d] = b.state[int64_t(d) * n + i];
     e.t = b.ctrl_step[i];
     e.resets = b.episode[i];
-    e.flags = b.flags[i];
+    unpack_flags<KIND, real>(e, b.flags[i]);
     real st[NX];
     reset_env_body<KIND, real, ATT>(h, cold, b, inj, key, n, i, e, st);
 #pragma unroll
     for (int d = 0; d < NX; ++d) b.state[int64_t(d) * n + i] = e.x[d];
-    b.ctrl_step[i] = e.t; b.episode[i] = e.resets; b.flags[i] = e.flags;
+    b.ctrl_step[i] = e.t; b.episode[i] = e.resets; b.flags[i] = pack_flags<KIND, real>(e);
     if (b.env_state) {
 #pragma unroll
         for (int d = 0; d < NX; ++d) b.env_state[int64_t(d) * n + i] = st[d];
@@ -605,7 +623,7 @@ k_reset(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold
 
 // K fused control steps (scg_step is K = 1 with the per-step outputs)
 template <int KIND, typename real, int ATT, bool LEAN>
-__global__ void __launch_bounds__(ENV_BLOCK)
+__global__ void __launch_bounds__(ENV_BLOCK, (LEAN && sizeof(real) == 4) ? 7 : 1)
 k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, const Buf<real> b, const Roll<real> ro) {
     constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
     const int64_t n = b.n;
@@ -620,8 +638,8 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     for (int d = 0; d < NX; ++d) e.x[d] = b.state[int64_t(d) * n + ii];
     e.t = b.ctrl_step[ii];
     e.resets = b.episode[ii];
-    e.flags = b.flags[ii];
-    real st[NX];
+    unpack_flags<KIND, real>(e, b.flags[ii]);
+    real st[NX];   // env.state after the last step (LEAN: rebuilt from the registers after the loop)
     load_inertia<KIND, real>(h, LEAN ? nullptr : b.inertia, n, ii, e.in);
     derive_attitude<KIND, real, ATT>(e);
     real ep_ret = b.ep_return ? b.ep_return[ii] : real(0);
@@ -644,21 +662,28 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     real spare[LEAN ? NX : 1], ang0[3] = {real(0), real(0), real(0)};
     bool spare_ok = false;
     const bool ahead = ro.k_steps >= 16;   // uniform: host-driven single steps draw on demand only
+    const bool any_out = ro.reward_out != nullptr || ro.done_out != nullptr || ro.log_out != nullptr;   // uniform
 #pragma unroll 1
     for (int k = 0; k < ro.k_steps; ++k) {
 #pragma unroll
         for (int j = 0; j < NU; ++j) raw[j] = nxt[j];
         if (k + 1 < ro.k_steps) load_action<NU, real>(ro.actions + (int64_t(k + 1) * n + ii) * NU, nxt);
-        step_env<KIND, real, ATT, LEAN>(h, cold, b, key, n, ii, e, raw, full, st, reward, done, info, mse, mot, c_out);
+        // LEAN: env.state of this step is loop-local (it aliases the registers of e); what is observed
+        // after the loop is rebuilt from e there
+        real sl[LEAN ? NX : 1];
+        real (&sk)[NX] = *reinterpret_cast<real (*)[NX]>(LEAN ? sl : st);
+        step_env<KIND, real, ATT, LEAN>(h, cold, b, key, n, ii, e, raw, full, sk, reward, done, info, mse, mot, c_out);
         ep_ret += reward; ep_len += 1;
         const bool viol = (info & SCG_INFO_VIOLATION) != 0u;
         ep_viol += viol ? 1 : 0;
         s_viol += viol ? 1.f : 0.f;
         s_mse += float(mse);
-        if (ro.reward_out) ro.reward_out[int64_t(k) * n + ii] = reward;
-        if (ro.done_out) ro.done_out[int64_t(k) * n + ii] = done ? 1 : 0;
-        if (ro.log_out && (k % ro.log_stride) == 0)
-            write_log<KIND, real>(e, mot, ro.log_out + int64_t(k / ro.log_stride) * 16 * n + ii, n);
+        if (any_out) {
+            if (ro.reward_out) ro.reward_out[int64_t(k) * n + ii] = reward;
+            if (ro.done_out) ro.done_out[int64_t(k) * n + ii] = done ? 1 : 0;
+            if (ro.log_out && (k % ro.log_stride) == 0)
+                write_log<KIND, real>(e, mot, ro.log_out + int64_t(k / ro.log_stride) * 16 * n + ii, n);
+        }
         fresh = false;
         if (done) {
             s_eps += 1.f; s_ret += float(ep_ret); s_len += float(ep_len);
@@ -669,7 +694,7 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
                 if (ro.step_outputs && b.terminal_obs) {
                     real tl[NX];
 #pragma unroll
-                    for (int d = 0; d < NX; ++d) tl[d] = st[d];
+                    for (int d = 0; d < NX; ++d) tl[d] = sk[d];
                     write_obs<KIND, real>(h, cold, b.dist_offset, b.terminal_obs, tl, e.t - 1, uint32_t(e.t), key,
                                           h.reseed_on_reset ? 0u : uint32_t(e.resets - 1), n, ii);
                 }
@@ -700,9 +725,15 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
         }
     }
     if constexpr (LEAN) {
-        if (fresh) make_state<KIND, real>(e, ang0, st);   // env.state of the fresh episode, observed below
-    }
-    if constexpr (KIND == SCG_QUAD_3D) {
+        // env.state as observed after the loop: the fresh episode's (PyBullet still holds INIT_ANG_VEL)
+        // or the last step's (ang_v = rpy_rates)
+        real ang[3] = {ang0[0], ang0[1], ang0[2]};
+        if (!fresh) {
+            if constexpr (KIND == SCG_QUAD_3D) { ang[0] = e.x[9]; ang[1] = e.x[10]; ang[2] = e.x[11]; }
+            else if constexpr (KIND == SCG_QUAD_2D) { ang[0] = real(0); ang[1] = e.x[5]; ang[2] = real(0); }
+        }
+        make_state<KIND, real>(e, ang, st);
+    } else if constexpr (KIND == SCG_QUAD_3D) {
         if (!full && !fresh) {   // the final observation needs p, q, r
             attitude3_complete<real>(e.a3);
             const real* R = e.a3.R;
@@ -713,7 +744,7 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     }
 #pragma unroll
     for (int d = 0; d < NX; ++d) b.state[int64_t(d) * n + ii] = e.x[d];
-    b.ctrl_step[ii] = e.t; b.episode[ii] = e.resets; b.flags[ii] = e.flags;
+    b.ctrl_step[ii] = e.t; b.episode[ii] = e.resets; b.flags[ii] = pack_flags<KIND, real>(e);
     if (b.env_state) {
 #pragma unroll
         for (int d = 0; d < NX; ++d) b.env_state[int64_t(d) * n + ii] = st[d];

@@ -12,7 +12,7 @@ import bench  # noqa: E402
 from safe_control_gym_b200.envs.quadrotor import BatchedQuadrotor  # noqa: E402
 
 ap = argparse.ArgumentParser()
-ap.add_argument("--attitude", default="fast")
+ap.add_argument("--attitude", default="fast_intrinsic")
 ap.add_argument("--k", type=int, default=200)
 ap.add_argument("--envs", type=int, default=65536)
 ap.add_argument("--launches", type=int, default=3)
