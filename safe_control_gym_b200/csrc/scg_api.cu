@@ -196,6 +196,11 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
         if (c.cost == SCG_COST_QUADRATIC) rates = true;   // Q weighs the rates (identity by default); goal_reached norms the full state
     }
     h.need_full_state = rates ? 1 : 0;
+    h.cfg = (c.task == SCG_TASK_STABILIZATION ? CFG_STAB : 0u) | (c.cost == SCG_COST_RL_REWARD ? CFG_COST_RL : 0u) |
+            (c.cost == SCG_COST_QUADRATIC ? CFG_COST_QUAD : 0u) | (c.rew_exponential ? CFG_REW_EXP : 0u) |
+            (c.done_on_out_of_bound ? CFG_OOB : 0u) | (c.done_on_completion ? CFG_DONE_COMPLETION : 0u) |
+            (c.done_on_violation ? CFG_DONE_VIOLATION : 0u) | (c.auto_reset ? CFG_AUTO_RESET : 0u) |
+            (rates ? CFG_FULL_STATE : 0u) | (c.reseed_on_reset ? CFG_RESEED : 0u) | ((h.mse_mask & 0xE00u) ? CFG_MSE_RATES : 0u);
     // ---- LEAN kernel specialisation (scg_step.cuh): none of the rare features is configured
     bool symmetric = false;
     for (int q = 0; q < nb; ++q) symmetric |= h.bounded[q].symmetric != 0;
@@ -223,6 +228,8 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
         }
     }
     h.box_thr = (nb > 0 && h.bounded[0].strict) ? std::nextafter(real(-0.5), -INF) : real(0.5);
+    if (h.n_rows > 0) h.cfg |= CFG_HAS_ROWS;
+    if (h.ubox_mask) h.cfg |= CFG_UBOX;
     // (the extended observation lives in write_obs, outside the loop)
     *lean_out = c.n_dist[0] == 0 && c.n_dist[1] == 0 && c.n_dist[2] == 0 && c.adversary_channel < 0 && !c.dyn_applies_force &&
                 !(h.any_init_rand & 2) && !h.any_inertia_rand &&

@@ -332,7 +332,7 @@ template <int KIND, typename real, bool LEAN>
 SCG_DEV void eval_constraints(const Hot<real>& h, const Cold<real>* __restrict__ cold,
                               const real (&st)[Dims<KIND>::NX], const real (&raw)[Dims<KIND>::NU],
                               bool state_only, real* __restrict__ c_out, int64_t n, int64_t i,
-                              bool& violated, bool& almost) {
+                              bool& violated, bool& almost, uint32_t cfg = CFG_FULL_STATE | CFG_UBOX) {
     constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
     violated = false; almost = false;
     if (c_out != nullptr || (!LEAN && h.need_cold_constraints)) {
@@ -347,20 +347,27 @@ SCG_DEV void eval_constraints(const Hot<real>& h, const Cold<real>* __restrict__
     }
     if constexpr (LEAN) {
         // one merged box: violated <=> the largest c = max(lo - x, x - hi) over all bounded dims rounds above 0
-        // (unbounded dims carry lo = -inf, hi = +inf; whole groups of three dims without a bound are skipped
-        // by a uniform branch, inside a group every dim costs two subtractions and one three-way max)
-        real worst = -INFINITY;
+        // (unbounded dims carry lo = -inf, hi = +inf: every dim is evaluated, branch-free, at two subtractions and
+        // one three-way max each; p, q, r only where something reads them)
+        constexpr int NB = KIND == SCG_QUAD_3D ? 9 : NX;
+        real w0 = -INFINITY, w1 = -INFINITY;   // two chains
 #pragma unroll
-        for (int g = 0; g < NX; g += 3) {
-            if (!((h.box_mask >> g) & 7u)) continue;   // uniform
-#pragma unroll
-            for (int d = g; d < g + 3 && d < NX; ++d) worst = m_max3(worst, h.box_lo[d] - st[d], st[d] - h.box_hi[d]);
+        for (int d = 0; d < NB; ++d) {
+            real& w = (d & 1) ? w1 : w0;
+            w = m_max3(w, h.box_lo[d] - st[d], st[d] - h.box_hi[d]);
         }
-        if (!state_only && h.ubox_mask) {
+        if (NB < NX && (cfg & CFG_FULL_STATE)) {
 #pragma unroll
-            for (int d = 0; d < NU; ++d) worst = m_max3(worst, h.ubox_lo[d] - raw[d], raw[d] - h.ubox_hi[d]);
+            for (int d = NB; d < NX; ++d) w0 = m_max3(w0, h.box_lo[d] - st[d], st[d] - h.box_hi[d]);
         }
-        violated = worst * real(1e8) > h.box_thr;
+        if (!state_only && (cfg & CFG_UBOX)) {
+#pragma unroll
+            for (int d = 0; d < NU; ++d) {
+                real& w = (d & 1) ? w1 : w0;
+                w = m_max3(w, h.ubox_lo[d] - raw[d], raw[d] - h.ubox_hi[d]);
+            }
+        }
+        violated = m_max(w0, w1) * real(1e8) > h.box_thr;
     } else {
         for (int k = 0; k < h.n_bounded; ++k) {
             const BoundedCon<real>& bc = h.bounded[k];

@@ -71,6 +71,23 @@ template <typename real> struct Hot {
     uint32_t init_block_mask;       // Philox blocks (4 labels each) holding a randomised init label
     uint32_t seed;
     uint32_t env_id_base_lo;
+    // the uniform switches the control-step loop tests, packed (CFG_*): one constant-bank word feeds all of
+    // them, where a separate field per switch costs a dependent load -> compare -> branch chain each
+    uint32_t cfg;
+};
+
+enum : uint32_t {
+    CFG_STAB = 1u << 0,             // task == stabilization
+    CFG_COST_RL = 1u << 1, CFG_COST_QUAD = 1u << 2, CFG_REW_EXP = 1u << 3,
+    CFG_OOB = 1u << 4,              // done_on_out_of_bound
+    CFG_DONE_COMPLETION = 1u << 5, CFG_DONE_VIOLATION = 1u << 6,
+    CFG_HAS_ROWS = 1u << 7,         // some constraint row exists
+    CFG_AUTO_RESET = 1u << 8,
+    CFG_FULL_STATE = 1u << 9,       // a per-step consumer reads p, q, r (or the launch writes per-step outputs)
+    CFG_RESEED = 1u << 10,
+    CFG_UBOX = 1u << 11,            // LEAN: an input dim carries a bound
+    CFG_MSE_RATES = 1u << 12,       // 3D: info["mse"] weighs p, q, r
+    CFG_STEP_OUTPUTS = 1u << 13,    // set per launch
 };
 
 template <typename real> struct DenseRow {     // linear: c = a . x - b ; quadratic: c = x' P x - b

@@ -16,6 +16,11 @@
 
 namespace scg {
 
+// 65,536 envs -> 1,024 blocks = 6.9 per SM.  The register file is split per scheduler (16,384 registers each), so
+// the 3.5 warps per scheduler of that batch are resident together only at <= 128 registers per thread: the LEAN
+// fp32 kernel is bounded to 8 blocks per SM (one wave); at 255 registers half of the blocks wait for a second wave.
+constexpr int ENV_BLOCK = 64;
+
 template <int KIND, typename real> struct EnvRegs {
     static constexpr int NX = Dims<KIND>::NX;
     real x[NX];          // internal state, reference order; 3D angles pre-round-trip, rates = rpy_rates
@@ -258,29 +263,77 @@ SCG_DEV void draw_init_lean(const Hot<real>& h, const RngKey& key, uint32_t ep, 
     }
 }
 
+// The spare lives in shared memory, one column per thread ([slot][ENV_BLOCK], conflict-free, never
+// shared between threads), together with everything reset() derives from it -- the wrapped angles,
+// their sin / cos and the thrust direction -- so that the lanes that restart only move registers.
+template <int KIND, typename real, int ATT> struct Spare {
+    static constexpr int NX = Dims<KIND>::NX;
+    // fp64 evaluates the gimbal band with the literal sequence (full R): it derives the attitude on the spot
+    static constexpr bool PRE3 = KIND == SCG_QUAD_3D && sizeof(real) == 4 && ATT != SCG_ATT_ROUNDTRIP;
+    static constexpr int N = NX + (PRE3 ? 12 : KIND == SCG_QUAD_2D ? 4 : 0);
+};
+
 template <int KIND, typename real, int ATT>
-SCG_DEV void reset_from_spare(const real (&init)[Dims<KIND>::NX], EnvRegs<KIND, real>& e, real (&ang0)[3]) {
+SCG_DEV void spare_store(const real (&init)[Dims<KIND>::NX], real* __restrict__ sp) {
+    constexpr int NX = Dims<KIND>::NX;
+#pragma unroll
+    for (int d = 0; d < NX; ++d) sp[d * ENV_BLOCK] = init[d];
+    if constexpr (Spare<KIND, real, ATT>::PRE3) {
+        Att3<real> a;
+        const real pre[3] = {init[6], init[7], init[8]};
+        attitude3<real, ATT>(pre, a);
+#pragma unroll
+        for (int j = 0; j < 3; ++j) sp[(NX + j) * ENV_BLOCK] = a.rpy[j];
+#pragma unroll
+        for (int j = 0; j < 6; ++j) sp[(NX + 3 + j) * ENV_BLOCK] = a.sc[j];
+        sp[(NX + 9) * ENV_BLOCK] = a.R[2]; sp[(NX + 10) * ENV_BLOCK] = a.R[5]; sp[(NX + 11) * ENV_BLOCK] = a.R[8];
+    } else if constexpr (KIND == SCG_QUAD_2D) {
+        Att2<real> a;
+        attitude2<real>(init[4], 0u, a);
+        sp[(NX + 0) * ENV_BLOCK] = a.theta; sp[(NX + 1) * ENV_BLOCK] = a.r3x; sp[(NX + 2) * ENV_BLOCK] = a.r3z;
+        sp[(NX + 3) * ENV_BLOCK] = a.flipped ? real(1) : real(0);
+    }
+}
+
+template <int KIND, typename real, int ATT>
+SCG_DEV void reset_from_spare(const real* __restrict__ sp, EnvRegs<KIND, real>& e) {
+    constexpr int NX = Dims<KIND>::NX;
     e.resets += 1;
     e.t = 0;
     e.at_goal = e.completed = false; e.gate = e.hold = 0u; e.a2.flipped = 0u;   // cnstr_violation survives reset (benchmark_env.py:218)
-    ang0[0] = ang0[1] = ang0[2] = real(0);
     if constexpr (KIND == SCG_QUAD_3D) {
 #pragma unroll
-        for (int d = 0; d < 9; ++d) e.x[d] = init[d];
+        for (int d = 0; d < 9; ++d) e.x[d] = sp[d * ENV_BLOCK];
         e.x[9] = e.x[10] = e.x[11] = real(0);          // rpy_rates restart at 0 (base_aviary.py:232-233)
-        ang0[0] = init[9]; ang0[1] = init[10]; ang0[2] = init[11];   // INIT_ANG_VEL lives in PyBullet only
+        if constexpr (Spare<KIND, real, ATT>::PRE3) {
+#pragma unroll
+            for (int j = 0; j < 3; ++j) e.a3.rpy[j] = sp[(NX + j) * ENV_BLOCK];
+#pragma unroll
+            for (int j = 0; j < 6; ++j) e.a3.sc[j] = sp[(NX + 3 + j) * ENV_BLOCK];
+            e.a3.R[2] = sp[(NX + 9) * ENV_BLOCK]; e.a3.R[5] = sp[(NX + 10) * ENV_BLOCK]; e.a3.R[8] = sp[(NX + 11) * ENV_BLOCK];
+            e.a3.form = 1;
+        } else derive_attitude<KIND, real, ATT>(e);
     } else if constexpr (KIND == SCG_QUAD_2D) {
 #pragma unroll
-        for (int d = 0; d < 5; ++d) e.x[d] = init[d];
+        for (int d = 0; d < 4; ++d) e.x[d] = sp[d * ENV_BLOCK];
         e.x[5] = real(0);
-        ang0[1] = init[5];
+        e.a2.theta = sp[(NX + 0) * ENV_BLOCK]; e.a2.r3x = sp[(NX + 1) * ENV_BLOCK]; e.a2.r3z = sp[(NX + 2) * ENV_BLOCK];
+        e.a2.flipped = sp[(NX + 3) * ENV_BLOCK] != real(0) ? 1u : 0u;
+        e.x[4] = e.a2.theta;
     } else if constexpr (KIND == SCG_CARTPOLE) {
 #pragma unroll
-        for (int d = 0; d < 4; ++d) e.x[d] = init[d];
+        for (int d = 0; d < 4; ++d) e.x[d] = sp[d * ENV_BLOCK];
     } else {
         e.x[0] = real(0); e.x[1] = real(0);
     }
-    derive_attitude<KIND, real, ATT>(e);
+}
+
+// PyBullet-side INIT_ANG_VEL of the episode the spare started (valid until the next draw)
+template <int KIND, typename real>
+SCG_DEV void spare_ang0(const real* __restrict__ sp, real (&ang0)[3]) {
+    ang0[0] = ang0[1] = ang0[2] = real(0);
+    if constexpr (KIND == SCG_QUAD_3D) { ang0[0] = sp[9 * ENV_BLOCK]; ang0[1] = sp[10 * ENV_BLOCK]; ang0[2] = sp[11 * ENV_BLOCK]; }
+    else if constexpr (KIND == SCG_QUAD_2D) { ang0[1] = sp[5 * ENV_BLOCK]; }
 }
 
 // The auto-reset inside the rollout loop: one out-of-line copy, entered by the lanes whose episode
@@ -304,12 +357,13 @@ __device__ __noinline__ void reset_env_cold(const Hot<real>& h, const Cold<real>
 template <int KIND, typename real, int ATT, bool LEAN>
 SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, const Buf<real>& b,
                       const RngKey& key, int64_t n, int64_t i, EnvRegs<KIND, real>& e,
-                      const real (&raw)[Dims<KIND>::NU], bool full, real (&st)[Dims<KIND>::NX], real& reward, bool& done,
+                      const real (&raw)[Dims<KIND>::NU], uint32_t cfg, real (&st)[Dims<KIND>::NX], real& reward, bool& done,
                       uint32_t& info, real& mse, Motors<real>& mot, real* __restrict__ c_out) {
     constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
     constexpr bool FASTMATH = sizeof(real) == 4 && ATT != SCG_ATT_ROUNDTRIP;
-    const uint32_t ep = h.reseed_on_reset ? 0u : uint32_t(e.resets - 1);
+    const uint32_t ep = (cfg & CFG_RESEED) ? 0u : uint32_t(e.resets - 1);
     const int32_t t = e.t;
+    const bool full = (cfg & CFG_FULL_STATE) != 0u;   // uniform
     info = 0u;
     // ---- before_step / _preprocess_control (quadrotor.py:815-842)
     real thr[NU], pre[NU];
@@ -407,8 +461,9 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
         make_state<KIND, real, false>(e, ang, st);
         st[9] = st[10] = st[11] = real(0);
         if (full) {   // uniform: h.need_full_state or per-step outputs
-            attitude3_complete<real>(e.a3);
-            const real* R = e.a3.R;
+            Att3<real> c = e.a3;   // a copy: columns 0 and 1 must not stay live across control steps
+            attitude3_complete<real>(c);
+            const real* R = c.R;
             st[9] = (R[0] * ang[0] + R[3] * ang[1]) + R[6] * ang[2];
             st[10] = (R[1] * ang[0] + R[4] * ang[1]) + R[7] * ang[2];
             st[11] = (R[2] * ang[0] + R[5] * ang[1]) + R[8] * ang[2];
@@ -418,7 +473,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
     const bool gate_passed = false;
     e.at_goal = false;
     if constexpr (KIND == SCG_QUAD_3D) {
-        if (e.gate == uint32_t(h.n_gates) && h.task == SCG_TASK_STABILIZATION) {   // quadrotor.py:1117-1130
+        if (e.gate == uint32_t(h.n_gates) && (cfg & CFG_STAB)) {   // quadrotor.py:1117-1130
             const real dx = st[0] - h.x_goal0[0], dy = st[2] - h.x_goal0[2], dz = st[4] - h.x_goal0[4];
             // sqrt(d2) < tol  <=>  d2 < tol^2 up to one rounding of the square; the literal modes keep the sqrt
             const real d2 = dx * dx + dy * dy + dz * dz;
@@ -431,13 +486,13 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
     info = (e.at_goal ? SCG_INFO_AT_GOAL : 0u) | (e.completed ? SCG_INFO_COMPLETED : 0u) | (gate_passed ? SCG_INFO_GATE_PASSED : 0u);
     // ---- _get_done (quadrotor.py:956-1002)
     done = false;
-    if (h.task == SCG_TASK_STABILIZATION && h.cost == SCG_COST_QUADRATIC) {
+    if ((cfg & (CFG_STAB | CFG_COST_QUAD)) == (CFG_STAB | CFG_COST_QUAD)) {
         real nn = real(0);
 #pragma unroll
         for (int d = 0; d < NX; ++d) { const real er = st[d] - h.x_goal0[d]; nn += er * er; }
         if (m_sqrt(nn) < h.goal_tol) { done = true; info |= SCG_INFO_GOAL_REACHED; }
     }
-    if (h.done_on_out_of_bound) {
+    if (cfg & CFG_OOB) {
         bool oob = false;
 #pragma unroll
         for (int d = 0; d < NX; ++d) {
@@ -447,27 +502,29 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
         }
         if (oob) { done = true; info |= SCG_INFO_OUT_OF_BOUND; }
     }
-    if (h.done_on_completion && e.completed) done = true;
+    if ((cfg & CFG_DONE_COMPLETION) && e.completed) done = true;
     // ---- info["mse"] (quadrotor.py:1016-1021) and _get_reward (quadrotor.py:886-954); t is still the
     // pre-increment counter.  Written once against a goal accessor so that a stabilisation goal stays
     // a constant-bank operand and only trajectory tracking loads a row into registers.
     auto costs = [&](auto goal_at, auto goal_q_at) {
+        // a zero weight contributes exactly 0: every dim is evaluated, branch-free (p, q, r only where they are weighed)
         mse = real(0);
+        constexpr int NM = KIND == SCG_QUAD_3D ? 9 : NX;
 #pragma unroll
-        for (int g = 0; g < NX; g += 2) {
-            if (!((h.mse_mask >> g) & 3u)) continue;   // uniform; a zero weight contributes exactly 0
+        for (int d = 0; d < NM; ++d) { const real er = (st[d] - goal_at(d)) * h.mse_weight[d]; mse += er * er; }
+        if (NM < NX && (cfg & CFG_MSE_RATES)) {
 #pragma unroll
-            for (int d = g; d < g + 2 && d < NX; ++d) { const real er = (st[d] - goal_at(d)) * h.mse_weight[d]; mse += er * er; }
+            for (int d = NM; d < NX; ++d) { const real er = (st[d] - goal_at(d)) * h.mse_weight[d]; mse += er * er; }
         }
-        if (h.cost == SCG_COST_RL_REWARD) {
+        if (cfg & CFG_COST_RL) {
             real dist = real(0), dact = real(0);
 #pragma unroll
             for (int d = 0; d < NX; ++d) { const real er = st[d] - goal_at(d); dist += h.rew_state_weight[d] * er * er; }
 #pragma unroll
             for (int j = 0; j < NU; ++j) { const real er = pre[j] - h.u_goal[j]; dact += h.rew_act_weight[j] * er * er; }
             reward = -(dist + dact);
-            if (h.rew_exponential) reward = m_exp(reward);
-        } else if (h.cost == SCG_COST_QUADRATIC) {
+            if (cfg & CFG_REW_EXP) reward = m_exp(reward);
+        } else if (cfg & CFG_COST_QUAD) {
             real lx = real(0), lu = real(0);
             if (LEAN || h.quadratic_diag) {
 #pragma unroll
@@ -501,7 +558,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             if (e.viol) reward -= real(100);   // previous step's flag (F8)
         }
     };
-    if (h.task == SCG_TASK_STABILIZATION) {
+    if (cfg & CFG_STAB) {
         auto g0 = [&](int d) { return h.x_goal0[d]; };
         costs(g0, g0);
     } else {
@@ -516,11 +573,11 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
     }
     // ---- after_step (benchmark_env.py:422-463)
     e.t = t + 1;
-    if (h.n_rows > 0) {
+    if (cfg & CFG_HAS_ROWS) {
         bool violated, almost;
-        eval_constraints<KIND, real, LEAN>(h, cold, st, raw, false, c_out, n, i, violated, almost);
+        eval_constraints<KIND, real, LEAN>(h, cold, st, raw, false, c_out, n, i, violated, almost, cfg);
         e.viol = violated;
-        if (violated) { info |= SCG_INFO_VIOLATION; if (h.done_on_violation) done = true; }
+        if (violated) { info |= SCG_INFO_VIOLATION; if (cfg & CFG_DONE_VIOLATION) done = true; }
         if (!LEAN && h.cost == SCG_COST_RL_REWARD && h.use_constraint_penalty && almost) reward += h.constraint_penalty;
     }
     if (e.t >= h.ctrl_steps) {
@@ -581,7 +638,6 @@ template <int NU, typename real> SCG_DEV void load_action(const real* __restrict
     }
 }
 
-constexpr int ENV_BLOCK = 64;   // 65,536 envs -> 1,024 blocks: 6.9 per SM, within 1.2 % of an even split over 148 SMs
 
 // MODE 0: reset (mask optional)
 template <int KIND, typename real, int ATT>
@@ -623,7 +679,7 @@ k_reset(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold
 
 // K fused control steps (scg_step is K = 1 with the per-step outputs)
 template <int KIND, typename real, int ATT, bool LEAN>
-__global__ void __launch_bounds__(ENV_BLOCK, (LEAN && sizeof(real) == 4) ? 7 : 1)
+__global__ void __launch_bounds__(ENV_BLOCK, (LEAN && sizeof(real) == 4) ? 8 : 1)
 k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, const Buf<real> b, const Roll<real> ro) {
     constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
     const int64_t n = b.n;
@@ -651,15 +707,17 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     bool done = false;
     uint32_t info = 0u;
     Motors<real> mot;
-    const bool full = h.need_full_state != 0 || ro.step_outputs != 0;   // uniform
+    // the uniform switches of the loop in one word (see CFG_*)
+    const uint32_t cfg = h.cfg | (ro.step_outputs ? (CFG_FULL_STATE | CFG_STEP_OUTPUTS) : 0u);
+    const bool full = (cfg & CFG_FULL_STATE) != 0u;
     real* const c_out = ro.step_outputs ? b.c_values : nullptr;
     // software prefetch of the next action (one 16-byte load per 3D env per step)
     real raw[NU], nxt[NU];
     load_action<NU, real>(ro.actions + ii * NU, nxt);
     bool fresh = false;   // obs must come from a reset this step
-    // LEAN: spare initial state for the next episode (drawn ahead, see draw_init_lean) and the
-    // PyBullet-side INIT_ANG_VEL of the current one
-    real spare[LEAN ? NX : 1], ang0[3] = {real(0), real(0), real(0)};
+    // LEAN: spare initial state for the next episode (drawn ahead, see draw_init_lean)
+    __shared__ real sp_buf[LEAN ? Spare<KIND, real, ATT>::N * ENV_BLOCK : 1];
+    real* const sp = sp_buf + threadIdx.x;
     bool spare_ok = false;
     const bool ahead = ro.k_steps >= 16;   // uniform: host-driven single steps draw on demand only
     const bool any_out = ro.reward_out != nullptr || ro.done_out != nullptr || ro.log_out != nullptr;   // uniform
@@ -672,7 +730,7 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
         // after the loop is rebuilt from e there
         real sl[LEAN ? NX : 1];
         real (&sk)[NX] = *reinterpret_cast<real (*)[NX]>(LEAN ? sl : st);
-        step_env<KIND, real, ATT, LEAN>(h, cold, b, key, n, ii, e, raw, full, sk, reward, done, info, mse, mot, c_out);
+        step_env<KIND, real, ATT, LEAN>(h, cold, b, key, n, ii, e, raw, cfg, sk, reward, done, info, mse, mot, c_out);
         ep_ret += reward; ep_len += 1;
         const bool viol = (info & SCG_INFO_VIOLATION) != 0u;
         ep_viol += viol ? 1 : 0;
@@ -690,13 +748,13 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
             s_trunc += (info & SCG_INFO_TRUNCATED) ? 1.f : 0.f;
             s_compl += (info & SCG_INFO_COMPLETED) ? 1.f : 0.f;
             s_vep += ep_viol > 0 ? 1.f : 0.f;
-            if (h.auto_reset) {   // DummyVecEnv.step_wait (dummy_vec_env.py:38-49)
-                if (ro.step_outputs && b.terminal_obs) {
+            if (cfg & CFG_AUTO_RESET) {   // DummyVecEnv.step_wait (dummy_vec_env.py:38-49)
+                if ((cfg & CFG_STEP_OUTPUTS) && b.terminal_obs) {
                     real tl[NX];
 #pragma unroll
                     for (int d = 0; d < NX; ++d) tl[d] = sk[d];
                     write_obs<KIND, real>(h, cold, b.dist_offset, b.terminal_obs, tl, e.t - 1, uint32_t(e.t), key,
-                                          h.reseed_on_reset ? 0u : uint32_t(e.resets - 1), n, ii);
+                                          (cfg & CFG_RESEED) ? 0u : uint32_t(e.resets - 1), n, ii);
                 }
                 if constexpr (!LEAN) {
                     EnvRegs<KIND, real> ec = e;
@@ -711,15 +769,17 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
             }
         }
         if constexpr (LEAN) {
-            const bool restart = done && h.auto_reset != 0;
+            const bool restart = done && (cfg & CFG_AUTO_RESET) != 0u;
             // one inline copy of the draw: at the cadence every lane that used its spare refills it together;
             // a lane that ends two episodes inside one period draws on the spot
             if (!spare_ok && (restart || (ahead && (k & 15) == 0))) {
-                draw_init_lean<KIND, real>(h, key, h.reseed_on_reset ? 0u : uint32_t(e.resets), spare);
+                real init[NX];
+                draw_init_lean<KIND, real>(h, key, (cfg & CFG_RESEED) ? 0u : uint32_t(e.resets), init);
+                spare_store<KIND, real, ATT>(init, sp);
                 spare_ok = true;
             }
             if (restart) {
-                reset_from_spare<KIND, real, ATT>(spare, e, ang0);
+                reset_from_spare<KIND, real, ATT>(sp, e);
                 spare_ok = false;
             }
         }
@@ -727,11 +787,13 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     if constexpr (LEAN) {
         // env.state as observed after the loop: the fresh episode's (PyBullet still holds INIT_ANG_VEL)
         // or the last step's (ang_v = rpy_rates)
-        real ang[3] = {ang0[0], ang0[1], ang0[2]};
-        if (!fresh) {
-            if constexpr (KIND == SCG_QUAD_3D) { ang[0] = e.x[9]; ang[1] = e.x[10]; ang[2] = e.x[11]; }
-            else if constexpr (KIND == SCG_QUAD_2D) { ang[0] = real(0); ang[1] = e.x[5]; ang[2] = real(0); }
-        }
+        real ang[3] = {real(0), real(0), real(0)};
+        if (fresh) spare_ang0<KIND, real>(sp, ang);
+        else if constexpr (KIND == SCG_QUAD_3D) { ang[0] = e.x[9]; ang[1] = e.x[10]; ang[2] = e.x[11]; }
+        else if constexpr (KIND == SCG_QUAD_2D) { ang[1] = e.x[5]; }
+        // sin / cos of the angles are not carried through the loop: the same arithmetic on the stored
+        // pre-round-trip angles gives them back bit for bit
+        if constexpr (KIND == SCG_QUAD_3D) derive_attitude<KIND, real, ATT>(e);
         make_state<KIND, real>(e, ang, st);
     } else if constexpr (KIND == SCG_QUAD_3D) {
         if (!full && !fresh) {   // the final observation needs p, q, r
