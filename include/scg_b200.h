@@ -273,6 +273,9 @@ int scg_symbolic_loss(scg_env* env, const void* x, const void* u, const void* xr
 int scg_measure_fp32_peak(double* tflops_out);
 /* number of kernels this handle has launched (bench.py "gpu_launches") */
 int64_t scg_launch_count(const scg_env* env);
+/* Which instantiation of the step kernel the config selected: 1 = LEAN (no disturbances / adversary / external force,
+ * bounded constraints without tolerances, nominal inertia, diagonal Q and R), 0 = GENERAL.  Same results either way. */
+int scg_kernel_variant(const scg_env* env);
 const char* scg_last_error(void);
 const char* scg_version(void);
 

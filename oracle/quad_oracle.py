@@ -846,6 +846,12 @@ class QuadOracle:
         info["mse"] = np.sum(err ** 2)
         info["collision"] = (None, False)
         self.currently_collided = False
+        if self.gate_geometry and self.QUAD_TYPE == 3:   # extension: the contact scan on the integrated pose
+            from .gate_geometry import drone_collides
+            self.currently_collided = drone_collides(self.pos, np.array(bm.matrix_from_quat(self.quat)).reshape(3, 3),
+                                                     self.EFFECTIVE_GATES_POSITIONS, [g[6] for g in self.GATES],
+                                                     self.EFFECTIVE_OBSTACLES)
+            info["collision"] = (None, self.currently_collided)
         if self.pyb_step_counter > 0.5 * self.PYB_FREQ and self.NUM_GATES > 0 and self.current_gate < self.NUM_GATES:
             self.stepped_through_gate = False
             if self.gate_geometry:

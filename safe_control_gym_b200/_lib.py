@@ -33,7 +33,8 @@ STAT_NAMES = ["episodes", "return", "length", "violation_steps", "mse", "gates",
 
 EXPORTS = ["scg_create", "scg_destroy", "scg_bind_buffers", "scg_set_injection", "scg_reset", "scg_step",
            "scg_rollout", "scg_rollout_host", "scg_stats_reset", "scg_stats_read", "scg_constraints_eval",
-           "scg_symbolic_eval", "scg_symbolic_loss", "scg_measure_fp32_peak", "scg_launch_count", "scg_last_error", "scg_version"]
+           "scg_symbolic_eval", "scg_symbolic_loss", "scg_measure_fp32_peak", "scg_launch_count", "scg_kernel_variant",
+           "scg_last_error", "scg_version"]
 
 
 class Constraint(C.Structure):
@@ -133,6 +134,7 @@ def load():
     lib.scg_measure_fp32_peak.argtypes = [C.POINTER(C.c_double)]
     lib.scg_launch_count.argtypes = [vp]
     lib.scg_launch_count.restype = i64
+    lib.scg_kernel_variant.argtypes = [vp]
     lib.scg_last_error.restype = C.c_char_p
     lib.scg_version.restype = C.c_char_p
     for name in EXPORTS:

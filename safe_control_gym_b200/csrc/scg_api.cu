@@ -194,6 +194,7 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
         for (int q = 0; q < nd; ++q) if (k.dense[q].var == SCG_VAR_STATE) rates = true;
         if (c.cost == SCG_COST_RL_REWARD) for (int d = 9; d < 12; ++d) if (c.rew_state_weight[d] != 0.0) rates = true;
         if (c.cost == SCG_COST_QUADRATIC) rates = true;   // Q weighs the rates (identity by default); goal_reached norms the full state
+        if (c.gate_geometry) rates = true;                // the gate rays need the whole rotation matrix
     }
     h.need_full_state = rates ? 1 : 0;
     h.cfg = (c.task == SCG_TASK_STABILIZATION ? CFG_STAB : 0u) | (c.cost == SCG_COST_RL_REWARD ? CFG_COST_RL : 0u) |
@@ -241,6 +242,7 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
 extern "C" const char* scg_last_error(void) { return g_err.c_str(); }
 extern "C" const char* scg_version(void) { return "scg_b200 0.1 (sm_100a)"; }
 extern "C" int64_t scg_launch_count(const scg_env* env) { return env ? env->launches : 0; }
+extern "C" int scg_kernel_variant(const scg_env* env) { return env && env->lean ? 1 : 0; }
 
 template <typename real> static int upload_params(scg_env* e) {
     Cold<real>* k = new (std::nothrow) Cold<real>;

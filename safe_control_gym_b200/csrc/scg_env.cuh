@@ -388,6 +388,121 @@ SCG_DEV void eval_constraints(const Hot<real>& h, const Cold<real>* __restrict__
     }
 }
 
+// ------------------------------------------------------------------ gate progress + contact scan (row A10)
+// Closed-form stand-ins for the two PyBullet queries of Quadrotor._get_info (quadrotor.py:1046-1092), evaluated on
+// the integrated pose when the gate_geometry extension is on (in DYN the reference's own queries see a frozen
+// drone).  Same shapes and constants as oracle/gate_geometry.py.  Out of line: GENERAL kernel only.
+template <typename real> struct Geo {
+    static constexpr real drone_r = real(0.06), drone_hl = real(0.0125);
+};
+
+template <typename real>
+SCG_DEV bool segment_hits_cylinder(const real (&a)[3], const real (&b)[3], real r, real hl) {
+    const real d0 = b[0] - a[0], d1 = b[1] - a[1], d2 = b[2] - a[2];
+    real t0 = real(0), t1 = real(1);
+    if (d2 == real(0)) {
+        if (m_abs(a[2]) > hl) return false;
+    } else {
+        const real ta = (-hl - a[2]) / d2, tb = (hl - a[2]) / d2;
+        t0 = m_max(t0, m_min(ta, tb)); t1 = m_min(t1, m_max(ta, tb));
+    }
+    const real qa = d0 * d0 + d1 * d1, qb = a[0] * d0 + a[1] * d1, qc = a[0] * a[0] + a[1] * a[1] - r * r;
+    if (qa == real(0)) {
+        if (qc > real(0)) return false;
+    } else {
+        const real disc = qb * qb - qa * qc;
+        if (disc < real(0)) return false;
+        const real s = m_sqrt(disc);
+        t0 = m_max(t0, (-qb - s) / qa); t1 = m_min(t1, (-qb + s) / qa);
+    }
+    return t0 <= t1 && t0 < real(0.9999);
+}
+
+template <typename real> SCG_DEV bool sphere_box(const real (&p)[3], real cx, real cy, real cz, real hx, real hy, real hz) {
+    const real q0 = m_max(m_abs(p[0] - cx) - hx, real(0)), q1 = m_max(m_abs(p[1] - cy) - hy, real(0)),
+               q2 = m_max(m_abs(p[2] - cz) - hz, real(0));
+    return q0 * q0 + q1 * q1 + q2 * q2 < Geo<real>::drone_r * Geo<real>::drone_r;
+}
+template <typename real> SCG_DEV bool sphere_vcyl(const real (&p)[3], real cz, real r, real hl) {
+    const real dxy = m_max(m_sqrt(p[0] * p[0] + p[1] * p[1]) - r, real(0)), dz = m_max(m_abs(p[2] - cz) - hl, real(0));
+    return dxy * dxy + dz * dz < Geo<real>::drone_r * Geo<real>::drone_r;
+}
+
+// (dx, dy, dyaw) of gate / obstacle `idx` for this episode: block idx of its reset stream (quadrotor.py:379-384, 415-421)
+template <typename real>
+SCG_DEV void pose_offsets(const RandP<real>& rp, uint32_t stream, uint32_t idx, const RngKey& key, uint32_t ep, real (&off)[3]) {
+    off[0] = off[1] = off[2] = real(0);
+    if (rp.distrib == SCG_RAND_NONE) return;
+    const U4 w = philox4x32_10(0u, ep, stream, idx, key.seed, key.env);
+    if (rp.distrib == SCG_RAND_UNIFORM) {
+#pragma unroll
+        for (int j = 0; j < 3; ++j) off[j] = rp.a + (rp.b - rp.a) * u01<real>(word_of(w, j));
+    } else {
+        real n[4];
+        normal_pair<real>(w.x, w.y, &n[0], &n[1]);
+        normal_pair<real>(w.z, w.w, &n[2], &n[3]);
+#pragma unroll
+        for (int j = 0; j < 3; ++j) off[j] = rp.a + rp.b * n[j];
+    }
+}
+
+// returns bit 0: a ray of the current gate hit the drone; bit 1: the drone touches a gate, an obstacle or the ground
+template <typename real>
+__device__ __noinline__ uint32_t gate_scan(const Hot<real>& h, const Cold<real>* __restrict__ cold, RngKey key, uint32_t ep,
+                                           real px, real py, real pz, const real* __restrict__ R, uint32_t cur_gate, bool check_gate) {
+    const real pos[3] = {px, py, pz};
+    bool collided = false, passed = false;
+    for (int g = 0; g < h.n_gates; ++g) {
+        const bool is_cur = check_gate && uint32_t(g) == cur_gate;
+        const real* G = cold->gates[g];
+        // nominal broad phase (offsets are bounded only for uniform draws: take the exact pose when in doubt)
+        real off[3];
+        pose_offsets<real>(cold->gate_rand, STREAM_RESET_GATES, uint32_t(g), key, ep, off);
+        const real gx = G[0] + off[0], gy = G[1] + off[1], yaw = G[5] + off[2];
+        const real height = G[6] == real(0) ? real(1.0) : real(0.525);
+        real sy, cy;
+        m_sincos(yaw, &sy, &cy);
+        if (is_cur) {   // quadrotor.py:1060-1092
+            const real dx = real(0.05) * cy, dy = real(0.05) * sy;
+#pragma unroll 1
+            for (int i = -3; i <= 3; ++i) {
+                const real fx = gx + real(i) * dx - pos[0], fy = gy + real(i) * dy - pos[1];
+                const real zl = height - real(0.1875) - pos[2], zh = height + real(0.1875) - pos[2];
+                const real a[3] = {R[0] * fx + R[3] * fy + R[6] * zl, R[1] * fx + R[4] * fy + R[7] * zl, R[2] * fx + R[5] * fy + R[8] * zl};
+                const real b[3] = {R[0] * fx + R[3] * fy + R[6] * zh, R[1] * fx + R[4] * fy + R[7] * zh, R[2] * fx + R[5] * fy + R[8] * zh};
+                passed |= segment_hits_cylinder<real>(a, b, Geo<real>::drone_r, Geo<real>::drone_hl);
+            }
+        }
+        const real ex = pos[0] - gx, ey = pos[1] - gy;
+        if (ex * ex + ey * ey > real(0.35 * 0.35)) continue;
+        const real p[3] = {cy * ex + sy * ey, -sy * ex + cy * ey, pos[2] - (G[2] + height)};
+        bool hit = sphere_box<real>(p, 0, 0, real(0.225), real(0.25), real(0.025), real(0.025)) |
+                   sphere_box<real>(p, 0, 0, real(-0.225), real(0.25), real(0.025), real(0.025)) |
+                   sphere_box<real>(p, real(0.225), 0, 0, real(0.025), real(0.025), real(0.25)) |
+                   sphere_box<real>(p, real(-0.225), 0, 0, real(0.025), real(0.025), real(0.25));
+        hit |= G[6] == real(0) ? sphere_vcyl<real>(p, real(-0.6), real(0.05), real(0.4))
+                               : sphere_box<real>(p, 0, 0, real(-0.4), real(0.075), real(0.075), real(0.125));
+        collided |= hit;
+    }
+    for (int o = 0; o < cold->n_obstacles; ++o) {
+        const real* O = cold->obstacles[o];
+        real off[3];
+        pose_offsets<real>(cold->obstacle_rand, STREAM_RESET_OBSTACLES, uint32_t(o), key, ep, off);
+        const real ex = pos[0] - (O[0] + off[0]), ey = pos[1] - (O[1] + off[1]);
+        if (ex * ex + ey * ey > real(0.35 * 0.35)) continue;
+        real sy, cy;
+        m_sincos(O[5] + off[2], &sy, &cy);
+        const real p[3] = {cy * ex + sy * ey, -sy * ex + cy * ey, pos[2] - (O[2] + real(0.525))};
+        collided |= sphere_vcyl<real>(p, real(0), real(0.05), real(0.4)) |
+                    sphere_box<real>(p, 0, 0, real(-0.4), real(0.075), real(0.075), real(0.125));
+    }
+    // ground plane against the collision cylinder: its support along -z
+    const real r22 = R[8];
+    const real support = Geo<real>::drone_hl * m_abs(r22) + Geo<real>::drone_r * m_sqrt(m_max(real(0), real(1) - r22 * r22));
+    collided |= pos[2] - support < real(0);
+    return (passed ? 1u : 0u) | (collided ? 2u : 0u);
+}
+
 // ------------------------------------------------------------------ disturbances (row A5)
 // Additive, applied in YAML order (DisturbanceList.apply, disturbances.py:69-79).
 // t = ctrl_step_counter (pre-increment); index = Philox counter word 0 for this call.

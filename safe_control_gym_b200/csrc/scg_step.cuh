@@ -457,6 +457,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
     if constexpr (KIND == SCG_QUAD_3D) { ang[0] = e.x[9]; ang[1] = e.x[10]; ang[2] = e.x[11]; }
     else if constexpr (KIND == SCG_QUAD_2D) { ang[0] = real(0); ang[1] = e.x[5]; ang[2] = real(0); }
     else { ang[0] = ang[1] = ang[2] = real(0); }
+    real Rw[(!LEAN && KIND == SCG_QUAD_3D) ? 9 : 1];   // body-to-world rotation for the gate geometry
     if constexpr (KIND == SCG_QUAD_3D) {
         make_state<KIND, real, false>(e, ang, st);
         st[9] = st[10] = st[11] = real(0);
@@ -464,13 +465,30 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             Att3<real> c = e.a3;   // a copy: columns 0 and 1 must not stay live across control steps
             attitude3_complete<real>(c);
             const real* R = c.R;
+            if constexpr (!LEAN) {
+#pragma unroll
+                for (int j = 0; j < 9; ++j) Rw[j] = R[j];
+            }
             st[9] = (R[0] * ang[0] + R[3] * ang[1]) + R[6] * ang[2];
             st[10] = (R[1] * ang[0] + R[4] * ang[1]) + R[7] * ang[2];
             st[11] = (R[2] * ang[0] + R[5] * ang[1]) + R[8] * ang[2];
         }
     } else make_state<KIND, real>(e, ang, st);
     // ---- _get_info (quadrotor.py:1004-1134): goal hold (collision scan is dead in DYN, F5)
-    const bool gate_passed = false;
+    bool gate_passed = false, collided = false;
+    if constexpr (!LEAN && KIND == SCG_QUAD_3D) {
+        if (h.gate_geometry) {   // extension: the contact scan and the gate rays on the integrated pose
+            // pyb_step_counter > 0.5 PYB_FREQ, the counter still at t * S (it advances in after_step, benchmark_env.py:427)
+            //   <=>  2 t > CTRL_FREQ (quadrotor.py:1060)
+            const bool check_gate = 2 * t > h.ctrl_freq && e.gate < uint32_t(h.n_gates);
+            real Rl[9];
+#pragma unroll
+            for (int j = 0; j < 9; ++j) Rl[j] = Rw[j];
+            const uint32_t bits = gate_scan<real>(h, cold, key, ep, st[0], st[2], st[4], Rl, e.gate, check_gate);
+            if (bits & 1u) { e.gate += 1u; gate_passed = true; }
+            collided = (bits & 2u) != 0u;
+        }
+    }
     e.at_goal = false;
     if constexpr (KIND == SCG_QUAD_3D) {
         if (e.gate == uint32_t(h.n_gates) && (cfg & CFG_STAB)) {   // quadrotor.py:1117-1130
@@ -483,7 +501,8 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             if (e.hold > uint32_t(2 * h.ctrl_freq)) e.completed = true;
         }
     }
-    info = (e.at_goal ? SCG_INFO_AT_GOAL : 0u) | (e.completed ? SCG_INFO_COMPLETED : 0u) | (gate_passed ? SCG_INFO_GATE_PASSED : 0u);
+    info = (e.at_goal ? SCG_INFO_AT_GOAL : 0u) | (e.completed ? SCG_INFO_COMPLETED : 0u) | (gate_passed ? SCG_INFO_GATE_PASSED : 0u) |
+           (collided ? SCG_INFO_COLLISION : 0u);
     // ---- _get_done (quadrotor.py:956-1002)
     done = false;
     if ((cfg & (CFG_STAB | CFG_COST_QUAD)) == (CFG_STAB | CFG_COST_QUAD)) {
@@ -502,6 +521,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
         }
         if (oob) { done = true; info |= SCG_INFO_OUT_OF_BOUND; }
     }
+    if (!LEAN && h.done_on_collision && collided) done = true;
     if ((cfg & CFG_DONE_COMPLETION) && e.completed) done = true;
     // ---- info["mse"] (quadrotor.py:1016-1021) and _get_reward (quadrotor.py:886-954); t is still the
     // pre-increment counter.  Written once against a goal accessor so that a stabilisation goal stays
@@ -555,6 +575,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             reward = real(0);
             if (gate_passed) reward += real(100);
             if (e.at_goal) reward += real(100);
+            if (collided) reward -= real(1000);
             if (e.viol) reward -= real(100);   // previous step's flag (F8)
         }
     };
@@ -703,6 +724,7 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     int32_t ep_viol = b.ep_violations ? b.ep_violations[ii] : 0;
     // per-thread statistics (reduced once at the end)
     float s_eps = 0.f, s_ret = 0.f, s_len = 0.f, s_viol = 0.f, s_mse = 0.f, s_trunc = 0.f, s_compl = 0.f, s_vep = 0.f;
+    float s_gates = 0.f, s_coll = 0.f;   // GENERAL kernel with gate_geometry only
     real reward = real(0), mse = real(0);
     bool done = false;
     uint32_t info = 0u;
@@ -736,6 +758,10 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
         ep_viol += viol ? 1 : 0;
         s_viol += viol ? 1.f : 0.f;
         s_mse += float(mse);
+        if constexpr (!LEAN) {
+            s_gates += (info & SCG_INFO_GATE_PASSED) ? 1.f : 0.f;
+            s_coll += (info & SCG_INFO_COLLISION) ? 1.f : 0.f;
+        }
         if (any_out) {
             if (ro.reward_out) ro.reward_out[int64_t(k) * n + ii] = reward;
             if (ro.done_out) ro.done_out[int64_t(k) * n + ii] = done ? 1 : 0;
@@ -825,11 +851,13 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     if (b.ep_violations) b.ep_violations[ii] = ep_viol;
     if (b.stats) {   // warp-shuffle reduction, one atomic per warp per statistic
         const float steps = valid ? float(ro.k_steps) : 0.f;
-        float v[9] = {s_eps, s_ret, s_len, s_viol, s_mse, s_trunc, s_compl, s_vep, steps};
-        const int slot[9] = {SCG_STAT_EPISODES, SCG_STAT_RETURN, SCG_STAT_LENGTH, SCG_STAT_VIOLATION_STEPS,
-                             SCG_STAT_MSE, SCG_STAT_TRUNCATED, SCG_STAT_COMPLETED, SCG_STAT_VIOLATED_EPISODES, SCG_STAT_ENV_STEPS};
+        constexpr int NS = LEAN ? 9 : 11;
+        float v[11] = {s_eps, s_ret, s_len, s_viol, s_mse, s_trunc, s_compl, s_vep, steps, s_gates, s_coll};
+        const int slot[11] = {SCG_STAT_EPISODES, SCG_STAT_RETURN, SCG_STAT_LENGTH, SCG_STAT_VIOLATION_STEPS,
+                              SCG_STAT_MSE, SCG_STAT_TRUNCATED, SCG_STAT_COMPLETED, SCG_STAT_VIOLATED_EPISODES, SCG_STAT_ENV_STEPS,
+                              SCG_STAT_GATES, SCG_STAT_COLLISIONS};
 #pragma unroll
-        for (int j = 0; j < 9; ++j) {
+        for (int j = 0; j < NS; ++j) {
             const float r = warp_sum(valid ? v[j] : 0.f);
             if ((threadIdx.x & 31) == 0 && r != 0.f) atomicAdd(b.stats + slot[j], double(r));
         }

@@ -144,6 +144,11 @@ class BatchedEnvBase:
     def launch_count(self):
         return int(self.lib.scg_launch_count(self._h))
 
+    @property
+    def lean(self):
+        """True when the config selected the LEAN instantiation of the step kernel (scg_kernel_variant)."""
+        return bool(self.lib.scg_kernel_variant(self._h))
+
     def set_injection(self, channel, k, tensor):
         """Feed pre-drawn noise for disturbance ``k`` of ``channel`` ([dim, N]); None = Philox."""
         ch = {"observation": L.CH_OBSERVATION, "action": L.CH_ACTION, "dynamics": L.CH_DYNAMICS}[channel]
@@ -173,11 +178,16 @@ class BatchedEnvBase:
             "task_completed": bit(L.INFO_COMPLETED),
             "goal_reached": bit(L.INFO_GOAL_REACHED),
             "out_of_bound": bit(L.INFO_OUT_OF_BOUND),
-            "current_target_gate_id": lambda: (self.buf_flags >> L.FLAG_GATE_SHIFT) & 0xFF,
+            "current_target_gate_id": self._gate_id,
             "terminal_observation": lambda: self.buf_terminal_obs.t(),
             "state": lambda: self.buf_env_state.t(),
             "info_bits": lambda: bits,
         })
+
+    def _gate_id(self):
+        """info["current_target_gate_id"]: the gate index, -1 once all gates are passed (quadrotor.py:1093-1112)."""
+        g = ((self.buf_flags >> L.FLAG_GATE_SHIFT) & 0xFF).to(torch.int32)
+        return torch.where(g >= int(getattr(self, "NUM_GATES", 0)), torch.full_like(g, -1), g)
 
     def reset(self, mask=None, inject_init=None, inject_inertia=None, inject_offsets=None):
         """Quadrotor.reset() for every env (or those with ``mask[i] != 0``)."""

@@ -1,0 +1,81 @@
+"""Row A10 with the gate_geometry extension: gate progress (ray test against the drone's collision cylinder), the
+contact scan (gates, obstacles, ground) and their consequences (reward, done_on_collision, auto-reset, randomised
+gate / obstacle poses per episode) -- kernel against the numpy oracle on the same Philox counters."""
+import numpy as np
+import pytest
+import torch
+
+from oracle.quad_oracle import PhiloxEnvDraws, QuadOracle
+
+pytestmark = pytest.mark.gpu
+
+M, G = 0.03454, 9.8
+
+
+def _kwargs(randomized):
+    """Drones start 0.7 m in front of level0's first gate (tall, yaw -1.57: its opening faces +x) and fly at 1 m/s
+    through / into it; hover thrust keeps the height."""
+    u = lambda lo, hi: dict(distrib="uniform", low=lo, high=hi)
+    return dict(quad_type=3, ctrl_freq=60, pyb_freq=240, episode_len_sec=3, cost="competition", task="stabilization",
+                task_info=dict(stabilization_goal=[1.6, -2.5, 1.0], stabilization_goal_tolerance=0.15),
+                init_state=dict(init_x=-0.2, init_x_dot=1.0, init_y=-2.5, init_y_dot=0, init_z=1.0, init_z_dot=0,
+                                init_phi=0, init_theta=0, init_psi=0, init_p=0, init_q=0, init_r=0),
+                randomized_init=True,
+                init_state_randomization_info={"init_x": u(-0.05, 0.05), "init_y": u(-0.35, 0.35), "init_z": u(-0.35, 0.35),
+                                               "init_x_dot": u(-0.2, 0.4), "init_theta": u(-0.2, 0.2), "init_phi": u(-0.2, 0.2)},
+                gates=[[0.5, -2.5, 0, 0, 0, -1.57, 0], [1.3, -2.5, 0, 0, 0, -1.57, 1]],
+                obstacles=[[0.9, -2.3, 0, 0, 0, 0], [0.9, -2.75, 0, 0, 0, 0.3]],
+                randomized_gates_and_obstacles=randomized,
+                gates_and_obstacles_randomization_info=dict(gates=u(-0.1, 0.1), obstacles=u(-0.1, 0.1)),
+                constraints=[dict(constraint_form="default_constraint", constrained_variable="input")],
+                done_on_violation=False, done_on_completion=True, done_on_collision=True, done_on_out_of_bound=False,
+                normalized_rl_action_space=False, gate_geometry=True, seed=77)
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("randomized", [False, True])
+def test_gate_progress_and_collisions_match_oracle(dtype, randomized):
+    from safe_control_gym_b200.envs.quadrotor import BatchedQuadrotor
+    n, steps, base = 96, 110, 100
+    kw = _kwargs(randomized)
+    env = BatchedQuadrotor(num_envs=n, dtype=dtype, attitude="fast", seed_offset=base, auto_reset=True, **kw)
+    assert not env.lean
+    okw = dict(kw)
+    seed = okw.pop("seed")
+    refs = [QuadOracle(draws=PhiloxEnvDraws(seed, base + i), **okw) for i in range(n)]
+    env.reset()
+    for r in refs:
+        r.reset()
+    act = np.full((n, 4), M * G / 4)
+    passed = collided = resets = 0
+    dropped = set()   # fp32 only: a lane whose contact / ray decision fell within rounding of its threshold
+    for t in range(steps):
+        obs, rew, done, info = env.step(act)
+        g_pass = info["stepped_through_gate"].cpu().numpy()
+        g_col = info["collision"].cpu().numpy()
+        g_id = info["current_target_gate_id"].cpu().numpy()
+        g_done, g_rew = done.cpu().numpy(), rew.double().cpu().numpy()
+        for i, r in enumerate(refs):
+            if i in dropped:
+                continue
+            _, o_rew, o_done, o_info = r.step(act[i])
+            same = (bool(g_pass[i]) == bool(r.stepped_through_gate) and bool(g_col[i]) == bool(r.currently_collided)
+                    and bool(g_done[i]) == bool(o_done) and g_rew[i] == float(o_rew))
+            if not same and dtype == torch.float32:
+                dropped.add(i)
+                continue
+            assert same, (t, i, g_pass[i], r.stepped_through_gate, g_col[i], r.currently_collided, g_done[i], o_done, g_rew[i], o_rew)
+            passed += int(r.stepped_through_gate)
+            collided += int(r.currently_collided)
+            if o_done:
+                resets += 1
+                r.reset()
+            else:
+                assert int(g_id[i]) == int(o_info["current_target_gate_id"]), (t, i)
+    assert passed >= 10 and collided >= 10 and resets >= 10, (passed, collided, resets)
+    assert len(dropped) <= 2, dropped
+    st = env.stats()
+    print(f"gates {dtype} randomized={randomized}: {passed} gate passes, {collided} contacts, {resets} resets; stats {st['gates']:.0f} / {st['collisions']:.0f}")
+    if not dropped:
+        assert st["gates"] == passed and st["collisions"] == collided
+    env.close()
