@@ -1,0 +1,63 @@
+"""BASELINE config 4 in small: Quadrotor 2D DYN with impulse + step action disturbances (offsets drawn per episode)
+and per-episode mass / Iyy that reach the integrator (dyn_uses_episode_inertia extension) -- the
+GENERAL kernel against the numpy oracle on the same Philox counters, free-running with auto-reset."""
+import numpy as np
+import pytest
+import torch
+
+from oracle.quad_oracle import PhiloxEnvDraws, QuadOracle
+
+pytestmark = pytest.mark.gpu
+
+U = lambda lo, hi: dict(distrib="uniform", low=lo, high=hi)
+CFG = dict(quad_type=2, ctrl_freq=60, pyb_freq=240, episode_len_sec=1, task="stabilization", cost="rl_reward",
+           task_info=dict(stabilization_goal=[0, 1], stabilization_goal_tolerance=0.05),
+           init_state=dict(init_x=0, init_x_dot=0, init_z=1.0, init_z_dot=0, init_theta=0, init_theta_dot=0),
+           randomized_init=True,
+           init_state_randomization_info={"init_x": U(-0.3, 0.3), "init_z": U(-0.3, 0.3), "init_theta": U(-0.2, 0.2),
+                                          "init_theta_dot": U(-0.5, 0.5)},
+           randomized_inertial_prop=True, dyn_uses_episode_inertia=True,
+           inertial_prop_randomization_info={"M": U(-0.005, 0.005), "Iyy": U(-1e-6, 1e-6)},
+           disturbances={"action": [dict(disturbance_func="impulse", magnitude=0.01, step_offset=None, duration=2, decay_rate=0.9),
+                                    dict(disturbance_func="step", magnitude=0.005, step_offset=None)]},
+           constraints=[dict(constraint_form="default_constraint", constrained_variable="input"),
+                        dict(constraint_form="default_constraint", constrained_variable="state")],
+           done_on_violation=False, done_on_out_of_bound=True, rew_exponential=True, seed=44)
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float64, 1e-10), (torch.float32, 2e-4)])
+def test_config4_matches_oracle(dtype, tol):
+    from safe_control_gym_b200.envs.quadrotor import BatchedQuadrotor
+    n, steps, base = 64, 150, 500
+    env = BatchedQuadrotor(num_envs=n, dtype=dtype, auto_reset=True, seed_offset=base, info_in_reset=True, **CFG)
+    assert not env.lean
+    kw = {k: v for k, v in CFG.items() if k != "seed"}
+    lanes = [0, 7, 31, 32, 63]
+    refs = {i: QuadOracle(draws=PhiloxEnvDraws(CFG["seed"], base + i), info_in_reset=True, **kw) for i in lanes}
+    hover = env.MASS * 9.8 / 2
+    rng = np.random.default_rng(9)
+    acts = np.clip(hover + rng.normal(0, 0.01, size=(steps, n, 2)), 0, 4 * hover)
+    obs, _ = env.reset()
+    for i in lanes:
+        o_obs, _ = refs[i].reset()
+        assert np.max(np.abs(obs[i].double().cpu().numpy() - o_obs)) <= tol
+    worst, resets = 0.0, 0
+    for t in range(steps):
+        obs, rew, done, info = env.step(acts[t])
+        term = info["terminal_observation"]
+        for i in lanes:
+            o_obs, o_rew, o_done, o_info = refs[i].step(acts[t, i])
+            assert bool(done[i]) == bool(o_done), (t, i)
+            assert int(info["constraint_violation"][i]) == int(o_info["constraint_violation"]), (t, i)
+            got = (term if o_done else obs)[i].double().cpu().numpy()
+            err = float(np.max(np.abs(got - o_obs) / np.maximum(1.0, np.abs(o_obs))))
+            err = max(err, abs(float(rew[i]) - o_rew) / max(1.0, abs(o_rew)))
+            worst = max(worst, err)
+            assert err <= tol, (str(dtype), t, i, err)
+            if o_done:
+                resets += 1
+                r_obs, _ = refs[i].reset()
+                assert np.max(np.abs(obs[i].double().cpu().numpy() - r_obs)) <= tol
+    assert resets >= 5   # episodes are 60 steps long: every lane restarts at least twice, with new mass / offsets
+    print(f"config 4 {dtype}: worst rel err {worst:.2e}, {resets} auto-resets")
+    env.close()
