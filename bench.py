@@ -101,10 +101,20 @@ def make_actions(torch, n, k, device, seed, std=0.005):
     return a.clamp_(0.0281616878, 0.1483414471)
 
 
+def host_threads():
+    """All host threads this process may use (torchrun exports OMP_NUM_THREADS=1 for its workers: the CPU arm
+    asks for its thread count explicitly instead of inheriting that)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def cpu_reference(sample_envs, sample_steps, repeats, threads=0):
     """Times the C/OpenMP oracle on the host cores: env-steps/s over `repeats` rollouts of a bounded
     sample (sample_envs envs x sample_steps control steps) of the same workload."""
     import numpy as np
+    threads = threads or host_threads()
     from oracle.c_oracle import COracle3D
     from oracle.quad_oracle import QuadOracle
     kw = env_kwargs()
