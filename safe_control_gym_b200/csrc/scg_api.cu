@@ -180,8 +180,23 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
     h.any_gate_rand = (c.gate_rand.distrib != SCG_RAND_NONE || c.obstacle_rand.distrib != SCG_RAND_NONE) ? 1 : 0;
     if (c.n_gates < 0 || c.n_gates > SCG_MAX_GATES || c.n_obstacles < 0 || c.n_obstacles > SCG_MAX_OBSTACLES)
         return fail(SCG_ERR_BAD_CONFIG, "too many gates / obstacles");
-    for (int g = 0; g < c.n_gates; ++g) for (int j = 0; j < 7; ++j) k.gates[g][j] = real(c.gates[g][j]);
-    for (int g = 0; g < c.n_obstacles; ++g) for (int j = 0; j < 6; ++j) k.obstacles[g][j] = real(c.obstacles[g][j]);
+    for (int g = 0; g < c.n_gates; ++g) {
+        for (int j = 0; j < 7; ++j) k.gates[g][j] = real(c.gates[g][j]);
+        k.gates[g][7] = real(std::cos(c.gates[g][5])); k.gates[g][8] = real(std::sin(c.gates[g][5]));
+    }
+    for (int g = 0; g < c.n_obstacles; ++g) {
+        for (int j = 0; j < 6; ++j) k.obstacles[g][j] = real(c.obstacles[g][j]);
+        k.obstacles[g][6] = real(std::cos(c.obstacles[g][5])); k.obstacles[g][7] = real(std::sin(c.obstacles[g][5]));
+    }
+    {   // broad phase of the contact scan: 0.35 m covers every part of a gate / obstacle plus the drone; a uniform
+        // pose offset widens it by sqrt(2) max|offset|, a normal one is unbounded
+        auto broad2 = [](const scg_rand& r) -> double {
+            if (r.distrib == SCG_RAND_NONE) return 0.35 * 0.35;
+            if (r.distrib == SCG_RAND_UNIFORM) { const double m = std::max(std::fabs(r.a), std::fabs(r.b)); const double d = 0.35 + 1.4143 * m; return d * d; }
+            return double(INFINITY);
+        };
+        k.gate_broad2 = real(broad2(c.gate_rand)); k.obstacle_broad2 = real(broad2(c.obstacle_rand));
+    }
     k.n_obstacles = c.n_obstacles;
     h.seed = c.seed; h.env_id_base_lo = uint32_t(c.env_id_base & 0xFFFFFFFFll);
     h.viol_thr = real(5e-9);
@@ -201,7 +216,8 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
             (c.cost == SCG_COST_QUADRATIC ? CFG_COST_QUAD : 0u) | (c.rew_exponential ? CFG_REW_EXP : 0u) |
             (c.done_on_out_of_bound ? CFG_OOB : 0u) | (c.done_on_completion ? CFG_DONE_COMPLETION : 0u) |
             (c.done_on_violation ? CFG_DONE_VIOLATION : 0u) | (c.auto_reset ? CFG_AUTO_RESET : 0u) |
-            (rates ? CFG_FULL_STATE : 0u) | (c.reseed_on_reset ? CFG_RESEED : 0u) | ((h.mse_mask & 0xE00u) ? CFG_MSE_RATES : 0u);
+            (rates ? CFG_FULL_STATE : 0u) | (c.reseed_on_reset ? CFG_RESEED : 0u) | ((h.mse_mask & 0xE00u) ? CFG_MSE_RATES : 0u) |
+            ((c.gate_geometry && c.env_kind == SCG_QUAD_3D) ? CFG_GATE_GEOMETRY : 0u);
     // ---- LEAN kernel specialisation (scg_step.cuh): none of the rare features is configured
     bool symmetric = false;
     for (int q = 0; q < nb; ++q) symmetric |= h.bounded[q].symmetric != 0;
@@ -234,7 +250,7 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
     // (the extended observation lives in write_obs, outside the loop)
     *lean_out = c.n_dist[0] == 0 && c.n_dist[1] == 0 && c.n_dist[2] == 0 && c.adversary_channel < 0 && !c.dyn_applies_force &&
                 !(h.any_init_rand & 2) && !h.any_inertia_rand &&
-                !c.dyn_uses_episode_inertia && nd == 0 && !h.any_tolerance && !symmetric && same_strict && h.quadratic_diag && !c.gate_geometry &&
+                !c.dyn_uses_episode_inertia && nd == 0 && !h.any_tolerance && !symmetric && same_strict && h.quadratic_diag &&
                 !(c.env_kind == SCG_CARTPOLE && (h.any_inertia_rand != 0));
     return SCG_OK;
 }

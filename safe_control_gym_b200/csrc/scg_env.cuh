@@ -446,36 +446,41 @@ SCG_DEV void pose_offsets(const RandP<real>& rp, uint32_t stream, uint32_t idx, 
     }
 }
 
-// returns bit 0: a ray of the current gate hit the drone; bit 1: the drone touches a gate, an obstacle or the ground
+// returns bit 0: a ray of the current gate hit the drone; bit 1: the drone touches a gate, an obstacle or the ground.
+// Broad phase first: an object whose NOMINAL axis is farther than `broad2` (0.35 m + the largest pose offset) from the
+// drone is skipped before its pose offsets are even drawn -- almost every (env, object) pair of a step.
 template <typename real>
 __device__ __noinline__ uint32_t gate_scan(const Hot<real>& h, const Cold<real>* __restrict__ cold, RngKey key, uint32_t ep,
-                                           real px, real py, real pz, const real* __restrict__ R, uint32_t cur_gate, bool check_gate) {
-    const real pos[3] = {px, py, pz};
+                                           real px, real py, real pz, real r0, real r1, real r2, real r3, real r4, real r5,
+                                           real r6, real r7, real r8, uint32_t cur_gate, bool check_gate) {
     bool collided = false, passed = false;
     for (int g = 0; g < h.n_gates; ++g) {
-        const bool is_cur = check_gate && uint32_t(g) == cur_gate;
         const real* G = cold->gates[g];
-        // nominal broad phase (offsets are bounded only for uniform draws: take the exact pose when in doubt)
-        real off[3];
-        pose_offsets<real>(cold->gate_rand, STREAM_RESET_GATES, uint32_t(g), key, ep, off);
-        const real gx = G[0] + off[0], gy = G[1] + off[1], yaw = G[5] + off[2];
+        const real nx = px - G[0], ny = py - G[1];
+        if (nx * nx + ny * ny > cold->gate_broad2) continue;
+        real gx = G[0], gy = G[1], cy = G[7], sy = G[8];
+        if (cold->gate_rand.distrib != SCG_RAND_NONE) {
+            real off[3];
+            pose_offsets<real>(cold->gate_rand, STREAM_RESET_GATES, uint32_t(g), key, ep, off);
+            gx += off[0]; gy += off[1];
+            m_sincos(G[5] + off[2], &sy, &cy);
+        }
         const real height = G[6] == real(0) ? real(1.0) : real(0.525);
-        real sy, cy;
-        m_sincos(yaw, &sy, &cy);
-        if (is_cur) {   // quadrotor.py:1060-1092
+        if (check_gate && uint32_t(g) == cur_gate) {   // quadrotor.py:1060-1092
             const real dx = real(0.05) * cy, dy = real(0.05) * sy;
+            const real zl = height - real(0.1875) - pz, zh = height + real(0.1875) - pz;
 #pragma unroll 1
             for (int i = -3; i <= 3; ++i) {
-                const real fx = gx + real(i) * dx - pos[0], fy = gy + real(i) * dy - pos[1];
-                const real zl = height - real(0.1875) - pos[2], zh = height + real(0.1875) - pos[2];
-                const real a[3] = {R[0] * fx + R[3] * fy + R[6] * zl, R[1] * fx + R[4] * fy + R[7] * zl, R[2] * fx + R[5] * fy + R[8] * zl};
-                const real b[3] = {R[0] * fx + R[3] * fy + R[6] * zh, R[1] * fx + R[4] * fy + R[7] * zh, R[2] * fx + R[5] * fy + R[8] * zh};
+                const real fx = gx + real(i) * dx - px, fy = gy + real(i) * dy - py;
+                const real bx = r0 * fx + r3 * fy, by = r1 * fx + r4 * fy, bz = r2 * fx + r5 * fy;   // R^T (horizontal part)
+                const real a[3] = {bx + r6 * zl, by + r7 * zl, bz + r8 * zl};
+                const real b[3] = {bx + r6 * zh, by + r7 * zh, bz + r8 * zh};
                 passed |= segment_hits_cylinder<real>(a, b, Geo<real>::drone_r, Geo<real>::drone_hl);
             }
         }
-        const real ex = pos[0] - gx, ey = pos[1] - gy;
+        const real ex = px - gx, ey = py - gy;
         if (ex * ex + ey * ey > real(0.35 * 0.35)) continue;
-        const real p[3] = {cy * ex + sy * ey, -sy * ex + cy * ey, pos[2] - (G[2] + height)};
+        const real p[3] = {cy * ex + sy * ey, -sy * ex + cy * ey, pz - (G[2] + height)};
         bool hit = sphere_box<real>(p, 0, 0, real(0.225), real(0.25), real(0.025), real(0.025)) |
                    sphere_box<real>(p, 0, 0, real(-0.225), real(0.25), real(0.025), real(0.025)) |
                    sphere_box<real>(p, real(0.225), 0, 0, real(0.025), real(0.025), real(0.25)) |
@@ -486,20 +491,24 @@ __device__ __noinline__ uint32_t gate_scan(const Hot<real>& h, const Cold<real>*
     }
     for (int o = 0; o < cold->n_obstacles; ++o) {
         const real* O = cold->obstacles[o];
-        real off[3];
-        pose_offsets<real>(cold->obstacle_rand, STREAM_RESET_OBSTACLES, uint32_t(o), key, ep, off);
-        const real ex = pos[0] - (O[0] + off[0]), ey = pos[1] - (O[1] + off[1]);
+        const real nx = px - O[0], ny = py - O[1];
+        if (nx * nx + ny * ny > cold->obstacle_broad2) continue;
+        real ox = O[0], oy = O[1], cy = O[6], sy = O[7];
+        if (cold->obstacle_rand.distrib != SCG_RAND_NONE) {
+            real off[3];
+            pose_offsets<real>(cold->obstacle_rand, STREAM_RESET_OBSTACLES, uint32_t(o), key, ep, off);
+            ox += off[0]; oy += off[1];
+            m_sincos(O[5] + off[2], &sy, &cy);
+        }
+        const real ex = px - ox, ey = py - oy;
         if (ex * ex + ey * ey > real(0.35 * 0.35)) continue;
-        real sy, cy;
-        m_sincos(O[5] + off[2], &sy, &cy);
-        const real p[3] = {cy * ex + sy * ey, -sy * ex + cy * ey, pos[2] - (O[2] + real(0.525))};
+        const real p[3] = {cy * ex + sy * ey, -sy * ex + cy * ey, pz - (O[2] + real(0.525))};
         collided |= sphere_vcyl<real>(p, real(0), real(0.05), real(0.4)) |
                     sphere_box<real>(p, 0, 0, real(-0.4), real(0.075), real(0.075), real(0.125));
     }
     // ground plane against the collision cylinder: its support along -z
-    const real r22 = R[8];
-    const real support = Geo<real>::drone_hl * m_abs(r22) + Geo<real>::drone_r * m_sqrt(m_max(real(0), real(1) - r22 * r22));
-    collided |= pos[2] - support < real(0);
+    const real support = Geo<real>::drone_hl * m_abs(r8) + Geo<real>::drone_r * m_sqrt(m_max(real(0), real(1) - r8 * r8));
+    collided |= pz - support < real(0);
     return (passed ? 1u : 0u) | (collided ? 2u : 0u);
 }
 

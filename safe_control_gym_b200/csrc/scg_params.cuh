@@ -88,6 +88,7 @@ enum : uint32_t {
     CFG_UBOX = 1u << 11,            // LEAN: an input dim carries a bound
     CFG_MSE_RATES = 1u << 12,       // 3D: info["mse"] weighs p, q, r
     CFG_STEP_OUTPUTS = 1u << 13,    // set per launch
+    CFG_GATE_GEOMETRY = 1u << 14,   // 3D: gate rays + contact scan on the integrated pose (extension)
 };
 
 template <typename real> struct DenseRow {     // linear: c = a . x - b ; quadratic: c = x' P x - b
@@ -113,7 +114,8 @@ template <typename real> struct Cold {
     real Q[SCG_MAX_NX * SCG_MAX_NX], R[SCG_MAX_NU * SCG_MAX_NU];
     DistP<real> dist[3][SCG_MAX_DIST];
     RandP<real> gate_rand, obstacle_rand;
-    real gates[SCG_MAX_GATES][7], obstacles[SCG_MAX_OBSTACLES][6];
+    real gates[SCG_MAX_GATES][9], obstacles[SCG_MAX_OBSTACLES][8];   // reference rows + (cos, sin) of the nominal yaw
+    real gate_broad2, obstacle_broad2;   // squared horizontal distance from the NOMINAL axis beyond which nothing can touch (inf: unbounded draws)
     int32_t n_obstacles;
     const real* x_goal;             // [n_goal_rows][nx] device
 };

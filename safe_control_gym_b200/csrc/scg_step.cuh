@@ -457,7 +457,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
     if constexpr (KIND == SCG_QUAD_3D) { ang[0] = e.x[9]; ang[1] = e.x[10]; ang[2] = e.x[11]; }
     else if constexpr (KIND == SCG_QUAD_2D) { ang[0] = real(0); ang[1] = e.x[5]; ang[2] = real(0); }
     else { ang[0] = ang[1] = ang[2] = real(0); }
-    real Rw[(!LEAN && KIND == SCG_QUAD_3D) ? 9 : 1];   // body-to-world rotation for the gate geometry
+    real Rw[KIND == SCG_QUAD_3D ? 9 : 1];   // body-to-world rotation for the gate geometry (dead otherwise)
     if constexpr (KIND == SCG_QUAD_3D) {
         make_state<KIND, real, false>(e, ang, st);
         st[9] = st[10] = st[11] = real(0);
@@ -465,10 +465,8 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             Att3<real> c = e.a3;   // a copy: columns 0 and 1 must not stay live across control steps
             attitude3_complete<real>(c);
             const real* R = c.R;
-            if constexpr (!LEAN) {
 #pragma unroll
-                for (int j = 0; j < 9; ++j) Rw[j] = R[j];
-            }
+            for (int j = 0; j < 9; ++j) Rw[j] = R[j];
             st[9] = (R[0] * ang[0] + R[3] * ang[1]) + R[6] * ang[2];
             st[10] = (R[1] * ang[0] + R[4] * ang[1]) + R[7] * ang[2];
             st[11] = (R[2] * ang[0] + R[5] * ang[1]) + R[8] * ang[2];
@@ -476,15 +474,13 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
     } else make_state<KIND, real>(e, ang, st);
     // ---- _get_info (quadrotor.py:1004-1134): goal hold (collision scan is dead in DYN, F5)
     bool gate_passed = false, collided = false;
-    if constexpr (!LEAN && KIND == SCG_QUAD_3D) {
-        if (h.gate_geometry) {   // extension: the contact scan and the gate rays on the integrated pose
+    if constexpr (KIND == SCG_QUAD_3D) {
+        if (cfg & CFG_GATE_GEOMETRY) {   // extension: the contact scan and the gate rays on the integrated pose (implies `full`)
             // pyb_step_counter > 0.5 PYB_FREQ, the counter still at t * S (it advances in after_step, benchmark_env.py:427)
             //   <=>  2 t > CTRL_FREQ (quadrotor.py:1060)
             const bool check_gate = 2 * t > h.ctrl_freq && e.gate < uint32_t(h.n_gates);
-            real Rl[9];
-#pragma unroll
-            for (int j = 0; j < 9; ++j) Rl[j] = Rw[j];
-            const uint32_t bits = gate_scan<real>(h, cold, key, ep, st[0], st[2], st[4], Rl, e.gate, check_gate);
+            const uint32_t bits = gate_scan<real>(h, cold, key, ep, st[0], st[2], st[4], Rw[0], Rw[1], Rw[2], Rw[3], Rw[4], Rw[5],
+                                                  Rw[6], Rw[7], Rw[8], e.gate, check_gate);
             if (bits & 1u) { e.gate += 1u; gate_passed = true; }
             collided = (bits & 2u) != 0u;
         }
@@ -521,7 +517,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
         }
         if (oob) { done = true; info |= SCG_INFO_OUT_OF_BOUND; }
     }
-    if (!LEAN && h.done_on_collision && collided) done = true;
+    if (collided && h.done_on_collision) done = true;
     if ((cfg & CFG_DONE_COMPLETION) && e.completed) done = true;
     // ---- info["mse"] (quadrotor.py:1016-1021) and _get_reward (quadrotor.py:886-954); t is still the
     // pre-increment counter.  Written once against a goal accessor so that a stabilisation goal stays
@@ -724,7 +720,7 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     int32_t ep_viol = b.ep_violations ? b.ep_violations[ii] : 0;
     // per-thread statistics (reduced once at the end)
     float s_eps = 0.f, s_ret = 0.f, s_len = 0.f, s_viol = 0.f, s_mse = 0.f, s_trunc = 0.f, s_compl = 0.f, s_vep = 0.f;
-    float s_gates = 0.f, s_coll = 0.f;   // GENERAL kernel with gate_geometry only
+    float s_gates = 0.f, s_coll = 0.f;   // gate_geometry only
     real reward = real(0), mse = real(0);
     bool done = false;
     uint32_t info = 0u;
@@ -758,7 +754,7 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
         ep_viol += viol ? 1 : 0;
         s_viol += viol ? 1.f : 0.f;
         s_mse += float(mse);
-        if constexpr (!LEAN) {
+        if (cfg & CFG_GATE_GEOMETRY) {
             s_gates += (info & SCG_INFO_GATE_PASSED) ? 1.f : 0.f;
             s_coll += (info & SCG_INFO_COLLISION) ? 1.f : 0.f;
         }
@@ -851,7 +847,7 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     if (b.ep_violations) b.ep_violations[ii] = ep_viol;
     if (b.stats) {   // warp-shuffle reduction, one atomic per warp per statistic
         const float steps = valid ? float(ro.k_steps) : 0.f;
-        constexpr int NS = LEAN ? 9 : 11;
+        constexpr int NS = 11;
         float v[11] = {s_eps, s_ret, s_len, s_viol, s_mse, s_trunc, s_compl, s_vep, steps, s_gates, s_coll};
         const int slot[11] = {SCG_STAT_EPISODES, SCG_STAT_RETURN, SCG_STAT_LENGTH, SCG_STAT_VIOLATION_STEPS,
                               SCG_STAT_MSE, SCG_STAT_TRUNCATED, SCG_STAT_COMPLETED, SCG_STAT_VIOLATED_EPISODES, SCG_STAT_ENV_STEPS,

@@ -39,7 +39,6 @@ def test_gate_progress_and_collisions_match_oracle(dtype, randomized):
     n, steps, base = 96, 110, 100
     kw = _kwargs(randomized)
     env = BatchedQuadrotor(num_envs=n, dtype=dtype, attitude="fast", seed_offset=base, auto_reset=True, **kw)
-    assert not env.lean
     okw = dict(kw)
     seed = okw.pop("seed")
     refs = [QuadOracle(draws=PhiloxEnvDraws(seed, base + i), **okw) for i in range(n)]
