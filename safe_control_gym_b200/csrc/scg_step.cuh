@@ -696,7 +696,7 @@ k_reset(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold
 
 // K fused control steps (scg_step is K = 1 with the per-step outputs)
 template <int KIND, typename real, int ATT, bool LEAN>
-__global__ void __launch_bounds__(ENV_BLOCK, (LEAN && sizeof(real) == 4) ? 8 : 1)
+__global__ void __launch_bounds__(ENV_BLOCK, sizeof(real) == 4 ? 8 : 1)
 k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, const Buf<real> b, const Roll<real> ro) {
     constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
     const int64_t n = b.n;
