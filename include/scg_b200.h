@@ -272,6 +272,12 @@ int scg_symbolic_loss(scg_env* env, const void* x, const void* u, const void* xr
  * compute-bound fused rollout, since MEASURED_PEAKS.json carries no non-tensor fp32 figure. */
 int scg_measure_fp32_peak(double* tflops_out);
 /* number of kernels this handle has launched (bench.py "gpu_launches") */
+/* info["current_target_gate_in_range"] / ["current_target_gate_pos"] of Quadrotor._get_info (quadrotor.py:1093-1112)
+ * for every env, from the bound state / flags / episode buffers: out_pose [6][n] (precision of the env) = the
+ * current gate's true pose (x, y, z + height, r, p, yaw incl. this episode's offsets) when the drone is within the
+ * 0.45 m visibility range of the gate body, else its nominal row; zeros once all gates are passed.
+ * out_in_range [n] u8.  Either output may be NULL.  quad_type 3 only. */
+int scg_gate_info(scg_env* env, void* out_pose, uint8_t* out_in_range, void* stream);
 int64_t scg_launch_count(const scg_env* env);
 /* Which instantiation of the step kernel the config selected: 1 = LEAN (no disturbances / adversary / external force,
  * bounded constraints without tolerances, nominal inertia, diagonal Q and R), 0 = GENERAL.  Same results either way. */

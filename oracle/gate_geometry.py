@@ -105,3 +105,28 @@ def drone_collides(pos, R, gates_eff, gate_types, obstacles_eff):
     # ground plane z = 0 against the collision cylinder: its support along -z
     support = DRONE_HL * abs(R[2, 2]) + DRONE_R * np.sqrt(max(0.0, 1.0 - R[2, 2] ** 2))
     return bool(pos[2] - support < 0.0)
+
+
+VISIBILITY_RANGE = 0.45       # quadrotor.py:1094
+
+
+def _dist_box(p, centre, half):
+    q = np.maximum(np.abs(p - np.asarray(centre)) - np.asarray(half), 0.0)
+    return float(np.sqrt(q @ q))
+
+
+def _dist_vcyl(p, centre, r, hl):
+    q = p - np.asarray(centre)
+    dxy = max(np.hypot(q[0], q[1]) - r, 0.0)
+    dz = max(abs(q[2]) - hl, 0.0)
+    return float(np.sqrt(dxy * dxy + dz * dz))
+
+
+def gate_in_range(pos, gate_eff, gate_type):
+    """getClosestPoints(gate, drone, distance=0.45) non-empty (quadrotor.py:1095-1100): distance from the drone sphere to
+    the gate's bars and support."""
+    p = _local(np.asarray(pos, dtype=float), gate_eff[0], gate_eff[1], gate_eff[2], gate_eff[5])
+    d = min(_dist_box(p, (0, 0, 0.225), (0.25, 0.025, 0.025)), _dist_box(p, (0, 0, -0.225), (0.25, 0.025, 0.025)),
+            _dist_box(p, (0.225, 0, 0), (0.025, 0.025, 0.25)), _dist_box(p, (-0.225, 0, 0), (0.025, 0.025, 0.25)))
+    d = min(d, _dist_vcyl(p, (0, 0, -0.6), 0.05, 0.4) if gate_type == 0 else _dist_box(p, (0, 0, -0.4), (0.075, 0.075, 0.125)))
+    return bool(d - DRONE_R <= VISIBILITY_RANGE)

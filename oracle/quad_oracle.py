@@ -865,9 +865,18 @@ class QuadOracle:
         if self.current_gate < self.NUM_GATES:
             info["current_target_gate_id"] = self.current_gate
             info["current_target_gate_type"] = self.GATES[self.current_gate][6]
+            if self.gate_geometry:   # quadrotor.py:1093-1108 on the integrated pose
+                from .gate_geometry import gate_in_range
+                g = self.EFFECTIVE_GATES_POSITIONS[self.current_gate]
+                rng = gate_in_range(self.pos, g, self.GATES[self.current_gate][6])
+                info["current_target_gate_in_range"] = rng
+                info["current_target_gate_pos"] = list(g) if rng else list(self.GATES[self.current_gate][0:6])
         else:
             info["current_target_gate_id"] = -1
             info["current_target_gate_type"] = -1
+            if self.gate_geometry:
+                info["current_target_gate_in_range"] = False
+                info["current_target_gate_pos"] = []
         info["at_goal_position"] = False
         info["task_completed"] = False
         if self.current_gate == self.NUM_GATES and self.QUAD_TYPE == 3:

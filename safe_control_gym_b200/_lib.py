@@ -33,7 +33,7 @@ STAT_NAMES = ["episodes", "return", "length", "violation_steps", "mse", "gates",
 
 EXPORTS = ["scg_create", "scg_destroy", "scg_bind_buffers", "scg_set_injection", "scg_reset", "scg_step",
            "scg_rollout", "scg_rollout_host", "scg_stats_reset", "scg_stats_read", "scg_constraints_eval",
-           "scg_symbolic_eval", "scg_symbolic_loss", "scg_measure_fp32_peak", "scg_launch_count", "scg_kernel_variant",
+           "scg_symbolic_eval", "scg_symbolic_loss", "scg_gate_info", "scg_measure_fp32_peak", "scg_launch_count", "scg_kernel_variant",
            "scg_last_error", "scg_version"]
 
 
@@ -131,6 +131,7 @@ def load():
     lib.scg_constraints_eval.argtypes = [vp, vp, vp, i64, vp, vp, vp]
     lib.scg_symbolic_eval.argtypes = [vp, C.c_int, vp, vp, i64, C.c_double, vp, vp, vp]
     lib.scg_symbolic_loss.argtypes = [vp, vp, vp, vp, vp, C.POINTER(C.c_double), C.POINTER(C.c_double), i64, vp, vp, vp, vp]
+    lib.scg_gate_info.argtypes = [vp, vp, vp, vp]
     lib.scg_measure_fp32_peak.argtypes = [C.POINTER(C.c_double)]
     lib.scg_launch_count.argtypes = [vp]
     lib.scg_launch_count.restype = i64

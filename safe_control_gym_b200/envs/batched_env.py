@@ -167,7 +167,9 @@ class BatchedEnvBase:
 
         def bit(mask, as_int=False):
             return (lambda: (bits & mask).ne(0).to(torch.int32)) if as_int else (lambda: (bits & mask).ne(0))
+        extra = self._extra_info()
         return LazyInfo({
+            **extra,
             "constraint_values": lambda: self.buf_c_values[:self._n_rows].t(),
             "constraint_violation": bit(L.INFO_VIOLATION, True),
             "TimeLimit.truncated": bit(L.INFO_TRUNCATED),
@@ -183,6 +185,10 @@ class BatchedEnvBase:
             "state": lambda: self.buf_env_state.t(),
             "info_bits": lambda: bits,
         })
+
+    def _extra_info(self):
+        """Env-specific lazy info keys (name -> maker)."""
+        return {}
 
     def _gate_id(self):
         """info["current_target_gate_id"]: the gate index, -1 once all gates are passed (quadrotor.py:1093-1112)."""

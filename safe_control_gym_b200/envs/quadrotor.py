@@ -391,6 +391,31 @@ class BatchedQuadrotor(BatchedEnvBase):
         self._h, self._cfg = handle, cfg
         self._bind()
 
+    # ------------------------------------------------------------------ gate info (quadrotor.py:1093-1112)
+    def _gate_info(self):
+        """(pose [N, 6], in_range [N] bool) of the current target gate: one launch of scg_gate_info, cached per step."""
+        tag = self.launch_count
+        if getattr(self, "_gate_cache_tag", None) != tag:
+            pose = torch.empty(6, self.num_envs, dtype=self.dtype, device=self.device)
+            rng = torch.empty(self.num_envs, dtype=torch.uint8, device=self.device)
+            with torch.cuda.device(self.device):
+                L.check(self.lib.scg_gate_info(self._h, C.c_void_p(pose.data_ptr()), C.c_void_p(rng.data_ptr()), self._stream()))
+            self._gate_cache = (pose.t(), rng.bool())
+            self._gate_cache_tag = self.launch_count
+        return self._gate_cache
+
+    def _extra_info(self):
+        if self.QUAD_TYPE != 3 or self.NUM_GATES == 0:
+            return {}
+        types = torch.tensor([int(g[6]) for g in self.GATES] + [-1], dtype=torch.int32, device=self.device)
+
+        def gate_type():
+            g = self._gate_id().long()
+            return types[torch.where(g < 0, torch.full_like(g, self.NUM_GATES), g)]
+        return {"current_target_gate_in_range": lambda: self._gate_info()[1],
+                "current_target_gate_pos": lambda: self._gate_info()[0],
+                "current_target_gate_type": gate_type}
+
     def _reset_info(self):
         """quadrotor.py:1136-1202 (host constants only; nothing here touches the device)."""
         info = {"symbolic_model": self.symbolic,

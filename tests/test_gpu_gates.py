@@ -46,13 +46,16 @@ def test_gate_progress_and_collisions_match_oracle(dtype, randomized):
     for r in refs:
         r.reset()
     act = np.full((n, 4), M * G / 4)
-    passed = collided = resets = 0
+    passed = collided = resets = in_range = out_range = 0
     dropped = set()   # fp32 only: a lane whose contact / ray decision fell within rounding of its threshold
     for t in range(steps):
         obs, rew, done, info = env.step(act)
         g_pass = info["stepped_through_gate"].cpu().numpy()
         g_col = info["collision"].cpu().numpy()
         g_id = info["current_target_gate_id"].cpu().numpy()
+        g_rng = info["current_target_gate_in_range"].cpu().numpy()
+        g_pos = info["current_target_gate_pos"].double().cpu().numpy()
+        g_typ = info["current_target_gate_type"].cpu().numpy()
         g_done, g_rew = done.cpu().numpy(), rew.double().cpu().numpy()
         for i, r in enumerate(refs):
             if i in dropped:
@@ -71,8 +74,16 @@ def test_gate_progress_and_collisions_match_oracle(dtype, randomized):
                 r.reset()
             else:
                 assert int(g_id[i]) == int(o_info["current_target_gate_id"]), (t, i)
+                assert int(g_typ[i]) == int(o_info["current_target_gate_type"]), (t, i)
+                if dtype == torch.float64:   # (fp32: the 0.45 m threshold can fall within rounding)
+                    assert bool(g_rng[i]) == bool(o_info["current_target_gate_in_range"]), (t, i)
+                    want = np.array(o_info["current_target_gate_pos"] or [0.0] * 6, dtype=float)
+                    assert np.max(np.abs(g_pos[i] - want)) <= 1e-12, (t, i, g_pos[i], want)
+                    in_range += int(g_rng[i]); out_range += int(not g_rng[i] and g_id[i] >= 0)
     assert passed >= 10 and collided >= 10 and resets >= 10, (passed, collided, resets)
     assert len(dropped) <= 2, dropped
+    if dtype == torch.float64:
+        assert in_range >= 100 and out_range >= 100, (in_range, out_range)
     st = env.stats()
     print(f"gates {dtype} randomized={randomized}: {passed} gate passes, {collided} contacts, {resets} resets; stats {st['gates']:.0f} / {st['collisions']:.0f}")
     if not dropped:
