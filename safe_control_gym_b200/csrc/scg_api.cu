@@ -45,7 +45,12 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
     for (int j = 0; j < 3; ++j) { h.J[j] = real(c.J[j]); h.J_inv[j] = real(c.J_inv[j]); }
     h.pwm_scale = real(c.pwm2rpm_scale); h.pwm_const = real(c.pwm2rpm_const);
     h.pwm_min = real(c.pwm_min); h.pwm_max = real(c.pwm_max); h.inv_pwm_scale = real(1.0 / c.pwm2rpm_scale);
-    if (c.env_kind != SCG_CARTPOLE) h.inv_nkf = real(1.0 / ((4 / nu) * c.kf));
+    if (c.env_kind != SCG_CARTPOLE) {
+        h.inv_nkf = real(1.0 / ((4 / nu) * c.kf));
+        const double rmin = c.pwm2rpm_scale * c.pwm_min + c.pwm2rpm_const, rmax = c.pwm2rpm_scale * c.pwm_max + c.pwm2rpm_const;
+        h.f_min = real(c.kf * rmin * rmin); h.f_max = real(c.kf * rmax * rmax);
+        h.inv_n_motor = real(1.0 / (4 / nu)); h.km_over_kf = real(c.km / c.kf); h.inv_kf = real(1.0 / c.kf);
+    }
     h.gravity_acc = real(c.gravity_acc); h.cp_length = real(c.cp_length); h.cp_pole_mass = real(c.cp_pole_mass); h.cp_cart_mass = real(c.cp_cart_mass);
     h.normalized_action = c.normalized_action; h.norm_act_scale = real(c.norm_act_scale); h.hover_thrust = real(c.hover_thrust);
     for (int j = 0; j < nu; ++j) { h.act_low[j] = real(c.act_low[j]); h.act_high[j] = real(c.act_high[j]); }

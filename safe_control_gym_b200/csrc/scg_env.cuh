@@ -172,7 +172,7 @@ SCG_DEV void attitude2(real alpha_pre, uint32_t flipped_in, Att2<real>& a) {
 template <typename real> struct Motors {
     real T;            // sum of the four rotor forces
     real tx, ty, tz;   // body torques before the gyroscopic term
-    real rpm[4];
+    real rpm[4];       // literal map: the commanded RPMs; fast map: the rotor FORCES (see motor_rpm)
 };
 
 // quadrotor.py:815-842, quadrotor_utils.py:21-67, base_aviary.py:538-551.
@@ -180,6 +180,25 @@ template <typename real> struct Motors {
 template <int KIND, typename real, bool FASTMATH>
 SCG_DEV void motors_from_thrust(const Hot<real>& h, const real (&thrust)[Dims<KIND>::NU], Motors<real>& m) {
     constexpr int NU = Dims<KIND>::NU;
+    if constexpr (FASTMATH) {
+        // thrust -> PWM -> clip -> RPM -> KF rpm^2 is the identity on the rotor force apart from the clip, which maps
+        // to force bounds (sqrt is monotone): f = clip(thrust / n, KF rpm_min^2, KF rpm_max^2).  Same value up to the
+        // rounding of the chain it skips; the RPMs are formed only where they are logged (motor_rpm).
+        real fi[NU];
+#pragma unroll
+        for (int j = 0; j < NU; ++j) fi[j] = m_clip((NU == 4 ? thrust[j] : thrust[j] * h.inv_n_motor), h.f_min, h.f_max);
+        real f[4];
+        if (KIND == SCG_QUAD_1D) { f[0] = f[1] = f[2] = f[3] = fi[0]; }
+        else if (KIND == SCG_QUAD_2D) { f[0] = fi[0]; f[1] = fi[NU - 1]; f[2] = fi[NU - 1]; f[3] = fi[0]; }
+        else { f[0] = fi[0]; f[1] = fi[1 % NU]; f[2] = fi[2 % NU]; f[3] = fi[3 % NU]; }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) m.rpm[j] = f[j];
+        m.T = ((f[0] + f[1]) + f[2]) + f[3];
+        m.tz = (((f[0] - f[1]) + f[2]) - f[3]) * h.km_over_kf;
+        m.tx = (((f[0] + f[1]) - f[2]) - f[3]) * h.arm_s2;
+        m.ty = (((-f[0] + f[1]) + f[2]) - f[3]) * h.arm_s2;
+        return;
+    }
     real rp[NU];
 #pragma unroll
     for (int j = 0; j < NU; ++j) {
@@ -198,6 +217,12 @@ SCG_DEV void motors_from_thrust(const Hot<real>& h, const real (&thrust)[Dims<KI
     m.tz = ((zt[0] - zt[1]) + zt[2]) - zt[3];
     m.tx = (((f[0] + f[1]) - f[2]) - f[3]) * h.arm_s2;
     m.ty = (((-f[0] + f[1]) + f[2]) - f[3]) * h.arm_s2;
+}
+
+// the RPM of rotor j as the Logger records it
+template <typename real, bool FASTMATH> SCG_DEV real motor_rpm(const Hot<real>& h, const Motors<real>& m, int j) {
+    if constexpr (FASTMATH) return sqrt_fast(m.rpm[j] * h.inv_kf);
+    else return m.rpm[j];
 }
 
 // per-episode inertial constants (nominal in parity mode, F9)

@@ -32,6 +32,7 @@ template <typename real> struct Hot {
     real J[3], J_inv[3];
     real pwm_scale, pwm_const, pwm_min, pwm_max, inv_pwm_scale;
     real inv_nkf;                   // 1 / (n_motor * KF)
+    real f_min, f_max, inv_n_motor, km_over_kf, inv_kf;   // per-rotor force at PWM_min / PWM_max, 1 / n_motor, KM / KF, 1 / KF (fast motor map)
     real gravity_acc, cp_length, cp_pole_mass, cp_cart_mass;   // cart-pole (A13): effective (half) pole length, masses
     // action map
     int32_t normalized_action;

@@ -610,8 +610,8 @@ SCG_DEV float warp_sum(float v) {
 }
 
 // the Logger record (Logger.py:50-66): pos3 vel3 rpy3 ang_vel3 rpm4, [16][n] per logged step
-template <int KIND, typename real>
-SCG_DEV void write_log(const EnvRegs<KIND, real>& e, const Motors<real>& mot, real* __restrict__ L, int64_t n) {
+template <int KIND, typename real, bool FASTMATH>
+SCG_DEV void write_log(const Hot<real>& h, const EnvRegs<KIND, real>& e, const Motors<real>& mot, real* __restrict__ L, int64_t n) {
     real rec[16];
     if constexpr (KIND == SCG_QUAD_3D) {
         rec[0] = e.x[0]; rec[1] = e.x[2]; rec[2] = e.x[4]; rec[3] = e.x[1]; rec[4] = e.x[3]; rec[5] = e.x[5];
@@ -628,7 +628,7 @@ SCG_DEV void write_log(const EnvRegs<KIND, real>& e, const Motors<real>& mot, re
         rec[6] = rec[7] = rec[8] = rec[9] = rec[10] = rec[11] = 0;
     }
 #pragma unroll
-    for (int j = 0; j < 4; ++j) rec[12 + j] = mot.rpm[j];
+    for (int j = 0; j < 4; ++j) rec[12 + j] = motor_rpm<real, FASTMATH>(h, mot, j);
 #pragma unroll
     for (int j = 0; j < 16; ++j) L[int64_t(j) * n] = rec[j];
 }
@@ -719,7 +719,13 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     int32_t ep_len = b.ep_length ? b.ep_length[ii] : 0;
     int32_t ep_viol = b.ep_violations ? b.ep_violations[ii] : 0;
     // per-thread statistics (reduced once at the end)
-    float s_eps = 0.f, s_ret = 0.f, s_len = 0.f, s_viol = 0.f, s_mse = 0.f, s_trunc = 0.f, s_compl = 0.f, s_vep = 0.f;
+    float s_viol = 0.f, s_mse = 0.f;
+    // the statistics that only change when an episode ends live in a per-thread column of shared memory: six values
+    // that would otherwise be held (or spilled) across every control step for an update on 2 % of them
+    __shared__ float ep_acc_buf[6 * ENV_BLOCK];
+    float* const ep_acc = ep_acc_buf + threadIdx.x;   // [episodes, return, length, truncated, completed, violated episodes]
+#pragma unroll
+    for (int j = 0; j < 6; ++j) ep_acc[j * ENV_BLOCK] = 0.f;
     float s_gates = 0.f, s_coll = 0.f;   // gate_geometry only
     real reward = real(0), mse = real(0);
     bool done = false;
@@ -762,14 +768,14 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
             if (ro.reward_out) ro.reward_out[int64_t(k) * n + ii] = reward;
             if (ro.done_out) ro.done_out[int64_t(k) * n + ii] = done ? 1 : 0;
             if (ro.log_out && (k % ro.log_stride) == 0)
-                write_log<KIND, real>(e, mot, ro.log_out + int64_t(k / ro.log_stride) * 16 * n + ii, n);
+                write_log<KIND, real, (sizeof(real) == 4 && ATT != SCG_ATT_ROUNDTRIP)>(h, e, mot, ro.log_out + int64_t(k / ro.log_stride) * 16 * n + ii, n);
         }
         fresh = false;
         if (done) {
-            s_eps += 1.f; s_ret += float(ep_ret); s_len += float(ep_len);
-            s_trunc += (info & SCG_INFO_TRUNCATED) ? 1.f : 0.f;
-            s_compl += (info & SCG_INFO_COMPLETED) ? 1.f : 0.f;
-            s_vep += ep_viol > 0 ? 1.f : 0.f;
+            ep_acc[0 * ENV_BLOCK] += 1.f; ep_acc[1 * ENV_BLOCK] += float(ep_ret); ep_acc[2 * ENV_BLOCK] += float(ep_len);
+            if (info & SCG_INFO_TRUNCATED) ep_acc[3 * ENV_BLOCK] += 1.f;
+            if (info & SCG_INFO_COMPLETED) ep_acc[4 * ENV_BLOCK] += 1.f;
+            if (ep_viol > 0) ep_acc[5 * ENV_BLOCK] += 1.f;
             if (cfg & CFG_AUTO_RESET) {   // DummyVecEnv.step_wait (dummy_vec_env.py:38-49)
                 if ((cfg & CFG_STEP_OUTPUTS) && b.terminal_obs) {
                     real tl[NX];
@@ -848,7 +854,8 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     if (b.stats) {   // warp-shuffle reduction, one atomic per warp per statistic
         const float steps = valid ? float(ro.k_steps) : 0.f;
         constexpr int NS = 11;
-        float v[11] = {s_eps, s_ret, s_len, s_viol, s_mse, s_trunc, s_compl, s_vep, steps, s_gates, s_coll};
+        float v[11] = {ep_acc[0 * ENV_BLOCK], ep_acc[1 * ENV_BLOCK], ep_acc[2 * ENV_BLOCK], s_viol, s_mse, ep_acc[3 * ENV_BLOCK],
+                       ep_acc[4 * ENV_BLOCK], ep_acc[5 * ENV_BLOCK], steps, s_gates, s_coll};
         const int slot[11] = {SCG_STAT_EPISODES, SCG_STAT_RETURN, SCG_STAT_LENGTH, SCG_STAT_VIOLATION_STEPS,
                               SCG_STAT_MSE, SCG_STAT_TRUNCATED, SCG_STAT_COMPLETED, SCG_STAT_VIOLATED_EPISODES, SCG_STAT_ENV_STEPS,
                               SCG_STAT_GATES, SCG_STAT_COLLISIONS};

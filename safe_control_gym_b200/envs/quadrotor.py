@@ -407,14 +407,16 @@ class BatchedQuadrotor(BatchedEnvBase):
     def _extra_info(self):
         if self.QUAD_TYPE != 3 or self.NUM_GATES == 0:
             return {}
-        types = torch.tensor([int(g[6]) for g in self.GATES] + [-1], dtype=torch.int32, device=self.device)
-
-        def gate_type():
-            g = self._gate_id().long()
-            return types[torch.where(g < 0, torch.full_like(g, self.NUM_GATES), g)]
-        return {"current_target_gate_in_range": lambda: self._gate_info()[1],
-                "current_target_gate_pos": lambda: self._gate_info()[0],
-                "current_target_gate_type": gate_type}
+        if getattr(self, "_gate_makers", None) is None:   # built once: step() must not touch the device for lazy keys
+            def gate_type():
+                if getattr(self, "_gate_types", None) is None:
+                    self._gate_types = torch.tensor([int(g[6]) for g in self.GATES] + [-1], dtype=torch.int32, device=self.device)
+                g = self._gate_id().long()
+                return self._gate_types[torch.where(g < 0, torch.full_like(g, self.NUM_GATES), g)]
+            self._gate_makers = {"current_target_gate_in_range": lambda: self._gate_info()[1],
+                                 "current_target_gate_pos": lambda: self._gate_info()[0],
+                                 "current_target_gate_type": gate_type}
+        return self._gate_makers
 
     def _reset_info(self):
         """quadrotor.py:1136-1202 (host constants only; nothing here touches the device)."""
