@@ -279,8 +279,10 @@ int scg_measure_fp32_peak(double* tflops_out);
  * out_in_range [n] u8.  Either output may be NULL.  quad_type 3 only. */
 int scg_gate_info(scg_env* env, void* out_pose, uint8_t* out_in_range, void* stream);
 int64_t scg_launch_count(const scg_env* env);
-/* Which instantiation of the step kernel the config selected: 1 = LEAN (no disturbances / adversary / external force,
- * bounded constraints without tolerances, nominal inertia, diagonal Q and R), 0 = GENERAL.  Same results either way. */
+/* Which instantiation of the step kernel the config selected.  0 = GENERAL; 1 = LEAN: reset() draws nothing but
+ * uniform initial-state offsets, so the auto-reset takes a spare state drawn ahead of time; 2 = LEAN + PLAIN: in
+ * addition no per-step extra is configured (disturbances, adversary, external force, dense / tolerance / symmetric
+ * constraints, off-diagonal Q or R, constraint penalty, gate geometry).  Same results in every variant. */
 int scg_kernel_variant(const scg_env* env);
 const char* scg_last_error(void);
 const char* scg_version(void);

@@ -252,24 +252,35 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
     h.box_thr = (nb > 0 && h.bounded[0].strict) ? std::nextafter(real(-0.5), -INF) : real(0.5);
     if (h.n_rows > 0) h.cfg |= CFG_HAS_ROWS;
     if (h.ubox_mask) h.cfg |= CFG_UBOX;
-    // (the extended observation lives in write_obs, outside the loop)
-    *lean_out = c.n_dist[0] == 0 && c.n_dist[1] == 0 && c.n_dist[2] == 0 && c.adversary_channel < 0 && !c.dyn_applies_force &&
-                !(h.any_init_rand & 2) && !h.any_inertia_rand &&
-                !c.dyn_uses_episode_inertia && nd == 0 && !h.any_tolerance && !symmetric && same_strict && h.quadratic_diag &&
-                !(c.env_kind == SCG_CARTPOLE && (h.any_inertia_rand != 0));
+    if (h.need_cold_constraints || !same_strict) h.cfg |= CFG_COLD_CONSTRAINTS;
+    if (c.n_dist[1] > 0 || c.n_dist[2] > 0 || c.adversary_channel == SCG_CH_ACTION || c.adversary_channel == SCG_CH_DYNAMICS)
+        h.cfg |= CFG_DISTURBED;
+    if (!h.quadratic_diag) h.cfg |= CFG_QR_DENSE;
+    if (c.cost == SCG_COST_RL_REWARD && c.use_constraint_penalty) h.cfg |= CFG_PENALTY;
+    // ---- LEAN kernel (scg_step.cuh): the auto-reset can take a spare initial state drawn ahead of time, i.e. reset()
+    // draws nothing but uniform initial-state offsets -- no disturbance offsets, no inertial properties, no normal
+    // draws.  Per-step features (disturbances, adversary, dense constraints, ...) are uniform branches in both kernels.
+    bool reset_draws = (h.any_init_rand & 2) != 0 || h.any_inertia_rand != 0 || c.dyn_uses_episode_inertia != 0;
+    for (int ch = 0; ch < 3; ++ch)
+        for (int q = 0; q < c.n_dist[ch]; ++q) {
+            const scg_disturbance& s = c.dist[ch][q];
+            if ((s.kind == SCG_DIST_IMPULSE || s.kind == SCG_DIST_STEP) && s.step_offset < 0) reset_draws = true;
+        }
+    *lean_out = !reset_draws;
     return SCG_OK;
 }
 
 extern "C" const char* scg_last_error(void) { return g_err.c_str(); }
 extern "C" const char* scg_version(void) { return "scg_b200 0.1 (sm_100a)"; }
 extern "C" int64_t scg_launch_count(const scg_env* env) { return env ? env->launches : 0; }
-extern "C" int scg_kernel_variant(const scg_env* env) { return env && env->lean ? 1 : 0; }
+extern "C" int scg_kernel_variant(const scg_env* env) { return !env ? 0 : env->lean ? (env->plain ? 2 : 1) : 0; }
 
 template <typename real> static int upload_params(scg_env* e) {
     Cold<real>* k = new (std::nothrow) Cold<real>;
     if (!k) return fail(SCG_ERR_BAD_CONFIG, "out of host memory");
     Hot<real>& h = *reinterpret_cast<Hot<real>*>(sizeof(real) == 4 ? (void*)&e->hf : (void*)&e->hd);
     int rc = build_params<real>(e->cfg, e->nx, e->nu, h, *k, &e->n_rows, &e->n_slots, &e->lean);
+    e->plain = e->lean && !(h.cfg & (CFG_DISTURBED | CFG_COLD_CONSTRAINTS | CFG_QR_DENSE | CFG_PENALTY | CFG_GATE_GEOMETRY));
     if (rc != SCG_OK) { delete k; return rc; }
     const int rows = e->cfg.n_goal_rows > 0 ? e->cfg.n_goal_rows : 1;
     real* goal_host = new real[size_t(rows) * e->nx];

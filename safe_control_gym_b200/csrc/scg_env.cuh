@@ -351,16 +351,17 @@ __device__ __noinline__ uint32_t constraint_values_cold(const Hot<real>& h, cons
     return (violated ? 1u : 0u) | (almost ? 2u : 0u);   // by value: the caller's flags stay in registers
 }
 
-// The in-loop part: violation flags of the bounded / default constraints (the only kind a LEAN
-// config has); anything else is delegated to constraint_values_cold.
-template <int KIND, typename real, bool LEAN>
+// The in-loop part: the violation flag of bounded / default constraints that merge into one box per dimension
+// (no tolerances, one strictness -- CFG_COLD_CONSTRAINTS clear); anything else, and every call that wants the
+// rounded values, is delegated to constraint_values_cold.
+template <int KIND, typename real, bool PLAIN = false>
 SCG_DEV void eval_constraints(const Hot<real>& h, const Cold<real>* __restrict__ cold,
                               const real (&st)[Dims<KIND>::NX], const real (&raw)[Dims<KIND>::NU],
                               bool state_only, real* __restrict__ c_out, int64_t n, int64_t i,
-                              bool& violated, bool& almost, uint32_t cfg = CFG_FULL_STATE | CFG_UBOX) {
+                              bool& violated, bool& almost, uint32_t cfg) {
     constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
     violated = false; almost = false;
-    if (c_out != nullptr || (!LEAN && h.need_cold_constraints)) {
+    if (c_out != nullptr || (!PLAIN && (cfg & CFG_COLD_CONSTRAINTS))) {
         real sl[NX], rl[NU];   // the out-of-line call takes copies, the caller's registers stay registers
 #pragma unroll
         for (int d = 0; d < NX; ++d) sl[d] = st[d];
@@ -370,47 +371,28 @@ SCG_DEV void eval_constraints(const Hot<real>& h, const Cold<real>* __restrict__
         violated = (bits & 1u) != 0u; almost = (bits & 2u) != 0u;
         return;
     }
-    if constexpr (LEAN) {
-        // one merged box: violated <=> the largest c = max(lo - x, x - hi) over all bounded dims rounds above 0
-        // (unbounded dims carry lo = -inf, hi = +inf: every dim is evaluated, branch-free, at two subtractions and
-        // one three-way max each; p, q, r only where something reads them)
-        constexpr int NB = KIND == SCG_QUAD_3D ? 9 : NX;
-        real w0 = -INFINITY, w1 = -INFINITY;   // two chains
+    // one merged box: violated <=> the largest c = max(lo - x, x - hi) over all bounded dims rounds above 0
+    // (unbounded dims carry lo = -inf, hi = +inf: every dim is evaluated, branch-free, at two subtractions and
+    // one three-way max each; p, q, r only where something reads them)
+    constexpr int NB = KIND == SCG_QUAD_3D ? 9 : NX;
+    real w0 = -INFINITY, w1 = -INFINITY;   // two chains
 #pragma unroll
-        for (int d = 0; d < NB; ++d) {
+    for (int d = 0; d < NB; ++d) {
+        real& w = (d & 1) ? w1 : w0;
+        w = m_max3(w, h.box_lo[d] - st[d], st[d] - h.box_hi[d]);
+    }
+    if (NB < NX && (cfg & CFG_FULL_STATE)) {
+#pragma unroll
+        for (int d = NB; d < NX; ++d) w0 = m_max3(w0, h.box_lo[d] - st[d], st[d] - h.box_hi[d]);
+    }
+    if (!state_only && (cfg & CFG_UBOX)) {
+#pragma unroll
+        for (int d = 0; d < NU; ++d) {
             real& w = (d & 1) ? w1 : w0;
-            w = m_max3(w, h.box_lo[d] - st[d], st[d] - h.box_hi[d]);
-        }
-        if (NB < NX && (cfg & CFG_FULL_STATE)) {
-#pragma unroll
-            for (int d = NB; d < NX; ++d) w0 = m_max3(w0, h.box_lo[d] - st[d], st[d] - h.box_hi[d]);
-        }
-        if (!state_only && (cfg & CFG_UBOX)) {
-#pragma unroll
-            for (int d = 0; d < NU; ++d) {
-                real& w = (d & 1) ? w1 : w0;
-                w = m_max3(w, h.ubox_lo[d] - raw[d], raw[d] - h.ubox_hi[d]);
-            }
-        }
-        violated = m_max(w0, w1) * real(1e8) > h.box_thr;
-    } else {
-        for (int k = 0; k < h.n_bounded; ++k) {
-            const BoundedCon<real>& bc = h.bounded[k];
-            if (bc.var == SCG_VAR_STATE) {
-#pragma unroll
-                for (int d = 0; d < NX; ++d) {
-                    if (!((bc.mask >> d) & 1u)) continue;   // uniform
-                    violated |= viol_test(bc.lo[d] - st[d], bc.strict) | viol_test(st[d] - bc.hi[d], bc.strict);
-                }
-            } else if (!state_only) {
-#pragma unroll
-                for (int d = 0; d < NU; ++d) {
-                    if (!((bc.mask >> d) & 1u)) continue;
-                    violated |= viol_test(bc.lo[d] - raw[d], bc.strict) | viol_test(raw[d] - bc.hi[d], bc.strict);
-                }
-            }
+            w = m_max3(w, h.ubox_lo[d] - raw[d], raw[d] - h.ubox_hi[d]);
         }
     }
+    violated = m_max(w0, w1) * real(1e8) > h.box_thr;
 }
 
 // ------------------------------------------------------------------ gate progress + contact scan (row A10)

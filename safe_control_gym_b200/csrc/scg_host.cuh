@@ -10,6 +10,7 @@ struct scg_env {
     scg_config cfg;
     int nx, nu, obs_dim, n_rows, n_slots;
     bool lean = false;             // the LEAN kernel specialisation applies (scg_step.cuh)
+    bool plain = false;            // ... and none of the per-step extras is configured (PLAIN)
     scg::Hot<float> hf;
     scg::Hot<double> hd;
     void* cold_dev = nullptr;      // Cold<float> or Cold<double>

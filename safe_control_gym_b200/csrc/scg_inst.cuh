@@ -29,8 +29,9 @@ int launch_reset(scg_env* e, const ResetInject<real>& inj, const uint8_t* mask, 
 template <int KIND, typename real, int ATT>
 static void launch_rollout_att(scg_env* e, const Hot<real>& h, const Cold<real>* cold, const Buf<real>& b, const Roll<real>& ro,
                                unsigned blocks, cudaStream_t st) {
-    if (e->lean) k_rollout<KIND, real, ATT, true><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro);
-    else k_rollout<KIND, real, ATT, false><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro);
+    if (e->lean && e->plain && sizeof(real) == 4) k_rollout<KIND, real, ATT, true, sizeof(real) == 4><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro);
+    else if (e->lean) k_rollout<KIND, real, ATT, true, false><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro);
+    else k_rollout<KIND, real, ATT, false, false><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro);
 }
 
 template <int KIND, typename real>
@@ -41,7 +42,7 @@ int launch_rollout(scg_env* e, const Roll<real>& ro, cudaStream_t st) {
     const Cold<real>* cold = static_cast<const Cold<real>*>(e->cold_dev);
     const int att = e->cfg.attitude_mode;
     if constexpr (KIND == SCG_QUAD_3D || KIND == SCG_QUAD_2D) {
-        if (att == SCG_ATT_ROUNDTRIP) k_rollout<KIND, real, SCG_ATT_ROUNDTRIP, false><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro);
+        if (att == SCG_ATT_ROUNDTRIP) k_rollout<KIND, real, SCG_ATT_ROUNDTRIP, false, false><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro);
         else if (att == SCG_ATT_FAST_INTRINSIC && sizeof(real) == 4 && KIND == SCG_QUAD_3D)
             launch_rollout_att<KIND, real, (sizeof(real) == 4 && KIND == SCG_QUAD_3D) ? SCG_ATT_FAST_INTRINSIC : SCG_ATT_FAST>(e, h, cold, b, ro, blocks, st);
         else launch_rollout_att<KIND, real, SCG_ATT_FAST>(e, h, cold, b, ro, blocks, st);
@@ -67,7 +68,7 @@ k_constraints(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict_
 #pragma unroll
     for (int j = 0; j < NU; ++j) raw[j] = action ? action[i * NU + j] : real(0);
     bool violated, almost;
-    eval_constraints<KIND, real, false>(h, cold, st, raw, action == nullptr, out_values, n, i, violated, almost);
+    eval_constraints<KIND, real>(h, cold, st, raw, action == nullptr, out_values, n, i, violated, almost, h.cfg | CFG_FULL_STATE);
     if (out_flags) out_flags[i] = (violated ? 1 : 0) | (almost ? 2 : 0);
 }
 

@@ -90,6 +90,10 @@ enum : uint32_t {
     CFG_MSE_RATES = 1u << 12,       // 3D: info["mse"] weighs p, q, r
     CFG_STEP_OUTPUTS = 1u << 13,    // set per launch
     CFG_GATE_GEOMETRY = 1u << 14,   // 3D: gate rays + contact scan on the integrated pose (extension)
+    CFG_DISTURBED = 1u << 15,       // an action / dynamics disturbance, an adversary or an external force acts per step
+    CFG_COLD_CONSTRAINTS = 1u << 16,// dense rows, tolerances, symmetric or mixed-strictness bounds: no merged box
+    CFG_QR_DENSE = 1u << 17,        // quadratic cost with off-diagonal Q / R
+    CFG_PENALTY = 1u << 18,         // rl_reward with use_constraint_penalty
 };
 
 template <typename real> struct DenseRow {     // linear: c = a . x - b ; quadratic: c = x' P x - b

@@ -352,9 +352,55 @@ __device__ __noinline__ void reset_env_cold(const Hot<real>& h, const Cold<real>
     for (int d = 0; d < NX; ++d) st_out[d] = st[d];
 }
 
+// Action-channel disturbances + adversary on the commanded thrusts, and the external force of the dynamics channel
+// (extension, F5: the reference never integrates it in DYN).  Out of line: the undisturbed loop must not carry it.
+template <int KIND, typename real>
+__device__ __noinline__ void disturb_inputs(const Hot<real>& h, const Cold<real>* __restrict__ cold, const int32_t* __restrict__ dist_offset,
+                                            const real* __restrict__ adv_action, RngKey key, int32_t t, uint32_t ep, int64_t n, int64_t i,
+                                            real* __restrict__ thr_io, real* __restrict__ f_out) {
+    constexpr int NU = Dims<KIND>::NU, NF = Dims<KIND>::NF;
+    const real t_sim = real(t * h.substeps) * h.dt;
+    real thr[NU];
+#pragma unroll
+    for (int j = 0; j < NU; ++j) thr[j] = thr_io[j];
+    if (h.n_dist_act) apply_channel<real, NU>(cold, SCG_CH_ACTION, h.n_dist_act, thr, t, t_sim, key, uint32_t(t), ep, dist_offset, n, i);
+    if (h.adversary_channel == SCG_CH_ACTION && adv_action) {
+#pragma unroll
+        for (int j = 0; j < NU; ++j) thr[j] += adv_action[i * NU + j];
+    }
+#pragma unroll
+    for (int j = 0; j < NU; ++j) thr_io[j] = thr[j];
+    f_out[0] = f_out[1] = f_out[2] = real(0);
+    if (h.dyn_applies_force && (h.n_dist_dyn || h.adversary_channel == SCG_CH_DYNAMICS)) {
+        real f[NF];
+#pragma unroll
+        for (int d = 0; d < NF; ++d) f[d] = real(0);
+        if (h.n_dist_dyn) apply_channel<real, NF>(cold, SCG_CH_DYNAMICS, h.n_dist_dyn, f, t, t_sim, key, uint32_t(t), ep, dist_offset, n, i);
+        if (h.adversary_channel == SCG_CH_DYNAMICS && adv_action) {
+#pragma unroll
+            for (int d = 0; d < NF; ++d) f[d] += adv_action[i * NF + d];
+        }
+        if constexpr (KIND == SCG_QUAD_1D) { f_out[2] = f[0]; }
+        else if constexpr (KIND == SCG_QUAD_2D || KIND == SCG_CARTPOLE) { f_out[0] = f[0]; f_out[2] = f[1]; }
+        else { f_out[0] = f[0]; f_out[1] = f[1]; f_out[2] = f[2]; }
+    }
+}
+
+// e' M e for a dense weight matrix (quadratic cost with off-diagonal Q / R); out of line
+template <typename real, int DIM, int LD>
+__device__ __noinline__ real dense_form(const real* __restrict__ M, const real* __restrict__ e) {
+    real acc = real(0);
+    for (int a = 0; a < DIM; ++a) {
+        real row = real(0);
+        for (int c = 0; c < DIM; ++c) row += M[a * LD + c] * e[c];
+        acc += e[a] * row;
+    }
+    return acc;
+}
+
 // One Quadrotor.step(): returns reward / done / info bits, leaves env.state in st
 // (3D: p, q, r only when `full`).
-template <int KIND, typename real, int ATT, bool LEAN>
+template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN>
 SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, const Buf<real>& b,
                       const RngKey& key, int64_t n, int64_t i, EnvRegs<KIND, real>& e,
                       const real (&raw)[Dims<KIND>::NU], uint32_t cfg, real (&st)[Dims<KIND>::NX], real& reward, bool& done,
@@ -375,36 +421,14 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
         thr[j] = pre[j];
     }
     real fx = real(0), fy = real(0), fz = real(0);
-    if constexpr (!LEAN) {
-        const real t_sim = real(t * h.substeps) * h.dt;
-        if (h.n_dist_act) {
-            real tmp[NU];
+    if (!PLAIN && (cfg & CFG_DISTURBED)) {   // uniform; one out-of-line call on private copies
+        real tl[NU], fl[3];
 #pragma unroll
-            for (int j = 0; j < NU; ++j) tmp[j] = thr[j];
-            apply_channel<real, NU>(cold, SCG_CH_ACTION, h.n_dist_act, tmp, t, t_sim, key, uint32_t(t), ep, b.dist_offset, n, i);
+        for (int j = 0; j < NU; ++j) tl[j] = thr[j];
+        disturb_inputs<KIND, real>(h, cold, b.dist_offset, b.adv_action, key, t, ep, n, i, tl, fl);
 #pragma unroll
-            for (int j = 0; j < NU; ++j) thr[j] = tmp[j];
-        }
-        if (h.adversary_channel == SCG_CH_ACTION && b.adv_action) {
-#pragma unroll
-            for (int j = 0; j < NU; ++j) thr[j] += b.adv_action[i * NU + j];
-        }
-        // ---- external force (extension, F5: the reference never integrates it in DYN)
-        if (h.dyn_applies_force && (h.n_dist_dyn || h.adversary_channel == SCG_CH_DYNAMICS)) {
-            constexpr int NF = Dims<KIND>::NF;
-            real f[NF];
-#pragma unroll
-            for (int d = 0; d < NF; ++d) f[d] = real(0);
-            if (h.n_dist_dyn)
-                apply_channel<real, NF>(cold, SCG_CH_DYNAMICS, h.n_dist_dyn, f, t, t_sim, key, uint32_t(t), ep, b.dist_offset, n, i);
-            if (h.adversary_channel == SCG_CH_DYNAMICS && b.adv_action) {
-#pragma unroll
-                for (int d = 0; d < NF; ++d) f[d] += b.adv_action[i * NF + d];
-            }
-            if constexpr (KIND == SCG_QUAD_1D) { fz = f[0]; }
-            else if constexpr (KIND == SCG_QUAD_2D || KIND == SCG_CARTPOLE) { fx = f[0]; fz = f[1]; }
-            else { fx = f[0]; fy = f[1]; fz = f[2]; }
-        }
+        for (int j = 0; j < NU; ++j) thr[j] = tl[j];
+        fx = fl[0]; fy = fl[1]; fz = fl[2];
     }
     if constexpr (KIND != SCG_CARTPOLE) motors_from_thrust<KIND, real, FASTMATH>(h, thr, mot);
     else { mot.T = mot.tx = mot.ty = mot.tz = real(0); mot.rpm[0] = mot.rpm[1] = mot.rpm[2] = mot.rpm[3] = real(0); }
@@ -474,7 +498,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
     } else make_state<KIND, real>(e, ang, st);
     // ---- _get_info (quadrotor.py:1004-1134): goal hold (collision scan is dead in DYN, F5)
     bool gate_passed = false, collided = false;
-    if constexpr (KIND == SCG_QUAD_3D) {
+    if constexpr (KIND == SCG_QUAD_3D && !PLAIN) {
         if (cfg & CFG_GATE_GEOMETRY) {   // extension: the contact scan and the gate rays on the integrated pose (implies `full`)
             // pyb_step_counter > 0.5 PYB_FREQ, the counter still at t * S (it advances in after_step, benchmark_env.py:427)
             //   <=>  2 t > CTRL_FREQ (quadrotor.py:1060)
@@ -542,7 +566,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             if (cfg & CFG_REW_EXP) reward = m_exp(reward);
         } else if (cfg & CFG_COST_QUAD) {
             real lx = real(0), lu = real(0);
-            if (LEAN || h.quadratic_diag) {
+            if (PLAIN || !(cfg & CFG_QR_DENSE)) {
 #pragma unroll
                 for (int d = 0; d < NX; ++d) { const real er = st[d] - goal_q_at(d); lx += h.q_diag[d] * er * er; }
 #pragma unroll
@@ -553,18 +577,8 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
                 for (int c = 0; c < NX; ++c) ex[c] = st[c] - goal_q_at(c);
 #pragma unroll
                 for (int c = 0; c < NU; ++c) eu[c] = pre[c] - h.u_goal[c];
-                for (int a = 0; a < NX; ++a) {
-                    real row = real(0), ea = real(0);
-#pragma unroll
-                    for (int c = 0; c < NX; ++c) { row += cold->Q[a * SCG_MAX_NX + c] * ex[c]; ea = c == a ? ex[c] : ea; }
-                    lx += ea * row;
-                }
-                for (int a = 0; a < NU; ++a) {
-                    real row = real(0), ea = real(0);
-#pragma unroll
-                    for (int c = 0; c < NU; ++c) { row += cold->R[a * SCG_MAX_NU + c] * eu[c]; ea = c == a ? eu[c] : ea; }
-                    lu += ea * row;
-                }
+                lx = dense_form<real, NX, SCG_MAX_NX>(cold->Q, ex);
+                lu = dense_form<real, NU, SCG_MAX_NU>(cold->R, eu);
             }
             reward = -(real(0.5) * lx + real(0.5) * lu);
         } else {
@@ -592,10 +606,10 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
     e.t = t + 1;
     if (cfg & CFG_HAS_ROWS) {
         bool violated, almost;
-        eval_constraints<KIND, real, LEAN>(h, cold, st, raw, false, c_out, n, i, violated, almost, cfg);
+        eval_constraints<KIND, real, PLAIN>(h, cold, st, raw, false, c_out, n, i, violated, almost, cfg);
         e.viol = violated;
         if (violated) { info |= SCG_INFO_VIOLATION; if (cfg & CFG_DONE_VIOLATION) done = true; }
-        if (!LEAN && h.cost == SCG_COST_RL_REWARD && h.use_constraint_penalty && almost) reward += h.constraint_penalty;
+        if (!PLAIN && (cfg & CFG_PENALTY) && almost) reward += h.constraint_penalty;
     }
     if (e.t >= h.ctrl_steps) {
         if (!done) info |= SCG_INFO_TRUNCATED;
@@ -690,12 +704,16 @@ k_reset(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold
         real raw0[NU];
 #pragma unroll
         for (int j = 0; j < NU; ++j) raw0[j] = real(0);
-        eval_constraints<KIND, real, false>(h, cold, st, raw0, true, b.c_values, n, i, v, a);
+        eval_constraints<KIND, real>(h, cold, st, raw0, true, b.c_values, n, i, v, a, h.cfg | CFG_FULL_STATE);
     }
 }
 
 // K fused control steps (scg_step is K = 1 with the per-step outputs)
-template <int KIND, typename real, int ATT, bool LEAN>
+// LEAN: the auto-reset takes a spare initial state drawn ahead (reset() draws nothing but uniform init offsets).
+// PLAIN (LEAN only): none of the per-step extras is configured -- disturbances, adversary, external force, dense /
+// tolerance / symmetric constraints, off-diagonal Q / R, constraint penalty, gate geometry -- and their uniform
+// branches are compiled out (the headline workload: the loop must stay inside the instruction cache).
+template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN = false>
 __global__ void __launch_bounds__(ENV_BLOCK, sizeof(real) == 4 ? 8 : 1)
 k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, const Buf<real> b, const Roll<real> ro) {
     constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
@@ -754,13 +772,13 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
         // after the loop is rebuilt from e there
         real sl[LEAN ? NX : 1];
         real (&sk)[NX] = *reinterpret_cast<real (*)[NX]>(LEAN ? sl : st);
-        step_env<KIND, real, ATT, LEAN>(h, cold, b, key, n, ii, e, raw, cfg, sk, reward, done, info, mse, mot, c_out);
+        step_env<KIND, real, ATT, LEAN, PLAIN>(h, cold, b, key, n, ii, e, raw, cfg, sk, reward, done, info, mse, mot, c_out);
         ep_ret += reward; ep_len += 1;
         const bool viol = (info & SCG_INFO_VIOLATION) != 0u;
         ep_viol += viol ? 1 : 0;
         s_viol += viol ? 1.f : 0.f;
         s_mse += float(mse);
-        if (cfg & CFG_GATE_GEOMETRY) {
+        if (!PLAIN && (cfg & CFG_GATE_GEOMETRY)) {
             s_gates += (info & SCG_INFO_GATE_PASSED) ? 1.f : 0.f;
             s_coll += (info & SCG_INFO_COLLISION) ? 1.f : 0.f;
         }
@@ -853,7 +871,7 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     if (b.ep_violations) b.ep_violations[ii] = ep_viol;
     if (b.stats) {   // warp-shuffle reduction, one atomic per warp per statistic
         const float steps = valid ? float(ro.k_steps) : 0.f;
-        constexpr int NS = 11;
+        constexpr int NS = PLAIN ? 9 : 11;
         float v[11] = {ep_acc[0 * ENV_BLOCK], ep_acc[1 * ENV_BLOCK], ep_acc[2 * ENV_BLOCK], s_viol, s_mse, ep_acc[3 * ENV_BLOCK],
                        ep_acc[4 * ENV_BLOCK], ep_acc[5 * ENV_BLOCK], steps, s_gates, s_coll};
         const int slot[11] = {SCG_STAT_EPISODES, SCG_STAT_RETURN, SCG_STAT_LENGTH, SCG_STAT_VIOLATION_STEPS,
