@@ -147,3 +147,26 @@ def test_config2_size_is_deterministic():
     st = out[0][2]
     assert st["env_steps"] == n * k and st["length"] <= st["env_steps"] and st["episodes"] == st["violated_episodes"] + st["truncated"] + st["completed"]
     assert not torch.isnan(out[0][0]).any()
+
+
+def test_kernel_variant_selection():
+    """scg_kernel_variant: 2 = LEAN + PLAIN for the headline workload, 1 = LEAN when only per-step extras are
+    configured (the spare reset still applies), 0 = GENERAL as soon as reset() must draw more than uniform init offsets."""
+    from safe_control_gym_b200.envs.cartpole import BatchedCartPole
+    lib_variant = lambda env: int(env.lib.scg_kernel_variant(env._h))
+    a = _quad(64)
+    assert lib_variant(a) == 2 and a.lean
+    b = _quad(64, gate_geometry=True)
+    assert lib_variant(b) == 1
+    c = _quad(64, disturbances={"action": [dict(disturbance_func="white_noise", std=0.01)]})
+    assert lib_variant(c) == 1
+    d = _quad(64, disturbances={"action": [dict(disturbance_func="impulse", magnitude=0.01, step_offset=None, duration=2, decay_rate=0.9)]})
+    assert lib_variant(d) == 0 and not d.lean
+    e = _quad(64, disturbances={"action": [dict(disturbance_func="impulse", magnitude=0.01, step_offset=3, duration=2, decay_rate=0.9)]})
+    assert lib_variant(e) == 1
+    f = _quad(64, randomized_inertial_prop=True)
+    assert lib_variant(f) == 0
+    g = BatchedCartPole(num_envs=64, disturbances={"action": [dict(disturbance_func="white_noise", std=0.2)]})
+    assert lib_variant(g) == 1
+    for env in (a, b, c, d, e, f, g):
+        env.close()
