@@ -272,6 +272,21 @@ int scg_symbolic_loss(scg_env* env, const void* x, const void* u, const void* xr
  * compute-bound fused rollout, since MEASURED_PEAKS.json carries no non-tensor fp32 figure. */
 int scg_measure_fp32_peak(double* tflops_out);
 /* number of kernels this handle has launched (bench.py "gpu_launches") */
+/* Gains and motor constants of the DSL CF2.x PID (quadrotor_utils.py:76-122, `PIDController.__init__`). */
+typedef struct scg_pid_config {
+    double g, m, kf, km, pwm2rpm_scale, pwm2rpm_const, min_pwm, max_pwm;
+    double p_coeff_for[3], i_coeff_for[3], d_coeff_for[3], p_coeff_tor[3], i_coeff_tor[3], d_coeff_tor[3];
+} scg_pid_config;
+
+/* Closed-loop fused rollout: like scg_rollout, but the action of every control step is computed on the device by the
+ * PID from the env's state before the step and the reference point X_GOAL (stabilisation) / X_GOAL[ctrl_step]
+ * (trajectory tracking), as the reference's loops do on the host (competition_utils.py:338-356 `thrusts` for
+ * quad_type 3, controllers/pid/pid.py:97-141 for quad_type 2).  args->actions is ignored.  pid_mem [9][n] (precision
+ * of the env) is the controller memory (integral position error, last rpy, integral rotation error); zero it for a
+ * fresh controller; it is zeroed for an env whenever that env auto-resets.  actions_out (optional) [k][n][nu]. */
+int scg_rollout_pid(scg_env* env, const scg_pid_config* pid, void* pid_mem, const scg_rollout_args* args, void* actions_out,
+                    void* stream);
+
 /* info["current_target_gate_in_range"] / ["current_target_gate_pos"] of Quadrotor._get_info (quadrotor.py:1093-1112)
  * for every env, from the bound state / flags / episode buffers: out_pose [6][n] (precision of the env) = the
  * current gate's true pose (x, y, z + height, r, p, yaw incl. this episode's offsets) when the drone is within the

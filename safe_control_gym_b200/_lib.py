@@ -32,7 +32,7 @@ STAT_NAMES = ["episodes", "return", "length", "violation_steps", "mse", "gates",
               "completed", "env_steps", "violated_episodes"]
 
 EXPORTS = ["scg_create", "scg_destroy", "scg_bind_buffers", "scg_set_injection", "scg_reset", "scg_step",
-           "scg_rollout", "scg_rollout_host", "scg_stats_reset", "scg_stats_read", "scg_constraints_eval",
+           "scg_rollout", "scg_rollout_host", "scg_rollout_pid", "scg_stats_reset", "scg_stats_read", "scg_constraints_eval",
            "scg_symbolic_eval", "scg_symbolic_loss", "scg_gate_info", "scg_measure_fp32_peak", "scg_launch_count", "scg_kernel_variant",
            "scg_last_error", "scg_version"]
 
@@ -105,6 +105,24 @@ class RolloutArgs(C.Structure):
                 ("log_out", C.c_void_p), ("log_stride", C.c_int32)]
 
 
+class PidConfig(C.Structure):
+    """scg_pid_config: defaults = PIDController.__init__ (quadrotor_utils.py:76-90)."""
+    _fields_ = [("g", C.c_double), ("m", C.c_double), ("kf", C.c_double), ("km", C.c_double),
+                ("pwm2rpm_scale", C.c_double), ("pwm2rpm_const", C.c_double), ("min_pwm", C.c_double), ("max_pwm", C.c_double),
+                ("p_coeff_for", C.c_double * 3), ("i_coeff_for", C.c_double * 3), ("d_coeff_for", C.c_double * 3),
+                ("p_coeff_tor", C.c_double * 3), ("i_coeff_tor", C.c_double * 3), ("d_coeff_tor", C.c_double * 3)]
+
+    def __init__(self, g=9.8, m=0.027, kf=3.16e-10, km=7.94e-12, pwm2rpm_scale=0.2685, pwm2rpm_const=4070.3, min_pwm=20000,
+                 max_pwm=65535, p_coeff_for=(.4, .4, 1.25), i_coeff_for=(.05, .05, .05), d_coeff_for=(.2, .2, .5),
+                 p_coeff_tor=(70000., 70000., 60000.), i_coeff_tor=(.0, .0, 500.), d_coeff_tor=(20000., 20000., 12000.)):
+        super().__init__()
+        self.g, self.m, self.kf, self.km = g, m, kf, km
+        self.pwm2rpm_scale, self.pwm2rpm_const, self.min_pwm, self.max_pwm = pwm2rpm_scale, pwm2rpm_const, min_pwm, max_pwm
+        for name, v in (("p_coeff_for", p_coeff_for), ("i_coeff_for", i_coeff_for), ("d_coeff_for", d_coeff_for),
+                        ("p_coeff_tor", p_coeff_tor), ("i_coeff_tor", i_coeff_tor), ("d_coeff_tor", d_coeff_tor)):
+            setattr(self, name, (C.c_double * 3)(*[float(x) for x in v]))
+
+
 _lib = None
 
 
@@ -126,6 +144,7 @@ def load():
     lib.scg_step.argtypes = [vp, vp, vp]
     lib.scg_rollout.argtypes = [vp, C.POINTER(RolloutArgs), vp]
     lib.scg_rollout_host.argtypes = [vp, vp, i32, i32, vp]
+    lib.scg_rollout_pid.argtypes = [vp, C.POINTER(PidConfig), vp, C.POINTER(RolloutArgs), vp, vp]
     lib.scg_stats_reset.argtypes = [vp, vp]
     lib.scg_stats_read.argtypes = [vp, C.POINTER(C.c_double), vp]
     lib.scg_constraints_eval.argtypes = [vp, vp, vp, i64, vp, vp, vp]

@@ -412,14 +412,34 @@ extern "C" int scg_reset(scg_env* e, const uint8_t* mask, const void* inject_ini
     return rc;
 }
 
-static int run_steps(scg_env* e, const void* actions, int k_steps, void* reward_out, uint8_t* done_out, void* log_out,
-                     int log_stride, int step_outputs, cudaStream_t st) {
-    if (e->cfg.precision == 32) {
-        Roll<float> ro{(const float*)actions, k_steps, (float*)reward_out, done_out, (float*)log_out, log_stride, step_outputs};
-        return dispatch_rollout<float>(e, ro, st);
+template <typename real>
+static int run_steps_t(scg_env* e, const void* actions, int k_steps, void* reward_out, uint8_t* done_out, void* log_out,
+                       int log_stride, int step_outputs, const scg_pid_config* pid, void* pid_mem, void* actions_out, cudaStream_t st) {
+    Roll<real> ro{};
+    ro.actions = (const real*)actions; ro.k_steps = k_steps; ro.reward_out = (real*)reward_out; ro.done_out = done_out;
+    ro.log_out = (real*)log_out; ro.log_stride = log_stride; ro.step_outputs = step_outputs;
+    if (pid) {
+        ro.use_pid = 1; ro.pid_mem = (real*)pid_mem; ro.actions_out = (real*)actions_out;
+        PidP<real>& P = ro.pid;
+        for (int j = 0; j < 3; ++j) {
+            P.p_for[j] = real(pid->p_coeff_for[j]); P.i_for[j] = real(pid->i_coeff_for[j]); P.d_for[j] = real(pid->d_coeff_for[j]);
+            P.p_tor[j] = real(pid->p_coeff_tor[j]); P.i_tor[j] = real(pid->i_coeff_tor[j]); P.d_tor[j] = real(pid->d_coeff_tor[j]);
+        }
+        P.gravity = real(pid->g * pid->m); P.inv_4kf = real(1.0 / (4.0 * pid->kf)); P.kf = real(pid->kf);
+        P.pwm_scale = real(pid->pwm2rpm_scale); P.pwm_const = real(pid->pwm2rpm_const); P.inv_pwm_scale = real(1.0 / pid->pwm2rpm_scale);
+        P.min_pwm = real(pid->min_pwm); P.max_pwm = real(pid->max_pwm);
+        const double dt = 1.0 / double(e->cfg.ctrl_freq);
+        P.dt = real(dt); P.inv_dt = real(double(e->cfg.ctrl_freq));
     }
-    Roll<double> ro{(const double*)actions, k_steps, (double*)reward_out, done_out, (double*)log_out, log_stride, step_outputs};
-    return dispatch_rollout<double>(e, ro, st);
+    return dispatch_rollout<real>(e, ro, st);
+}
+
+static int run_steps(scg_env* e, const void* actions, int k_steps, void* reward_out, uint8_t* done_out, void* log_out,
+                     int log_stride, int step_outputs, cudaStream_t st, const scg_pid_config* pid = nullptr, void* pid_mem = nullptr,
+                     void* actions_out = nullptr) {
+    if (e->cfg.precision == 32)
+        return run_steps_t<float>(e, actions, k_steps, reward_out, done_out, log_out, log_stride, step_outputs, pid, pid_mem, actions_out, st);
+    return run_steps_t<double>(e, actions, k_steps, reward_out, done_out, log_out, log_stride, step_outputs, pid, pid_mem, actions_out, st);
 }
 
 extern "C" int scg_step(scg_env* e, const void* action, void* stream) {
@@ -437,6 +457,21 @@ extern "C" int scg_rollout(scg_env* e, const scg_rollout_args* a, void* stream) 
     if (a->log_out && a->log_stride < 1) return fail(SCG_ERR_SHAPE, "log_stride must be >= 1");
     return run_steps(e, a->actions, a->k_steps, a->reward_out, a->done_out, a->log_out, a->log_stride > 0 ? a->log_stride : 1,
                      0, static_cast<cudaStream_t>(stream));
+}
+
+// Closed loop: K fused control steps whose actions come from the on-device DSL PID tracking the env's X_GOAL
+// (quadrotor_utils.py:70-278; competition_utils.py:338-356 / controllers/pid/pid.py:97-141).
+extern "C" int scg_rollout_pid(scg_env* e, const scg_pid_config* pid, void* pid_mem, const scg_rollout_args* a, void* actions_out,
+                               void* stream) {
+    if (!e || !pid || !pid_mem || !a) return fail(SCG_ERR_NULL, "scg_rollout_pid: null argument");
+    if (!e->bound) return fail(SCG_ERR_STATE, "scg_rollout_pid: buffers not bound");
+    if (!e->did_reset) return fail(SCG_ERR_STATE, "[ERROR] You must call env.reset() at least once before using env.step().");
+    if (e->cfg.env_kind != SCG_QUAD_3D && e->cfg.env_kind != SCG_QUAD_2D)
+        return fail(SCG_ERR_BAD_CONFIG, "scg_rollout_pid: the PID drives quad_type 2 and 3");
+    if (a->k_steps < 1) return fail(SCG_ERR_SHAPE, "k_steps must be >= 1");
+    if (a->log_out && a->log_stride < 1) return fail(SCG_ERR_SHAPE, "log_stride must be >= 1");
+    return run_steps(e, nullptr, a->k_steps, a->reward_out, a->done_out, a->log_out, a->log_stride > 0 ? a->log_stride : 1, 0,
+                     static_cast<cudaStream_t>(stream), pid, pid_mem, actions_out);
 }
 
 // Actions in pinned host memory: chunked H2D copies on a private stream, double-buffered against

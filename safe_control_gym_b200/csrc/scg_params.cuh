@@ -134,9 +134,19 @@ template <typename real> struct Buf {
     const real* adv_action;
 };
 
+// the DSL PID's gains and motor constants (quadrotor_utils.py:76-122), for closed-loop rollouts (scg_pid.cuh)
+template <typename real> struct PidP {
+    real p_for[3], i_for[3], d_for[3], p_tor[3], i_tor[3], d_tor[3];
+    real gravity, inv_4kf, kf, pwm_scale, pwm_const, inv_pwm_scale, min_pwm, max_pwm, dt, inv_dt;
+};
+
 template <typename real> struct Roll {
     const real* actions; int32_t k_steps; real* reward_out; uint8_t* done_out; real* log_out; int32_t log_stride;
     int32_t step_outputs;           // 1: write the per-step outputs of Buf (scg_step), 0: only final obs/state
+    int32_t use_pid;                // closed loop: actions come from the on-device PID instead of `actions`
+    real* pid_mem;                  // [9][n] controller memory
+    real* actions_out;              // optional [K][n][nu]: the actions the PID commanded
+    PidP<real> pid;
 };
 
 template <typename real> struct ResetInject { const real* init; const real* inertia; const int32_t* offsets; };

@@ -1,0 +1,74 @@
+// scg_pid.cuh -- the DSL CF2.x PID (quadrotor_utils.py:70-278, `PIDController`) as an on-device action source for
+// closed-loop fused rollouts: position PID -> target thrust vector and attitude ->
+// attitude PID -> mixer -> PWM clip -> RPM -> per-rotor thrust KF rpm^2 (competition_utils.py:338-356 for 3D,
+// controllers/pid/pid.py:97-141 for 2D).  One call per env and control step; the controller's memory (integral of the
+// position error, last Euler angles, integral of the rotation error: 9 values) lives in a caller-owned [9][N] buffer.
+#pragma once
+#include "scg_params.cuh"
+#include "scg_math.cuh"
+
+namespace scg {
+
+// pos / vel / rpy: the env's current state (world frame; rpy = the canonical angles the reference reads back from
+// PyBullet); tpos / tvel: the reference point.  act: 4 rotor thrusts (3D) or the two pair sums (2D).
+template <int KIND, typename real>
+__device__ __noinline__ void pid_action(const PidP<real>& P, const real* __restrict__ pos, const real* __restrict__ vel,
+                                        const real* __restrict__ rpy, const real* __restrict__ tpos, const real* __restrict__ tvel,
+                                        real* __restrict__ mem, int64_t n, int64_t i, real* __restrict__ act) {
+    real ipos[3], last[3], irot[3];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) { ipos[j] = mem[int64_t(j) * n + i]; last[j] = mem[int64_t(3 + j) * n + i]; irot[j] = mem[int64_t(6 + j) * n + i]; }
+    // body-to-world rotation of the current attitude: getMatrixFromQuaternion(getQuaternionFromEuler(rpy)) = Rz Ry Rx
+    real sph, cph, sth, cth, sps, cps;
+    m_sincos(rpy[0], &sph, &cph); m_sincos(rpy[1], &sth, &cth); m_sincos(rpy[2], &sps, &cps);
+    const real R[9] = {cps * cth, cps * sth * sph - sps * cph, cps * sth * cph + sps * sph,
+                       sps * cth, sps * sth * sph + cps * cph, sps * sth * cph - cps * sph,
+                       -sth, cth * sph, cth * cph};
+    // ---- _compute_force_and_euler (quadrotor_utils.py:188-237)
+    real tt[3];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+        const real pe = tpos[j] - pos[j], ve = tvel[j] - vel[j];
+        ipos[j] = m_clip(ipos[j] + pe * P.dt, real(-2), real(2));
+        if (j == 2) ipos[j] = m_clip(ipos[j], real(-0.15), real(0.15));
+        tt[j] = (P.p_for[j] * pe + P.i_for[j] * ipos[j]) + P.d_for[j] * ve;
+    }
+    tt[2] += P.gravity;
+    const real scalar = m_max(real(0), (tt[0] * R[2] + tt[1] * R[5]) + tt[2] * R[8]);
+    const real thrust = (m_sqrt(scalar * P.inv_4kf) - P.pwm_const) * P.inv_pwm_scale;
+    const real inv_n = real(1) / m_sqrt((tt[0] * tt[0] + tt[1] * tt[1]) + tt[2] * tt[2]);
+    const real z[3] = {tt[0] * inv_n, tt[1] * inv_n, tt[2] * inv_n};
+    // target yaw 0: x_c = (1, 0, 0); y = z x x_c / |.|, x = y x z; M = [x y z] (columns)
+    real y[3] = {real(0), z[2], -z[1]};
+    const real inv_y = real(1) / m_sqrt(y[1] * y[1] + y[2] * y[2]);
+    y[1] *= inv_y; y[2] *= inv_y;
+    const real x[3] = {y[1] * z[2] - y[2] * z[1], y[2] * z[0] - y[0] * z[2], y[0] * z[1] - y[1] * z[0]};
+    const real M[9] = {x[0], y[0], z[0], x[1], y[1], z[1], x[2], y[2], z[2]};
+    // ---- _compute_rpms (quadrotor_utils.py:239-278): E = M^T R - R^T M, rot_e = (E21, E02, E10)
+    auto mtr = [&](int a, int b) { return (M[0 + a] * R[0 + b] + M[3 + a] * R[3 + b]) + M[6 + a] * R[6 + b]; };   // (M^T R)[a][b]
+    const real rot_e[3] = {mtr(2, 1) - mtr(1, 2), mtr(0, 2) - mtr(2, 0), mtr(1, 0) - mtr(0, 1)};
+    real tq[3];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+        const real rate_e = -(rpy[j] - last[j]) * P.inv_dt;   // target rates are 0
+        last[j] = rpy[j];
+        irot[j] = m_clip(irot[j] - rot_e[j] * P.dt, real(-1500), real(1500));
+        if (j < 2) irot[j] = m_clip(irot[j], real(-1), real(1));
+        tq[j] = m_clip((-P.p_tor[j] * rot_e[j] + P.d_tor[j] * rate_e) + P.i_tor[j] * irot[j], real(-3200), real(3200));
+    }
+    // MIXER_MATRIX (quadrotor_utils.py:121)
+    const real mix[4] = {real(0.5) * tq[0] - real(0.5) * tq[1] + tq[2], real(0.5) * tq[0] + real(0.5) * tq[1] - tq[2],
+                         -real(0.5) * tq[0] + real(0.5) * tq[1] + tq[2], -real(0.5) * tq[0] - real(0.5) * tq[1] - tq[2]};
+    real f[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const real rpm = P.pwm_scale * m_clip(thrust + mix[j], P.min_pwm, P.max_pwm) + P.pwm_const;
+        f[j] = P.kf * rpm * rpm;
+    }
+    if constexpr (KIND == SCG_QUAD_3D) { act[0] = f[0]; act[1] = f[1]; act[2] = f[2]; act[3] = f[3]; }
+    else { act[0] = f[0] + f[3]; act[1] = f[1] + f[2]; }
+#pragma unroll
+    for (int j = 0; j < 3; ++j) { mem[int64_t(j) * n + i] = ipos[j]; mem[int64_t(3 + j) * n + i] = last[j]; mem[int64_t(6 + j) * n + i] = irot[j]; }
+}
+
+}  // namespace scg

@@ -13,6 +13,7 @@
 // those features out, GENERAL keeps them behind uniform branches.
 #pragma once
 #include "scg_env.cuh"
+#include "scg_pid.cuh"
 
 namespace scg {
 
@@ -755,7 +756,12 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     real* const c_out = ro.step_outputs ? b.c_values : nullptr;
     // software prefetch of the next action (one 16-byte load per 3D env per step)
     real raw[NU], nxt[NU];
-    load_action<NU, real>(ro.actions + ii * NU, nxt);
+    const bool closed_loop = !PLAIN && ro.use_pid != 0;   // uniform: actions from the on-device PID (scg_pid.cuh)
+    if (!closed_loop) load_action<NU, real>(ro.actions + ii * NU, nxt);
+    else {
+#pragma unroll
+        for (int j = 0; j < NU; ++j) nxt[j] = real(0);
+    }
     bool fresh = false;   // obs must come from a reset this step
     // LEAN: spare initial state for the next episode (drawn ahead, see draw_init_lean)
     __shared__ real sp_buf[LEAN ? Spare<KIND, real, ATT>::N * ENV_BLOCK : 1];
@@ -767,7 +773,33 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     for (int k = 0; k < ro.k_steps; ++k) {
 #pragma unroll
         for (int j = 0; j < NU; ++j) raw[j] = nxt[j];
-        if (k + 1 < ro.k_steps) load_action<NU, real>(ro.actions + (int64_t(k + 1) * n + ii) * NU, nxt);
+        if constexpr (!PLAIN && (KIND == SCG_QUAD_3D || KIND == SCG_QUAD_2D)) {
+            if (closed_loop) {   // action = PID(state before the step, reference point of this step)
+                real pos[3], vel[3], rpy[3], tp[3], tv[3], act[NU];
+                const int32_t gi = e.t < h.n_goal_rows - 1 ? e.t : h.n_goal_rows - 1;
+                const bool stab = (cfg & CFG_STAB) != 0u;
+                auto goal_at = [&](int d) { return stab ? h.x_goal0[d] : cold->x_goal[int64_t(gi) * NX + d]; };
+                if constexpr (KIND == SCG_QUAD_3D) {
+                    pos[0] = e.x[0]; pos[1] = e.x[2]; pos[2] = e.x[4]; vel[0] = e.x[1]; vel[1] = e.x[3]; vel[2] = e.x[5];
+                    rpy[0] = e.a3.rpy[0]; rpy[1] = e.a3.rpy[1]; rpy[2] = e.a3.rpy[2];
+                    tp[0] = goal_at(0); tp[1] = goal_at(2); tp[2] = goal_at(4);
+                    tv[0] = stab ? real(0) : goal_at(1); tv[1] = stab ? real(0) : goal_at(3); tv[2] = stab ? real(0) : goal_at(5);
+                } else {
+                    pos[0] = e.x[0]; pos[1] = real(0); pos[2] = e.x[2]; vel[0] = e.x[1]; vel[1] = real(0); vel[2] = e.x[3];
+                    rpy[0] = real(0); rpy[1] = e.a2.theta; rpy[2] = real(0);
+                    tp[0] = goal_at(0); tp[1] = real(0); tp[2] = goal_at(2);
+                    tv[0] = stab ? real(0) : goal_at(1); tv[1] = real(0); tv[2] = stab ? real(0) : goal_at(3);
+                }
+                pid_action<KIND, real>(ro.pid, pos, vel, rpy, tp, tv, ro.pid_mem, n, ii, act);
+#pragma unroll
+                for (int j = 0; j < NU; ++j) raw[j] = act[j];
+                if (ro.actions_out) {
+#pragma unroll
+                    for (int j = 0; j < NU; ++j) ro.actions_out[(int64_t(k) * n + ii) * NU + j] = act[j];
+                }
+            }
+        }
+        if (!closed_loop && k + 1 < ro.k_steps) load_action<NU, real>(ro.actions + (int64_t(k + 1) * n + ii) * NU, nxt);
         // LEAN: env.state of this step is loop-local (it aliases the registers of e); what is observed
         // after the loop is rebuilt from e there
         real sl[LEAN ? NX : 1];
@@ -812,6 +844,10 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
                 }
                 ep_ret = real(0); ep_len = 0; ep_viol = 0;
                 fresh = true;
+                if (closed_loop) {   // PIDController.reset() with the env (quadrotor_utils.py:124-135)
+#pragma unroll
+                    for (int j = 0; j < 9; ++j) ro.pid_mem[int64_t(j) * n + ii] = real(0);
+                }
             }
         }
         if constexpr (LEAN) {

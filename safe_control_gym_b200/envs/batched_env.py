@@ -267,6 +267,29 @@ class BatchedEnvBase:
             L.check(self.lib.scg_rollout(self._h, C.byref(args), self._stream()))
         return self.buf_obs.t()
 
+    def rollout_pid(self, k_steps, pid=None, pid_mem=None, actions_out=None, reward_out=None, done_out=None, log_out=None,
+                    log_stride=1):
+        """K fused CLOSED-LOOP control steps: the action of every step comes from the on-device DSL PID
+        (quadrotor_utils.py:70-278) tracking ``X_GOAL`` -- the loop of competition_utils.thrusts /
+        controllers/pid/pid.py in one launch, no action table.  ``pid``: ``_lib.PidConfig`` (default gains);
+        ``pid_mem``: [9, N] controller memory, kept on the env between calls when omitted."""
+        if not self.initial_reset:
+            raise RuntimeError("[ERROR] You must call env.reset() at least once before using env.step().")
+        pid = pid if pid is not None else L.PidConfig()
+        if pid_mem is None:
+            if getattr(self, "pid_mem", None) is None:
+                self.pid_mem = torch.zeros(9, self.num_envs, dtype=self.dtype, device=self.device)
+            pid_mem = self.pid_mem
+        args = L.RolloutArgs()
+        args.actions, args.k_steps, args.log_stride = None, int(k_steps), int(log_stride)
+        args.reward_out = reward_out.data_ptr() if reward_out is not None else None
+        args.done_out = done_out.data_ptr() if done_out is not None else None
+        args.log_out = log_out.data_ptr() if log_out is not None else None
+        out = C.c_void_p(actions_out.data_ptr()) if actions_out is not None else None
+        with torch.cuda.device(self.device):
+            L.check(self.lib.scg_rollout_pid(self._h, C.byref(pid), C.c_void_p(pid_mem.data_ptr()), C.byref(args), out, self._stream()))
+        return self.buf_obs.t()
+
     def rollout_host(self, host_actions, chunk_steps=50):
         """Same as ``rollout`` with the action table in pinned HOST memory [K, N, nu]; the
         library pipelines the host->device copies against the kernel launches."""

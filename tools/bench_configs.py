@@ -102,6 +102,20 @@ def config5(scale, repeats, gate_geometry):
                 lean=bool(env.lean))
 
 
+def config_pid(scale, repeats):
+    """Closed loop: the headline 3D workload with the action of every step computed by the on-device DSL
+    PID (stabilisation at level0's goal) instead of read from a table -- no host or HBM action traffic at all."""
+    n, k = int(65536 * scale), 1000
+    kw = bench.env_kwargs()
+    env = BatchedQuadrotor(num_envs=n, device=DEV, dtype=torch.float32, attitude="fast_intrinsic", auto_reset=True, **kw)
+    env.reset()
+    dt = timed(lambda: env.rollout_pid(k), repeats)
+    st = env.stats()
+    return dict(config="closed loop: 3D 65,536 envs x 1,000 steps, on-device PID", envs=n, k=k, sec_per_launch=dt,
+                env_steps_per_sec=n * k / dt, flops_per_step=bench.FLOPS_PER_STEP + 330, bytes_per_step=72, episodes=st["episodes"],
+                completed=st["completed"], lean=bool(env.lean))
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--configs", default="3,4,5")
@@ -111,7 +125,8 @@ if __name__ == "__main__":
     args = ap.parse_args()
     for c in args.configs.split(","):
         r = {"3": lambda: config3(args.scale, args.repeats), "4": lambda: config4(args.scale, args.repeats),
-             "5": lambda: config5(args.scale, args.repeats, args.gate_geometry)}[c]()
+             "5": lambda: config5(args.scale, args.repeats, args.gate_geometry),
+             "pid": lambda: config_pid(args.scale, args.repeats)}[c]()
         r["tflops"] = r["flops_per_step"] * r["env_steps_per_sec"] / 1e12
         r["gbs"] = r["bytes_per_step"] * r["env_steps_per_sec"] / 1e9
         print(json.dumps(r), flush=True)
