@@ -294,10 +294,12 @@ int scg_rollout_pid(scg_env* env, const scg_pid_config* pid, void* pid_mem, cons
  * out_in_range [n] u8.  Either output may be NULL.  quad_type 3 only. */
 int scg_gate_info(scg_env* env, void* out_pose, uint8_t* out_in_range, void* stream);
 int64_t scg_launch_count(const scg_env* env);
-/* Which instantiation of the step kernel the config selected.  0 = GENERAL; 1 = LEAN: reset() draws nothing but
- * uniform initial-state offsets, so the auto-reset takes a spare state drawn ahead of time; 2 = LEAN + PLAIN: in
- * addition no per-step extra is configured (disturbances, adversary, external force, dense / tolerance / symmetric
- * constraints, off-diagonal Q or R, constraint penalty, gate geometry).  Same results in every variant. */
+/* Which instantiation of the step kernel the config selected.  1 = LEAN: the auto-reset takes a spare episode start
+ * (initial state, inertial properties, disturbance offsets) drawn ahead of time at a warp-convergent cadence;
+ * 2 = LEAN + PLAIN (fp32): in addition reset() draws nothing but uniform initial-state offsets and no per-step extra
+ * is configured (disturbances, adversary, external force, dense / tolerance / symmetric constraints, off-diagonal Q
+ * or R, constraint penalty, gate geometry), so all of that is compiled out; 0 = GENERAL: SCG_ATT_ROUNDTRIP only
+ * (validation: literal quaternion round trip, reset one lane at a time).  Same results in every variant. */
 int scg_kernel_variant(const scg_env* env);
 const char* scg_last_error(void);
 const char* scg_version(void);

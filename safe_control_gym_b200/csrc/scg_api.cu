@@ -266,21 +266,27 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
             const scg_disturbance& s = c.dist[ch][q];
             if ((s.kind == SCG_DIST_IMPULSE || s.kind == SCG_DIST_STEP) && s.step_offset < 0) reset_draws = true;
         }
-    *lean_out = !reset_draws;
+    if (reset_draws) h.cfg |= CFG_RESET_EXTRAS;
+    *lean_out = true;   // every config takes the spare reset; SCG_ATT_ROUNDTRIP (validation) is routed to the GENERAL kernel by the launcher
     return SCG_OK;
 }
 
 extern "C" const char* scg_last_error(void) { return g_err.c_str(); }
 extern "C" const char* scg_version(void) { return "scg_b200 0.1 (sm_100a)"; }
 extern "C" int64_t scg_launch_count(const scg_env* env) { return env ? env->launches : 0; }
-extern "C" int scg_kernel_variant(const scg_env* env) { return !env ? 0 : env->lean ? (env->plain ? 2 : 1) : 0; }
+extern "C" int scg_kernel_variant(const scg_env* env) {
+    if (!env || !env->lean) return 0;
+    const bool quad_att = env->cfg.env_kind == SCG_QUAD_3D || env->cfg.env_kind == SCG_QUAD_2D;
+    if (quad_att && env->cfg.attitude_mode == SCG_ATT_ROUNDTRIP) return 0;   // validation mode: GENERAL kernel (scg_inst.cuh)
+    return env->plain && env->cfg.precision == 32 ? 2 : 1;
+}
 
 template <typename real> static int upload_params(scg_env* e) {
     Cold<real>* k = new (std::nothrow) Cold<real>;
     if (!k) return fail(SCG_ERR_BAD_CONFIG, "out of host memory");
     Hot<real>& h = *reinterpret_cast<Hot<real>*>(sizeof(real) == 4 ? (void*)&e->hf : (void*)&e->hd);
     int rc = build_params<real>(e->cfg, e->nx, e->nu, h, *k, &e->n_rows, &e->n_slots, &e->lean);
-    e->plain = e->lean && !(h.cfg & (CFG_DISTURBED | CFG_COLD_CONSTRAINTS | CFG_QR_DENSE | CFG_PENALTY | CFG_GATE_GEOMETRY));
+    e->plain = e->lean && !(h.cfg & (CFG_DISTURBED | CFG_COLD_CONSTRAINTS | CFG_QR_DENSE | CFG_PENALTY | CFG_GATE_GEOMETRY | CFG_RESET_EXTRAS));
     if (rc != SCG_OK) { delete k; return rc; }
     const int rows = e->cfg.n_goal_rows > 0 ? e->cfg.n_goal_rows : 1;
     real* goal_host = new real[size_t(rows) * e->nx];

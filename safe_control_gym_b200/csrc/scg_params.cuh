@@ -94,6 +94,7 @@ enum : uint32_t {
     CFG_COLD_CONSTRAINTS = 1u << 16,// dense rows, tolerances, symmetric or mixed-strictness bounds: no merged box
     CFG_QR_DENSE = 1u << 17,        // quadratic cost with off-diagonal Q / R
     CFG_PENALTY = 1u << 18,         // rl_reward with use_constraint_penalty
+    CFG_RESET_EXTRAS = 1u << 19,    // reset() draws more than uniform init offsets: inertial properties, disturbance offsets, normal draws
 };
 
 template <typename real> struct DenseRow {     // linear: c = a . x - b ; quadratic: c = x' P x - b

@@ -329,6 +329,73 @@ SCG_DEV void reset_from_spare(const real* __restrict__ sp, EnvRegs<KIND, real>& 
     }
 }
 
+// The general spare (CFG_RESET_EXTRAS): everything Quadrotor.reset() draws for episode `ep` -- initial state with
+// uniform or normal offsets, inertial properties, impulse / step disturbance offsets -- with the same Philox
+// counters as reset_env_body.  Slots after the state / attitude block: 4 inertial properties, then one per
+// disturbance slot.  Out of line: it runs for all lanes together at the refill cadence.
+constexpr int SPARE_EXTRA = 4 + 3 * SCG_MAX_DIST;
+
+template <int KIND, typename real, int ATT>
+__device__ __noinline__ void draw_spare_general(const Hot<real>& h, const Cold<real>* __restrict__ cold, RngKey key, uint32_t ep,
+                                                real* __restrict__ sp) {
+    constexpr int NX = Dims<KIND>::NX, N0 = Spare<KIND, real, ATT>::N;
+    real init[NX];
+#pragma unroll
+    for (int d = 0; d < NX; ++d) init[d] = h.init_state[d];
+    if (h.any_init_rand) {
+        real u[NX], z[NX];
+#pragma unroll
+        for (int d = 0; d < NX; ++d) { u[d] = real(0); z[d] = real(0); }
+        if (h.any_init_rand & 1) draw_uniforms<real, NX>(key, 0u, ep, STREAM_RESET_INIT, u);
+        if (h.any_init_rand & 2) draw_normals<real, NX>(key, 0u, ep, STREAM_RESET_INIT, z);
+#pragma unroll
+        for (int d = 0; d < NX; ++d) init[d] += rand_value(h.init_rand[d], u[d], z[d]);
+    }
+    spare_store<KIND, real, ATT>(init, sp);
+    if (h.any_inertia_rand) {   // quadrotor.py:447-467
+        real u[4] = {real(0), real(0), real(0), real(0)}, z[4] = {real(0), real(0), real(0), real(0)};
+        if (h.any_inertia_rand & 1) draw_uniforms<real, 4>(key, 0u, ep, STREAM_RESET_INERTIA, u);
+        if (h.any_inertia_rand & 2) draw_normals<real, 4>(key, 0u, ep, STREAM_RESET_INERTIA, z);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) sp[(N0 + j) * ENV_BLOCK] = h.inertia_nominal[j] + rand_value(h.inertia_rand[j], u[j], z[j]);
+    }
+    for (int ch = 0; ch < 3; ++ch) {   // disturbances.py:122-126, 169-172
+        const int nd = ch == 0 ? h.n_dist_obs : ch == 1 ? h.n_dist_act : h.n_dist_dyn;
+        for (int k = 0; k < nd; ++k) {
+            const DistP<real>& D = cold->dist[ch][k];
+            if ((D.kind == SCG_DIST_IMPULSE || D.kind == SCG_DIST_STEP) && D.step_offset < 0 && D.slot < 3 * SCG_MAX_DIST) {
+                const U4 w = philox4x32_10(0u, ep, STREAM_RESET_OFFSETS, uint32_t(D.slot >> 2), key.seed, key.env);
+                sp[(N0 + 4 + D.slot) * ENV_BLOCK] = real(randint(word_of(w, D.slot & 3), D.max_step));   // exact: offsets are small integers
+            }
+        }
+    }
+}
+
+// ... and what the restarting lane does with it beyond reset_from_spare: publish the episode's inertial properties
+// and disturbance offsets to the batch buffers the step reads them from.
+template <int KIND, typename real, int ATT>
+__device__ __noinline__ void apply_spare_extras(const Hot<real>& h, const Cold<real>* __restrict__ cold, real* __restrict__ inertia,
+                                                int32_t* __restrict__ dist_offset, const real* __restrict__ sp, int64_t n, int64_t i,
+                                                Inertia<real>* in_out) {
+    constexpr int N0 = Spare<KIND, real, ATT>::N;
+    if (inertia) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            inertia[int64_t(j) * n + i] = h.any_inertia_rand ? sp[(N0 + j) * ENV_BLOCK] : h.inertia_nominal[j];
+    }
+    Inertia<real> in;
+    load_inertia<KIND, real>(h, inertia, n, i, in);
+    *in_out = in;
+    for (int ch = 0; ch < 3; ++ch) {
+        const int nd = ch == 0 ? h.n_dist_obs : ch == 1 ? h.n_dist_act : h.n_dist_dyn;
+        for (int k = 0; k < nd; ++k) {
+            const DistP<real>& D = cold->dist[ch][k];
+            if ((D.kind == SCG_DIST_IMPULSE || D.kind == SCG_DIST_STEP) && D.step_offset < 0 && D.slot < 3 * SCG_MAX_DIST)
+                dist_offset[int64_t(D.slot) * n + i] = int32_t(sp[(N0 + 4 + D.slot) * ENV_BLOCK]);
+        }
+    }
+}
+
 // PyBullet-side INIT_ANG_VEL of the episode the spare started (valid until the next draw)
 template <int KIND, typename real>
 SCG_DEV void spare_ang0(const real* __restrict__ sp, real (&ang0)[3]) {
@@ -732,7 +799,7 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     e.resets = b.episode[ii];
     unpack_flags<KIND, real>(e, b.flags[ii]);
     real st[NX];   // env.state after the last step (LEAN: rebuilt from the registers after the loop)
-    load_inertia<KIND, real>(h, LEAN ? nullptr : b.inertia, n, ii, e.in);
+    load_inertia<KIND, real>(h, PLAIN ? nullptr : b.inertia, n, ii, e.in);
     derive_attitude<KIND, real, ATT>(e);
     real ep_ret = b.ep_return ? b.ep_return[ii] : real(0);
     int32_t ep_len = b.ep_length ? b.ep_length[ii] : 0;
@@ -764,7 +831,7 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     }
     bool fresh = false;   // obs must come from a reset this step
     // LEAN: spare initial state for the next episode (drawn ahead, see draw_init_lean)
-    __shared__ real sp_buf[LEAN ? Spare<KIND, real, ATT>::N * ENV_BLOCK : 1];
+    __shared__ real sp_buf[LEAN ? (Spare<KIND, real, ATT>::N + (PLAIN ? 0 : SPARE_EXTRA)) * ENV_BLOCK : 1];
     real* const sp = sp_buf + threadIdx.x;
     bool spare_ok = false;
     const bool ahead = ro.k_steps >= 16;   // uniform: host-driven single steps draw on demand only
@@ -855,13 +922,22 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
             // one inline copy of the draw: at the cadence every lane that used its spare refills it together;
             // a lane that ends two episodes inside one period draws on the spot
             if (!spare_ok && (restart || (ahead && (k & 15) == 0))) {
-                real init[NX];
-                draw_init_lean<KIND, real>(h, key, (cfg & CFG_RESEED) ? 0u : uint32_t(e.resets), init);
-                spare_store<KIND, real, ATT>(init, sp);
+                const uint32_t next_ep = (cfg & CFG_RESEED) ? 0u : uint32_t(e.resets);
+                if (!PLAIN && (cfg & CFG_RESET_EXTRAS)) draw_spare_general<KIND, real, ATT>(h, cold, key, next_ep, sp);
+                else {
+                    real init[NX];
+                    draw_init_lean<KIND, real>(h, key, next_ep, init);
+                    spare_store<KIND, real, ATT>(init, sp);
+                }
                 spare_ok = true;
             }
             if (restart) {
                 reset_from_spare<KIND, real, ATT>(sp, e);
+                if (!PLAIN && (cfg & CFG_RESET_EXTRAS)) {
+                    Inertia<real> in;
+                    apply_spare_extras<KIND, real, ATT>(h, cold, b.inertia, b.dist_offset, sp, n, ii, &in);
+                    e.in = in;
+                }
                 spare_ok = false;
             }
         }

@@ -150,23 +150,42 @@ def test_config2_size_is_deterministic():
 
 
 def test_kernel_variant_selection():
-    """scg_kernel_variant: 2 = LEAN + PLAIN for the headline workload, 1 = LEAN when only per-step extras are
-    configured (the spare reset still applies), 0 = GENERAL as soon as reset() must draw more than uniform init offsets."""
+    """scg_kernel_variant: 2 = LEAN + PLAIN for the headline workload, 1 = LEAN as soon as a per-step extra or a
+    reset-time draw beyond uniform init offsets is configured (the spare reset carries those too), 0 = GENERAL for the
+    literal round-trip attitude (validation)."""
     from safe_control_gym_b200.envs.cartpole import BatchedCartPole
     lib_variant = lambda env: int(env.lib.scg_kernel_variant(env._h))
-    a = _quad(64)
-    assert lib_variant(a) == 2 and a.lean
-    b = _quad(64, gate_geometry=True)
-    assert lib_variant(b) == 1
-    c = _quad(64, disturbances={"action": [dict(disturbance_func="white_noise", std=0.01)]})
-    assert lib_variant(c) == 1
-    d = _quad(64, disturbances={"action": [dict(disturbance_func="impulse", magnitude=0.01, step_offset=None, duration=2, decay_rate=0.9)]})
-    assert lib_variant(d) == 0 and not d.lean
-    e = _quad(64, disturbances={"action": [dict(disturbance_func="impulse", magnitude=0.01, step_offset=3, duration=2, decay_rate=0.9)]})
-    assert lib_variant(e) == 1
-    f = _quad(64, randomized_inertial_prop=True)
-    assert lib_variant(f) == 0
-    g = BatchedCartPole(num_envs=64, disturbances={"action": [dict(disturbance_func="white_noise", std=0.2)]})
-    assert lib_variant(g) == 1
-    for env in (a, b, c, d, e, f, g):
+    imp = lambda off: {"action": [dict(disturbance_func="impulse", magnitude=0.01, step_offset=off, duration=2, decay_rate=0.9)]}
+    cases = [(_quad(64), 2), (_quad(64, gate_geometry=True), 1),
+             (_quad(64, disturbances={"action": [dict(disturbance_func="white_noise", std=0.01)]}), 1),
+             (_quad(64, disturbances=imp(None)), 1), (_quad(64, disturbances=imp(3)), 1),
+             (_quad(64, randomized_inertial_prop=True), 1), (_quad(64, attitude="roundtrip"), 0),
+             (_quad(64, dtype=torch.float64), 1),
+             (BatchedCartPole(num_envs=64, disturbances={"action": [dict(disturbance_func="white_noise", std=0.2)]}), 1)]
+    for env, want in cases:
+        assert lib_variant(env) == want, (want, lib_variant(env))
         env.close()
+
+
+def test_spare_reset_with_inertia_and_offsets_equals_stepping():
+    """The general spare (inertial properties + disturbance offsets drawn ahead) in a fused rollout against K
+    single-step launches of the same env: bit-identical state, inertia and offset buffers after many auto-resets."""
+    U = lambda lo, hi: dict(distrib="uniform", low=lo, high=hi)
+    over = dict(randomized_inertial_prop=True, dyn_uses_episode_inertia=True,
+                inertial_prop_randomization_info={"M": U(-0.005, 0.005), "Ixx": U(-1e-6, 1e-6), "Iyy": dict(distrib="normal", loc=0.0, scale=3e-7)},
+                disturbances={"action": [dict(disturbance_func="impulse", magnitude=0.01, step_offset=None, duration=2, decay_rate=0.9),
+                                         dict(disturbance_func="step", magnitude=0.002, step_offset=None)],
+                              "observation": [dict(disturbance_func="step", magnitude=0.001, step_offset=None)]},
+                episode_len_sec=1)
+    n, k = 4096, 150
+    acts = _actions(n, k)
+    a, b = _quad(n, **over), _quad(n, **over)
+    a.reset(); b.reset()
+    a.rollout(acts)
+    for t in range(k):
+        b.step(acts[t])
+    torch.cuda.synchronize()
+    for name in ("state", "ctrl_step", "episode", "flags", "obs", "inertia", "dist_offset", "ep_length"):
+        assert torch.equal(getattr(a, "buf_" + name), getattr(b, "buf_" + name)), name
+    assert int(a.buf_episode.max()) >= 3   # 60-step episodes: every env restarted at least twice
+    a.close(); b.close()

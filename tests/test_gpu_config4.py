@@ -30,7 +30,7 @@ def test_config4_matches_oracle(dtype, tol):
     from safe_control_gym_b200.envs.quadrotor import BatchedQuadrotor
     n, steps, base = 64, 150, 500
     env = BatchedQuadrotor(num_envs=n, dtype=dtype, auto_reset=True, seed_offset=base, info_in_reset=True, **CFG)
-    assert not env.lean
+    assert int(env.lib.scg_kernel_variant(env._h)) == 1   # spare reset carrying inertia + offsets
     kw = {k: v for k, v in CFG.items() if k != "seed"}
     lanes = [0, 7, 31, 32, 63]
     refs = {i: QuadOracle(draws=PhiloxEnvDraws(CFG["seed"], base + i), info_in_reset=True, **kw) for i in lanes}
