@@ -323,6 +323,51 @@ class BatchedEnvBase:
         c = self.ctrl_step_counter
         return c * self.PYB_STEPS_PER_CTRL
 
+    # ------------------------------------------------------------------ VecEnv attribute / method access
+    def _get_indices(self, indices):
+        """vec_env.py:154-163: None -> all envs, an int -> [int]."""
+        if indices is None:
+            return list(range(self.num_envs))
+        return [indices] if isinstance(indices, (int, np.integer)) else list(indices)
+
+    def get_attr(self, attr_name, indices=None):
+        """dummy_vec_env.py:102-110: one value per selected env.  Per-env tensors ([N, ...]) are indexed, scenario
+        constants (shared by the lock-step batch) are repeated."""
+        idx = self._get_indices(indices)
+        v = getattr(self, attr_name)
+        if isinstance(v, torch.Tensor) and v.dim() >= 1 and v.shape[0] == self.num_envs:
+            return [v[i] for i in idx]
+        return [v for _ in idx]
+
+    def set_attr(self, attr_name, values, indices=None):
+        """dummy_vec_env.py:112-123.  The batch shares its scenario constants, so one value (or equal values) for ALL
+        envs is the only assignment that has a meaning; anything else raises."""
+        idx = self._get_indices(indices)
+        vals = list(values) if isinstance(values, (list, tuple)) else [values] * len(idx)
+        if len(vals) != len(idx):
+            raise ValueError("set_attr: one value per selected env is required")
+        if len(idx) != self.num_envs or any(not np.array_equal(np.asarray(v), np.asarray(vals[0])) for v in vals[1:]):
+            raise ValueError("set_attr: the envs of a batch share their attributes; set one value for all of them")
+        setattr(self, attr_name, vals[0])
+
+    def env_method(self, method_name, *method_args, indices=None, **method_kwargs):
+        """dummy_vec_env.py:125-143: the method runs once on the batch; its result is repeated per selected env."""
+        idx = self._get_indices(indices)
+        out = getattr(self, method_name)(*method_args, **method_kwargs)
+        return [out for _ in idx]
+
+    def get_env_random_state(self):
+        """dummy_vec_env.py:88-92.  The env's randomness is counter-based: (seed, first global env id) plus the per-env
+        episode counters determine every future draw."""
+        return [{"seed": int(self._cfg.seed), "env_id_base": int(self._cfg.env_id_base), "episode": self.buf_episode.clone()}]
+
+    def set_env_random_state(self, worker_random_states):
+        """dummy_vec_env.py:94-100."""
+        st = worker_random_states[0]
+        if int(st["seed"]) != int(self._cfg.seed) or int(st["env_id_base"]) != int(self._cfg.env_id_base):
+            raise ValueError("set_env_random_state: the state belongs to an env with another seed / env id range")
+        self.buf_episode.copy_(st["episode"])
+
     def state_dict(self):
         """Checkpoint of the batch: a handful of tensors."""
         names = ["state", "ctrl_step", "episode", "flags", "dist_offset", "inertia", "ep_return", "ep_length",

@@ -55,3 +55,54 @@ def test_logged_rollout_exports_the_stepped_trajectory(tmp_path):
     z = np.load(tl.save())
     assert z["states"].shape == (3, 16, k) and np.all(z["states"][:, 12:16] > 0)   # rpm rows
     a.close(); b.close()
+
+
+def test_runtime_error_conventions():
+    """benchmark_env.py:272-275 (step before reset), :252-254 (cost parameters after the first reset), :256-266
+    (adversary control without an adversary), quadrotor.py:464-465 (negative randomised inertia)."""
+    env = _make(8)
+    with pytest.raises(RuntimeError, match="reset"):
+        env.step(torch.zeros(8, 4, device="cuda:0"))
+    with pytest.raises(RuntimeError, match="reset"):
+        env.rollout(torch.zeros(2, 8, 4, device="cuda:0"))
+    env.set_cost_function_param(np.eye(12), np.eye(4))
+    env.reset()
+    with pytest.raises(RuntimeError, match="after the first reset"):
+        env.set_cost_function_param(np.eye(12), np.eye(4))
+    with pytest.raises(RuntimeError, match="adversary_disturbance does not exist"):
+        env.set_adversary_control(np.zeros(4))
+    env.close()
+    with pytest.raises(ValueError, match="negative randomized inertial"):
+        _make(8, randomized_inertial_prop=True,
+              inertial_prop_randomization_info={"M": dict(distrib="uniform", low=-1.0, high=0.0)})
+
+
+def test_vec_env_attribute_access_and_random_state():
+    """vec_env.py:130-163, dummy_vec_env.py:88-143 on the batch: get_attr / set_attr / env_method, and the random state
+    (seed, env-id range, episode counters) restores the exact continuation."""
+    n = 64
+    env = _make(n, seed=5)
+    assert env.get_attr("CTRL_FREQ") == [60] * n and env.get_attr("CTRL_FREQ", indices=[3, 9]) == [60, 60]
+    assert len(env.get_attr("MASS", indices=7)) == 1
+    env.set_attr("my_tag", "a")
+    assert env.get_attr("my_tag", 0) == ["a"]
+    with pytest.raises(ValueError):
+        env.set_attr("my_tag", ["a", "b"], indices=[0, 1])
+    seeds = env.env_method("seed", 5, indices=[0, 1])
+    assert seeds == [[5], [5]]
+    env.reset()
+    acts = bench.make_actions(torch, n, 60, torch.device("cuda:0"), 9, 0.02)
+    env.rollout(acts[:30])
+    rnd, sd = env.get_env_random_state(), env.state_dict()
+    env.rollout(acts[30:])
+    want = env.state.clone()
+    assert int(env.stats()["episodes"]) > 0                 # resets happened, so the draws matter
+    env.load_state_dict(sd)
+    env.set_env_random_state(rnd)
+    env.rollout(acts[30:])
+    assert torch.equal(env.state, want)
+    other = _make(n, seed=6)
+    with pytest.raises(ValueError):
+        other.set_env_random_state(rnd)
+    other.close()
+    env.close()
