@@ -286,7 +286,8 @@ template <typename real> static int upload_params(scg_env* e) {
     if (!k) return fail(SCG_ERR_BAD_CONFIG, "out of host memory");
     Hot<real>& h = *reinterpret_cast<Hot<real>*>(sizeof(real) == 4 ? (void*)&e->hf : (void*)&e->hd);
     int rc = build_params<real>(e->cfg, e->nx, e->nu, h, *k, &e->n_rows, &e->n_slots, &e->lean);
-    e->plain = e->lean && !(h.cfg & (CFG_DISTURBED | CFG_COLD_CONSTRAINTS | CFG_QR_DENSE | CFG_PENALTY | CFG_GATE_GEOMETRY | CFG_RESET_EXTRAS));
+    e->plain = e->lean && !(h.cfg & (CFG_DISTURBED | CFG_COLD_CONSTRAINTS | CFG_QR_DENSE | CFG_PENALTY | CFG_GATE_GEOMETRY | CFG_RESET_EXTRAS)) &&
+               !h.normalized_action;
     if (rc != SCG_OK) { delete k; return rc; }
     const int rows = e->cfg.n_goal_rows > 0 ? e->cfg.n_goal_rows : 1;
     real* goal_host = new real[size_t(rows) * e->nx];

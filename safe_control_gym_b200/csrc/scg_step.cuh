@@ -12,6 +12,8 @@
 // inertia, diagonal Q/R, plain observation: what scg_create() finds in e.g. level0.yaml) compiles
 // those features out, GENERAL keeps them behind uniform branches.
 #pragma once
+#include <type_traits>
+
 #include "scg_env.cuh"
 #include "scg_pid.cuh"
 
@@ -485,6 +487,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
     for (int j = 0; j < NU; ++j) {
         const real c = m_clip(raw[j], h.act_low[j], h.act_high[j]);
         if constexpr (KIND == SCG_CARTPOLE) pre[j] = h.normalized_action ? c * h.hover_thrust : c;   // force = action_scale * a
+        else if constexpr (PLAIN) pre[j] = c;   // a normalised action space takes the LEAN kernel
         else pre[j] = h.normalized_action ? (real(1) + h.norm_act_scale * c) * h.hover_thrust : c;
         thr[j] = pre[j];
     }
@@ -505,9 +508,13 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
     const real dt = h.dt;
     if constexpr (KIND == SCG_QUAD_3D) {
         const real axf = fx * e.in.inv_mass, ayf = fy * e.in.inv_mass, azf = fz * e.in.inv_mass - e.in.g_over_m;
-#pragma unroll 1
-        for (int s = 0; s < h.substeps; ++s) {
-            const real ax = e.a3.R[2] * Tm + axf, ay = e.a3.R[5] * Tm + ayf, az = e.a3.R[8] * Tm + azf;
+        // One substep.  LAST = false (all but the final substep of a control step, LEAN kernels): the pre-round-trip
+        // angles are not copied into e.x[6..8] -- only the final ones are ever read (derive_attitude, the next launch).
+        auto substep = [&](auto last_tag) {
+            constexpr bool LAST = decltype(last_tag)::value;
+            real ax, ay, az;
+            if constexpr (PLAIN) { ax = e.a3.R[2] * Tm; ay = e.a3.R[5] * Tm; az = e.a3.R[8] * Tm - e.in.g_over_m; }
+            else { ax = e.a3.R[2] * Tm + axf; ay = e.a3.R[5] * Tm + ayf; az = e.a3.R[8] * Tm + azf; }
             const real w0 = e.x[9], w1 = e.x[10], w2 = e.x[11];
             const real jw0 = e.in.J[0] * w0, jw1 = e.in.J[1] * w1, jw2 = e.in.J[2] * w2;
             const real d0 = e.in.J_inv[0] * (mot.tx - (w1 * jw2 - w2 * jw1));
@@ -517,8 +524,16 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             e.x[9] += dt * d0; e.x[10] += dt * d1; e.x[11] += dt * d2;         // then rates
             e.x[0] += dt * e.x[1]; e.x[2] += dt * e.x[3]; e.x[4] += dt * e.x[5];   // pos uses NEW vel
             const real pre3[3] = {e.a3.rpy[0] + dt * e.x[9], e.a3.rpy[1] + dt * e.x[10], e.a3.rpy[2] + dt * e.x[11]};
-            e.x[6] = pre3[0]; e.x[7] = pre3[1]; e.x[8] = pre3[2];
+            if constexpr (LAST) { e.x[6] = pre3[0]; e.x[7] = pre3[1]; e.x[8] = pre3[2]; }
             attitude3<real, ATT>(pre3, e.a3);
+        };
+        if constexpr (LEAN) {
+#pragma unroll 1
+            for (int s = 1; s < h.substeps; ++s) substep(std::false_type{});
+            substep(std::true_type{});
+        } else {
+#pragma unroll 1
+            for (int s = 0; s < h.substeps; ++s) substep(std::true_type{});
         }
     } else if constexpr (KIND == SCG_QUAD_2D) {
         const real axf = fx * e.in.inv_mass, azf = fz * e.in.inv_mass - e.in.g_over_m;
@@ -921,7 +936,8 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
             const bool restart = done && (cfg & CFG_AUTO_RESET) != 0u;
             // one inline copy of the draw: at the cadence every lane that used its spare refills it together;
             // a lane that ends two episodes inside one period draws on the spot
-            if (!spare_ok && (restart || (ahead && (k & 15) == 0))) {
+            const bool cadence = ahead && (k & 15) == 0;   // uniform
+            if (bool(int(!spare_ok) & (int(restart) | int(cadence)))) {
                 const uint32_t next_ep = (cfg & CFG_RESEED) ? 0u : uint32_t(e.resets);
                 if (!PLAIN && (cfg & CFG_RESET_EXTRAS)) draw_spare_general<KIND, real, ATT>(h, cold, key, next_ep, sp);
                 else {
