@@ -239,7 +239,8 @@ def run_gpu(args):
         if world > 1:
             dist.destroy_process_group()
         return
-    # ---- roofline of the dominant kernel (k_rollout<3, float, ATT, LEAN>): one launch per step
+    # ---- roofline of the dominant kernel (k_rollout<3, float, ATT, ...>): one launch per step
+    variant = {0: "GENERAL", 1: "LEAN", 2: "LEAN,PLAIN", 3: "LEAN,PLAIN,SPEC"}[int(env.lib.scg_kernel_variant(env._h))]
     peak = C.c_double()
     L.check(L.load().scg_measure_fp32_peak(C.byref(peak)))
     kernel_ms = sum(per) / len(per)   # one launch per step; stats all-reduce excluded at N = 1
@@ -267,7 +268,7 @@ def run_gpu(args):
                    "substeps": SUBSTEPS, "env_substeps_per_sec": value * SUBSTEPS, "mode": "fused rollout, auto-reset, Philox init", "attitude": args.attitude, "action_std": args.action_std,
                    "l2_policy": "inputs larger than L2 (1.05 GB action table re-streamed each step)"},
         "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": peak.value, "unit": "TFLOP/s", "frac": achieved_tf / peak.value,
-                     "traffic": traffic, "kernel": "scg::k_rollout<3,float,%s,LEAN,PLAIN>" % args.attitude, "kernel_ms": kernel_ms,
+                     "traffic": traffic, "kernel": "scg::k_rollout<3,float,%s,%s>" % (args.attitude, variant), "kernel_ms": kernel_ms,
                      "flops_per_env_step": FLOPS_PER_STEP,
                      "peak_source": "measured live: register-only FFMA kernel (scg_measure_fp32_peak); MEASURED_PEAKS.json has no non-tensor fp32 figure",
                      "hbm": {"bound": "hbm", "achieved": hbm_bytes / (kernel_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",

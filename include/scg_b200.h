@@ -298,7 +298,10 @@ int64_t scg_launch_count(const scg_env* env);
  * (initial state, inertial properties, disturbance offsets) drawn ahead of time at a warp-convergent cadence;
  * 2 = LEAN + PLAIN (fp32): in addition reset() draws nothing but uniform initial-state offsets and no per-step extra
  * is configured (disturbances, adversary, external force, dense / tolerance / symmetric constraints, off-diagonal Q
- * or R, constraint penalty, gate geometry), so all of that is compiled out; 0 = GENERAL: SCG_ATT_ROUNDTRIP only
+ * or R, constraint penalty, gate geometry), so all of that is compiled out; 3 = PLAIN + SPEC: a Quadrotor 3D config of
+ * the competition family (stabilisation task, cost "competition", done on violation and completion, position box +
+ * input bounds, positions-only mse, auto-reset) whose fused launches without per-step outputs run with those switches
+ * as compile-time constants (scg_step and launches with per-step outputs take variant 2); 0 = GENERAL: SCG_ATT_ROUNDTRIP only
  * (validation: literal quaternion round trip, reset one lane at a time).  Same results in every variant. */
 int scg_kernel_variant(const scg_env* env);
 const char* scg_last_error(void);

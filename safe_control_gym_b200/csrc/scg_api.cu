@@ -252,6 +252,8 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
     h.box_thr = (nb > 0 && h.bounded[0].strict) ? std::nextafter(real(-0.5), -INF) : real(0.5);
     if (h.n_rows > 0) h.cfg |= CFG_HAS_ROWS;
     if (h.ubox_mask) h.cfg |= CFG_UBOX;
+    if (c.env_kind == SCG_QUAD_3D && !(h.mse_mask & ~0x15u)) h.cfg |= CFG_MSE_POS;
+    if (c.env_kind == SCG_QUAD_3D && !(h.box_mask & ~0x15u)) h.cfg |= CFG_BOX_POS;
     if (h.need_cold_constraints || !same_strict) h.cfg |= CFG_COLD_CONSTRAINTS;
     if (c.n_dist[1] > 0 || c.n_dist[2] > 0 || c.adversary_channel == SCG_CH_ACTION || c.adversary_channel == SCG_CH_DYNAMICS)
         h.cfg |= CFG_DISTURBED;
@@ -278,7 +280,8 @@ extern "C" int scg_kernel_variant(const scg_env* env) {
     if (!env || !env->lean) return 0;
     const bool quad_att = env->cfg.env_kind == SCG_QUAD_3D || env->cfg.env_kind == SCG_QUAD_2D;
     if (quad_att && env->cfg.attitude_mode == SCG_ATT_ROUNDTRIP) return 0;   // validation mode: GENERAL kernel (scg_inst.cuh)
-    return env->plain && env->cfg.precision == 32 ? 2 : 1;
+    if (!(env->plain && env->cfg.precision == 32)) return 1;
+    return env->cfg.env_kind == SCG_QUAD_3D && (env->hf.cfg & CFG_SPEC_MASK) == CFG_SPEC_VAL ? 3 : 2;
 }
 
 template <typename real> static int upload_params(scg_env* e) {

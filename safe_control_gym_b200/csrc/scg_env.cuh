@@ -376,12 +376,18 @@ SCG_DEV void eval_constraints(const Hot<real>& h, const Cold<real>* __restrict__
     // one three-way max each; p, q, r only where something reads them)
     constexpr int NB = KIND == SCG_QUAD_3D ? 9 : NX;
     real w0 = -INFINITY, w1 = -INFINITY;   // two chains
+    if (KIND == SCG_QUAD_3D && (cfg & CFG_BOX_POS)) {   // nothing but x, y, z is bounded (the other dims would contribute -inf)
+        w0 = m_max3(w0, h.box_lo[0] - st[0], st[0] - h.box_hi[0]);
+        w1 = m_max3(w1, h.box_lo[2] - st[2], st[2] - h.box_hi[2]);
+        w0 = m_max3(w0, h.box_lo[4] - st[4], st[4] - h.box_hi[4]);
+    } else {
 #pragma unroll
-    for (int d = 0; d < NB; ++d) {
-        real& w = (d & 1) ? w1 : w0;
-        w = m_max3(w, h.box_lo[d] - st[d], st[d] - h.box_hi[d]);
+        for (int d = 0; d < NB; ++d) {
+            real& w = (d & 1) ? w1 : w0;
+            w = m_max3(w, h.box_lo[d] - st[d], st[d] - h.box_hi[d]);
+        }
     }
-    if (NB < NX && (cfg & CFG_FULL_STATE)) {
+    if (NB < NX && !(KIND == SCG_QUAD_3D && (cfg & CFG_BOX_POS)) && (cfg & CFG_FULL_STATE)) {
 #pragma unroll
         for (int d = NB; d < NX; ++d) w0 = m_max3(w0, h.box_lo[d] - st[d], st[d] - h.box_hi[d]);
     }

@@ -29,7 +29,12 @@ int launch_reset(scg_env* e, const ResetInject<real>& inj, const uint8_t* mask, 
 template <int KIND, typename real, int ATT>
 static void launch_rollout_att(scg_env* e, const Hot<real>& h, const Cold<real>* cold, const Buf<real>& b, const Roll<real>& ro,
                                unsigned blocks, cudaStream_t st) {
-    if (e->lean && e->plain && !ro.use_pid && sizeof(real) == 4) k_rollout<KIND, real, ATT, true, sizeof(real) == 4><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro);
+    constexpr bool F32 = sizeof(real) == 4;
+    if (e->lean && e->plain && !ro.use_pid && F32) {
+        if (KIND == SCG_QUAD_3D && !ro.step_outputs && (h.cfg & CFG_SPEC_MASK) == CFG_SPEC_VAL)
+            k_rollout<KIND, real, ATT, true, F32, (F32 && KIND == SCG_QUAD_3D)><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro);
+        else k_rollout<KIND, real, ATT, true, F32><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro);
+    }
     else if (e->lean) k_rollout<KIND, real, ATT, true, false><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro);
     else k_rollout<KIND, real, ATT, false, false><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro);
 }

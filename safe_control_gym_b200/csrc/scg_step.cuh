@@ -633,8 +633,13 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
         // a zero weight contributes exactly 0: every dim is evaluated, branch-free (p, q, r only where they are weighed)
         mse = real(0);
         constexpr int NM = KIND == SCG_QUAD_3D ? 9 : NX;
+        if (KIND == SCG_QUAD_3D && (cfg & CFG_MSE_POS)) {   // same sum: the skipped terms are exact zeros
 #pragma unroll
-        for (int d = 0; d < NM; ++d) { const real er = (st[d] - goal_at(d)) * h.mse_weight[d]; mse += er * er; }
+            for (int d = 0; d < 6; d += 2) { const real er = (st[d] - goal_at(d)) * h.mse_weight[d]; mse += er * er; }
+        } else {
+#pragma unroll
+            for (int d = 0; d < NM; ++d) { const real er = (st[d] - goal_at(d)) * h.mse_weight[d]; mse += er * er; }
+        }
         if (NM < NX && (cfg & CFG_MSE_RATES)) {
 #pragma unroll
             for (int d = NM; d < NX; ++d) { const real er = (st[d] - goal_at(d)) * h.mse_weight[d]; mse += er * er; }
@@ -796,7 +801,8 @@ k_reset(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold
 // PLAIN (LEAN only): none of the per-step extras is configured -- disturbances, adversary, external force, dense /
 // tolerance / symmetric constraints, off-diagonal Q / R, constraint penalty, gate geometry -- and their uniform
 // branches are compiled out (the headline workload: the loop must stay inside the instruction cache).
-template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN = false>
+// SPEC (PLAIN only): the scenario switches of CFG_SPEC_MASK are compile-time constants (scg_params.cuh).
+template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN = false, bool SPEC = false>
 __global__ void __launch_bounds__(ENV_BLOCK, sizeof(real) == 4 ? 8 : 1)
 k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, const Buf<real> b, const Roll<real> ro) {
     constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
@@ -833,9 +839,10 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     uint32_t info = 0u;
     Motors<real> mot;
     // the uniform switches of the loop in one word (see CFG_*)
-    const uint32_t cfg = h.cfg | (ro.step_outputs ? (CFG_FULL_STATE | CFG_STEP_OUTPUTS) : 0u);
+    const uint32_t cfg_rt = h.cfg | (ro.step_outputs ? (CFG_FULL_STATE | CFG_STEP_OUTPUTS) : 0u);
+    const uint32_t cfg = SPEC ? ((cfg_rt & ~CFG_SPEC_MASK) | CFG_SPEC_VAL) : cfg_rt;
     const bool full = (cfg & CFG_FULL_STATE) != 0u;
-    real* const c_out = ro.step_outputs ? b.c_values : nullptr;
+    real* const c_out = SPEC ? nullptr : (ro.step_outputs ? b.c_values : nullptr);
     // software prefetch of the next action (one 16-byte load per 3D env per step)
     real raw[NU], nxt[NU];
     const bool closed_loop = !PLAIN && ro.use_pid != 0;   // uniform: actions from the on-device PID (scg_pid.cuh)

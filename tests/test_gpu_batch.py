@@ -150,13 +150,14 @@ def test_config2_size_is_deterministic():
 
 
 def test_kernel_variant_selection():
-    """scg_kernel_variant: 2 = LEAN + PLAIN for the headline workload, 1 = LEAN as soon as a per-step extra or a
+    """scg_kernel_variant: 3 = PLAIN + SPEC for the headline workload (competition switches compiled in), 2 = PLAIN for
+    other extra-free fp32 configs, 1 = LEAN as soon as a per-step extra or a
     reset-time draw beyond uniform init offsets is configured (the spare reset carries those too), 0 = GENERAL for the
     literal round-trip attitude (validation)."""
     from safe_control_gym_b200.envs.cartpole import BatchedCartPole
     lib_variant = lambda env: int(env.lib.scg_kernel_variant(env._h))
     imp = lambda off: {"action": [dict(disturbance_func="impulse", magnitude=0.01, step_offset=off, duration=2, decay_rate=0.9)]}
-    cases = [(_quad(64), 2), (_quad(64, gate_geometry=True), 1),
+    cases = [(_quad(64), 3), (_quad(64, done_on_completion=False), 2), (_quad(64, cost="rl_reward"), 2), (_quad(64, gate_geometry=True), 1),
              (_quad(64, disturbances={"action": [dict(disturbance_func="white_noise", std=0.01)]}), 1),
              (_quad(64, disturbances=imp(None)), 1), (_quad(64, disturbances=imp(3)), 1),
              (_quad(64, randomized_inertial_prop=True), 1), (_quad(64, attitude="roundtrip"), 0),
