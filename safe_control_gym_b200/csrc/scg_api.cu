@@ -43,6 +43,7 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
     h.kf = real(c.kf); h.km = real(c.km); h.arm_s2 = real(c.arm / std::sqrt(2.0));
     h.inv_mass = real(1.0 / c.mass); h.gravity_force = real(c.gravity_force);
     for (int j = 0; j < 3; ++j) { h.J[j] = real(c.J[j]); h.J_inv[j] = real(c.J_inv[j]); }
+    for (int j = 0; j < 3; ++j) { h.dJ[j] = h.J[(j + 2) % 3] - h.J[(j + 1) % 3]; h.kJ[j] = h.dt * h.J_inv[j]; }
     h.pwm_scale = real(c.pwm2rpm_scale); h.pwm_const = real(c.pwm2rpm_const);
     h.pwm_min = real(c.pwm_min); h.pwm_max = real(c.pwm_max); h.inv_pwm_scale = real(1.0 / c.pwm2rpm_scale);
     if (c.env_kind != SCG_CARTPOLE) {

@@ -226,7 +226,7 @@ template <typename real, bool FASTMATH> SCG_DEV real motor_rpm(const Hot<real>& 
 }
 
 // per-episode inertial constants (nominal in parity mode, F9)
-template <typename real> struct Inertia { real inv_mass, g_over_m, J[3], J_inv[3]; real cp_l, cp_mp, cp_mc; };
+template <typename real> struct Inertia { real inv_mass, g_over_m, J[3], J_inv[3]; real dJ[3], kJ[3]; real cp_l, cp_mp, cp_mc; };
 
 // ------------------------------------------------------------------ cart-pole ODE (row A13)
 // Frictionless cart-pole (Barto et al.), x = [x, x_dot, theta, theta_dot], theta = 0 upright,

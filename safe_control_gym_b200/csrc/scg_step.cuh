@@ -65,11 +65,13 @@ template <int KIND, typename real> SCG_DEV void load_inertia(const Hot<real>& h,
         in.g_over_m = h.gravity_force * h.inv_mass;   // g * m_env / m_env == GRAVITY_ACC
 #pragma unroll
         for (int j = 0; j < 3; ++j) { in.J[j] = inertia[int64_t(j + 1) * n + i]; in.J_inv[j] = real(1) / in.J[j]; }
+#pragma unroll
+        for (int j = 0; j < 3; ++j) { in.dJ[j] = in.J[(j + 2) % 3] - in.J[(j + 1) % 3]; in.kJ[j] = h.dt * in.J_inv[j]; }
     } else {
         in.inv_mass = h.inv_mass;
         in.g_over_m = h.gravity_force * h.inv_mass;
 #pragma unroll
-        for (int j = 0; j < 3; ++j) { in.J[j] = h.J[j]; in.J_inv[j] = h.J_inv[j]; }
+        for (int j = 0; j < 3; ++j) { in.J[j] = h.J[j]; in.J_inv[j] = h.J_inv[j]; in.dJ[j] = h.dJ[j]; in.kJ[j] = h.kJ[j]; }
     }
 }
 
@@ -508,20 +510,35 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
     const real dt = h.dt;
     if constexpr (KIND == SCG_QUAD_3D) {
         const real axf = fx * e.in.inv_mass, ayf = fy * e.in.inv_mass, azf = fz * e.in.inv_mass - e.in.g_over_m;
+        const real Tdt = Tm * dt, gdt = e.in.g_over_m * dt;
+        (void)Tdt; (void)gdt;
         // One substep.  LAST = false (all but the final substep of a control step, LEAN kernels): the pre-round-trip
         // angles are not copied into e.x[6..8] -- only the final ones are ever read (derive_attitude, the next launch).
         auto substep = [&](auto last_tag) {
             constexpr bool LAST = decltype(last_tag)::value;
-            real ax, ay, az;
-            if constexpr (PLAIN) { ax = e.a3.R[2] * Tm; ay = e.a3.R[5] * Tm; az = e.a3.R[8] * Tm - e.in.g_over_m; }
-            else { ax = e.a3.R[2] * Tm + axf; ay = e.a3.R[5] * Tm + ayf; az = e.a3.R[8] * Tm + azf; }
             const real w0 = e.x[9], w1 = e.x[10], w2 = e.x[11];
-            const real jw0 = e.in.J[0] * w0, jw1 = e.in.J[1] * w1, jw2 = e.in.J[2] * w2;
-            const real d0 = e.in.J_inv[0] * (mot.tx - (w1 * jw2 - w2 * jw1));
-            const real d1 = e.in.J_inv[1] * (mot.ty - (w2 * jw0 - w0 * jw2));
-            const real d2 = e.in.J_inv[2] * (mot.tz - (w0 * jw1 - w1 * jw0));
-            e.x[1] += dt * ax; e.x[3] += dt * ay; e.x[5] += dt * az;          // vel first
-            e.x[9] += dt * d0; e.x[10] += dt * d1; e.x[11] += dt * d2;         // then rates
+            if constexpr (FASTMATH) {
+                // same update with the constants folded (fp32 fast modes; a few ulp from the literal order below):
+                // w x Jw = (w1 w2 (Izz - Iyy), w2 w0 (Ixx - Izz), w0 w1 (Iyy - Ixx)) for a diagonal J; dt / J and dt T / m premultiplied
+                if constexpr (PLAIN) {
+                    e.x[1] = m_fma(e.a3.R[2], Tdt, e.x[1]); e.x[3] = m_fma(e.a3.R[5], Tdt, e.x[3]);
+                    e.x[5] = m_fma(e.a3.R[8], Tdt, e.x[5] - gdt);
+                } else {
+                    e.x[1] = m_fma(e.a3.R[2], Tdt, e.x[1] + axf * dt); e.x[3] = m_fma(e.a3.R[5], Tdt, e.x[3] + ayf * dt);
+                    e.x[5] = m_fma(e.a3.R[8], Tdt, e.x[5] + azf * dt);
+                }
+                e.x[9] = m_fma(m_fma(-(w1 * w2), e.in.dJ[0], mot.tx), e.in.kJ[0], e.x[9]);
+                e.x[10] = m_fma(m_fma(-(w2 * w0), e.in.dJ[1], mot.ty), e.in.kJ[1], e.x[10]);
+                e.x[11] = m_fma(m_fma(-(w0 * w1), e.in.dJ[2], mot.tz), e.in.kJ[2], e.x[11]);
+            } else {
+                const real ax = e.a3.R[2] * Tm + axf, ay = e.a3.R[5] * Tm + ayf, az = e.a3.R[8] * Tm + azf;
+                const real jw0 = e.in.J[0] * w0, jw1 = e.in.J[1] * w1, jw2 = e.in.J[2] * w2;
+                const real d0 = e.in.J_inv[0] * (mot.tx - (w1 * jw2 - w2 * jw1));
+                const real d1 = e.in.J_inv[1] * (mot.ty - (w2 * jw0 - w0 * jw2));
+                const real d2 = e.in.J_inv[2] * (mot.tz - (w0 * jw1 - w1 * jw0));
+                e.x[1] += dt * ax; e.x[3] += dt * ay; e.x[5] += dt * az;          // vel first
+                e.x[9] += dt * d0; e.x[10] += dt * d1; e.x[11] += dt * d2;         // then rates
+            }
             e.x[0] += dt * e.x[1]; e.x[2] += dt * e.x[3]; e.x[4] += dt * e.x[5];   // pos uses NEW vel
             const real pre3[3] = {e.a3.rpy[0] + dt * e.x[9], e.a3.rpy[1] + dt * e.x[10], e.a3.rpy[2] + dt * e.x[11]};
             if constexpr (LAST) { e.x[6] = pre3[0]; e.x[7] = pre3[1]; e.x[8] = pre3[2]; }
