@@ -255,6 +255,11 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
     if (h.ubox_mask) h.cfg |= CFG_UBOX;
     if (c.env_kind == SCG_QUAD_3D && !(h.mse_mask & ~0x15u)) h.cfg |= CFG_MSE_POS;
     if (c.env_kind == SCG_QUAD_3D && !(h.box_mask & ~0x15u)) h.cfg |= CFG_BOX_POS;
+    if (c.env_kind == SCG_QUAD_3D && !c.normalized_action) {
+        bool inside = true;
+        for (int j = 0; j < nu; ++j) inside = inside && h.act_low[j] >= h.f_min && h.act_high[j] <= h.f_max;
+        if (inside) h.cfg |= CFG_CLIP_ONCE;
+    }
     if (h.need_cold_constraints || !same_strict) h.cfg |= CFG_COLD_CONSTRAINTS;
     if (c.n_dist[1] > 0 || c.n_dist[2] > 0 || c.adversary_channel == SCG_CH_ACTION || c.adversary_channel == SCG_CH_DYNAMICS)
         h.cfg |= CFG_DISTURBED;

@@ -30,6 +30,13 @@ SCG_DEV float wrap_pi(float x) {
     const float k = fast_rint(x * 0.15915494309189535f);
     return fmaf(-k, -1.7484555e-07f, fmaf(-k, 6.2831855f, x));   // 2 pi = 6.2831855f - 1.7484555e-07f
 }
+// wrap for SCG_ATT_FAST_INTRINSIC: one-constant reduction (an actual wrap is off by k * 1.7e-7 rad, below the MUFU error;
+// still the identity inside [-pi, pi])
+template <int ATT> SCG_DEV float att_wrap(float x) {
+    if (ATT == SCG_ATT_FAST_INTRINSIC) return fmaf(-fast_rint(x * 0.15915494309189535f), 6.2831855f, x);
+    return wrap_pi(x);
+}
+template <int ATT> SCG_DEV double att_wrap(double x) { return wrap_pi(x); }
 template <int ATT> SCG_DEV void att_sincos(float x, float* s, float* c) {
     if (ATT == SCG_ATT_FAST_INTRINSIC) __sincosf(x, s, c);   // MUFU.SIN/COS, |err| <= 2^-21.4 on [-pi, pi]
     else sincos_pi(x, s, c);                                  // |x| <= pi after wrap_pi
@@ -94,14 +101,14 @@ __device__ __noinline__ void attitude3_roundtrip(real p0, real p1, real p2, Att3
 template <typename real, int ATT>
 SCG_DEV void attitude3(const real (&pre)[3], Att3<real>& a) {
     if (ATT != SCG_ATT_ROUNDTRIP) {
-        const real thw = wrap_pi(pre[1]);
+        const real thw = att_wrap<ATT>(pre[1]);
         real th = thw, ph = pre[0], ps = pre[2];
         const bool folded = m_abs(th) > Consts<real>::half_pi;
         if (folded) {
             th = (th > real(0) ? Consts<real>::pi : -Consts<real>::pi) - th;
             ph += Consts<real>::pi; ps += Consts<real>::pi;
         }
-        ph = wrap_pi(ph); ps = wrap_pi(ps);
+        ph = att_wrap<ATT>(ph); ps = att_wrap<ATT>(ps);
         real sth, cth;
         att_sincos<ATT>(th, &sth, &cth);
         const bool band = !(m_abs(sth) < real(sizeof(real) == 4 ? 0.99999 : 0.99998));
@@ -178,7 +185,7 @@ template <typename real> struct Motors {
 // quadrotor.py:815-842, quadrotor_utils.py:21-67, base_aviary.py:538-551.
 // thrust[] is the (possibly disturbed) commanded thrust per input.
 template <int KIND, typename real, bool FASTMATH>
-SCG_DEV void motors_from_thrust(const Hot<real>& h, const real (&thrust)[Dims<KIND>::NU], Motors<real>& m) {
+SCG_DEV void motors_from_thrust(const Hot<real>& h, const real (&thrust)[Dims<KIND>::NU], Motors<real>& m, bool clip = true) {
     constexpr int NU = Dims<KIND>::NU;
     if constexpr (FASTMATH) {
         // thrust -> PWM -> clip -> RPM -> KF rpm^2 is the identity on the rotor force apart from the clip, which maps
@@ -186,7 +193,10 @@ SCG_DEV void motors_from_thrust(const Hot<real>& h, const real (&thrust)[Dims<KI
         // rounding of the chain it skips; the RPMs are formed only where they are logged (motor_rpm).
         real fi[NU];
 #pragma unroll
-        for (int j = 0; j < NU; ++j) fi[j] = m_clip((NU == 4 ? thrust[j] : thrust[j] * h.inv_n_motor), h.f_min, h.f_max);
+        for (int j = 0; j < NU; ++j) {
+            const real t = NU == 4 ? thrust[j] : thrust[j] * h.inv_n_motor;
+            fi[j] = clip ? m_clip(t, h.f_min, h.f_max) : t;   // clip == false: the caller's action clip already implies it (CFG_CLIP_ONCE)
+        }
         real f[4];
         if (KIND == SCG_QUAD_1D) { f[0] = f[1] = f[2] = f[3] = fi[0]; }
         else if (KIND == SCG_QUAD_2D) { f[0] = fi[0]; f[1] = fi[NU - 1]; f[2] = fi[NU - 1]; f[3] = fi[0]; }

@@ -97,6 +97,7 @@ enum : uint32_t {
     CFG_PENALTY = 1u << 18,         // rl_reward with use_constraint_penalty
     CFG_MSE_POS = 1u << 20,         // 3D: info["mse"] weighs nothing but the positions x, y, z (the default)
     CFG_BOX_POS = 1u << 21,         // 3D: the merged state box bounds nothing but x, y, z
+    CFG_CLIP_ONCE = 1u << 22,       // 3D: the action bounds lie inside the rotor force bounds, the motor map needs no second clip
     CFG_RESET_EXTRAS = 1u << 19,    // reset() draws more than uniform init offsets: inertial properties, disturbance offsets, normal draws
 };
 // SPEC kernels (scg_step.cuh): the switches of the competition scenario family (competition/level0-3.yaml: stabilisation
@@ -105,9 +106,9 @@ enum : uint32_t {
 // its runtime word agrees with CFG_SPEC_VAL on every bit of CFG_SPEC_MASK.
 constexpr uint32_t CFG_SPEC_MASK = CFG_STAB | CFG_COST_RL | CFG_COST_QUAD | CFG_OOB | CFG_DONE_COMPLETION | CFG_DONE_VIOLATION |
                                    CFG_HAS_ROWS | CFG_AUTO_RESET | CFG_FULL_STATE | CFG_RESEED | CFG_UBOX | CFG_MSE_RATES |
-                                   CFG_STEP_OUTPUTS | CFG_MSE_POS | CFG_BOX_POS;
+                                   CFG_STEP_OUTPUTS | CFG_MSE_POS | CFG_BOX_POS | CFG_CLIP_ONCE;
 constexpr uint32_t CFG_SPEC_VAL = CFG_STAB | CFG_DONE_COMPLETION | CFG_DONE_VIOLATION | CFG_HAS_ROWS | CFG_AUTO_RESET | CFG_UBOX |
-                                  CFG_MSE_POS | CFG_BOX_POS;
+                                  CFG_MSE_POS | CFG_BOX_POS | CFG_CLIP_ONCE;
 
 
 template <typename real> struct DenseRow {     // linear: c = a . x - b ; quadratic: c = x' P x - b

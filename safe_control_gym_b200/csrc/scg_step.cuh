@@ -503,7 +503,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
         for (int j = 0; j < NU; ++j) thr[j] = tl[j];
         fx = fl[0]; fy = fl[1]; fz = fl[2];
     }
-    if constexpr (KIND != SCG_CARTPOLE) motors_from_thrust<KIND, real, FASTMATH>(h, thr, mot);
+    if constexpr (KIND != SCG_CARTPOLE) motors_from_thrust<KIND, real, FASTMATH>(h, thr, mot, !(PLAIN && (cfg & CFG_CLIP_ONCE)));
     else { mot.T = mot.tx = mot.ty = mot.tz = real(0); mot.rpm[0] = mot.rpm[1] = mot.rpm[2] = mot.rpm[3] = real(0); }
     // ---- _advance_simulation: S explicit substeps (base_aviary.py:266-322, 522-576)
     const real Tm = mot.T * e.in.inv_mass;
@@ -863,7 +863,8 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     // software prefetch of the next action (one 16-byte load per 3D env per step)
     real raw[NU], nxt[NU];
     const bool closed_loop = !PLAIN && ro.use_pid != 0;   // uniform: actions from the on-device PID (scg_pid.cuh)
-    if (!closed_loop) load_action<NU, real>(ro.actions + ii * NU, nxt);
+    const real* ap = ro.actions + ii * NU;   // action row of this env at the step being prefetched
+    if (!closed_loop) load_action<NU, real>(ap, nxt);
     else {
 #pragma unroll
         for (int j = 0; j < NU; ++j) nxt[j] = real(0);
@@ -905,7 +906,8 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
                 }
             }
         }
-        if (!closed_loop && k + 1 < ro.k_steps) load_action<NU, real>(ro.actions + (int64_t(k + 1) * n + ii) * NU, nxt);
+        ap += n * NU;
+        if (!closed_loop && k + 1 < ro.k_steps) load_action<NU, real>(ap, nxt);
         // LEAN: env.state of this step is loop-local (it aliases the registers of e); what is observed
         // after the loop is rebuilt from e there
         real sl[LEAN ? NX : 1];
