@@ -154,7 +154,7 @@ def run_reference(args):
                              "sample": f"{sample_envs} envs x {sample_steps} ctrl steps, C/OpenMP oracle (oracle/scg_oracle.c), fp64"},
             "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "wall_s": time.perf_counter() - t0}
-    print(json.dumps(line))
+    emit(line)
 
 
 def run_gpu(args):
@@ -281,9 +281,21 @@ def run_gpu(args):
         "gpu_launches": launches, "clocks": clk.summary(),
         "episode_stats": {kk: stats[kk] for kk in ("episodes", "return", "length", "violation_steps", "env_steps")},
     }
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
+
+
+_REAL_STDOUT = None
+
+
+def emit(line):
+    text = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(text.decode()); sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_REAL_STDOUT, text)
 
 
 def main():
@@ -298,6 +310,12 @@ def main():
     ap.add_argument("--attitude", default="fast_intrinsic", help="fast_intrinsic (MUFU sin/cos) | fast (polynomial sin/cos) | roundtrip (literal)")
     ap.add_argument("--action-std", type=float, default=0.005)
     args = ap.parse_args()
+    # stdout carries exactly one JSON line: anything a library prints there (NCCL's version banner under torchrun) goes
+    # to stderr instead -- fd 1 is pointed at fd 2 for the run and the line is written to the saved descriptor
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
