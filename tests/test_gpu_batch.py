@@ -190,3 +190,42 @@ def test_spare_reset_with_inertia_and_offsets_equals_stepping():
         assert torch.equal(getattr(a, "buf_" + name), getattr(b, "buf_" + name)), name
     assert int(a.buf_episode.max()) >= 3   # 60-step episodes: every env restarted at least twice
     a.close(); b.close()
+
+
+def test_ragged_batch_and_masked_reset():
+    """Edge cases of the batch layout: a batch that does not fill its last block (100 envs in blocks of 64: the idle
+    lanes shadow the last env and stay out of the statistics) equals the first 100 envs of a 128-env batch, and
+    reset(mask) restarts exactly the masked envs (DummyVecEnv-style partial reset) leaving the others untouched."""
+    k = 40
+    small, big = _quad(100, attitude="fast_intrinsic"), _quad(128, attitude="fast_intrinsic")
+    small.reset(); big.reset()
+    acts = _actions(128, k, std=0.02)
+    small.rollout(acts[:, :100].contiguous()); big.rollout(acts)
+    assert torch.equal(small.state, big.state[:100])
+    assert torch.equal(small.buf_ctrl_step, big.buf_ctrl_step[:100]) and torch.equal(small.buf_episode, big.buf_episode[:100])
+    st = small.stats()
+    assert st["env_steps"] == 100 * k and st["episodes"] > 0
+    # one env, one step: the smallest launch
+    one = _quad(1, attitude="fast_intrinsic")
+    one.reset()
+    one.step(acts[0, :1])
+    assert torch.equal(one.state[0], _first_step_state(acts))
+    # masked reset
+    before_state, before_t, before_ep = big.state.clone(), big.buf_ctrl_step.clone(), big.buf_episode.clone()
+    mask = (torch.arange(128, device="cuda:0") % 3 == 0)
+    big.reset(mask=mask.to(torch.uint8))
+    keep = ~mask
+    assert torch.equal(big.state[keep], before_state[keep]) and torch.equal(big.buf_ctrl_step[keep], before_t[keep])
+    assert int(big.buf_ctrl_step[mask].abs().sum()) == 0 and torch.equal(big.buf_episode[mask], before_ep[mask] + 1)
+    assert torch.equal(big.buf_episode[keep], before_ep[keep])
+    for e in (small, big, one):
+        e.close()
+
+
+def _first_step_state(acts):
+    ref = _quad(64, attitude="fast_intrinsic")
+    ref.reset()
+    ref.step(acts[0, :64].contiguous())
+    s = ref.state[0].clone()
+    ref.close()
+    return s
