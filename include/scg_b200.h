@@ -304,6 +304,16 @@ int64_t scg_launch_count(const scg_env* env);
  * as compile-time constants (scg_step and launches with per-step outputs take variant 2); 0 = GENERAL: SCG_ATT_ROUNDTRIP only
  * (validation: literal quaternion round trip, reset one lane at a time).  Same results in every variant. */
 int scg_kernel_variant(const scg_env* env);
+/* Scheduling of the fused rollout launches (scg_rollout / scg_rollout_host / scg_rollout_pid; no reference counterpart:
+ * the reference steps one env at a time).  mode -1 (default) = automatic: launches of >= 64 control steps whose env
+ * blocks fill the resident block slots of the GPU unevenly (between half a wave and six waves) are cut into chunks of
+ * control steps that the resident blocks take from a ticket counter, so every SM sub-partition stays equally loaded;
+ * 0 = always one block per 64 envs for the whole launch; 1 = always through the queue.  chunk_steps 0 = default (64).
+ * The environment variables SCG_QUEUE / SCG_QUEUE_CHUNK give the initial values.  Results do not depend on it (a K-step
+ * rollout equals any split of it into launches); the episode statistics agree up to the order of their float sums. */
+int scg_set_rollout_queue(scg_env* env, int32_t mode, int32_t chunk_steps);
+/* 1 when the last fused rollout launch went through the ticket queue, else 0 */
+int scg_last_rollout_queue(const scg_env* env);
 const char* scg_last_error(void);
 const char* scg_version(void);
 

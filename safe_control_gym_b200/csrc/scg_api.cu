@@ -3,6 +3,7 @@
 // kernels of scg_step.cuh / scg_symbolic.cuh on the caller's stream.
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <new>
@@ -279,6 +280,13 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
     return SCG_OK;
 }
 
+extern "C" int scg_set_rollout_queue(scg_env* env, int32_t mode, int32_t chunk_steps) {
+    if (!env) return scg_fail(SCG_ERR_NULL, "scg_set_rollout_queue: null env");
+    if (mode < -1 || mode > 1 || chunk_steps < 0) return scg_fail(SCG_ERR_BAD_CONFIG, "scg_set_rollout_queue: mode in {-1, 0, 1}, chunk_steps >= 0");
+    env->queue_mode = mode; env->queue_chunk = chunk_steps;
+    return SCG_OK;
+}
+extern "C" int scg_last_rollout_queue(const scg_env* env) { return env ? env->last_queue : 0; }
 extern "C" const char* scg_last_error(void) { return g_err.c_str(); }
 extern "C" const char* scg_version(void) { return "scg_b200 0.1 (sm_100a)"; }
 extern "C" int64_t scg_launch_count(const scg_env* env) { return env ? env->launches : 0; }
@@ -338,6 +346,8 @@ extern "C" int scg_create(const scg_config* cfg, scg_env** out) {
     int rc = cfg->precision == 32 ? upload_params<float>(e) : upload_params<double>(e);
     if (rc != SCG_OK) { scg_destroy(e); return rc; }
     e->cfg.x_goal = nullptr;   // host table was copied; do not keep the caller's pointer
+    if (const char* q = getenv("SCG_QUEUE")) { const int m = atoi(q); e->queue_mode = m < 0 ? -1 : (m > 0 ? 1 : 0); }
+    if (const char* q = getenv("SCG_QUEUE_CHUNK")) { const int c = atoi(q); e->queue_chunk = c > 0 ? c : 0; }
     *out = e;
     return SCG_OK;
 }
@@ -345,6 +355,7 @@ extern "C" int scg_create(const scg_config* cfg, scg_env** out) {
 extern "C" int scg_destroy(scg_env* e) {
     if (!e) return SCG_OK;
     if (e->cold_dev) cudaFree(e->cold_dev);
+    if (e->q_mem) cudaFree(e->q_mem);
     if (e->x_goal_dev) cudaFree(e->x_goal_dev);
     for (int j = 0; j < 2; ++j) {
         if (e->stage[j]) cudaFree(e->stage[j]);

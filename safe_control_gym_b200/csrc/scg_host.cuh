@@ -24,6 +24,13 @@ struct scg_env {
     cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};
     void* stage[2] = {nullptr, nullptr};
     size_t stage_bytes = 0;
+    // time-chunk queue of the fused rollout (scg_step.cuh: k_rollout<..., QUEUE>)
+    int32_t* q_mem = nullptr;      // [1 + env blocks]: ticket counter, chunks finished per env block
+    int64_t q_cap = 0;
+    int n_sms = 0;
+    int queue_mode = -1;           // -1 auto, 0 off, 1 on (SCG_QUEUE)
+    int queue_chunk = 0;           // 0 auto (SCG_QUEUE_CHUNK)
+    int last_queue = 0;            // the last rollout launch went through the queue (scg_last_rollout_queue)
 };
 
 int scg_fail(int code, const std::string& msg);

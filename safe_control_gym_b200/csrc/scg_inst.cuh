@@ -26,17 +26,66 @@ int launch_reset(scg_env* e, const ResetInject<real>& inj, const uint8_t* mask, 
     return SCG_OK;
 }
 
+// The queue pays when the launch is long and the env blocks fill the resident slots unevenly (at most a few waves):
+// a static grid of 1,024 blocks leaves schedulers with three and with four warps, a grid of 1,300 runs two waves.
+template <typename K>
+static bool launch_queued(scg_env* e, K kernel, const int64_t n, int k_steps, int32_t* q_chunk, int32_t* q_env_blocks, int32_t* q_tickets,
+                          unsigned* grid) {
+    if (e->queue_mode == 0 || k_steps < 64) return false;
+    if (e->n_sms == 0) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&e->n_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return false;
+    }
+    int occ = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, ENV_BLOCK, 0) != cudaSuccess || occ < 1) return false;
+    const int64_t resident = int64_t(occ) * e->n_sms, env_blocks = (n + ENV_BLOCK - 1) / ENV_BLOCK;
+    if (e->queue_mode < 0 && (env_blocks > 6 * resident || env_blocks * 2 < resident || env_blocks == resident)) return false;
+    int chunk = e->queue_chunk > 0 ? e->queue_chunk : 64;
+    if (chunk > k_steps) chunk = k_steps;
+    const int64_t chunks = (k_steps + chunk - 1) / chunk, tickets = chunks * env_blocks;
+    if (tickets > 0x7fffffff || env_blocks > 0x7fffffff) return false;
+    if (e->q_cap < 1 + env_blocks) {
+        if (e->q_mem) cudaFree(e->q_mem);
+        e->q_mem = nullptr; e->q_cap = 0;
+        if (cudaMalloc(&e->q_mem, sizeof(int32_t) * (1 + env_blocks)) != cudaSuccess) return false;
+        e->q_cap = 1 + env_blocks;
+    }
+    *q_chunk = chunk; *q_env_blocks = int32_t(env_blocks); *q_tickets = int32_t(tickets);
+    *grid = unsigned(tickets < resident ? tickets : resident);
+    return true;
+}
+
+template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN, bool SPEC>
+static void launch_rollout_v(scg_env* e, const Hot<real>& h, const Cold<real>* cold, const Buf<real>& b, const Roll<real>& ro,
+                             unsigned blocks, cudaStream_t st) {
+    if constexpr (LEAN && sizeof(real) == 4) {
+        Roll<real> rq = ro;
+        unsigned grid = 0;
+        if (!ro.step_outputs && launch_queued(e, k_rollout<KIND, real, ATT, LEAN, PLAIN, SPEC, true>, b.n, ro.k_steps, &rq.q_chunk,
+                                              &rq.q_env_blocks, &rq.q_tickets, &grid)) {
+            rq.q_mem = e->q_mem;
+            if (cudaMemsetAsync(e->q_mem, 0, sizeof(int32_t) * (1 + rq.q_env_blocks), st) == cudaSuccess) {
+                k_rollout<KIND, real, ATT, LEAN, PLAIN, SPEC, true><<<grid, ENV_BLOCK, 0, st>>>(h, cold, b, rq);
+                e->last_queue = 1;
+                return;
+            }
+        }
+    }
+    e->last_queue = 0;
+    k_rollout<KIND, real, ATT, LEAN, PLAIN, SPEC, false><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro);
+}
+
 template <int KIND, typename real, int ATT>
 static void launch_rollout_att(scg_env* e, const Hot<real>& h, const Cold<real>* cold, const Buf<real>& b, const Roll<real>& ro,
                                unsigned blocks, cudaStream_t st) {
     constexpr bool F32 = sizeof(real) == 4;
     if (e->lean && e->plain && !ro.use_pid && F32) {
         if (KIND == SCG_QUAD_3D && !ro.step_outputs && (h.cfg & CFG_SPEC_MASK) == CFG_SPEC_VAL)
-            k_rollout<KIND, real, ATT, true, F32, (F32 && KIND == SCG_QUAD_3D)><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro);
-        else k_rollout<KIND, real, ATT, true, F32><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro);
+            launch_rollout_v<KIND, real, ATT, true, F32, (F32 && KIND == SCG_QUAD_3D)>(e, h, cold, b, ro, blocks, st);
+        else launch_rollout_v<KIND, real, ATT, true, F32, false>(e, h, cold, b, ro, blocks, st);
     }
-    else if (e->lean) k_rollout<KIND, real, ATT, true, false><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro);
-    else k_rollout<KIND, real, ATT, false, false><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro);
+    else if (e->lean) launch_rollout_v<KIND, real, ATT, true, false, false>(e, h, cold, b, ro, blocks, st);
+    else launch_rollout_v<KIND, real, ATT, false, false, false>(e, h, cold, b, ro, blocks, st);
 }
 
 template <int KIND, typename real>
@@ -47,7 +96,7 @@ int launch_rollout(scg_env* e, const Roll<real>& ro, cudaStream_t st) {
     const Cold<real>* cold = static_cast<const Cold<real>*>(e->cold_dev);
     const int att = e->cfg.attitude_mode;
     if constexpr (KIND == SCG_QUAD_3D || KIND == SCG_QUAD_2D) {
-        if (att == SCG_ATT_ROUNDTRIP) k_rollout<KIND, real, SCG_ATT_ROUNDTRIP, false, false><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro);
+        if (att == SCG_ATT_ROUNDTRIP) { e->last_queue = 0; k_rollout<KIND, real, SCG_ATT_ROUNDTRIP, false, false><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro); }
         else if (att == SCG_ATT_FAST_INTRINSIC && sizeof(real) == 4 && KIND == SCG_QUAD_3D)
             launch_rollout_att<KIND, real, (sizeof(real) == 4 && KIND == SCG_QUAD_3D) ? SCG_ATT_FAST_INTRINSIC : SCG_ATT_FAST>(e, h, cold, b, ro, blocks, st);
         else launch_rollout_att<KIND, real, SCG_ATT_FAST>(e, h, cold, b, ro, blocks, st);

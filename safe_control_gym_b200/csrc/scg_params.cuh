@@ -162,6 +162,9 @@ template <typename real> struct Roll {
     real* pid_mem;                  // [9][n] controller memory
     real* actions_out;              // optional [K][n][nu]: the actions the PID commanded
     PidP<real> pid;
+    // time-chunk queue (k_rollout<..., QUEUE>): q_mem[0] = ticket counter, q_mem[1 + env block] = chunks finished;
+    // ticket t = chunk t / q_env_blocks of env block t % q_env_blocks, q_chunk control steps each
+    int32_t* q_mem; int32_t q_chunk; int32_t q_env_blocks; int32_t q_tickets;
 };
 
 template <typename real> struct ResetInject { const real* init; const real* inertia; const int32_t* offsets; };

@@ -819,12 +819,17 @@ k_reset(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold
 // tolerance / symmetric constraints, off-diagonal Q / R, constraint penalty, gate geometry -- and their uniform
 // branches are compiled out (the headline workload: the loop must stay inside the instruction cache).
 // SPEC (PLAIN only): the scenario switches of CFG_SPEC_MASK are compile-time constants (scg_params.cuh).
-template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN = false, bool SPEC = false>
-__global__ void __launch_bounds__(ENV_BLOCK, sizeof(real) == 4 ? 8 : 1)
-k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, const Buf<real> b, const Roll<real> ro) {
+//
+// rollout_range runs control steps [k0, k1) of env i: state from / to Buf, exactly what a launch of k1 - k0 steps does
+// (a K-step rollout equals any split of it into launches).  Statistics go to the caller's shared-memory columns
+// acc[j * ACC_LD], j < N_ACC, which the kernel reduces once at its end.
+constexpr int ACC_LD = ENV_BLOCK + 1;   // column ENV_BLOCK is the scratch column of out-of-range lanes
+constexpr int N_ACC = 11;   // episodes, return, length, truncated, completed, violated episodes, violation steps, mse, env steps, gates, collisions
+template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN, bool SPEC>
+SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ cold, const Buf<real>& b, const Roll<real>& ro,
+                           const int64_t i, const int k0, const int k1, float* const ep_acc, real* const sp) {
     constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
     const int64_t n = b.n;
-    const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
     const bool valid = i < n;
     // out-of-range lanes shadow the last env: they compute and store the same values as its owner
     // (benign duplicates) and only stay out of the statistics
@@ -842,14 +847,10 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     real ep_ret = b.ep_return ? b.ep_return[ii] : real(0);
     int32_t ep_len = b.ep_length ? b.ep_length[ii] : 0;
     int32_t ep_viol = b.ep_violations ? b.ep_violations[ii] : 0;
-    // per-thread statistics (reduced once at the end)
+    // per-thread statistics of this range (added to the shared-memory columns at its end)
     float s_viol = 0.f, s_mse = 0.f;
-    // the statistics that only change when an episode ends live in a per-thread column of shared memory: six values
-    // that would otherwise be held (or spilled) across every control step for an update on 2 % of them
-    __shared__ float ep_acc_buf[6 * ENV_BLOCK];
-    float* const ep_acc = ep_acc_buf + threadIdx.x;   // [episodes, return, length, truncated, completed, violated episodes]
-#pragma unroll
-    for (int j = 0; j < 6; ++j) ep_acc[j * ENV_BLOCK] = 0.f;
+    // the statistics that only change when an episode ends live in a per-thread column of shared memory (ep_acc[0..5]):
+    // six values that would otherwise be held (or spilled) across every control step for an update on 2 % of them
     float s_gates = 0.f, s_coll = 0.f;   // gate_geometry only
     real reward = real(0), mse = real(0);
     bool done = false;
@@ -863,7 +864,7 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     // software prefetch of the next action (one 16-byte load per 3D env per step)
     real raw[NU], nxt[NU];
     const bool closed_loop = !PLAIN && ro.use_pid != 0;   // uniform: actions from the on-device PID (scg_pid.cuh)
-    const real* ap = ro.actions + ii * NU;   // action row of this env at the step being prefetched
+    const real* ap = ro.actions + (int64_t(k0) * n + ii) * NU;   // action row of this env at the step being prefetched
     if (!closed_loop) load_action<NU, real>(ap, nxt);
     else {
 #pragma unroll
@@ -871,13 +872,11 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     }
     bool fresh = false;   // obs must come from a reset this step
     // LEAN: spare initial state for the next episode (drawn ahead, see draw_init_lean)
-    __shared__ real sp_buf[LEAN ? (Spare<KIND, real, ATT>::N + (PLAIN ? 0 : SPARE_EXTRA)) * ENV_BLOCK : 1];
-    real* const sp = sp_buf + threadIdx.x;
     bool spare_ok = false;
-    const bool ahead = ro.k_steps >= 16;   // uniform: host-driven single steps draw on demand only
+    const bool ahead = k1 - k0 >= 16;   // uniform: host-driven single steps draw on demand only
     const bool any_out = ro.reward_out != nullptr || ro.done_out != nullptr || ro.log_out != nullptr;   // uniform
 #pragma unroll 1
-    for (int k = 0; k < ro.k_steps; ++k) {
+    for (int k = k0; k < k1; ++k) {
 #pragma unroll
         for (int j = 0; j < NU; ++j) raw[j] = nxt[j];
         if constexpr (!PLAIN && (KIND == SCG_QUAD_3D || KIND == SCG_QUAD_2D)) {
@@ -907,7 +906,7 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
             }
         }
         ap += n * NU;
-        if (!closed_loop && k + 1 < ro.k_steps) load_action<NU, real>(ap, nxt);
+        if (!closed_loop && k + 1 < k1) load_action<NU, real>(ap, nxt);
         // LEAN: env.state of this step is loop-local (it aliases the registers of e); what is observed
         // after the loop is rebuilt from e there
         real sl[LEAN ? NX : 1];
@@ -930,10 +929,10 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
         }
         fresh = false;
         if (done) {
-            ep_acc[0 * ENV_BLOCK] += 1.f; ep_acc[1 * ENV_BLOCK] += float(ep_ret); ep_acc[2 * ENV_BLOCK] += float(ep_len);
-            if (info & SCG_INFO_TRUNCATED) ep_acc[3 * ENV_BLOCK] += 1.f;
-            if (info & SCG_INFO_COMPLETED) ep_acc[4 * ENV_BLOCK] += 1.f;
-            if (ep_viol > 0) ep_acc[5 * ENV_BLOCK] += 1.f;
+            ep_acc[0 * ACC_LD] += 1.f; ep_acc[1 * ACC_LD] += float(ep_ret); ep_acc[2 * ACC_LD] += float(ep_len);
+            if (info & SCG_INFO_TRUNCATED) ep_acc[3 * ACC_LD] += 1.f;
+            if (info & SCG_INFO_COMPLETED) ep_acc[4 * ACC_LD] += 1.f;
+            if (ep_viol > 0) ep_acc[5 * ACC_LD] += 1.f;
             if (cfg & CFG_AUTO_RESET) {   // DummyVecEnv.step_wait (dummy_vec_env.py:38-49)
                 if ((cfg & CFG_STEP_OUTPUTS) && b.terminal_obs) {
                     real tl[NX];
@@ -962,7 +961,7 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
             const bool restart = done && (cfg & CFG_AUTO_RESET) != 0u;
             // one inline copy of the draw: at the cadence every lane that used its spare refills it together;
             // a lane that ends two episodes inside one period draws on the spot
-            const bool cadence = ahead && (k & 15) == 0;   // uniform
+            const bool cadence = ahead && ((k - k0) & 15) == 0;   // uniform
             if (bool(int(!spare_ok) & (int(restart) | int(cadence)))) {
                 const uint32_t next_ep = (cfg & CFG_RESEED) ? 0u : uint32_t(e.resets);
                 if (!PLAIN && (cfg & CFG_RESET_EXTRAS)) draw_spare_general<KIND, real, ATT>(h, cold, key, next_ep, sp);
@@ -1023,17 +1022,70 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     if (b.ep_return) b.ep_return[ii] = ep_ret;
     if (b.ep_length) b.ep_length[ii] = ep_len;
     if (b.ep_violations) b.ep_violations[ii] = ep_viol;
+    // statistics of this range into the caller's columns (an out-of-range lane was handed the scratch column)
+    ep_acc[6 * ACC_LD] += s_viol; ep_acc[7 * ACC_LD] += s_mse; ep_acc[8 * ACC_LD] += float(k1 - k0);
+    if (!PLAIN) { ep_acc[9 * ACC_LD] += s_gates; ep_acc[10 * ACC_LD] += s_coll; }
+}
+
+SCG_DEV int32_t ld_acquire_gpu(const int32_t* p) {
+    int32_t v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+SCG_DEV void st_release_gpu(int32_t* p, int32_t v) { asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+
+// QUEUE = false: block b owns envs [64 b, 64 b + 64) for all K steps.
+// QUEUE = true (fused launches whose envs fit in a few waves): the K steps are cut into chunks of ro.q_chunk and the
+// resident blocks take (chunk, env block) tickets from a counter, chunk-major; chunk c of an env block waits for its
+// chunk c - 1 (release / acquire on q_mem[1 + env block]) and picks the state up from Buf.  With 65,536 envs the static
+// split leaves 272 of the 592 schedulers with four warps and 320 with three for the whole launch, and the four-warp ones
+// set the makespan; through the queue every scheduler hosts four warps, the ~14 % that wait for a ticket sleep, and a
+// scheduler that runs ahead simply takes more tickets (same result: the split into ranges is invisible, see rollout_range).
+template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN = false, bool SPEC = false, bool QUEUE = false>
+__global__ void __launch_bounds__(ENV_BLOCK, sizeof(real) == 4 ? 8 : 1)
+k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, const Buf<real> b, const Roll<real> ro) {
+    __shared__ float acc_buf[N_ACC * ACC_LD];
+    __shared__ real sp_buf[LEAN ? (Spare<KIND, real, ATT>::N + (PLAIN ? 0 : SPARE_EXTRA)) * ENV_BLOCK : 1];
+    real* const sp = sp_buf + threadIdx.x;
+#pragma unroll
+    for (int j = 0; j < N_ACC; ++j) acc_buf[j * ACC_LD + threadIdx.x] = 0.f;
+    if constexpr (!QUEUE) {
+        const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+        rollout_range<KIND, real, ATT, LEAN, PLAIN, SPEC>(h, cold, b, ro, i, 0, ro.k_steps, acc_buf + (i < b.n ? threadIdx.x : ENV_BLOCK), sp);
+    } else {
+        __shared__ int32_t s_ticket;
+        for (;;) {
+            __syncthreads();   // the previous range is complete (and everybody has read s_ticket)
+            if (threadIdx.x == 0) s_ticket = atomicAdd(ro.q_mem, 1);
+            __syncthreads();
+            const int32_t t = s_ticket;
+            if (t >= ro.q_tickets) break;
+            const int32_t chunk = t / ro.q_env_blocks, eb = t - chunk * ro.q_env_blocks;
+            int32_t* const progress = ro.q_mem + 1 + eb;
+            if (chunk > 0) {
+                if (threadIdx.x == 0) {
+                    while (ld_acquire_gpu(progress) < chunk) __nanosleep(64);
+                }
+                __syncthreads();
+            }
+            const int64_t i = int64_t(eb) * ENV_BLOCK + threadIdx.x;
+            const int k0 = chunk * ro.q_chunk, k1 = k0 + ro.q_chunk < ro.k_steps ? k0 + ro.q_chunk : ro.k_steps;
+            rollout_range<KIND, real, ATT, LEAN, PLAIN, SPEC>(h, cold, b, ro, i, k0, k1, acc_buf + (i < b.n ? threadIdx.x : ENV_BLOCK), sp);
+            __syncthreads();
+            if (threadIdx.x == 0) { __threadfence(); st_release_gpu(progress, chunk + 1); }
+        }
+    }
     if (b.stats) {   // warp-shuffle reduction, one atomic per warp per statistic
-        const float steps = valid ? float(ro.k_steps) : 0.f;
         constexpr int NS = PLAIN ? 9 : 11;
-        float v[11] = {ep_acc[0 * ENV_BLOCK], ep_acc[1 * ENV_BLOCK], ep_acc[2 * ENV_BLOCK], s_viol, s_mse, ep_acc[3 * ENV_BLOCK],
-                       ep_acc[4 * ENV_BLOCK], ep_acc[5 * ENV_BLOCK], steps, s_gates, s_coll};
+        const float* const a = acc_buf + threadIdx.x;
+        float v[11] = {a[0 * ACC_LD], a[1 * ACC_LD], a[2 * ACC_LD], a[6 * ACC_LD], a[7 * ACC_LD], a[3 * ACC_LD],
+                       a[4 * ACC_LD], a[5 * ACC_LD], a[8 * ACC_LD], a[9 * ACC_LD], a[10 * ACC_LD]};
         const int slot[11] = {SCG_STAT_EPISODES, SCG_STAT_RETURN, SCG_STAT_LENGTH, SCG_STAT_VIOLATION_STEPS,
                               SCG_STAT_MSE, SCG_STAT_TRUNCATED, SCG_STAT_COMPLETED, SCG_STAT_VIOLATED_EPISODES, SCG_STAT_ENV_STEPS,
                               SCG_STAT_GATES, SCG_STAT_COLLISIONS};
 #pragma unroll
         for (int j = 0; j < NS; ++j) {
-            const float r = warp_sum(valid ? v[j] : 0.f);
+            const float r = warp_sum(v[j]);
             if ((threadIdx.x & 31) == 0 && r != 0.f) atomicAdd(b.stats + slot[j], double(r));
         }
     }

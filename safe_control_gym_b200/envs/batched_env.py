@@ -149,6 +149,16 @@ class BatchedEnvBase:
         """True when the config selected the LEAN instantiation of the step kernel (scg_kernel_variant)."""
         return bool(self.lib.scg_kernel_variant(self._h))
 
+    def set_rollout_queue(self, mode=-1, chunk_steps=0):
+        """Scheduling of the fused rollout launches (scg_set_rollout_queue): -1 automatic, 0 one block per 64 envs for the
+        whole launch, 1 always through the time-chunk ticket queue; ``chunk_steps`` 0 = default.  Same results either way."""
+        L.check(self.lib.scg_set_rollout_queue(self._h, int(mode), int(chunk_steps)))
+
+    @property
+    def last_rollout_queued(self):
+        """True when the last fused rollout launch went through the ticket queue."""
+        return bool(self.lib.scg_last_rollout_queue(self._h))
+
     def set_injection(self, channel, k, tensor):
         """Feed pre-drawn noise for disturbance ``k`` of ``channel`` ([dim, N]); None = Philox."""
         ch = {"observation": L.CH_OBSERVATION, "action": L.CH_ACTION, "dynamics": L.CH_DYNAMICS}[channel]
