@@ -45,6 +45,7 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
     h.inv_mass = real(1.0 / c.mass); h.gravity_force = real(c.gravity_force);
     for (int j = 0; j < 3; ++j) { h.J[j] = real(c.J[j]); h.J_inv[j] = real(c.J_inv[j]); }
     for (int j = 0; j < 3; ++j) { h.dJ[j] = h.J[(j + 2) % 3] - h.J[(j + 1) % 3]; h.kJ[j] = h.dt * h.J_inv[j]; }
+    h.ndJ_xz[0] = -h.dJ[0]; h.ndJ_xz[1] = -h.dJ[2]; h.kJ_xz[0] = h.kJ[0]; h.kJ_xz[1] = h.kJ[2];
     h.pwm_scale = real(c.pwm2rpm_scale); h.pwm_const = real(c.pwm2rpm_const);
     h.pwm_min = real(c.pwm_min); h.pwm_max = real(c.pwm_max); h.inv_pwm_scale = real(1.0 / c.pwm2rpm_scale);
     if (c.env_kind != SCG_CARTPOLE) {

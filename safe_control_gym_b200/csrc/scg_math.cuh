@@ -91,6 +91,19 @@ SCG_DEV double atan2_fast(double y, double x) { return atan2(y, x); }
 // np.clip(x, lo, hi) == minimum(maximum(x, lo), hi)
 template <typename real> SCG_DEV real m_clip(real x, real lo, real hi) { return m_min(m_max(x, lo), hi); }
 
+// Packed fp32 pairs (sm_100a FFMA2 / FADD2 / FMUL2: two IEEE fp32 operations per lane in ONE issue slot; the fused
+// rollout is issue-bound, not pipe-bound).  Each half is the same round-to-nearest operation as the scalar instruction, so
+// pairing changes no result.  A pair lives in an aligned 64-bit register pair; ptxas folds pk2 of two equal values into
+// the broadcast operand form (R.F32 / UR.F32 / immediate) and reads halves in place.
+typedef unsigned long long f32x2;
+SCG_DEV f32x2 pk2(float lo, float hi) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+SCG_DEV f32x2 bc2(float v) { return pk2(v, v); }
+SCG_DEV float lo2(f32x2 v) { return __uint_as_float(unsigned(v)); }
+SCG_DEV float hi2(f32x2 v) { return __uint_as_float(unsigned(v >> 32)); }
+SCG_DEV f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+SCG_DEV f32x2 add2(f32x2 a, f32x2 b) { f32x2 d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+SCG_DEV f32x2 mul2(f32x2 a, f32x2 b) { f32x2 d; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+
 template <typename real> struct Consts;
 template <> struct Consts<float> {
     static constexpr float pi = 3.14159265358979323846f;

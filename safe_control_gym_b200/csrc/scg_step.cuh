@@ -544,7 +544,79 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             if constexpr (LAST) { e.x[6] = pre3[0]; e.x[7] = pre3[1]; e.x[8] = pre3[2]; }
             attitude3<real, ATT>(pre3, e.a3);
         };
-        if constexpr (LEAN) {
+        if constexpr (LEAN && PLAIN && FASTMATH) {
+            // The same substep on packed pairs (FFMA2 / FADD2, scg_math.cuh): every half is the scalar operation of
+            // `substep` above, bit for bit; the loop is issue-bound and a pair takes one issue slot instead of two.
+            // Pairing: (x, y) of position and velocity; (roll, yaw) of angles and rates, so that the two wraps that
+            // follow the pitch fold run as one; the z lane rides with the pitch lane: (z, pitch) and (vz, pitch rate).
+            f32x2 Pxy = pk2(e.x[0], e.x[2]), Vxy = pk2(e.x[1], e.x[3]), Wxz = pk2(e.x[9], e.x[11]), ZB = pk2(e.x[5], e.x[10]);
+            f32x2 ZA = pk2(e.x[4], e.a3.rpy[1]), Axz = pk2(e.a3.rpy[0], e.a3.rpy[2]), Rxy = pk2(e.a3.R[2], e.a3.R[5]);
+            float R8 = e.a3.R[8];
+            // PLAIN: nominal inertia, so the constant pairs come straight from the constant bank as 64-bit operands
+            const f32x2 ndJxz = *reinterpret_cast<const f32x2*>(h.ndJ_xz), kJxz = *reinterpret_cast<const f32x2*>(h.kJ_xz);
+            const f32x2 Txz = pk2(mot.tx, mot.tz);
+            const float ndJ1 = -h.dJ[1], kJ1 = h.kJ[1], ngm = -e.in.g_over_m;
+            float sph, cph, sth, cth, sps, cps;
+            auto substep2 = [&](auto last_tag) {
+                constexpr bool LAST = decltype(last_tag)::value;
+                const float w0 = lo2(Wxz), w2 = hi2(Wxz), w1 = hi2(ZB);
+                const float m0 = w1 * w2, m1 = w2 * w0, m2 = w0 * w1;
+                Vxy = fma2(Rxy, bc2(Tdt), Vxy);
+                const float vz0 = fmaf(ngm, dt, lo2(ZB));
+                const f32x2 in_xz = fma2(pk2(m0, m2), ndJxz, Txz);
+                const float in_y = fmaf(m1, ndJ1, mot.ty);
+                Wxz = fma2(in_xz, kJxz, Wxz);
+                ZB = pk2(fmaf(R8, Tdt, vz0), fmaf(in_y, kJ1, w1));   // scalar: the two products share no operand pair
+                Pxy = fma2(bc2(dt), Vxy, Pxy);
+                const f32x2 ZA2 = fma2(bc2(dt), ZB, ZA);      // (z, pre-round-trip pitch)
+                const f32x2 PRE = fma2(bc2(dt), Wxz, Axz);    // pre-round-trip (roll, yaw)
+                if constexpr (LAST) { e.x[6] = lo2(PRE); e.x[7] = hi2(ZA2); e.x[8] = hi2(PRE); }
+                // attitude3<float, ATT> on the pairs
+                const float thw = att_wrap<ATT>(hi2(ZA2));
+                const bool folded = fabsf(thw) > Consts<float>::half_pi;
+                float th = thw;
+                if (folded) th = copysignf(Consts<float>::pi, thw) - thw;
+                f32x2 PH = add2(PRE, bc2(folded ? Consts<float>::pi : 0.f));
+                {
+                    const f32x2 K = add2(fma2(PH, bc2(0.15915494309189535f), bc2(12582912.f)), bc2(-12582912.f));
+                    if (ATT == SCG_ATT_FAST_INTRINSIC) PH = fma2(K, bc2(-6.2831855f), PH);
+                    else PH = fma2(K, bc2(1.7484555e-07f), fma2(K, bc2(-6.2831855f), PH));
+                }
+                att_sincos<ATT>(th, &sth, &cth);
+                const bool band = !(fabsf(sth) < 0.99999f);
+                float r0 = lo2(PH), r1 = th, r2 = hi2(PH);
+                att_sincos<ATT>(r0, &sph, &cph);
+                att_sincos<ATT>(r2, &sps, &cps);
+                Rxy = pk2(cps * sth * cph + sps * sph, sps * sth * cph - cps * sph);
+                R8 = cth * cph;
+                if (band) {   // see attitude3
+                    const bool up = sth > 0.f;
+                    const float r = 0.5f * (thw - (up ? Consts<float>::half_pi : -Consts<float>::half_pi));
+                    const float sr = folded ? -sph : sph, cr = folded ? -cph : cph;
+                    const float u = up ? r * cr : -(r * cr);
+                    const float corr = 2.f * r * sr * (1.f - u + u * u);
+                    float yaw = (up ? hi2(PRE) - lo2(PRE) : hi2(PRE) + lo2(PRE)) + corr;
+                    const float k = fast_rint(yaw * 0.07957747154594767f);
+                    yaw = fmaf(-k, -3.4969110629390343e-07f, fmaf(-k, 12.566370964050293f, yaw));
+                    r0 = 0.f; r1 = up ? Consts<float>::half_pi : -Consts<float>::half_pi; r2 = yaw;
+                }
+                Axz = pk2(r0, r2);
+                ZA = pk2(lo2(ZA2), r1);
+            };
+            if (h.substeps == 4) {   // PYB_FREQ / CTRL_FREQ of every shipped config: straight-line code, no loop-carried copies
+                substep2(std::false_type{}); substep2(std::false_type{}); substep2(std::false_type{}); substep2(std::true_type{});
+            } else {
+#pragma unroll 1
+                for (int s = 1; s < h.substeps; ++s) substep2(std::false_type{});
+                substep2(std::true_type{});
+            }
+            e.x[0] = lo2(Pxy); e.x[2] = hi2(Pxy); e.x[1] = lo2(Vxy); e.x[3] = hi2(Vxy); e.x[4] = lo2(ZA); e.x[5] = lo2(ZB);
+            e.x[9] = lo2(Wxz); e.x[10] = hi2(ZB); e.x[11] = hi2(Wxz);
+            e.a3.rpy[0] = lo2(Axz); e.a3.rpy[1] = hi2(ZA); e.a3.rpy[2] = hi2(Axz);
+            e.a3.sc[0] = sph; e.a3.sc[1] = cph; e.a3.sc[2] = sth; e.a3.sc[3] = cth; e.a3.sc[4] = sps; e.a3.sc[5] = cps;
+            e.a3.R[2] = lo2(Rxy); e.a3.R[5] = hi2(Rxy); e.a3.R[8] = R8;
+            e.a3.form = 1;
+        } else if constexpr (LEAN) {
 #pragma unroll 1
             for (int s = 1; s < h.substeps; ++s) substep(std::false_type{});
             substep(std::true_type{});
@@ -824,10 +896,11 @@ k_reset(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold
 // (a K-step rollout equals any split of it into launches).  Statistics go to the caller's shared-memory columns
 // acc[j * ACC_LD], j < N_ACC, which the kernel reduces once at its end.
 constexpr int ACC_LD = ENV_BLOCK + 1;   // column ENV_BLOCK is the scratch column of out-of-range lanes
-constexpr int N_ACC = 11;   // episodes, return, length, truncated, completed, violated episodes, violation steps, mse, env steps, gates, collisions
+constexpr int N_ACC = 11;   // episodes, return, length, truncated, completed, violated episodes, violation steps, (mse: double column), env steps, gates, collisions
 template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN, bool SPEC>
 SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ cold, const Buf<real>& b, const Roll<real>& ro,
-                           const int64_t i, const int k0, const int k1, float* const ep_acc, real* const sp) {
+                           const int64_t i, const int k0, const int k1, float* const ep_acc, double* const mse_acc, real* const sp) {
+    ep_acc[1 * ACC_LD] = 0.f;   // return of the episodes that end in this range: summed in fp32 per range, in fp64 across ranges
     constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
     const int64_t n = b.n;
     const bool valid = i < n;
@@ -1023,7 +1096,10 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
     if (b.ep_length) b.ep_length[ii] = ep_len;
     if (b.ep_violations) b.ep_violations[ii] = ep_viol;
     // statistics of this range into the caller's columns (an out-of-range lane was handed the scratch column)
-    ep_acc[6 * ACC_LD] += s_viol; ep_acc[7 * ACC_LD] += s_mse; ep_acc[8 * ACC_LD] += float(k1 - k0);
+    // (the mse sum goes into a double column: a sum of fp32 terms in fp64 is exact, so the total does not depend on
+    // which resident thread ran which chunk; the other statistics are small integers, exact in fp32)
+    ep_acc[6 * ACC_LD] += s_viol; ep_acc[8 * ACC_LD] += float(k1 - k0);
+    mse_acc[0] += double(s_mse); mse_acc[ACC_LD] += double(ep_acc[1 * ACC_LD]);
     if (!PLAIN) { ep_acc[9 * ACC_LD] += s_gates; ep_acc[10 * ACC_LD] += s_coll; }
 }
 
@@ -1042,16 +1118,19 @@ SCG_DEV void st_release_gpu(int32_t* p, int32_t v) { asm volatile("st.release.gp
 // set the makespan; through the queue every scheduler hosts four warps, the ~14 % that wait for a ticket sleep, and a
 // scheduler that runs ahead simply takes more tickets (same result: the split into ranges is invisible, see rollout_range).
 template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN = false, bool SPEC = false, bool QUEUE = false>
-__global__ void __launch_bounds__(ENV_BLOCK, sizeof(real) == 4 ? 8 : 1)
+__global__ void __launch_bounds__(ENV_BLOCK, sizeof(real) == 4 ? 512 / ENV_BLOCK : 1)
 k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, const Buf<real> b, const Roll<real> ro) {
     __shared__ float acc_buf[N_ACC * ACC_LD];
+    __shared__ double mse_buf[2 * ACC_LD];   // fp64 columns: mse sum, return sum
+    mse_buf[threadIdx.x] = 0.0; mse_buf[ACC_LD + threadIdx.x] = 0.0;
     __shared__ real sp_buf[LEAN ? (Spare<KIND, real, ATT>::N + (PLAIN ? 0 : SPARE_EXTRA)) * ENV_BLOCK : 1];
     real* const sp = sp_buf + threadIdx.x;
 #pragma unroll
     for (int j = 0; j < N_ACC; ++j) acc_buf[j * ACC_LD + threadIdx.x] = 0.f;
     if constexpr (!QUEUE) {
         const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-        rollout_range<KIND, real, ATT, LEAN, PLAIN, SPEC>(h, cold, b, ro, i, 0, ro.k_steps, acc_buf + (i < b.n ? threadIdx.x : ENV_BLOCK), sp);
+        rollout_range<KIND, real, ATT, LEAN, PLAIN, SPEC>(h, cold, b, ro, i, 0, ro.k_steps, acc_buf + (i < b.n ? threadIdx.x : ENV_BLOCK),
+                                                          mse_buf + (i < b.n ? threadIdx.x : ENV_BLOCK), sp);
     } else {
         __shared__ int32_t s_ticket;
         for (;;) {
@@ -1070,7 +1149,8 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
             }
             const int64_t i = int64_t(eb) * ENV_BLOCK + threadIdx.x;
             const int k0 = chunk * ro.q_chunk, k1 = k0 + ro.q_chunk < ro.k_steps ? k0 + ro.q_chunk : ro.k_steps;
-            rollout_range<KIND, real, ATT, LEAN, PLAIN, SPEC>(h, cold, b, ro, i, k0, k1, acc_buf + (i < b.n ? threadIdx.x : ENV_BLOCK), sp);
+            rollout_range<KIND, real, ATT, LEAN, PLAIN, SPEC>(h, cold, b, ro, i, k0, k1, acc_buf + (i < b.n ? threadIdx.x : ENV_BLOCK),
+                                                              mse_buf + (i < b.n ? threadIdx.x : ENV_BLOCK), sp);
             __syncthreads();
             if (threadIdx.x == 0) { __threadfence(); st_release_gpu(progress, chunk + 1); }
         }
@@ -1085,9 +1165,15 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
                               SCG_STAT_GATES, SCG_STAT_COLLISIONS};
 #pragma unroll
         for (int j = 0; j < NS; ++j) {
+            if (slot[j] == SCG_STAT_MSE || slot[j] == SCG_STAT_RETURN) continue;
             const float r = warp_sum(v[j]);
             if ((threadIdx.x & 31) == 0 && r != 0.f) atomicAdd(b.stats + slot[j], double(r));
         }
+        double m = mse_buf[threadIdx.x], r = mse_buf[ACC_LD + threadIdx.x];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { m += __shfl_xor_sync(0xffffffffu, m, o); r += __shfl_xor_sync(0xffffffffu, r, o); }
+        if ((threadIdx.x & 31) == 0 && m != 0.0) atomicAdd(b.stats + SCG_STAT_MSE, m);
+        if ((threadIdx.x & 31) == 0 && r != 0.0) atomicAdd(b.stats + SCG_STAT_RETURN, r);
     }
 }
 

@@ -30,6 +30,37 @@ template <int MODE> __global__ void k(float* out, int iters, float s, unsigned m
     float r = 0; for (int i = 0; i < 8; ++i) r += a[i] + u[i]; for (int i = 0; i < 4; ++i) r += p[i].x + p[i].y;
     out[blockIdx.x * blockDim.x + threadIdx.x] = r;
 }
+template <int MODE> __global__ void mix(float* out, int iters, float s, unsigned m) {
+    float a[8]; unsigned u[4];
+    for (int i = 0; i < 8; ++i) a[i] = threadIdx.x * 0.001f + i;
+    for (int i = 0; i < 4; ++i) u[i] = threadIdx.x + i;
+    float2 p[4]; for (int i = 0; i < 4; ++i) p[i] = make_float2(a[2 * i], a[2 * i + 1]);
+    float2 s2 = make_float2(s, s), c2 = make_float2(0.5f, 0.5f);
+    for (int it = 0; it < iters; ++it) {
+        if (MODE == 0) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) a[i] = fmaf(a[i], s, 0.5f);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) p[i] = fma2(p[i], s2, c2);
+        }
+#pragma unroll
+        for (int i = 0; i < 2; ++i) u[i] = __funnelshift_l(u[i], u[i], 5) ^ (m + it);   // SHF + LOP3 per element
+    }
+    float r = 0; for (int i = 0; i < 8; ++i) r += a[i]; for (int i = 0; i < 4; ++i) r += p[i].x + p[i].y + u[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = r;
+}
+template <int MODE> void runmix(const char* name, int warps_per_smsp) {
+    float* d; cudaMalloc(&d, 148 * 8 * 256 * 4);
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    const int iters = 200000, threads = warps_per_smsp * 4 * 32;
+    mix<MODE><<<148, threads>>>(d, 1000, 0.999f, 0x5bd1e995u);
+    cudaEventRecord(e0); mix<MODE><<<148, threads>>>(d, iters, 0.999f, 0x5bd1e995u); cudaEventRecord(e1); cudaEventSynchronize(e1);
+    float ms; cudaEventElapsedTime(&ms, e0, e1);
+    printf("%-28s warps/SMSP %d: %.2f cycles per warp-iteration / warps (SMSP cycles per iteration of one warp)\n", name, warps_per_smsp,
+           ms * 1e-3 * 1.965e9 / iters / warps_per_smsp);
+    cudaFree(d);
+}
 template <int MODE> void run(const char* name) {
     float* d; cudaMalloc(&d, 148 * 8 * 256 * 4);
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
@@ -68,6 +99,7 @@ template <int MODE> void runlat(const char* name, int per) {
     cudaFree(d);
 }
 int main() {
+    for (int w = 1; w <= 4; ++w) { runmix<0>("8 FFMA + 4x(ALU)", w); runmix<1>("4 FFMA2 + 4x(ALU)", w); }
     runlat<0>("lat FFMA", 1); runlat<1>("lat FFMA2", 1); runlat<2>("lat FFMA+LOP3", 2); runlat<3>("lat FMUL", 1); runlat<4>("lat FMUL+MUFU.SIN", 1);
     run<0>("8 FFMA"); run<1>("4 FFMA2"); run<2>("8 FFMA + 16 ALU"); run<3>("4 FFMA2 + 16 ALU");
     return 0;
