@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libscg_b200.so")
+LIB_PATH = os.environ.get("SCG_LIB", os.path.join(HERE, "libscg_b200.so"))   # SCG_LIB: an alternative build of the same library (A/B measurements)
 
 MAX_NX, MAX_NU, MAX_CONSTRAINTS, MAX_CON_ROWS, MAX_ROWS = 12, 4, 8, 24, 64
 MAX_DIST, MAX_GATES, MAX_OBSTACLES, STATS_LEN = 4, 8, 8, 16

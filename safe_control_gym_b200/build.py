@@ -17,7 +17,7 @@ OBJ = os.path.join(HERE, "build")
 OUT = os.path.join(HERE, "libscg_b200.so")
 STAMP = OUT + ".stamp"
 NVCC_FLAGS = ["-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
-              "-Xcompiler", "-fPIC"]
+              "-Xcompiler", "-fPIC"] + os.environ.get("SCG_NVCC_EXTRA", "").split()   # e.g. -DSCG_NO_PAIRS=1 for an A/B build
 
 
 def _headers():

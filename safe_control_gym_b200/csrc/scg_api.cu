@@ -277,6 +277,11 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
             if ((s.kind == SCG_DIST_IMPULSE || s.kind == SCG_DIST_STEP) && s.step_offset < 0) reset_draws = true;
         }
     if (reset_draws) h.cfg |= CFG_RESET_EXTRAS;
+    for (int j = 0; j < 3; ++j) {
+        h.pos_pack[j] = h.box_lo[2 * j]; h.pos_pack[4 + j] = h.box_hi[2 * j];
+        h.pos_pack[8 + j] = h.x_goal0[2 * j]; h.pos_pack[12 + j] = h.mse_weight[2 * j];
+    }
+    h.pos_pack[3] = h.box_thr; h.pos_pack[7] = h.goal_tol * h.goal_tol; h.pos_pack[11] = h.goal_tol; h.pos_pack[15] = real(0);
     *lean_out = true;   // every config takes the spare reset; SCG_ATT_ROUNDTRIP (validation) is routed to the GENERAL kernel by the launcher
     return SCG_OK;
 }
@@ -348,6 +353,7 @@ extern "C" int scg_create(const scg_config* cfg, scg_env** out) {
     if (rc != SCG_OK) { scg_destroy(e); return rc; }
     e->cfg.x_goal = nullptr;   // host table was copied; do not keep the caller's pointer
     if (const char* q = getenv("SCG_QUEUE")) { const int m = atoi(q); e->queue_mode = m < 0 ? -1 : (m > 0 ? 1 : 0); }
+    if (const char* q = getenv("SCG_QUEUE_SLEEP")) { const int c = atoi(q); if (c >= 0) e->queue_sleep_ns = unsigned(c); }
     if (const char* q = getenv("SCG_QUEUE_CHUNK")) { const int c = atoi(q); e->queue_chunk = c > 0 ? c : 0; }
     *out = e;
     return SCG_OK;

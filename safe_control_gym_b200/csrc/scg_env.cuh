@@ -387,9 +387,10 @@ SCG_DEV void eval_constraints(const Hot<real>& h, const Cold<real>* __restrict__
     constexpr int NB = KIND == SCG_QUAD_3D ? 9 : NX;
     real w0 = -INFINITY, w1 = -INFINITY;   // two chains
     if (KIND == SCG_QUAD_3D && (cfg & CFG_BOX_POS)) {   // nothing but x, y, z is bounded (the other dims would contribute -inf)
-        w0 = m_max3(w0, h.box_lo[0] - st[0], st[0] - h.box_hi[0]);
-        w1 = m_max3(w1, h.box_lo[2] - st[2], st[2] - h.box_hi[2]);
-        w0 = m_max3(w0, h.box_lo[4] - st[4], st[4] - h.box_hi[4]);
+        const Row4<real> lo = ldc4(h.pos_pack), hi = ldc4(h.pos_pack + 4);   // box_lo / box_hi[0, 2, 4] (scg_params.cuh)
+        w0 = m_max3(w0, lo.x - st[0], st[0] - hi.x);
+        w1 = m_max3(w1, lo.y - st[2], st[2] - hi.y);
+        w0 = m_max3(w0, lo.z - st[4], st[4] - hi.z);
     } else {
 #pragma unroll
         for (int d = 0; d < NB; ++d) {

@@ -30,6 +30,7 @@ struct scg_env {
     int n_sms = 0;
     int queue_mode = -1;           // -1 auto, 0 off, 1 on (SCG_QUEUE)
     int queue_chunk = 0;           // 0 auto (SCG_QUEUE_CHUNK)
+    unsigned queue_sleep_ns = 500; // poll interval of a block that waits for its ticket's predecessor (SCG_QUEUE_SLEEP)
     int last_queue = 0;            // the last rollout launch went through the queue (scg_last_rollout_queue)
 };
 

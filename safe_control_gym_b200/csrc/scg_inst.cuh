@@ -63,7 +63,7 @@ static void launch_rollout_v(scg_env* e, const Hot<real>& h, const Cold<real>* c
         unsigned grid = 0;
         if (!ro.step_outputs && launch_queued(e, k_rollout<KIND, real, ATT, LEAN, PLAIN, SPEC, true>, b.n, ro.k_steps, &rq.q_chunk,
                                               &rq.q_env_blocks, &rq.q_tickets, &grid)) {
-            rq.q_mem = e->q_mem;
+            rq.q_mem = e->q_mem; rq.q_sleep_ns = e->queue_sleep_ns;
             if (cudaMemsetAsync(e->q_mem, 0, sizeof(int32_t) * (1 + rq.q_env_blocks), st) == cudaSuccess) {
                 k_rollout<KIND, real, ATT, LEAN, PLAIN, SPEC, true><<<grid, ENV_BLOCK, 0, st>>>(h, cold, b, rq);
                 e->last_queue = 1;

@@ -95,6 +95,10 @@ template <typename real> SCG_DEV real m_clip(real x, real lo, real hi) { return 
 // rollout is issue-bound, not pipe-bound).  Each half is the same round-to-nearest operation as the scalar instruction, so
 // pairing changes no result.  A pair lives in an aligned 64-bit register pair; ptxas folds pk2 of two equal values into
 // the broadcast operand form (R.F32 / UR.F32 / immediate) and reads halves in place.
+// one 16-byte row of kernel-parameter constants as ONE load (LDCU.128 into uniform registers)
+template <typename real> struct Row4 { real x, y, z, w; };
+SCG_DEV Row4<float> ldc4(const float* p) { const float4 v = *reinterpret_cast<const float4*>(p); return {v.x, v.y, v.z, v.w}; }
+SCG_DEV Row4<double> ldc4(const double* p) { return {p[0], p[1], p[2], p[3]}; }
 typedef unsigned long long f32x2;
 SCG_DEV f32x2 pk2(float lo, float hi) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
 SCG_DEV f32x2 bc2(float v) { return pk2(v, v); }

@@ -65,6 +65,9 @@ template <typename real> struct Hot {
     real box_lo[SCG_MAX_NX], box_hi[SCG_MAX_NX], ubox_lo[SCG_MAX_NU], ubox_hi[SCG_MAX_NU];
     uint32_t box_mask, ubox_mask;   // dims that carry a bound
     real box_thr;                   // violated <=> max_k(c_k) * 1e8 > box_thr (0.5, or just below -0.5 when strict)
+    // the per-step position constants of a 3D env in four 16-byte rows (one LDCU.128 each instead of a dozen scalar loads):
+    // [box_lo x y z, box_thr] [box_hi x y z, goal_tol^2] [x_goal0 x y z, goal_tol] [mse_weight x y z, 0]
+    alignas(16) real pos_pack[16];
     // feature switches (uniform branches)
     int32_t n_dist_obs, n_dist_act, n_dist_dyn, adversary_channel;
     int32_t n_gates, gate_geometry, dyn_uses_episode_inertia, dyn_applies_force, auto_reset;
@@ -166,7 +169,7 @@ template <typename real> struct Roll {
     PidP<real> pid;
     // time-chunk queue (k_rollout<..., QUEUE>): q_mem[0] = ticket counter, q_mem[1 + env block] = chunks finished;
     // ticket t = chunk t / q_env_blocks of env block t % q_env_blocks, q_chunk control steps each
-    int32_t* q_mem; int32_t q_chunk; int32_t q_env_blocks; int32_t q_tickets;
+    int32_t* q_mem; int32_t q_chunk; int32_t q_env_blocks; int32_t q_tickets; uint32_t q_sleep_ns;
 };
 
 template <typename real> struct ResetInject { const real* init; const real* inertia; const int32_t* offsets; };

@@ -544,7 +544,10 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             if constexpr (LAST) { e.x[6] = pre3[0]; e.x[7] = pre3[1]; e.x[8] = pre3[2]; }
             attitude3<real, ATT>(pre3, e.a3);
         };
-        if constexpr (LEAN && PLAIN && FASTMATH) {
+#ifndef SCG_NO_PAIRS
+#define SCG_NO_PAIRS 0
+#endif
+        if constexpr (LEAN && PLAIN && FASTMATH && !SCG_NO_PAIRS) {
             // The same substep on packed pairs (FFMA2 / FADD2, scg_math.cuh): every half is the scalar operation of
             // `substep` above, bit for bit; the loop is issue-bound and a pair takes one issue slot instead of two.
             // Pairing: (x, y) of position and velocity; (roll, yaw) of angles and rates, so that the two wraps that
@@ -617,9 +620,13 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             e.a3.R[2] = lo2(Rxy); e.a3.R[5] = hi2(Rxy); e.a3.R[8] = R8;
             e.a3.form = 1;
         } else if constexpr (LEAN) {
+            if (FASTMATH && h.substeps == 4) {   // straight-line code for the usual PYB_FREQ / CTRL_FREQ
+                substep(std::false_type{}); substep(std::false_type{}); substep(std::false_type{}); substep(std::true_type{});
+            } else {
 #pragma unroll 1
-            for (int s = 1; s < h.substeps; ++s) substep(std::false_type{});
-            substep(std::true_type{});
+                for (int s = 1; s < h.substeps; ++s) substep(std::false_type{});
+                substep(std::true_type{});
+            }
         } else {
 #pragma unroll 1
             for (int s = 0; s < h.substeps; ++s) substep(std::true_type{});
@@ -684,10 +691,11 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
     e.at_goal = false;
     if constexpr (KIND == SCG_QUAD_3D) {
         if (e.gate == uint32_t(h.n_gates) && (cfg & CFG_STAB)) {   // quadrotor.py:1117-1130
-            const real dx = st[0] - h.x_goal0[0], dy = st[2] - h.x_goal0[2], dz = st[4] - h.x_goal0[4];
+            const Row4<real> g = ldc4(h.pos_pack + 8);   // x_goal0[0, 2, 4]
+            const real dx = st[0] - g.x, dy = st[2] - g.y, dz = st[4] - g.z;
             // sqrt(d2) < tol  <=>  d2 < tol^2 up to one rounding of the square; the literal modes keep the sqrt
             const real d2 = dx * dx + dy * dy + dz * dz;
-            const bool inside = FASTMATH ? (d2 < h.goal_tol * h.goal_tol) : (m_sqrt(d2) < h.goal_tol);
+            const bool inside = FASTMATH ? (d2 < h.pos_pack[7]) : (m_sqrt(d2) < h.goal_tol);
             e.at_goal = inside;
             e.hold = inside ? (e.hold < 0xFFFFu ? e.hold + 1u : e.hold) : 0u;
             if (e.hold > uint32_t(2 * h.ctrl_freq)) e.completed = true;
@@ -718,13 +726,16 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
     // ---- info["mse"] (quadrotor.py:1016-1021) and _get_reward (quadrotor.py:886-954); t is still the
     // pre-increment counter.  Written once against a goal accessor so that a stabilisation goal stays
     // a constant-bank operand and only trajectory tracking loads a row into registers.
-    auto costs = [&](auto goal_at, auto goal_q_at) {
+    auto costs = [&](auto goal_at, auto goal_q_at, auto goal_pos_at) {
         // a zero weight contributes exactly 0: every dim is evaluated, branch-free (p, q, r only where they are weighed)
         mse = real(0);
         constexpr int NM = KIND == SCG_QUAD_3D ? 9 : NX;
         if (KIND == SCG_QUAD_3D && (cfg & CFG_MSE_POS)) {   // same sum: the skipped terms are exact zeros
 #pragma unroll
-            for (int d = 0; d < 6; d += 2) { const real er = (st[d] - goal_at(d)) * h.mse_weight[d]; mse += er * er; }
+            const Row4<real> wt = ldc4(h.pos_pack + 12);   // mse_weight[0, 2, 4]
+            { const real er = (st[0] - goal_pos_at(0)) * wt.x; mse += er * er; }
+            { const real er = (st[2] - goal_pos_at(2)) * wt.y; mse += er * er; }
+            { const real er = (st[4] - goal_pos_at(4)) * wt.z; mse += er * er; }
         } else {
 #pragma unroll
             for (int d = 0; d < NM; ++d) { const real er = (st[d] - goal_at(d)) * h.mse_weight[d]; mse += er * er; }
@@ -768,7 +779,9 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
     };
     if (cfg & CFG_STAB) {
         auto g0 = [&](int d) { return h.x_goal0[d]; };
-        costs(g0, g0);
+        const Row4<real> g4 = ldc4(h.pos_pack + 8);
+        auto gp = [&](int d) { return d == 0 ? g4.x : (d == 2 ? g4.y : g4.z); };   // x_goal0[d] for d = 0, 2, 4
+        costs(g0, g0, gp);
     } else {
         // X_GOAL[t]; the index is clamped to the last row where the reference would raise an IndexError
         // (t >= rows never happens inside an episode: rows == ctrl_steps, quadrotor.py:924-926, 1016-1021)
@@ -777,7 +790,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
 #pragma unroll
         for (int d = 0; d < NX; ++d) ga[d] = cold->x_goal[int64_t(gi) * NX + d];
         auto gt = [&](int d) { return ga[d]; };
-        costs(gt, gt);
+        costs(gt, gt, gt);
     }
     // ---- after_step (benchmark_env.py:422-463)
     e.t = t + 1;
@@ -1143,7 +1156,7 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
             int32_t* const progress = ro.q_mem + 1 + eb;
             if (chunk > 0) {
                 if (threadIdx.x == 0) {
-                    while (ld_acquire_gpu(progress) < chunk) __nanosleep(64);
+                    while (ld_acquire_gpu(progress) < chunk) __nanosleep(ro.q_sleep_ns);   // a polling warp still takes issue slots
                 }
                 __syncthreads();
             }
