@@ -35,7 +35,32 @@ template <int KIND, typename real> struct EnvRegs {
     Inertia<real> in;
     Att3<real> a3;       // 3D
     Att2<real> a2;       // 2D
+    // PAIRED loops (3D fp32 PLAIN, see step_env): the state of the control-step loop in packed pairs -- (x, y), (vx, vy),
+    // (roll rate, yaw rate), (z, pitch), (vz, pitch rate), (roll, yaw), thrust direction (x, y) and z.  While they are
+    // live, x[0..5], x[9..11], a3.rpy and a3.R[2 / 5 / 8] are not (x[6..8] and a3.sc stay scalar).
+    f32x2 Pxy, Vxy, Wxz, ZA, ZB, Axz, Rxy;
+    real R8;
 };
+
+#ifndef SCG_NO_PAIRS
+#define SCG_NO_PAIRS 0
+#endif
+template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN> struct Paired {
+    static constexpr bool value = KIND == SCG_QUAD_3D && sizeof(real) == 4 && ATT != SCG_ATT_ROUNDTRIP && LEAN && PLAIN && !SCG_NO_PAIRS;
+};
+SCG_DEV void pairs_from_scalars(EnvRegs<SCG_QUAD_3D, float>& e) {
+    e.Pxy = pk2(e.x[0], e.x[2]); e.Vxy = pk2(e.x[1], e.x[3]); e.Wxz = pk2(e.x[9], e.x[11]); e.ZB = pk2(e.x[5], e.x[10]);
+    e.ZA = pk2(e.x[4], e.a3.rpy[1]); e.Axz = pk2(e.a3.rpy[0], e.a3.rpy[2]); e.Rxy = pk2(e.a3.R[2], e.a3.R[5]); e.R8 = e.a3.R[8];
+}
+SCG_DEV void scalars_from_pairs(EnvRegs<SCG_QUAD_3D, float>& e) {
+    e.x[0] = lo2(e.Pxy); e.x[2] = hi2(e.Pxy); e.x[1] = lo2(e.Vxy); e.x[3] = hi2(e.Vxy); e.x[4] = lo2(e.ZA); e.x[5] = lo2(e.ZB);
+    e.x[9] = lo2(e.Wxz); e.x[10] = hi2(e.ZB); e.x[11] = hi2(e.Wxz);
+    e.a3.rpy[0] = lo2(e.Axz); e.a3.rpy[1] = hi2(e.ZA); e.a3.rpy[2] = hi2(e.Axz);
+    e.a3.R[2] = lo2(e.Rxy); e.a3.R[5] = hi2(e.Rxy); e.a3.R[8] = e.R8;
+    e.a3.form = 1;
+}
+template <int KIND, typename real> SCG_DEV void pairs_from_scalars(EnvRegs<KIND, real>&) {}
+template <int KIND, typename real> SCG_DEV void scalars_from_pairs(EnvRegs<KIND, real>&) {}
 
 template <int KIND, typename real> SCG_DEV void unpack_flags(EnvRegs<KIND, real>& e, uint32_t f) {
     e.viol = (f & SCG_FLAG_CNSTR_VIOLATION) != 0u;
@@ -88,12 +113,18 @@ template <int KIND, typename real, int ATT> SCG_DEV void derive_attitude(EnvRegs
 // env.state (quadrotor.py:853-869) from the registers; ang = the angular-velocity vector
 // PyBullet holds (rpy_rates after a step, INIT_ANG_VEL right after reset).  FULL = false leaves
 // the 3D body rates p, q, r (slots 9-11) untouched: they need the whole rotation matrix.
-template <int KIND, typename real, bool FULL = true>
+template <int KIND, typename real, bool FULL = true, bool PAIRED = false>
 SCG_DEV void make_state(EnvRegs<KIND, real>& e, const real (&ang)[3], real (&st)[Dims<KIND>::NX]) {
     if constexpr (KIND == SCG_QUAD_3D) {
+        if constexpr (PAIRED) {
+            static_assert(!FULL, "the paired state carries no full rotation matrix");
+            st[0] = lo2(e.Pxy); st[1] = lo2(e.Vxy); st[2] = hi2(e.Pxy); st[3] = hi2(e.Vxy); st[4] = lo2(e.ZA); st[5] = lo2(e.ZB);
+            st[6] = lo2(e.Axz); st[7] = hi2(e.ZA); st[8] = hi2(e.Axz);
+        } else {
 #pragma unroll
-        for (int d = 0; d < 6; ++d) st[d] = e.x[d];
-        st[6] = e.a3.rpy[0]; st[7] = e.a3.rpy[1]; st[8] = e.a3.rpy[2];
+            for (int d = 0; d < 6; ++d) st[d] = e.x[d];
+            st[6] = e.a3.rpy[0]; st[7] = e.a3.rpy[1]; st[8] = e.a3.rpy[2];
+        }
         if (FULL) {
             attitude3_complete<real>(e.a3);
             const real* R = e.a3.R;   // pqr = R^T ang_v (quadrotor.py:862-864)
@@ -300,13 +331,24 @@ SCG_DEV void spare_store(const real (&init)[Dims<KIND>::NX], real* __restrict__ 
     }
 }
 
-template <int KIND, typename real, int ATT>
+template <int KIND, typename real, int ATT, bool PAIRED = false>
 SCG_DEV void reset_from_spare(const real* __restrict__ sp, EnvRegs<KIND, real>& e) {
     constexpr int NX = Dims<KIND>::NX;
     e.resets += 1;
     e.t = 0;
     e.at_goal = e.completed = false; e.gate = e.hold = 0u; e.a2.flipped = 0u;   // cnstr_violation survives reset (benchmark_env.py:218)
-    if constexpr (KIND == SCG_QUAD_3D) {
+    if constexpr (PAIRED) {
+        static_assert(!PAIRED || Spare<KIND, real, ATT>::PRE3, "the paired loop takes the precomputed attitude from the spare");
+        e.Pxy = pk2(sp[0 * ENV_BLOCK], sp[2 * ENV_BLOCK]); e.Vxy = pk2(sp[1 * ENV_BLOCK], sp[3 * ENV_BLOCK]);
+        e.ZA = pk2(sp[4 * ENV_BLOCK], sp[(NX + 1) * ENV_BLOCK]); e.ZB = pk2(sp[5 * ENV_BLOCK], 0.f);
+        e.Wxz = pk2(0.f, 0.f);                                    // rpy_rates restart at 0 (base_aviary.py:232-233)
+        e.Axz = pk2(sp[(NX + 0) * ENV_BLOCK], sp[(NX + 2) * ENV_BLOCK]);
+#pragma unroll
+        for (int d = 6; d < 9; ++d) e.x[d] = sp[d * ENV_BLOCK];
+#pragma unroll
+        for (int j = 0; j < 6; ++j) e.a3.sc[j] = sp[(NX + 3 + j) * ENV_BLOCK];
+        e.Rxy = pk2(sp[(NX + 9) * ENV_BLOCK], sp[(NX + 10) * ENV_BLOCK]); e.R8 = sp[(NX + 11) * ENV_BLOCK];
+    } else if constexpr (KIND == SCG_QUAD_3D) {
 #pragma unroll
         for (int d = 0; d < 9; ++d) e.x[d] = sp[d * ENV_BLOCK];
         e.x[9] = e.x[10] = e.x[11] = real(0);          // rpy_rates restart at 0 (base_aviary.py:232-233)
@@ -544,17 +586,15 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             if constexpr (LAST) { e.x[6] = pre3[0]; e.x[7] = pre3[1]; e.x[8] = pre3[2]; }
             attitude3<real, ATT>(pre3, e.a3);
         };
-#ifndef SCG_NO_PAIRS
-#define SCG_NO_PAIRS 0
-#endif
-        if constexpr (LEAN && PLAIN && FASTMATH && !SCG_NO_PAIRS) {
+        if constexpr (Paired<KIND, real, ATT, LEAN, PLAIN>::value) {
             // The same substep on packed pairs (FFMA2 / FADD2, scg_math.cuh): every half is the scalar operation of
             // `substep` above, bit for bit; the loop is issue-bound and a pair takes one issue slot instead of two.
             // Pairing: (x, y) of position and velocity; (roll, yaw) of angles and rates, so that the two wraps that
             // follow the pitch fold run as one; the z lane rides with the pitch lane: (z, pitch) and (vz, pitch rate).
-            f32x2 Pxy = pk2(e.x[0], e.x[2]), Vxy = pk2(e.x[1], e.x[3]), Wxz = pk2(e.x[9], e.x[11]), ZB = pk2(e.x[5], e.x[10]);
-            f32x2 ZA = pk2(e.x[4], e.a3.rpy[1]), Axz = pk2(e.a3.rpy[0], e.a3.rpy[2]), Rxy = pk2(e.a3.R[2], e.a3.R[5]);
-            float R8 = e.a3.R[8];
+            // The pairs are the loop-carried state of the whole control-step loop (EnvRegs: Pxy ... R8; rollout_range packs
+            // them once before the loop), so no step pays for moving values between the two layouts.
+            f32x2 &Pxy = e.Pxy, &Vxy = e.Vxy, &Wxz = e.Wxz, &ZB = e.ZB, &ZA = e.ZA, &Axz = e.Axz, &Rxy = e.Rxy;
+            float& R8 = e.R8;
             // PLAIN: nominal inertia, so the constant pairs come straight from the constant bank as 64-bit operands
             const f32x2 ndJxz = *reinterpret_cast<const f32x2*>(h.ndJ_xz), kJxz = *reinterpret_cast<const f32x2*>(h.kJ_xz);
             const f32x2 Txz = pk2(mot.tx, mot.tz);
@@ -613,11 +653,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
                 for (int s = 1; s < h.substeps; ++s) substep2(std::false_type{});
                 substep2(std::true_type{});
             }
-            e.x[0] = lo2(Pxy); e.x[2] = hi2(Pxy); e.x[1] = lo2(Vxy); e.x[3] = hi2(Vxy); e.x[4] = lo2(ZA); e.x[5] = lo2(ZB);
-            e.x[9] = lo2(Wxz); e.x[10] = hi2(ZB); e.x[11] = hi2(Wxz);
-            e.a3.rpy[0] = lo2(Axz); e.a3.rpy[1] = hi2(ZA); e.a3.rpy[2] = hi2(Axz);
             e.a3.sc[0] = sph; e.a3.sc[1] = cph; e.a3.sc[2] = sth; e.a3.sc[3] = cth; e.a3.sc[4] = sps; e.a3.sc[5] = cps;
-            e.a3.R[2] = lo2(Rxy); e.a3.R[5] = hi2(Rxy); e.a3.R[8] = R8;
             e.a3.form = 1;
         } else if constexpr (LEAN) {
             if (FASTMATH && h.substeps == 4) {   // straight-line code for the usual PYB_FREQ / CTRL_FREQ
@@ -656,16 +692,19 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
         for (int s = 0; s < h.substeps; ++s) { e.x[1] += dt * az; e.x[0] += dt * e.x[1]; }
     }
     // ---- _get_observation: env.state (obs itself is written by the caller, it may be replaced on reset)
+    constexpr bool PAIRED = Paired<KIND, real, ATT, LEAN, PLAIN>::value;
     real ang[3];
-    if constexpr (KIND == SCG_QUAD_3D) { ang[0] = e.x[9]; ang[1] = e.x[10]; ang[2] = e.x[11]; }
+    if constexpr (PAIRED) { ang[0] = lo2(e.Wxz); ang[1] = hi2(e.ZB); ang[2] = hi2(e.Wxz); }
+    else if constexpr (KIND == SCG_QUAD_3D) { ang[0] = e.x[9]; ang[1] = e.x[10]; ang[2] = e.x[11]; }
     else if constexpr (KIND == SCG_QUAD_2D) { ang[0] = real(0); ang[1] = e.x[5]; ang[2] = real(0); }
     else { ang[0] = ang[1] = ang[2] = real(0); }
     real Rw[KIND == SCG_QUAD_3D ? 9 : 1];   // body-to-world rotation for the gate geometry (dead otherwise)
     if constexpr (KIND == SCG_QUAD_3D) {
-        make_state<KIND, real, false>(e, ang, st);
+        make_state<KIND, real, false, PAIRED>(e, ang, st);
         st[9] = st[10] = st[11] = real(0);
         if (full) {   // uniform: h.need_full_state or per-step outputs
             Att3<real> c = e.a3;   // a copy: columns 0 and 1 must not stay live across control steps
+            if constexpr (PAIRED) { c.R[2] = lo2(e.Rxy); c.R[5] = hi2(e.Rxy); c.R[8] = e.R8; }
             attitude3_complete<real>(c);
             const real* R = c.R;
 #pragma unroll
@@ -930,6 +969,8 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
     real st[NX];   // env.state after the last step (LEAN: rebuilt from the registers after the loop)
     load_inertia<KIND, real>(h, PLAIN ? nullptr : b.inertia, n, ii, e.in);
     derive_attitude<KIND, real, ATT>(e);
+    constexpr bool PAIRED = Paired<KIND, real, ATT, LEAN, PLAIN>::value;
+    if constexpr (PAIRED) pairs_from_scalars(e);
     real ep_ret = b.ep_return ? b.ep_return[ii] : real(0);
     int32_t ep_len = b.ep_length ? b.ep_length[ii] : 0;
     int32_t ep_viol = b.ep_violations ? b.ep_violations[ii] : 0;
@@ -1010,8 +1051,14 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
         if (any_out) {
             if (ro.reward_out) ro.reward_out[int64_t(k) * n + ii] = reward;
             if (ro.done_out) ro.done_out[int64_t(k) * n + ii] = done ? 1 : 0;
-            if (ro.log_out && (k % ro.log_stride) == 0)
+            if (ro.log_out && (k % ro.log_stride) == 0) {
+                if constexpr (PAIRED) {
+                    EnvRegs<KIND, real> el = e;   // the record reads the scalar layout
+                    scalars_from_pairs(el);
+                    write_log<KIND, real, true>(h, el, mot, ro.log_out + int64_t(k / ro.log_stride) * 16 * n + ii, n);
+                } else
                 write_log<KIND, real, (sizeof(real) == 4 && ATT != SCG_ATT_ROUNDTRIP)>(h, e, mot, ro.log_out + int64_t(k / ro.log_stride) * 16 * n + ii, n);
+            }
         }
         fresh = false;
         if (done) {
@@ -1059,7 +1106,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
                 spare_ok = true;
             }
             if (restart) {
-                reset_from_spare<KIND, real, ATT>(sp, e);
+                reset_from_spare<KIND, real, ATT, PAIRED>(sp, e);
                 if (!PLAIN && (cfg & CFG_RESET_EXTRAS)) {
                     Inertia<real> in;
                     apply_spare_extras<KIND, real, ATT>(h, cold, b.inertia, b.dist_offset, sp, n, ii, &in);
@@ -1069,6 +1116,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
             }
         }
     }
+    if constexpr (PAIRED) scalars_from_pairs(e);
     if constexpr (LEAN) {
         // env.state as observed after the loop: the fresh episode's (PyBullet still holds INIT_ANG_VEL)
         // or the last step's (ang_v = rpy_rates)
