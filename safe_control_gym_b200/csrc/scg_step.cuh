@@ -1061,6 +1061,23 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
             }
         }
         fresh = false;
+        if constexpr (LEAN) {
+            // The spare is made ready BEFORE the episode-end block so that statistics and restart share one divergent
+            // region.  One inline copy of the draw: at the cadence every lane that used its spare refills it together;
+            // a lane that ends two episodes inside one period draws on the spot.
+            const bool restart = done && (cfg & CFG_AUTO_RESET) != 0u;
+            const bool cadence = ahead && ((k - k0) & 15) == 0;   // uniform
+            if (bool(int(!spare_ok) & (int(restart) | int(cadence)))) {
+                const uint32_t next_ep = (cfg & CFG_RESEED) ? 0u : uint32_t(e.resets);
+                if (!PLAIN && (cfg & CFG_RESET_EXTRAS)) draw_spare_general<KIND, real, ATT>(h, cold, key, next_ep, sp);
+                else {
+                    real init[NX];
+                    draw_init_lean<KIND, real>(h, key, next_ep, init);
+                    spare_store<KIND, real, ATT>(init, sp);
+                }
+                spare_ok = true;
+            }
+        }
         if (done) {
             ep_acc[0 * ACC_LD] += 1.f; ep_acc[1 * ACC_LD] += float(ep_ret); ep_acc[2 * ACC_LD] += float(ep_len);
             if (info & SCG_INFO_TRUNCATED) ep_acc[3 * ACC_LD] += 1.f;
@@ -1088,31 +1105,15 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
 #pragma unroll
                     for (int j = 0; j < 9; ++j) ro.pid_mem[int64_t(j) * n + ii] = real(0);
                 }
-            }
-        }
-        if constexpr (LEAN) {
-            const bool restart = done && (cfg & CFG_AUTO_RESET) != 0u;
-            // one inline copy of the draw: at the cadence every lane that used its spare refills it together;
-            // a lane that ends two episodes inside one period draws on the spot
-            const bool cadence = ahead && ((k - k0) & 15) == 0;   // uniform
-            if (bool(int(!spare_ok) & (int(restart) | int(cadence)))) {
-                const uint32_t next_ep = (cfg & CFG_RESEED) ? 0u : uint32_t(e.resets);
-                if (!PLAIN && (cfg & CFG_RESET_EXTRAS)) draw_spare_general<KIND, real, ATT>(h, cold, key, next_ep, sp);
-                else {
-                    real init[NX];
-                    draw_init_lean<KIND, real>(h, key, next_ep, init);
-                    spare_store<KIND, real, ATT>(init, sp);
+                if constexpr (LEAN) {
+                    reset_from_spare<KIND, real, ATT, PAIRED>(sp, e);
+                    if (!PLAIN && (cfg & CFG_RESET_EXTRAS)) {
+                        Inertia<real> in;
+                        apply_spare_extras<KIND, real, ATT>(h, cold, b.inertia, b.dist_offset, sp, n, ii, &in);
+                        e.in = in;
+                    }
+                    spare_ok = false;
                 }
-                spare_ok = true;
-            }
-            if (restart) {
-                reset_from_spare<KIND, real, ATT, PAIRED>(sp, e);
-                if (!PLAIN && (cfg & CFG_RESET_EXTRAS)) {
-                    Inertia<real> in;
-                    apply_spare_extras<KIND, real, ATT>(h, cold, b.inertia, b.dist_offset, sp, n, ii, &in);
-                    e.in = in;
-                }
-                spare_ok = false;
             }
         }
     }
