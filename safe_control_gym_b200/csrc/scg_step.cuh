@@ -1118,6 +1118,14 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
         }
     }
     if constexpr (PAIRED) scalars_from_pairs(e);
+    // a range that ends inside the launch (ticket queue) hands over the state only: observation, env.state and the
+    // per-step scalars are rewritten by the range that ends the launch
+    const bool last_range = k1 >= ro.k_steps;   // uniform
+    if (!last_range) {
+#pragma unroll
+        for (int d = 0; d < NX; ++d) b.state[int64_t(d) * n + ii] = e.x[d];
+        b.ctrl_step[ii] = e.t; b.episode[ii] = e.resets; b.flags[ii] = pack_flags<KIND, real>(e);
+    } else {
     if constexpr (LEAN) {
         // env.state as observed after the loop: the fresh episode's (PyBullet still holds INIT_ANG_VEL)
         // or the last step's (ang_v = rpy_rates)
@@ -1154,6 +1162,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
     }
     b.reward[ii] = reward; b.done[ii] = done ? 1 : 0; b.info[ii] = uint8_t(info);
     if (b.mse) b.mse[ii] = mse;
+    }
     if (b.ep_return) b.ep_return[ii] = ep_ret;
     if (b.ep_length) b.ep_length[ii] = ep_len;
     if (b.ep_violations) b.ep_violations[ii] = ep_viol;
