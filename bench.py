@@ -204,6 +204,7 @@ def run_gpu(args):
     total_ms = ev[0].elapsed_time(ev[-1])
     per = [ev[s].elapsed_time(ev[s + 1]) for s in range(args.steps)]
     launches = env.launch_count - launches0
+    queued = bool(env.last_rollout_queued)   # the launches of the timed region went through the time-chunk ticket queue
     t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -241,6 +242,8 @@ def run_gpu(args):
         return
     # ---- roofline of the dominant kernel (k_rollout<3, float, ATT, ...>): one launch per step
     variant = {0: "GENERAL", 1: "LEAN", 2: "LEAN,PLAIN", 3: "LEAN,PLAIN,SPEC"}[int(env.lib.scg_kernel_variant(env._h))]
+    if queued:
+        variant += ",QUEUE"
     peak = C.c_double()
     L.check(L.load().scg_measure_fp32_peak(C.byref(peak)))
     kernel_ms = sum(per) / len(per)   # one launch per step; stats all-reduce excluded at N = 1
@@ -265,7 +268,9 @@ def run_gpu(args):
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": "quadrotor3d_dyn_65536x1000_level0_constraints", "envs_per_gpu": n, "ctrl_steps_per_step": k,
-                   "substeps": SUBSTEPS, "env_substeps_per_sec": value * SUBSTEPS, "mode": "fused rollout, auto-reset, Philox init", "attitude": args.attitude, "action_std": args.action_std,
+                   "substeps": SUBSTEPS, "env_substeps_per_sec": value * SUBSTEPS, "mode": "fused rollout, auto-reset, Philox init",
+                   "schedule": "ticket queue over (64-step chunk, 64-env block) units, one persistent launch" if queued else "one block per 64 envs",
+                   "attitude": args.attitude, "action_std": args.action_std,
                    "l2_policy": "inputs larger than L2 (1.05 GB action table re-streamed each step)"},
         "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": peak.value, "unit": "TFLOP/s", "frac": achieved_tf / peak.value,
                      "traffic": traffic, "kernel": "scg::k_rollout<3,float,%s,%s>" % (args.attitude, variant), "kernel_ms": kernel_ms,

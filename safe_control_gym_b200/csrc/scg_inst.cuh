@@ -29,9 +29,12 @@ int launch_reset(scg_env* e, const ResetInject<real>& inj, const uint8_t* mask, 
 // The queue pays when the launch is long and the env blocks fill the resident slots unevenly (at most a few waves):
 // a static grid of 1,024 blocks leaves schedulers with three and with four warps, a grid of 1,300 runs two waves.
 template <typename K>
-static bool launch_queued(scg_env* e, K kernel, const int64_t n, int k_steps, int32_t* q_chunk, int32_t* q_env_blocks, int32_t* q_tickets,
-                          unsigned* grid) {
+static bool launch_queued(scg_env* e, K kernel, bool plain, const int64_t n, int k_steps, int32_t* q_chunk, int32_t* q_env_blocks,
+                          int32_t* q_tickets, unsigned* grid) {
     if (e->queue_mode == 0 || k_steps < 64) return false;
+    // automatic mode: PLAIN kernels only -- a range of the other kernels starts with the general spare draw (inertia,
+    // disturbance offsets, normal draws), which costs more than the balance returns (level2-like config: 20.1 -> 18.1 G)
+    if (e->queue_mode < 0 && !plain) return false;
     if (e->n_sms == 0) {
         int dev = 0;
         if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&e->n_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return false;
@@ -61,7 +64,7 @@ static void launch_rollout_v(scg_env* e, const Hot<real>& h, const Cold<real>* c
     if constexpr (LEAN && sizeof(real) == 4) {
         Roll<real> rq = ro;
         unsigned grid = 0;
-        if (!ro.step_outputs && launch_queued(e, k_rollout<KIND, real, ATT, LEAN, PLAIN, SPEC, true>, b.n, ro.k_steps, &rq.q_chunk,
+        if (!ro.step_outputs && launch_queued(e, k_rollout<KIND, real, ATT, LEAN, PLAIN, SPEC, true>, PLAIN, b.n, ro.k_steps, &rq.q_chunk,
                                               &rq.q_env_blocks, &rq.q_tickets, &grid)) {
             rq.q_mem = e->q_mem; rq.q_sleep_ns = e->queue_sleep_ns;
             if (cudaMemsetAsync(e->q_mem, 0, sizeof(int32_t) * (1 + rq.q_env_blocks), st) == cudaSuccess) {
