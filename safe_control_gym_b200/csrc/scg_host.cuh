@@ -25,7 +25,7 @@ struct scg_env {
     void* stage[2] = {nullptr, nullptr};
     size_t stage_bytes = 0;
     // time-chunk queue of the fused rollout (scg_step.cuh: k_rollout<..., QUEUE>)
-    int32_t* q_mem = nullptr;      // [1 + env blocks]: ticket counter, chunks finished per env block
+    int32_t* q_mem = nullptr;      // [2 + ranges]: pop counter, push counter, ready list
     int64_t q_cap = 0;
     int n_sms = 0;
     int queue_mode = -1;           // -1 auto, 0 off, 1 on (SCG_QUEUE)

@@ -46,12 +46,12 @@ static bool launch_queued(scg_env* e, K kernel, bool plain, const int64_t n, int
     int chunk = e->queue_chunk > 0 ? e->queue_chunk : 64;
     if (chunk > k_steps) chunk = k_steps;
     const int64_t chunks = (k_steps + chunk - 1) / chunk, tickets = chunks * env_blocks;
-    if (tickets > 0x7fffffff || env_blocks > 0x7fffffff) return false;
-    if (e->q_cap < 1 + env_blocks) {
+    if (tickets + env_blocks > 0x7ffffff0) return false;   // an item is 1 + env block + env_blocks * chunk in 31 bits
+    if (e->q_cap < 2 + tickets) {   // pop counter, push counter, ready list
         if (e->q_mem) cudaFree(e->q_mem);
         e->q_mem = nullptr; e->q_cap = 0;
-        if (cudaMalloc(&e->q_mem, sizeof(int32_t) * (1 + env_blocks)) != cudaSuccess) return false;
-        e->q_cap = 1 + env_blocks;
+        if (cudaMalloc(&e->q_mem, sizeof(int32_t) * (2 + tickets)) != cudaSuccess) return false;
+        e->q_cap = 2 + tickets;
     }
     *q_chunk = chunk; *q_env_blocks = int32_t(env_blocks); *q_tickets = int32_t(tickets);
     *grid = unsigned(tickets < resident ? tickets : resident);
@@ -67,7 +67,7 @@ static void launch_rollout_v(scg_env* e, const Hot<real>& h, const Cold<real>* c
         if (!ro.step_outputs && launch_queued(e, k_rollout<KIND, real, ATT, LEAN, PLAIN, SPEC, true>, PLAIN, b.n, ro.k_steps, &rq.q_chunk,
                                               &rq.q_env_blocks, &rq.q_tickets, &grid)) {
             rq.q_mem = e->q_mem; rq.q_sleep_ns = e->queue_sleep_ns;
-            if (cudaMemsetAsync(e->q_mem, 0, sizeof(int32_t) * (1 + rq.q_env_blocks), st) == cudaSuccess) {
+            if (cudaMemsetAsync(e->q_mem, 0, sizeof(int32_t) * (2 + size_t(rq.q_tickets)), st) == cudaSuccess) {
                 k_rollout<KIND, real, ATT, LEAN, PLAIN, SPEC, true><<<grid, ENV_BLOCK, 0, st>>>(h, cold, b, rq);
                 e->last_queue = 1;
                 return;

@@ -167,8 +167,8 @@ template <typename real> struct Roll {
     real* pid_mem;                  // [9][n] controller memory
     real* actions_out;              // optional [K][n][nu]: the actions the PID commanded
     PidP<real> pid;
-    // time-chunk queue (k_rollout<..., QUEUE>): q_mem[0] = ticket counter, q_mem[1 + env block] = chunks finished;
-    // ticket t = chunk t / q_env_blocks of env block t % q_env_blocks, q_chunk control steps each
+    // time-chunk queue (k_rollout<..., QUEUE>): q_mem[0] = pop counter, q_mem[1] = push counter, q_mem[2 + s] = ready list;
+    // q_tickets = chunks * q_env_blocks ranges of q_chunk control steps each
     int32_t* q_mem; int32_t q_chunk; int32_t q_env_blocks; int32_t q_tickets; uint32_t q_sleep_ns;
 };
 

@@ -1182,12 +1182,13 @@ SCG_DEV int32_t ld_acquire_gpu(const int32_t* p) {
 SCG_DEV void st_release_gpu(int32_t* p, int32_t v) { asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
 
 // QUEUE = false: block b owns envs [64 b, 64 b + 64) for all K steps.
-// QUEUE = true (fused launches whose envs fit in a few waves): the K steps are cut into chunks of ro.q_chunk and the
-// resident blocks take (chunk, env block) tickets from a counter, chunk-major; chunk c of an env block waits for its
-// chunk c - 1 (release / acquire on q_mem[1 + env block]) and picks the state up from Buf.  With 65,536 envs the static
-// split leaves 272 of the 592 schedulers with four warps and 320 with three for the whole launch, and the four-warp ones
-// set the makespan; through the queue every scheduler hosts four warps, the ~14 % that wait for a ticket sleep, and a
-// scheduler that runs ahead simply takes more tickets (same result: the split into ranges is invisible, see rollout_range).
+// QUEUE = true (fused launches whose envs fit in a few waves): the K steps are cut into chunks of ro.q_chunk; the
+// resident blocks pop (chunk, env block) ranges from a ready list in global memory and a block that finishes a chunk
+// pushes the env block's next one (release / acquire on the list slot), the state travelling through Buf.  With 65,536 envs
+// the static split leaves 272 of the 592 schedulers with four warps and 320 with three for the whole launch, and the
+// four-warp ones set the makespan; through the queue every scheduler hosts four warps, the ~14 % that wait for a range
+// sleep, and a scheduler that runs ahead simply takes more ranges (same result: the split into ranges is invisible, see
+// rollout_range).
 template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN = false, bool SPEC = false, bool QUEUE = false>
 __global__ void __launch_bounds__(ENV_BLOCK, sizeof(real) == 4 ? 512 / ENV_BLOCK : 1)
 k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, const Buf<real> b, const Roll<real> ro) {
@@ -1203,27 +1204,36 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
         rollout_range<KIND, real, ATT, LEAN, PLAIN, SPEC>(h, cold, b, ro, i, 0, ro.k_steps, acc_buf + (i < b.n ? threadIdx.x : ENV_BLOCK),
                                                           mse_buf + (i < b.n ? threadIdx.x : ENV_BLOCK), sp);
     } else {
-        __shared__ int32_t s_ticket;
+        // q_mem: [0] pop counter, [1] push counter, [2 + s] the ready list: item s = 1 + env block + env_blocks * chunk.
+        // Items 0 .. env_blocks - 1 are implicit (chunk 0 of every env block is ready at launch); every finished chunk
+        // but the last of its env block pushes the next one, so the list fills in COMPLETION order and the block that
+        // has waited longest gets whichever env block is handed over first (no head-of-line blocking behind a slow one).
+        __shared__ int32_t s_item;
+        int32_t* const items = ro.q_mem + 2;
         for (;;) {
-            __syncthreads();   // the previous range is complete (and everybody has read s_ticket)
-            if (threadIdx.x == 0) s_ticket = atomicAdd(ro.q_mem, 1);
-            __syncthreads();
-            const int32_t t = s_ticket;
-            if (t >= ro.q_tickets) break;
-            const int32_t chunk = t / ro.q_env_blocks, eb = t - chunk * ro.q_env_blocks;
-            int32_t* const progress = ro.q_mem + 1 + eb;
-            if (chunk > 0) {
-                if (threadIdx.x == 0) {
-                    while (ld_acquire_gpu(progress) < chunk) __nanosleep(ro.q_sleep_ns);   // a polling warp still takes issue slots
+            __syncthreads();   // the previous range is complete (and everybody has read s_item)
+            if (threadIdx.x == 0) {
+                const int32_t slot = atomicAdd(ro.q_mem, 1);
+                int32_t item = slot < ro.q_env_blocks ? slot + 1 : 0;
+                if (slot >= ro.q_env_blocks && slot < ro.q_tickets) {
+                    while ((item = ld_acquire_gpu(items + slot)) == 0) __nanosleep(ro.q_sleep_ns);
                 }
-                __syncthreads();
+                s_item = slot < ro.q_tickets ? item : 0;
             }
+            __syncthreads();
+            const int32_t item = s_item;
+            if (item == 0) break;   // every range of the launch has been handed out
+            const int32_t chunk = (item - 1) / ro.q_env_blocks, eb = (item - 1) - chunk * ro.q_env_blocks;
             const int64_t i = int64_t(eb) * ENV_BLOCK + threadIdx.x;
             const int k0 = chunk * ro.q_chunk, k1 = k0 + ro.q_chunk < ro.k_steps ? k0 + ro.q_chunk : ro.k_steps;
             rollout_range<KIND, real, ATT, LEAN, PLAIN, SPEC>(h, cold, b, ro, i, k0, k1, acc_buf + (i < b.n ? threadIdx.x : ENV_BLOCK),
                                                               mse_buf + (i < b.n ? threadIdx.x : ENV_BLOCK), sp);
             __syncthreads();
-            if (threadIdx.x == 0) { __threadfence(); st_release_gpu(progress, chunk + 1); }
+            if (threadIdx.x == 0 && k1 < ro.k_steps) {
+                __threadfence();
+                const int32_t at = ro.q_env_blocks + atomicAdd(ro.q_mem + 1, 1);
+                st_release_gpu(items + at, item + ro.q_env_blocks);
+            }
         }
     }
     if (b.stats) {   // warp-shuffle reduction, one atomic per warp per statistic
