@@ -1210,10 +1210,14 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
         // has waited longest gets whichever env block is handed over first (no head-of-line blocking behind a slow one).
         __shared__ int32_t s_item;
         int32_t* const items = ro.q_mem + 2;
+        int32_t push = 0;   // thread 0: the item to publish for the range this block has just finished (0: none)
         for (;;) {
-            __syncthreads();   // the previous range is complete (and everybody has read s_item)
+            __syncthreads();   // the previous range is complete: its stores precede thread 0's release below (and everybody has read s_item)
             if (threadIdx.x == 0) {
+                // hand-over and pop in one go: the two counter atomics are independent and overlap; st.release.gpu carries
+                // the fence that makes the block's state stores visible before the item
                 const int32_t slot = atomicAdd(ro.q_mem, 1);
+                if (push) st_release_gpu(items + ro.q_env_blocks + atomicAdd(ro.q_mem + 1, 1), push);
                 int32_t item = slot < ro.q_env_blocks ? slot + 1 : 0;
                 if (slot >= ro.q_env_blocks && slot < ro.q_tickets) {
                     while ((item = ld_acquire_gpu(items + slot)) == 0) __nanosleep(ro.q_sleep_ns);
@@ -1228,12 +1232,7 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
             const int k0 = chunk * ro.q_chunk, k1 = k0 + ro.q_chunk < ro.k_steps ? k0 + ro.q_chunk : ro.k_steps;
             rollout_range<KIND, real, ATT, LEAN, PLAIN, SPEC>(h, cold, b, ro, i, k0, k1, acc_buf + (i < b.n ? threadIdx.x : ENV_BLOCK),
                                                               mse_buf + (i < b.n ? threadIdx.x : ENV_BLOCK), sp);
-            __syncthreads();
-            if (threadIdx.x == 0 && k1 < ro.k_steps) {
-                __threadfence();
-                const int32_t at = ro.q_env_blocks + atomicAdd(ro.q_mem + 1, 1);
-                st_release_gpu(items + at, item + ro.q_env_blocks);
-            }
+            push = k1 < ro.k_steps ? item + ro.q_env_blocks : 0;
         }
     }
     if (b.stats) {   // warp-shuffle reduction, one atomic per warp per statistic
