@@ -634,14 +634,15 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
                 R8 = cth * cph;
                 if (band) {   // see attitude3
                     const bool up = sth > 0.f;
-                    const float r = 0.5f * (thw - (up ? Consts<float>::half_pi : -Consts<float>::half_pi));
+                    const float hp = copysignf(Consts<float>::half_pi, sth);   // the snapped pitch
+                    const float r = 0.5f * (thw - hp);
                     const float sr = folded ? -sph : sph, cr = folded ? -cph : cph;
                     const float u = up ? r * cr : -(r * cr);
                     const float corr = 2.f * r * sr * (1.f - u + u * u);
                     float yaw = (up ? hi2(PRE) - lo2(PRE) : hi2(PRE) + lo2(PRE)) + corr;
                     const float k = fast_rint(yaw * 0.07957747154594767f);
                     yaw = fmaf(-k, -3.4969110629390343e-07f, fmaf(-k, 12.566370964050293f, yaw));
-                    r0 = 0.f; r1 = up ? Consts<float>::half_pi : -Consts<float>::half_pi; r2 = yaw;
+                    r0 = 0.f; r1 = hp; r2 = yaw;
                 }
                 Axz = pk2(r0, r2);
                 ZA = pk2(lo2(ZA2), r1);
