@@ -31,8 +31,8 @@ template <typename real> struct Hot {
     real inv_mass, gravity_force;   // nominal (parity mode)
     real J[3], J_inv[3];
     real dJ[3], kJ[3];             // fast substep (scg_step.cuh): (Izz-Iyy, Ixx-Izz, Iyy-Ixx) and dt / J
-    alignas(8) real ndJ_xz[2];     // (-dJ[0], -dJ[2]) and (kJ[0], kJ[2]) adjacent: one 64-bit constant operand of the packed substep
-    alignas(8) real kJ_xz[2];
+    alignas(16) real ndJ_xz[2];    // (-dJ[0], -dJ[2]) and (kJ[0], kJ[2]): 64-bit constant operands of the packed substep, one 16-byte row
+    real kJ_xz[2];
     real pwm_scale, pwm_const, pwm_min, pwm_max, inv_pwm_scale;
     real inv_nkf;                   // 1 / (n_motor * KF)
     real f_min, f_max, inv_n_motor, km_over_kf, inv_kf;   // per-rotor force at PWM_min / PWM_max, 1 / n_motor, KM / KF, 1 / KF (fast motor map)

@@ -618,7 +618,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
                 const float thw = att_wrap<ATT>(hi2(ZA2));
                 const bool folded = fabsf(thw) > Consts<float>::half_pi;
                 float th = thw;
-                if (folded) th = copysignf(Consts<float>::pi, thw) - thw;
+                if (folded) th = copysignf(Consts<float>::pi - fabsf(thw), thw);   // == copysign(pi, thw) - thw, one constant less
                 f32x2 PH = add2(PRE, bc2(folded ? Consts<float>::pi : 0.f));
                 {
                     const f32x2 K = add2(fma2(PH, bc2(0.15915494309189535f), bc2(12582912.f)), bc2(-12582912.f));
