@@ -409,7 +409,8 @@ SCG_DEV void eval_constraints(const Hot<real>& h, const Cold<real>* __restrict__
             w = m_max3(w, h.ubox_lo[d] - raw[d], raw[d] - h.ubox_hi[d]);
         }
     }
-    violated = m_max(w0, w1) * real(1e8) > h.box_thr;
+    // (positions-only box: the threshold rides in the fourth slot of the lower-bound row, same value)
+    violated = m_max(w0, w1) * real(1e8) > ((KIND == SCG_QUAD_3D && (cfg & CFG_BOX_POS)) ? ldc4(h.pos_pack).w : h.box_thr);
 }
 
 // ------------------------------------------------------------------ gate progress + contact scan (row A10)

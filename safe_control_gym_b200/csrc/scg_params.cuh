@@ -40,7 +40,8 @@ template <typename real> struct Hot {
     // action map
     int32_t normalized_action;
     real norm_act_scale, hover_thrust;
-    real act_low[SCG_MAX_NU], act_high[SCG_MAX_NU];
+    alignas(16) real act_low[SCG_MAX_NU];
+    alignas(16) real act_high[SCG_MAX_NU];
     // state space / termination
     real state_low[SCG_MAX_NX], state_high[SCG_MAX_NX];
     int32_t done_on_out_of_bound, done_on_violation, done_on_collision, done_on_completion;
@@ -62,7 +63,9 @@ template <typename real> struct Hot {
     BoundedCon<real> bounded[MAX_BOUNDED];
     real viol_thr;                  // fp32: 5e-9 (== round(c, 8) > 0 in exact arithmetic)
     // LEAN configs: all bounded constraints merged into one box per state / input dim (violation flag only)
-    real box_lo[SCG_MAX_NX], box_hi[SCG_MAX_NX], ubox_lo[SCG_MAX_NU], ubox_hi[SCG_MAX_NU];
+    real box_lo[SCG_MAX_NX], box_hi[SCG_MAX_NX];
+    alignas(16) real ubox_lo[SCG_MAX_NU];   // 16-byte rows: one LDCU.128 each
+    alignas(16) real ubox_hi[SCG_MAX_NU];
     uint32_t box_mask, ubox_mask;   // dims that carry a bound
     real box_thr;                   // violated <=> max_k(c_k) * 1e8 > box_thr (0.5, or just below -0.5 when strict)
     // the per-step position constants of a 3D env in four 16-byte rows (one LDCU.128 each instead of a dozen scalar loads):

@@ -735,7 +735,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             const real dx = st[0] - g.x, dy = st[2] - g.y, dz = st[4] - g.z;
             // sqrt(d2) < tol  <=>  d2 < tol^2 up to one rounding of the square; the literal modes keep the sqrt
             const real d2 = dx * dx + dy * dy + dz * dz;
-            const bool inside = FASTMATH ? (d2 < h.pos_pack[7]) : (m_sqrt(d2) < h.goal_tol);
+            const bool inside = FASTMATH ? (d2 < ldc4(h.pos_pack + 4).w) : (m_sqrt(d2) < h.goal_tol);   // goal_tol^2 rides in the upper-bound row
             e.at_goal = inside;
             e.hold = inside ? (e.hold < 0xFFFFu ? e.hold + 1u : e.hold) : 0u;
             if (e.hold > uint32_t(2 * h.ctrl_freq)) e.completed = true;
