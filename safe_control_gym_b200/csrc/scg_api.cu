@@ -277,6 +277,8 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
             if ((s.kind == SCG_DIST_IMPULSE || s.kind == SCG_DIST_STEP) && s.step_offset < 0) reset_draws = true;
         }
     if (reset_draws) h.cfg |= CFG_RESET_EXTRAS;
+    h.step_row[0] = h.dt; h.step_row[1] = h.arm_s2; h.step_row[2] = h.km_over_kf; h.step_row[3] = h.inv_mass;
+    h.step_row[4] = -h.dJ[1]; h.step_row[5] = h.kJ[1]; h.step_row[6] = -(h.gravity_force * h.inv_mass); h.step_row[7] = real(0);
     for (int j = 0; j < 3; ++j) {
         h.pos_pack[j] = h.box_lo[2 * j]; h.pos_pack[4 + j] = h.box_hi[2 * j];
         h.pos_pack[8 + j] = h.x_goal0[2 * j]; h.pos_pack[12 + j] = h.mse_weight[2 * j];

@@ -203,10 +203,11 @@ SCG_DEV void motors_from_thrust(const Hot<real>& h, const real (&thrust)[Dims<KI
         else { f[0] = fi[0]; f[1] = fi[1 % NU]; f[2] = fi[2 % NU]; f[3] = fi[3 % NU]; }
 #pragma unroll
         for (int j = 0; j < 4; ++j) m.rpm[j] = f[j];
+        const Row4<real> sr = ldc4(h.step_row);   // [dt, arm_s2, km_over_kf, inv_mass]: the same constants in one 16-byte row
         m.T = ((f[0] + f[1]) + f[2]) + f[3];
-        m.tz = (((f[0] - f[1]) + f[2]) - f[3]) * h.km_over_kf;
-        m.tx = (((f[0] + f[1]) - f[2]) - f[3]) * h.arm_s2;
-        m.ty = (((-f[0] + f[1]) + f[2]) - f[3]) * h.arm_s2;
+        m.tz = (((f[0] - f[1]) + f[2]) - f[3]) * sr.z;
+        m.tx = (((f[0] + f[1]) - f[2]) - f[3]) * sr.y;
+        m.ty = (((-f[0] + f[1]) + f[2]) - f[3]) * sr.y;
         return;
     }
     real rp[NU];

@@ -31,6 +31,8 @@ template <typename real> struct Hot {
     real inv_mass, gravity_force;   // nominal (parity mode)
     real J[3], J_inv[3];
     real dJ[3], kJ[3];             // fast substep (scg_step.cuh): (Izz-Iyy, Ixx-Izz, Iyy-Ixx) and dt / J
+    // per-step scalars of the fast 3D path in two 16-byte rows: [dt, arm_s2, km_over_kf, inv_mass] [-dJ[1], kJ[1], -g / m * m = -GRAVITY_ACC, 0]
+    alignas(16) real step_row[8];
     alignas(16) real ndJ_xz[2];    // (-dJ[0], -dJ[2]) and (kJ[0], kJ[2]): 64-bit constant operands of the packed substep, one 16-byte row
     real kJ_xz[2];
     real pwm_scale, pwm_const, pwm_min, pwm_max, inv_pwm_scale;

@@ -548,8 +548,9 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
     if constexpr (KIND != SCG_CARTPOLE) motors_from_thrust<KIND, real, FASTMATH>(h, thr, mot, !(PLAIN && (cfg & CFG_CLIP_ONCE)));
     else { mot.T = mot.tx = mot.ty = mot.tz = real(0); mot.rpm[0] = mot.rpm[1] = mot.rpm[2] = mot.rpm[3] = real(0); }
     // ---- _advance_simulation: S explicit substeps (base_aviary.py:266-322, 522-576)
-    const real Tm = mot.T * e.in.inv_mass;
-    const real dt = h.dt;
+    constexpr bool ROWS = PLAIN && KIND == SCG_QUAD_3D && sizeof(real) == 4 && ATT != SCG_ATT_ROUNDTRIP;   // nominal inertia: constants from Hot::step_row
+    const real Tm = mot.T * (ROWS ? ldc4(h.step_row).w : e.in.inv_mass);
+    const real dt = ROWS ? ldc4(h.step_row).x : h.dt;
     if constexpr (KIND == SCG_QUAD_3D) {
         const real axf = fx * e.in.inv_mass, ayf = fy * e.in.inv_mass, azf = fz * e.in.inv_mass - e.in.g_over_m;
         const real Tdt = Tm * dt, gdt = e.in.g_over_m * dt;
@@ -598,7 +599,8 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             // PLAIN: nominal inertia, so the constant pairs come straight from the constant bank as 64-bit operands
             const f32x2 ndJxz = *reinterpret_cast<const f32x2*>(h.ndJ_xz), kJxz = *reinterpret_cast<const f32x2*>(h.kJ_xz);
             const f32x2 Txz = pk2(mot.tx, mot.tz);
-            const float ndJ1 = -h.dJ[1], kJ1 = h.kJ[1], ngm = -e.in.g_over_m;
+            const Row4<float> sb = ldc4(h.step_row + 4);   // [-dJ[1], kJ[1], -g, 0]
+            const float ndJ1 = sb.x, kJ1 = sb.y, ngm = sb.z;
             float sph, cph, sth, cth, sps, cps;
             auto substep2 = [&](auto last_tag) {
                 constexpr bool LAST = decltype(last_tag)::value;
