@@ -175,18 +175,34 @@ def run_gpu(args):
     env = BatchedQuadrotor(num_envs=n, device=dev, dtype=torch.float32, attitude=args.attitude, auto_reset=True,
                            seed_offset=rank * n, **kw)   # Philox keyed by GLOBAL env id: shard-independent results
     actions = make_actions(torch, n, k, dev, 1337 + rank, args.action_std)
-    stats_all = torch.zeros(L.STATS_LEN, dtype=torch.float64, device=dev)
+    stats_all = [torch.zeros(L.STATS_LEN, dtype=torch.float64, device=dev) for _ in range(2)]
+    pending = [None, None]
+    turn = [0]
 
     def one_step():
         env.rollout(actions)
-        if world > 1:   # the only collective of the path: merge the episode statistics
-            stats_all.copy_(env.buf_stats)
-            dist.all_reduce(stats_all)
+        if world > 1:
+            # The only collective of the path: merge the episode statistics.  It runs on NCCL's
+            # stream behind a snapshot of the 16 doubles, two buffers in turn, so the next launch does not wait for it;
+            # drain() makes the timed region end only after the last merge has completed.
+            j = turn[0] & 1
+            turn[0] += 1
+            if pending[j] is not None:
+                pending[j].wait()
+            stats_all[j].copy_(env.buf_stats)
+            pending[j] = dist.all_reduce(stats_all[j], async_op=True)
+
+    def drain():
+        for j in range(2):
+            if pending[j] is not None:
+                pending[j].wait()
+                pending[j] = None
 
     env.reset()
     env.buf_stats.zero_()
     for _ in range(args.warmup):
         one_step()
+    drain()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -198,10 +214,13 @@ def run_gpu(args):
         for s in range(args.steps):
             one_step()
             ev[s + 1].record()
+        drain()
+        ev_end = torch.cuda.Event(enable_timing=True)
+        ev_end.record()
         torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
-    total_ms = ev[0].elapsed_time(ev[-1])
+    total_ms = ev[0].elapsed_time(ev_end)   # includes the last statistics merge
     per = [ev[s].elapsed_time(ev[s + 1]) for s in range(args.steps)]
     launches = env.launch_count - launches0
     queued = bool(env.last_rollout_queued)   # the launches of the timed region went through the time-chunk ticket queue
