@@ -175,9 +175,8 @@ def run_gpu(args):
     env = BatchedQuadrotor(num_envs=n, device=dev, dtype=torch.float32, attitude=args.attitude, auto_reset=True,
                            seed_offset=rank * n, **kw)   # Philox keyed by GLOBAL env id: shard-independent results
     actions = make_actions(torch, n, k, dev, 1337 + rank, args.action_std)
-    stats_all = [torch.zeros(L.STATS_LEN, dtype=torch.float64, device=dev) for _ in range(2)]
-    pending = [None, None]
-    turn = [0]
+    from safe_control_gym_b200.sharding import StatsMerger
+    merger = StatsMerger(dev)
 
     def one_step():
         env.rollout(actions)
@@ -185,18 +184,10 @@ def run_gpu(args):
             # The only collective of the path: merge the episode statistics.  It runs on NCCL's
             # stream behind a snapshot of the 16 doubles, two buffers in turn, so the next launch does not wait for it;
             # drain() makes the timed region end only after the last merge has completed.
-            j = turn[0] & 1
-            turn[0] += 1
-            if pending[j] is not None:
-                pending[j].wait()
-            stats_all[j].copy_(env.buf_stats)
-            pending[j] = dist.all_reduce(stats_all[j], async_op=True)
+            merger.submit(env.buf_stats)
 
     def drain():
-        for j in range(2):
-            if pending[j] is not None:
-                pending[j].wait()
-                pending[j] = None
+        merger.drain()
 
     env.reset()
     env.buf_stats.zero_()
