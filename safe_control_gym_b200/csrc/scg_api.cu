@@ -253,6 +253,24 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
         }
     }
     h.box_thr = (nb > 0 && h.bounded[0].strict) ? std::nextafter(real(-0.5), -INF) : real(0.5);
+    // flat value table (every row from a non-symmetric bounded object without tolerance, one strictness)
+    h.n_crows = 0; h.crow_strict = nb > 0 ? h.bounded[0].strict : 0;
+    if (nb > 0 && nd == 0 && !h.any_tolerance && !symmetric && same_strict && h.n_rows <= SCG_MAX_ROWS) {
+        int filled = 0;
+        for (int r = 0; r < SCG_MAX_ROWS; ++r) { h.crow_src[r] = -1; h.crow_sgn[r] = 0; h.crow_bound[r] = real(0); }
+        for (int q = 0; q < nb; ++q) {
+            const BoundedCon<real>& bc = h.bounded[q];
+            const int full = bc.var == SCG_VAR_STATE ? nx : nu, off = bc.var == SCG_VAR_STATE ? 0 : nx;
+            for (int d = 0; d < full; ++d) {
+                if (!((bc.mask >> d) & 1u)) continue;
+                const int rl = bc.row_lo[d], rh = bc.row_hi[d];
+                h.crow_src[rl] = int8_t(off + d); h.crow_sgn[rl] = -1; h.crow_bound[rl] = bc.lo[d];
+                h.crow_src[rh] = int8_t(off + d); h.crow_sgn[rh] = 1; h.crow_bound[rh] = bc.hi[d];
+                filled += 2;
+            }
+        }
+        if (filled == h.n_rows) h.n_crows = h.n_rows;
+    }
     if (h.n_rows > 0) h.cfg |= CFG_HAS_ROWS;
     if (h.ubox_mask) h.cfg |= CFG_UBOX;
     if (c.env_kind == SCG_QUAD_3D && !(h.mse_mask & ~0x15u)) h.cfg |= CFG_MSE_POS;

@@ -362,6 +362,28 @@ __device__ __noinline__ uint32_t constraint_values_cold(const Hot<real>& h, cons
     return (violated ? 1u : 0u) | (almost ? 2u : 0u);   // by value: the caller's flags stay in registers
 }
 
+// The same values for configs whose rows all come from plain bounded constraints (Hot::crow_*): one pass over the output
+// rows instead of the object / dim / kind loops above (the host-driven step of the level0 family spent 40 % of its
+// instructions there).  Same arithmetic per row: c = lo - x or x - hi, round8, viol_test.
+template <int KIND, typename real>
+__device__ __noinline__ uint32_t constraint_values_flat(const Hot<real>& h, const real* __restrict__ st, const real* __restrict__ raw,
+                                                        bool state_only, real* __restrict__ c_out, int64_t n, int64_t i) {
+    constexpr int NX = Dims<KIND>::NX;
+    bool violated = false;
+    real* p = c_out + i;
+    const int strict = h.crow_strict;
+    for (int r = 0; r < h.n_crows; ++r, p += n) {
+        const int src = h.crow_src[r];
+        if (src >= NX && state_only) continue;
+        const real x = src < NX ? st[src] : raw[src - NX];
+        const real b = h.crow_bound[r];
+        const real c = h.crow_sgn[r] > 0 ? x - b : b - x;
+        *p = round8(c);
+        violated |= viol_test(c, strict);
+    }
+    return violated ? 1u : 0u;
+}
+
 // The in-loop part: the violation flag of bounded / default constraints that merge into one box per dimension
 // (no tolerances, one strictness -- CFG_COLD_CONSTRAINTS clear); anything else, and every call that wants the
 // rounded values, is delegated to constraint_values_cold.
@@ -378,7 +400,8 @@ SCG_DEV void eval_constraints(const Hot<real>& h, const Cold<real>* __restrict__
         for (int d = 0; d < NX; ++d) sl[d] = st[d];
 #pragma unroll
         for (int d = 0; d < NU; ++d) rl[d] = raw[d];
-        const uint32_t bits = constraint_values_cold<KIND, real>(h, cold, sl, rl, state_only, c_out, n, i);
+        const uint32_t bits = (c_out != nullptr && h.n_crows > 0) ? constraint_values_flat<KIND, real>(h, sl, rl, state_only, c_out, n, i)
+                                                                 : constraint_values_cold<KIND, real>(h, cold, sl, rl, state_only, c_out, n, i);
         violated = (bits & 1u) != 0u; almost = (bits & 2u) != 0u;
         return;
     }
