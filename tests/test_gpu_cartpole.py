@@ -85,3 +85,25 @@ def test_cartpole_rollout_equals_stepping():
     sa, sb = a.stats(), b.stats()
     assert sa["env_steps"] == sb["env_steps"] == n * k and sa["episodes"] == sb["episodes"] > 0
     a.close(); b.close()
+
+
+def test_cartpole_queued_rollout_equals_static_rollout():
+    """The ready-list queue on the CartPole kernel (LEAN with the general spare: randomised inertia, white noise per
+    step): forced queue == static grid bit for bit, on a ragged batch, across two launches."""
+    from safe_control_gym_b200.envs.cartpole import BatchedCartPole
+    n, k = 3000, 150
+    acts = torch.randn(k, n, 1, generator=torch.Generator().manual_seed(11)).mul_(3.0).cuda()
+    a = BatchedCartPole(num_envs=n, dtype=torch.float32, auto_reset=True, **CFG)
+    b = BatchedCartPole(num_envs=n, dtype=torch.float32, auto_reset=True, **CFG)
+    a.set_rollout_queue(1, 48); b.set_rollout_queue(0)
+    a.reset(); b.reset()
+    for _ in range(2):
+        a.rollout(acts); b.rollout(acts)
+        torch.cuda.synchronize()
+        assert a.last_rollout_queued and not b.last_rollout_queued
+        for name in ("state", "ctrl_step", "episode", "flags", "obs", "ep_return", "ep_length", "inertia"):
+            assert torch.equal(getattr(a, "buf_" + name), getattr(b, "buf_" + name)), name
+    sa, sb = a.stats(), b.stats()
+    assert sa["env_steps"] == 2 * n * k and sa["episodes"] == sb["episodes"] > 0 and sa["violation_steps"] == sb["violation_steps"]
+    assert abs(sa["return"] - sb["return"]) <= 1e-9 * abs(sb["return"])
+    a.close(); b.close()

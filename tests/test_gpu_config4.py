@@ -61,3 +61,24 @@ def test_config4_matches_oracle(dtype, tol):
     assert resets >= 5   # episodes are 60 steps long: every lane restarts at least twice, with new mass / offsets
     print(f"config 4 {dtype}: worst rel err {worst:.2e}, {resets} auto-resets")
     env.close()
+
+
+def test_config4_queued_rollout_equals_static_rollout():
+    """The ready-list queue on the 2D LEAN kernel with impulse + step disturbances and per-episode mass / inertia (offsets
+    and inertial properties travel through the buffers between ranges): forced queue == static grid bit for bit."""
+    from safe_control_gym_b200.envs.quadrotor import BatchedQuadrotor
+    n, k = 2500, 140
+    acts = (0.16 + 0.01 * torch.randn(k, n, 2, generator=torch.Generator().manual_seed(3))).cuda()
+    a = BatchedQuadrotor(num_envs=n, dtype=torch.float32, auto_reset=True, **CFG)
+    b = BatchedQuadrotor(num_envs=n, dtype=torch.float32, auto_reset=True, **CFG)
+    a.set_rollout_queue(1, 32); b.set_rollout_queue(0)
+    a.reset(); b.reset()
+    for _ in range(2):
+        a.rollout(acts); b.rollout(acts)
+        torch.cuda.synchronize()
+        assert a.last_rollout_queued and not b.last_rollout_queued
+        for name in ("state", "ctrl_step", "episode", "flags", "obs", "ep_return", "ep_length", "inertia", "dist_offset"):
+            assert torch.equal(getattr(a, "buf_" + name), getattr(b, "buf_" + name)), name
+    sa, sb = a.stats(), b.stats()
+    assert sa["env_steps"] == 2 * n * k and sa["episodes"] == sb["episodes"] > 0
+    a.close(); b.close()
