@@ -950,6 +950,10 @@ k_reset(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold
 // rollout_range runs control steps [k0, k1) of env i: state from / to Buf, exactly what a launch of k1 - k0 steps does
 // (a K-step rollout equals any split of it into launches).  Statistics go to the caller's shared-memory columns
 // acc[j * ACC_LD], j < N_ACC, which the kernel reduces once at its end.
+#ifndef SCG_SPARE_CADENCE
+#define SCG_SPARE_CADENCE 16
+#endif
+constexpr int SPARE_CADENCE = SCG_SPARE_CADENCE;   // control steps between the warp-wide spare refills (power of two)
 constexpr int ACC_LD = ENV_BLOCK + 1;   // column ENV_BLOCK is the scratch column of out-of-range lanes
 constexpr int N_ACC = 11;   // episodes, return, length, truncated, completed, violated episodes, violation steps, (mse: double column), env steps, gates, collisions
 template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN, bool SPEC>
@@ -1069,7 +1073,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
             // region.  One inline copy of the draw: at the cadence every lane that used its spare refills it together;
             // a lane that ends two episodes inside one period draws on the spot.
             const bool restart = done && (cfg & CFG_AUTO_RESET) != 0u;
-            const bool cadence = ahead && ((k - k0) & 15) == 0;   // uniform
+            const bool cadence = ahead && ((k - k0) & (SPARE_CADENCE - 1)) == 0;   // uniform
             if (bool(int(!spare_ok) & (int(restart) | int(cadence)))) {
                 const uint32_t next_ep = (cfg & CFG_RESEED) ? 0u : uint32_t(e.resets);
                 if (!PLAIN && (cfg & CFG_RESET_EXTRAS)) draw_spare_general<KIND, real, ATT>(h, cold, key, next_ep, sp);
