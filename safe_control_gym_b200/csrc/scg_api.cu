@@ -374,6 +374,7 @@ extern "C" int scg_create(const scg_config* cfg, scg_env** out) {
     e->cfg.x_goal = nullptr;   // host table was copied; do not keep the caller's pointer
     if (const char* q = getenv("SCG_QUEUE")) { const int m = atoi(q); e->queue_mode = m < 0 ? -1 : (m > 0 ? 1 : 0); }
     if (const char* q = getenv("SCG_QUEUE_SLEEP")) { const int c = atoi(q); if (c >= 0) e->queue_sleep_ns = unsigned(c); }
+    if (const char* q = getenv("SCG_QUEUE_BLOCKS_PER_SM")) { const int c = atoi(q); if (c >= 0) e->queue_blocks_per_sm = c; }
     if (const char* q = getenv("SCG_QUEUE_CHUNK")) { const int c = atoi(q); e->queue_chunk = c > 0 ? c : 0; }
     *out = e;
     return SCG_OK;

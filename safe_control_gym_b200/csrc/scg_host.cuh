@@ -31,6 +31,7 @@ struct scg_env {
     int queue_mode = -1;           // -1 auto, 0 off, 1 on (SCG_QUEUE)
     int queue_chunk = 0;           // 0 auto (SCG_QUEUE_CHUNK)
     unsigned queue_sleep_ns = 500; // poll interval of a block that waits for its ticket's predecessor (SCG_QUEUE_SLEEP)
+    int queue_blocks_per_sm = 8;   // workers of a queued launch per SM (0: every resident slot); 8 x 148 for 1,024 env blocks measured best
     int last_queue = 0;            // the last rollout launch went through the queue (scg_last_rollout_queue)
 };
 

@@ -950,6 +950,10 @@ k_reset(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold
 // rollout_range runs control steps [k0, k1) of env i: state from / to Buf, exactly what a launch of k1 - k0 steps does
 // (a K-step rollout equals any split of it into launches).  Statistics go to the caller's shared-memory columns
 // acc[j * ACC_LD], j < N_ACC, which the kernel reduces once at its end.
+#ifndef SCG_BLOCKS_PER_SM
+#define SCG_BLOCKS_PER_SM 9   // resident 64-thread blocks per SM the SPEC rollout kernels are bounded for (96 registers, no spill); the other fp32
+                              // kernels: 8 (128 registers) -- at 96 the PLAIN kernel with per-step outputs spills and the single step goes 21 -> 29 us
+#endif
 #ifndef SCG_SPARE_CADENCE
 #define SCG_SPARE_CADENCE 16
 #endif
@@ -1197,7 +1201,7 @@ SCG_DEV void st_release_gpu(int32_t* p, int32_t v) { asm volatile("st.release.gp
 // sleep, and a scheduler that runs ahead simply takes more ranges (same result: the split into ranges is invisible, see
 // rollout_range).
 template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN = false, bool SPEC = false, bool QUEUE = false>
-__global__ void __launch_bounds__(ENV_BLOCK, sizeof(real) == 4 ? 512 / ENV_BLOCK : 1)
+__global__ void __launch_bounds__(ENV_BLOCK, sizeof(real) == 4 ? (SPEC ? SCG_BLOCKS_PER_SM : 8) : 1)
 k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, const Buf<real> b, const Roll<real> ro) {
     __shared__ float acc_buf[N_ACC * ACC_LD];
     __shared__ double mse_buf[2 * ACC_LD];   // fp64 columns: mse sum, return sum
