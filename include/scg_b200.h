@@ -71,7 +71,7 @@ enum { SCG_SYM_FC = 0, SCG_SYM_FD_RK4 = 1, SCG_SYM_DF = 2, SCG_SYM_LOSS = 3, SCG
 #define SCG_INFO_GATE_PASSED 0x08u  /* stepped_through_gate          */
 #define SCG_INFO_AT_GOAL     0x10u  /* info["at_goal_position"]      */
 #define SCG_INFO_COMPLETED   0x20u  /* info["task_completed"]        */
-#define SCG_INFO_GOAL_REACHED 0x40u /* info["goal_reached"]          */
+#define SCG_INFO_GOAL_REACHED 0x40u /* info["goal_reached"]: the PREVIOUS step's flag (the reference's _get_info runs before _get_done) */
 #define SCG_INFO_OUT_OF_BOUND 0x80u /* out-of-bound termination      */
 
 /* layout of the per-env packed "flags" word kept between steps */
@@ -79,6 +79,7 @@ enum { SCG_SYM_FC = 0, SCG_SYM_FD_RK4 = 1, SCG_SYM_DF = 2, SCG_SYM_LOSS = 3, SCG
 #define SCG_FLAG_AT_GOAL         0x2u
 #define SCG_FLAG_FLIPPED         0x4u  /* 2D: Euler fold left roll = yaw = pi */
 #define SCG_FLAG_COMPLETED       0x8u
+#define SCG_FLAG_GOAL_REACHED    0x10u /* goal_reached of the previous _get_done (quadrotor.py:965, read at :1013 one step later) */
 #define SCG_FLAG_GATE_SHIFT 8          /* bits 8..15  current_gate       */
 #define SCG_FLAG_HOLD_SHIFT 16         /* bits 16..31 steps_at_goal_pos  */
 
@@ -234,6 +235,9 @@ int scg_destroy(scg_env* env);
 int scg_bind_buffers(scg_env* env, const scg_buffers* buf);
 /* update injected-draw pointers / adversary pointer between calls (cheap, host only) */
 int scg_set_injection(scg_env* env, int channel, int k, const void* dev_ptr);
+/* BenchmarkEnv.seed(seed) (benchmark_env.py:220-235) after construction: every later reset / disturbance draw is keyed
+ * by (seed, global env id).  Host only, takes effect with the next launch. */
+int scg_set_seed(scg_env* env, uint32_t seed);
 /* Quadrotor.reset() (quadrotor.py:356-504): mask = NULL resets every env, else envs with
  * mask[i] != 0.  inject_* optional device tensors of pre-drawn additive offsets:
  * init [nx][n], inertia [4][n], dist offsets [slots][n]. */

@@ -423,6 +423,11 @@ class QuadOracle:
         self.initial_reset = False
         self.INFO_IN_RESET = info_in_reset
         self.cnstr_violation = False  # benchmark_env.py:218 -- NOT cleared by reset()
+        # F10: step() calls _get_info() before _get_done() (quadrotor.py:553-555) and _get_info reads self.goal_reached
+        # (:1013), which only _get_done assigns (:965) -- an AttributeError on the first step as shipped.  Minimal
+        # reading: False until the first _get_done; info["goal_reached"] is then the PREVIOUS step's flag and
+        # survives reset() (nothing clears it).
+        self.goal_reached = False
         self.episode = -1
         # ---- Quadrotor.__init__ post-super part (quadrotor.py:206-354)
         labels = STATE_LABELS[self.QUAD_TYPE]
@@ -541,6 +546,12 @@ class QuadOracle:
                 pt, vt = transform_trajectory(pos, vel, ti["proj_point"], ti["proj_normal"])
                 self.X_GOAL = np.vstack([pt[:, 0], vt[:, 0], pt[:, 1], vt[:, 1], pt[:, 2], vt[:, 2],
                                          z, z, z, z, z, z]).T
+
+    def set_cost_function_param(self, Q, R):
+        """benchmark_env.py:237-254."""
+        if self.initial_reset:
+            raise RuntimeError("[ERROR] env.set_cost_function_param() cannot be called after the first reset of the environment.")
+        self.Q, self.R = np.asarray(Q, dtype=float), np.asarray(R, dtype=float)
 
     def set_adversary_control(self, action):
         """benchmark_env.py:256-266 (adversary_action_space = Box(-1, 1))."""

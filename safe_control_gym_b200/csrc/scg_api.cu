@@ -313,6 +313,13 @@ extern "C" int scg_set_rollout_queue(scg_env* env, int32_t mode, int32_t chunk_s
     return SCG_OK;
 }
 extern "C" int scg_last_rollout_queue(const scg_env* env) { return env ? env->last_queue : 0; }
+// BenchmarkEnv.seed (benchmark_env.py:220-235): the Philox key of every later draw.  The constant block travels by value
+// with each launch, so the host copy is all there is to patch.
+extern "C" int scg_set_seed(scg_env* env, uint32_t seed) {
+    if (!env) return scg_fail(SCG_ERR_NULL, "scg_set_seed: null env");
+    env->cfg.seed = seed; env->hf.seed = seed; env->hd.seed = seed;
+    return SCG_OK;
+}
 extern "C" const char* scg_last_error(void) { return g_err.c_str(); }
 extern "C" const char* scg_version(void) { return "scg_b200 0.1 (sm_100a)"; }
 extern "C" int64_t scg_launch_count(const scg_env* env) { return env ? env->launches : 0; }
@@ -549,7 +556,12 @@ extern "C" int scg_rollout_host(scg_env* e, const void* host_actions, int32_t k_
     }
     if (need > e->stage_bytes) {
         CU(cudaStreamSynchronize(e->copy_stream));
-        for (int j = 0; j < 2; ++j) { if (e->stage[j]) CU(cudaFree(e->stage[j])); CU(cudaMalloc(&e->stage[j], need)); }
+        for (int j = 0; j < 2; ++j) {
+            if (e->stage_used[j]) CU(cudaEventSynchronize(e->ev_consumed[j]));   // the old buffer may still be read
+            if (e->stage[j]) CU(cudaFree(e->stage[j]));
+            CU(cudaMalloc(&e->stage[j], need));
+            e->stage_used[j] = false;
+        }
         e->stage_bytes = need;
     }
     const char* src = static_cast<const char*>(host_actions);
@@ -557,13 +569,17 @@ extern "C" int scg_rollout_host(scg_env* e, const void* host_actions, int32_t k_
     for (int k0 = 0; k0 < k_steps; k0 += chunk_steps, ++chunk) {
         const int ks = k_steps - k0 < chunk_steps ? k_steps - k0 : chunk_steps;
         const int s = chunk & 1;
-        if (chunk >= 2) CU(cudaStreamWaitEvent(e->copy_stream, e->ev_consumed[s], 0));
+        // a slot is rewritten only after its last consumer -- of this call or of an earlier one -- has run
+        if (e->stage_used[s]) CU(cudaStreamWaitEvent(e->copy_stream, e->ev_consumed[s], 0));
         CU(cudaMemcpyAsync(e->stage[s], src + size_t(k0) * step_bytes, step_bytes * ks, cudaMemcpyHostToDevice, e->copy_stream));
         CU(cudaEventRecord(e->ev_copied[s], e->copy_stream));
         CU(cudaStreamWaitEvent(st, e->ev_copied[s], 0));
         int rc = run_steps(e, e->stage[s], ks, nullptr, nullptr, nullptr, 1, 0, st);
+        // recorded on failure too: whatever was enqueued on `st` so far orders the next copy into this slot
+        const cudaError_t ce = cudaEventRecord(e->ev_consumed[s], st);
+        e->stage_used[s] = true;
         if (rc != SCG_OK) return rc;
-        CU(cudaEventRecord(e->ev_consumed[s], st));
+        CU(ce);
     }
     return SCG_OK;
 }

@@ -23,6 +23,7 @@ struct scg_env {
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};
     void* stage[2] = {nullptr, nullptr};
+    bool stage_used[2] = {false, false};   // ev_consumed[j] has been recorded: the next copy into slot j waits for it
     size_t stage_bytes = 0;
     // time-chunk queue of the fused rollout (scg_step.cuh: k_rollout<..., QUEUE>)
     int32_t* q_mem = nullptr;      // [2 + ranges]: pop counter, push counter, ready list

@@ -43,7 +43,7 @@ static bool launch_queued(scg_env* e, K kernel, bool plain, const int64_t n, int
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, ENV_BLOCK, 0) != cudaSuccess || occ < 1) return false;
     if (e->queue_blocks_per_sm > 0 && occ > e->queue_blocks_per_sm) occ = e->queue_blocks_per_sm;   // fewer workers than resident slots (SCG_QUEUE_BLOCKS_PER_SM)
     const int64_t resident = int64_t(occ) * e->n_sms, env_blocks = (n + ENV_BLOCK - 1) / ENV_BLOCK;
-    if (e->queue_mode < 0 && (env_blocks > 6 * resident || env_blocks * 2 < resident || env_blocks == resident)) return false;
+    if (e->queue_mode < 0 && (env_blocks > 6 * resident || env_blocks * 2 < resident || env_blocks % resident == 0)) return false;   // whole waves: nothing to balance
     int chunk = e->queue_chunk > 0 ? e->queue_chunk : 64;
     if (chunk > k_steps) chunk = k_steps;
     const int64_t chunks = (k_steps + chunk - 1) / chunk, tickets = chunks * env_blocks;

@@ -31,6 +31,7 @@ template <int KIND, typename real> struct EnvRegs {
     int32_t resets;      // number of resets so far (episode index = resets - 1)
     // SCG_FLAG_* of the flags buffer, unpacked while the env lives in registers (2D's fold bit is a2.flipped)
     bool viol, at_goal, completed;
+    bool goal_prev;      // goal_reached of the previous _get_done (info["goal_reached"] lags one step, F10); survives reset
     uint32_t gate, hold;
     Inertia<real> in;
     Att3<real> a3;       // 3D
@@ -66,6 +67,7 @@ template <int KIND, typename real> SCG_DEV void unpack_flags(EnvRegs<KIND, real>
     e.viol = (f & SCG_FLAG_CNSTR_VIOLATION) != 0u;
     e.at_goal = (f & SCG_FLAG_AT_GOAL) != 0u;
     e.completed = (f & SCG_FLAG_COMPLETED) != 0u;
+    e.goal_prev = (f & SCG_FLAG_GOAL_REACHED) != 0u;
     e.a2.flipped = (f & SCG_FLAG_FLIPPED) ? 1u : 0u;
     e.gate = (f >> SCG_FLAG_GATE_SHIFT) & 0xFFu;
     e.hold = f >> SCG_FLAG_HOLD_SHIFT;
@@ -73,7 +75,7 @@ template <int KIND, typename real> SCG_DEV void unpack_flags(EnvRegs<KIND, real>
 
 template <int KIND, typename real> SCG_DEV uint32_t pack_flags(const EnvRegs<KIND, real>& e) {
     uint32_t f = (e.viol ? SCG_FLAG_CNSTR_VIOLATION : 0u) | (e.at_goal ? SCG_FLAG_AT_GOAL : 0u) |
-                 (e.completed ? SCG_FLAG_COMPLETED : 0u) | (e.gate << SCG_FLAG_GATE_SHIFT) | (e.hold << SCG_FLAG_HOLD_SHIFT);
+                 (e.completed ? SCG_FLAG_COMPLETED : 0u) | (e.goal_prev ? SCG_FLAG_GOAL_REACHED : 0u) | (e.gate << SCG_FLAG_GATE_SHIFT) | (e.hold << SCG_FLAG_HOLD_SHIFT);
     if (KIND == SCG_QUAD_2D && e.a2.flipped) f |= SCG_FLAG_FLIPPED;
     return f;
 }
@@ -748,10 +750,15 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
     // ---- _get_done (quadrotor.py:956-1002)
     done = false;
     if ((cfg & (CFG_STAB | CFG_COST_QUAD)) == (CFG_STAB | CFG_COST_QUAD)) {
+        // _get_info ran BEFORE this _get_done (quadrotor.py:553-555): info["goal_reached"] is the previous step's flag (F10)
+        // (the cart-pole, absent from this fork, follows the upstream order: _get_done first, the flag is this step's)
+        if (KIND != SCG_CARTPOLE && e.goal_prev) info |= SCG_INFO_GOAL_REACHED;
         real nn = real(0);
 #pragma unroll
         for (int d = 0; d < NX; ++d) { const real er = st[d] - h.x_goal0[d]; nn += er * er; }
-        if (m_sqrt(nn) < h.goal_tol) { done = true; info |= SCG_INFO_GOAL_REACHED; }
+        e.goal_prev = m_sqrt(nn) < h.goal_tol;
+        if (e.goal_prev) done = true;
+        if (KIND == SCG_CARTPOLE && e.goal_prev) info |= SCG_INFO_GOAL_REACHED;
     }
     if (cfg & CFG_OOB) {
         bool oob = false;
@@ -963,13 +970,14 @@ constexpr int N_ACC = 11;   // episodes, return, length, truncated, completed, v
 template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN, bool SPEC>
 SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ cold, const Buf<real>& b, const Roll<real>& ro,
                            const int64_t i, const int k0, const int k1, float* const ep_acc, double* const mse_acc, real* const sp) {
-    ep_acc[1 * ACC_LD] = 0.f;   // return of the episodes that end in this range: summed in fp32 per range, in fp64 across ranges
     constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
     const int64_t n = b.n;
-    const bool valid = i < n;
-    // out-of-range lanes shadow the last env: they compute and store the same values as its owner
-    // (benign duplicates) and only stay out of the statistics
-    const int64_t ii = valid ? i : n - 1;
+    // Out-of-range lanes of the last env block take no part: every global side effect of the loop (state, PID memory,
+    // disturbance offsets, per-step outputs) belongs to exactly one lane.  The callers' block barriers and the final
+    // warp reduction sit outside this function, where the warp has reconverged.
+    if (i >= n) return;
+    ep_acc[1 * ACC_LD] = 0.f;   // return of the episodes that end in this range: summed in fp32 per range, in fp64 across ranges
+    const int64_t ii = i;
     const RngKey key{h.seed, h.env_id_base_lo + uint32_t(ii)};
     EnvRegs<KIND, real> e;
 #pragma unroll
@@ -1254,11 +1262,15 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
         const int slot[11] = {SCG_STAT_EPISODES, SCG_STAT_RETURN, SCG_STAT_LENGTH, SCG_STAT_VIOLATION_STEPS,
                               SCG_STAT_MSE, SCG_STAT_TRUNCATED, SCG_STAT_COMPLETED, SCG_STAT_VIOLATED_EPISODES, SCG_STAT_ENV_STEPS,
                               SCG_STAT_GATES, SCG_STAT_COLLISIONS};
+        // per-thread counts are exact in fp32 (<= 2^24 control steps per launch and thread); their sum over a warp is
+        // formed in fp64 so that it stays exact for any launch length
 #pragma unroll
         for (int j = 0; j < NS; ++j) {
             if (slot[j] == SCG_STAT_MSE || slot[j] == SCG_STAT_RETURN) continue;
-            const float r = warp_sum(v[j]);
-            if ((threadIdx.x & 31) == 0 && r != 0.f) atomicAdd(b.stats + slot[j], double(r));
+            double r = double(v[j]);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+            if ((threadIdx.x & 31) == 0 && r != 0.0) atomicAdd(b.stats + slot[j], r);
         }
         double m = mse_buf[threadIdx.x], r = mse_buf[ACC_LD + threadIdx.x];
 #pragma unroll

@@ -101,7 +101,8 @@ class BatchedEnvBase:
         self._obs_view = self.buf_obs.t()
         self._bind()
         self.initial_reset = False
-        self._keep = []   # tensors referenced by in-flight launches (injection buffers)
+        self._keep = []        # reset()'s temporaries: alive until the next reset
+        self._inject_keep = {}   # (channel, k) -> the injection tensor the device block points at
 
     def _bind(self, with_step_outputs=True):
         b = L.Buffers()
@@ -164,10 +165,13 @@ class BatchedEnvBase:
         ch = {"observation": L.CH_OBSERVATION, "action": L.CH_ACTION, "dynamics": L.CH_DYNAMICS}[channel]
         if tensor is None:
             L.check(self.lib.scg_set_injection(self._h, ch, k, None))
+            self._inject_keep.pop((ch, k), None)
             return
         t = self._as_real(tensor)
-        self._keep.append(t)
         L.check(self.lib.scg_set_injection(self._h, ch, k, C.c_void_p(t.data_ptr())))
+        # the device block keeps the pointer until it is replaced: so does this dict (the previous tensor of the slot may
+        # still be read by a launch in flight on this stream; torch's caching allocator orders its reuse behind that)
+        self._inject_keep[(ch, k)] = t
 
     # ------------------------------------------------------------------ reset / step
     def _info_from_buffers(self, reset=False):

@@ -358,6 +358,9 @@ class BatchedQuadrotor(BatchedEnvBase):
         self.np_random = np.random.RandomState(None if seed is None else int(seed) % (2 ** 32))
         self._seed_value = 0 if seed is None else int(seed) % (2 ** 32)
         self.action_space.seed(seed)
+        if getattr(self, "_h", None) is not None and self._h.value:   # after construction: re-key the device draws
+            L.check(self.lib.scg_set_seed(self._h, self._seed_value))
+            self._cfg.seed = self._seed_value
         return [seed]
 
     def set_cost_function_param(self, Q, R):

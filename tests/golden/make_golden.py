@@ -125,7 +125,76 @@ def scenarios():
                gates=[[5.0, 5.0, 0, 0, 0, 0, 0]])
     out["quad3d_tracking"] = dict(cfg=cfg, actions=hover_actions(rng, 90, 4, std=0.01),
                                   adv=rng.uniform(-1.5, 1.5, size=(90, 4)))
+    # ---- round 2.  Closed-loop scenarios: the actions come from the DSL PID (oracle/pid_oracle.py, pinned to the
+    # reference's PIDController by pid_controller.npz) fed with the reference env's own observations, plus seeded
+    # noise; what is recorded is the action sequence actually applied, so replays are open loop like the others.
+    rng2 = np.random.default_rng(2024)
+    # 7: cost "quadratic", stabilisation: reward = -SymbolicModel.loss (quadrotor.py:915-922) with a non-identity
+    #    diagonal Q / R (set_cost_function_param), and the goal_reached termination (quadrotor.py:963-967): the PID
+    #    brings the full 12-state within the tolerance ball, the episode ends, a second one follows (F10: the flag of
+    #    info["goal_reached"] lags by one step and survives the reset).
+    cfg = dict(physics="dyn", quad_type=3, ctrl_freq=60, pyb_freq=240, seed=17, episode_len_sec=6, cost="quadratic",
+               task="stabilization", task_info=dict(stabilization_goal=[0.2, -0.1, 1.0], stabilization_goal_tolerance=0.12),
+               init_state=dict(init_x=0.2, init_y=-0.1, init_z=1.3), randomized_init=True,
+               init_state_randomization_info={k: dict(distrib="uniform", low=-w, high=w) for k, w in
+                                              [("init_x", 0.05), ("init_y", 0.05), ("init_z", 0.05), ("init_theta", 0.02)]},
+               constraints=[dict(constraint_form="default_constraint", constrained_variable="input"),
+                            dict(constraint_form="bounded_constraint", constrained_variable="state", active_dims=[4, 5],
+                                 lower_bounds=[0.5, -1.0], upper_bounds=[1.6, 1.0])],
+               done_on_out_of_bound=True, info_in_reset=True)
+    out["quad3d_quadratic_stab"] = dict(cfg=cfg, steps=400, stop_after_dones=2, tail=12,
+                                        QR=(np.diag(0.5 * np.arange(1.0, 13.0)), np.diag([0.1, 0.2, 0.3, 0.4])),
+                                        policy=pid_policy(rng2, 0.0001, lambda env: ([0.2, -0.1, 1.0], [0, 0, 0])))
+    # 8: cost "quadratic", trajectory tracking: the reward reads X_GOAL[ctrl_step_counter] un-clamped
+    #    (quadrotor.py:924-930) with dense (off-diagonal, symmetric) Q and R; runs into the time limit and on into a
+    #    second episode.
+    Qd = np.diag(np.linspace(2.0, 0.2, 12))
+    Qd[0, 1] = Qd[1, 0] = 0.3; Qd[4, 5] = Qd[5, 4] = -0.2; Qd[2, 7] = Qd[7, 2] = 0.15; Qd[6, 9] = Qd[9, 6] = 0.05
+    Rd = np.diag([1.0, 0.5, 2.0, 1.5]); Rd[0, 3] = Rd[3, 0] = 0.25; Rd[1, 2] = Rd[2, 1] = -0.4
+    cfg = dict(physics="dyn", quad_type=3, ctrl_freq=60, pyb_freq=240, seed=23, episode_len_sec=1, cost="quadratic",
+               task="traj_tracking", task_info=dict(trajectory_type="figure8", num_cycles=1, trajectory_plane="xz",
+                                                    trajectory_position_offset=[0.0, 1.0], trajectory_scale=0.3,
+                                                    proj_point=[0, 0, 1.0], proj_normal=[0, 1, 1]),
+               init_state=dict(init_x=0.0, init_y=0.0, init_z=1.0), randomized_init=True,
+               init_state_randomization_info={k: dict(distrib="uniform", low=-w, high=w) for k, w in
+                                              [("init_x", 0.05), ("init_z", 0.05), ("init_phi", 0.05), ("init_psi", 0.1)]},
+               done_on_out_of_bound=True, gates=[[5.0, 5.0, 0, 0, 0, 0, 0]])
+    out["quad3d_quadratic_track"] = dict(cfg=cfg, steps=85, QR=(Qd, Rd),
+                                         policy=pid_policy(rng2, 0.001, lambda env: track_target(env)))
+    # 9: level0 + physics=dyn for 140 control steps WITHOUT a reset (north_star: "trajectory agreement reported over 100
+    #    steps"): the PID flies from the start pad towards the first gate, every constraint stays inactive.
+    out["level0_dyn_long"] = dict(cfg=level0(ctrl_freq=60, pyb_freq=240), steps=140, expect_dones=0,
+                                  policy=pid_policy(rng2, 0.0005, lambda env: ([-0.6, -2.7, 0.8], [0, 0, 0])))
+    # 10: competition/level2.yaml unchanged (+ physics=dyn at 60/240): randomized_gates_and_obstacles +
+    #     randomized_inertial_prop + randomized init pin the ORDER of the reset draws -- obstacles, gates, inertial
+    #     properties, initial state (quadrotor.py:371-488) -- over three episodes (raw actions below the input bound
+    #     end the first two).  The poses the reference hands to loadURDF and EFFECTIVE_GATES_POSITIONS are recorded.
+    cfg = yaml.safe_load(open(os.path.join(REF, "competition/level2.yaml")))["quadrotor_config"]
+    cfg.pop("gui", None); cfg.pop("camera_view", None)
+    cfg.update(physics="dyn", ctrl_freq=60, pyb_freq=240)
+    a = hover_actions(rng2, 45, 4, std=0.002, lo=0.03, hi=0.145)
+    a[14] = 0.0; a[29, 2] = 0.01
+    out["level2_dyn"] = dict(cfg=cfg, actions=a)
     return out
+
+
+def pid_policy(rng, noise_std, target_fn):
+    """action(env, obs) = DSL PID thrusts towards target_fn(env) + N(0, noise_std^2), clipped to the action space."""
+    from oracle.pid_oracle import PIDOracle
+    pid = PIDOracle(m=0.03454)   # the env's mass (the class default is the CF2.x 0.027 kg)
+
+    def policy(env, obs, fresh):
+        if fresh:
+            pid.reset()
+        tp, tv = target_fn(env)
+        a = pid.thrusts_3d(env.CTRL_TIMESTEP, np.asarray(obs)[:12], tp, tv) + rng.normal(0, noise_std, size=4)
+        return np.clip(a, env.action_space.low.astype(np.float64), env.action_space.high.astype(np.float64))
+    return policy
+
+
+def track_target(env):
+    row = env.X_GOAL[min(env.ctrl_step_counter, env.X_GOAL.shape[0] - 1)]
+    return [row[0], row[2], row[4]], [row[1], row[3], row[5]]
 
 
 def run(name, spec, Quadrotor):
@@ -133,7 +202,10 @@ def run(name, spec, Quadrotor):
     kwargs = {k: v for k, v in cfg.items()}
     ref_stubs.DRAW_LOG.clear()
     env = Quadrotor(**kwargs)
-    ev = {k: [] for k in ["type", "obs", "rew", "done", "viol", "trunc", "mse", "cvals", "state", "kin", "quat", "ndraw"]}
+    if "QR" in spec:   # benchmark_env.py:237-254, before the first reset
+        env.set_cost_function_param(np.array(spec["QR"][0], dtype=float), np.array(spec["QR"][1], dtype=float))
+    ev = {k: [] for k in ["type", "obs", "rew", "done", "viol", "trunc", "mse", "cvals", "state", "kin", "quat", "ndraw", "goal"]}
+    rs = {k: [] for k in ["gates", "obstacles", "inertia"]}   # per reset: what the draws turned into
     nc = env.num_constraints
 
     def record(kind, obs, rew, done, info):
@@ -144,6 +216,7 @@ def run(name, spec, Quadrotor):
         ev["viol"].append(int(info.get("constraint_violation", -1)))
         ev["trunc"].append(int(info.get("TimeLimit.truncated", -1)))
         ev["mse"].append(float(info.get("mse", np.nan)))
+        ev["goal"].append(int(info["goal_reached"]) if "goal_reached" in info else -1)
         c = np.full(max(nc, 1), np.nan)
         if "constraint_values" in info:
             v = np.asarray(info["constraint_values"], dtype=np.float64)
@@ -160,15 +233,41 @@ def run(name, spec, Quadrotor):
         if not env.INFO_IN_RESET and env.constraints is not None:
             info = {"constraint_values": env.constraints.get_values(env, only_state=True)}
         record(0, obs, 0.0, False, info)
+        import pybullet as fake
+        from oracle import bullet_math as bm
+        rs["gates"].append(np.array(env.EFFECTIVE_GATES_POSITIONS, dtype=np.float64).reshape(len(env.GATES), 6))
+        ob = []
+        for i in env.OBSTACLES_IDS:   # pose handed to loadURDF (quadrotor.py:385-388): position + yaw of the quaternion
+            b = fake.bodies[i]
+            ob.append(list(b["pos"]) + [bm.euler_from_quat(b["quat"])[2]])
+        rs["obstacles"].append(np.array(ob, dtype=np.float64).reshape(len(env.OBSTACLES), 4))
+        rs["inertia"].append(np.array([env.OVERRIDDEN_QUAD_MASS] + list(env.OVERRIDDEN_QUAD_INERTIA), dtype=np.float64))
+        return obs
 
-    do_reset()
-    for t, a in enumerate(spec["actions"]):
+    obs = do_reset()
+    applied, dones, fresh, stop_at = [], 0, True, None
+    steps = len(spec["actions"]) if "actions" in spec else spec["steps"]
+    for t in range(steps):
+        if stop_at is not None and t >= stop_at:
+            break
+        a = np.array(spec["actions"][t]) if "actions" in spec else spec["policy"](env, obs, fresh)
+        fresh = False
+        applied.append(np.array(a, dtype=np.float64))
         if "adv" in spec:
             env.set_adversary_control(spec["adv"][t])
         obs, rew, done, info = env.step(np.array(a))
         record(1, obs, rew, done, info)
         if done:  # DummyVecEnv.step_wait auto-reset (dummy_vec_env.py:38-49)
-            do_reset()
+            obs = do_reset()
+            dones += 1
+            fresh = True
+            if dones == spec.get("stop_after_dones", -1):
+                stop_at = t + 1 + spec.get("tail", 0)
+    if "expect_dones" in spec:
+        assert dones == spec["expect_dones"], (name, dones)
+    if "stop_after_dones" in spec:
+        assert dones >= spec["stop_after_dones"], (name, dones)
+    spec = dict(spec, actions=np.array(applied))
     draws = list(ref_stubs.DRAW_LOG)
     flat = np.concatenate([d[1].reshape(-1) for d in draws]) if draws else np.zeros(0)
     out = dict(config_json=np.array(json.dumps(cfg)), actions=np.asarray(spec["actions"], dtype=np.float64),
@@ -179,6 +278,10 @@ def run(name, spec, Quadrotor):
                state_low=env.state_space.low, state_high=env.state_space.high)
     if "adv" in spec:
         out["adv"] = np.asarray(spec["adv"], dtype=np.float64)
+    if "QR" in spec:
+        out["Q"], out["R"] = np.array(spec["QR"][0], dtype=np.float64), np.array(spec["QR"][1], dtype=np.float64)
+    for k, v in rs.items():
+        out["reset_" + k] = np.array(v)
     for k, v in ev.items():
         out["ev_" + k] = np.array(v)
     np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
@@ -188,5 +291,7 @@ def run(name, spec, Quadrotor):
 
 if __name__ == "__main__":
     Quadrotor = ref_stubs.install(REF)
+    only = sys.argv[1:]
     for name, spec in scenarios().items():
-        run(name, spec, Quadrotor)
+        if not only or name in only:
+            run(name, spec, Quadrotor)

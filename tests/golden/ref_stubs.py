@@ -10,8 +10,11 @@ casadi / matplotlib installed.  Nothing here ships, nothing here is read on the 
 * ``gym``: ``Env``, ``spaces.Box`` (float32 casting as gym 0.21) and
   ``utils.seeding.np_random`` (gym 0.21: sha512-hashed seed -> RandomState), with every
   draw recorded so the oracle / kernel can replay the identical numbers.
-* ``casadi``, ``matplotlib``: MagicMock (symbolic objects are built but never evaluated;
-  scenarios avoid ``cost: quadratic`` whose reward evaluates a casadi Function).
+* ``casadi``, ``matplotlib``: MagicMock (symbolic objects are built but never evaluated).  The one
+  casadi Function the env step EVALUATES -- ``SymbolicModel.loss`` inside ``_get_reward`` for
+  ``cost: quadratic`` (quadrotor.py:915-930) -- gets a numeric stand-in that computes the expression the
+  reference builds it from (quadrotor.py:682, symbolic_systems.py:114-123), so the reference's own
+  ``_get_reward`` / ``_get_done`` run for that cost too.
 """
 import hashlib
 import os
@@ -104,8 +107,8 @@ class FakeBullet(types.ModuleType):
     def loadURDF(self, path, basePosition=(0, 0, 0), baseOrientation=(0, 0, 0, 1), **k):
         i = self.next_id
         self.next_id += 1
-        self.bodies[i] = dict(pos=tuple(basePosition), quat=tuple(baseOrientation),
-                              vel=(0.0, 0.0, 0.0), angv=(0.0, 0.0, 0.0))
+        self.bodies[i] = dict(pos=tuple(float(v) for v in basePosition), quat=tuple(float(v) for v in baseOrientation),
+                              vel=(0.0, 0.0, 0.0), angv=(0.0, 0.0, 0.0), urdf=os.path.basename(str(path)))
         return i
 
     def resetBasePositionAndOrientation(self, i, pos, quat, **k):
@@ -192,5 +195,24 @@ def install(reference_root="/root/reference"):
         @property
         def TIMESTEP(self):
             return self.PYB_TIMESTEP
+
+        # F10: step() calls _get_info() BEFORE _get_done() (quadrotor.py:553-555), and _get_info reads
+        # self.goal_reached (:1013), which only _get_done assigns (:965): stabilisation + cost "quadratic" raises
+        # AttributeError on the first step as shipped.  The minimal reading that lets the reference's own code run is
+        # "not reached yet" before the first _get_done; info["goal_reached"] then reports the PREVIOUS step's flag
+        # (and survives reset(), which never clears it).
+        goal_reached = False
+
+        def _setup_symbolic(self):
+            super()._setup_symbolic()   # builds MagicMock expressions
+
+            def loss(x, u, Xr, Ur, Q, R):
+                """cost_func of quadrotor.py:682 evaluated on numbers (casadi would do the same arithmetic):
+                0.5 (X - Xr)' Q (X - Xr) + 0.5 (U - Ur)' R (U - Ur)."""
+                ex = np.asarray(x, dtype=np.float64).reshape(-1) - np.asarray(Xr, dtype=np.float64).reshape(-1)
+                eu = np.asarray(u, dtype=np.float64).reshape(-1) - np.asarray(Ur, dtype=np.float64).reshape(-1)
+                Qm, Rm = np.asarray(Q, dtype=np.float64), np.asarray(R, dtype=np.float64)
+                return {"l": 0.5 * ex @ Qm @ ex + 0.5 * eu @ Rm @ eu}
+            self.symbolic.loss = loss
 
     return DynQuadrotor

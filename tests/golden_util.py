@@ -6,7 +6,10 @@ import numpy as np
 
 GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 SCENARIOS = ["level0_dyn_s4", "level0_dyn_s1", "quad3d_tumble", "quad2d_disturbed",
-             "quad1d_tracking", "quad3d_tracking"]
+             "quad1d_tracking", "quad3d_tracking",
+             # round 2: cost "quadratic" (stabilisation with goal_reached; tracking with dense Q / R), a 140-step
+             # level0 trajectory without reset, competition/level2.yaml (randomised gates / obstacles / inertia)
+             "quad3d_quadratic_stab", "quad3d_quadratic_track", "level0_dyn_long", "level2_dyn"]
 
 
 def load(name):
@@ -27,8 +30,11 @@ def replay_oracle(g):
     Returns the list of events in the same layout make_golden.py recorded."""
     from oracle.quad_oracle import QuadOracle, ReplayDraws
     env = QuadOracle(draws=ReplayDraws(g["draws"]), **g["cfg"])
+    if "Q" in g:
+        env.set_cost_function_param(g["Q"], g["R"])
     nc = max(env.num_constraints, 1)
     ev = []
+    env.reset_log = dict(gates=[], obstacles=[], inertia=[])
 
     def rec(kind, obs, rew, done, info):
         c = np.full(nc, np.nan)
@@ -39,6 +45,7 @@ def replay_oracle(g):
                        viol=int(info.get("constraint_violation", -1)),
                        trunc=int(info.get("TimeLimit.truncated", -1)),
                        mse=float(info.get("mse", np.nan)), cvals=c, state=env.state.copy(),
+                       goal=int(info["goal_reached"]) if "goal_reached" in info else -1,
                        kin=np.hstack([env.pos, env.vel, env.rpy, env.rpy_rates])))
 
     def do_reset():
@@ -48,6 +55,10 @@ def replay_oracle(g):
             vals = [c.value(env) for c in env.constraints if c.var == "state"]
             info = {"constraint_values": np.concatenate(vals) if vals else np.zeros(0)}
         rec(0, obs, 0.0, False, info)
+        env.reset_log["gates"].append(np.array(env.EFFECTIVE_GATES_POSITIONS, dtype=float).reshape(len(env.GATES), 6))
+        env.reset_log["obstacles"].append(np.array([[o[0], o[1], o[2], o[5]] for o in env.EFFECTIVE_OBSTACLES],
+                                                   dtype=float).reshape(len(env.OBSTACLES), 4))
+        env.reset_log["inertia"].append(np.array([env.OVERRIDDEN_QUAD_MASS] + list(env.OVERRIDDEN_QUAD_INERTIA), dtype=float))
 
     do_reset()
     for t, a in enumerate(g["actions"]):
@@ -100,6 +111,9 @@ def cuda_reset(env, cur):
         for d in env.disturbances[mode].disturbances:
             if d.kind in (L.DIST_IMPULSE, L.DIST_STEP) and d.step_offset is None:
                 offsets[d.slot, :] = int(cur.take()[0])
+    if env.RANDOMIZED_GATES_AND_OBS:   # obstacles first, then gates: x, y, yaw each (quadrotor.py:371-421).  The kernel derives
+        for _ in range(3 * (len(env.OBSTACLES) + len(env.GATES))):   # its poses from Philox counters: nothing to inject
+            cur.take()
     inertia = np.zeros((4, n))
     if env.RANDOMIZED_INERTIAL_PROP:
         for j, key in enumerate(["M", "Ixx", "Iyy", "Izz"]):

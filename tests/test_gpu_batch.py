@@ -23,12 +23,14 @@ def _actions(n, k, seed=3, std=0.005, dtype=torch.float32):
     return bench.make_actions(torch, n, k, torch.device("cuda:0"), seed, std).to(dtype)
 
 
-@pytest.mark.parametrize("dtype,tol", [(torch.float64, 1e-10), (torch.float32, 1e-3)])
-def test_philox_mode_matches_oracle(dtype, tol):
+@pytest.mark.parametrize("dtype,tol,attitude", [(torch.float64, 1e-10, "fast"), (torch.float32, 1e-3, "fast"),
+                                                (torch.float32, 1e-3, "fast_intrinsic")])
+def test_philox_mode_matches_oracle(dtype, tol, attitude):
     """BASELINE config 2 in small (level0 constraints, Philox init randomisation, auto-reset on violation):
-    the kernel and the numpy oracle draw from the same (seed, env id, episode) counters."""
+    the kernel and the numpy oracle draw from the same (seed, env id, episode) counters.  Free-running (the fp32
+    bar is a drift bar; the per-step 1e-5 check of this config is test_gpu_teacher_forced.py)."""
     n, steps, base = 64, 90, 7000
-    env = _quad(n, dtype, "fast", seed_offset=base, info_in_reset=True)
+    env = _quad(n, dtype, attitude, seed_offset=base, info_in_reset=True)
     acts = _actions(n, steps, dtype=dtype).cpu().numpy().astype(np.float64)
     lanes = [0, 1, 33, 63]
     kw = bench.env_kwargs()
@@ -261,3 +263,47 @@ def _first_step_state(acts):
     s = ref.state[0].clone()
     ref.close()
     return s
+
+
+@pytest.mark.parametrize("k", [128, 200])
+def test_bench_path_matches_oracle_on_sampled_lanes(k):
+    """The EXACT kernel bench.py times -- BASELINE config 2 at full width (65,536 envs), attitude fast_intrinsic, SPEC
+    specialisation, AUTOMATIC time-chunk queue, K >= 128, no per-step outputs -- against QuadOracle(PhiloxEnvDraws) on
+    sampled lanes: after the launch the lanes' env.state, step / episode counters, lagged violation flag and running
+    episode length must be what the fp64 oracle reaches through the same actions and the same counter-based draws
+    (free-running fp32 over K steps with auto-resets: the drift bar 1e-3 of this config, integers exact)."""
+    n, base = 65536, 0
+    kw = bench.env_kwargs()
+    seed = kw.pop("seed")
+    env = _quad(n, torch.float32, "fast_intrinsic")
+    acts = _actions(n, k, seed=1337)
+    env.reset()
+    env.rollout(acts)
+    torch.cuda.synchronize()
+    assert env.last_rollout_queued, "the automatic schedule must pick the ticket queue for this shape"
+    assert int(env.lib.scg_kernel_variant(env._h)) == 3   # LEAN + PLAIN + SPEC
+    lanes = [0, 1, 31, 32, 63, 64, 4097, 20000, 40001, 65535]
+    a_host = acts[:, lanes].double().cpu().numpy()
+    state = env.buf_env_state.t()[lanes].double().cpu().numpy()
+    steps, eps = env.buf_ctrl_step[lanes].cpu().numpy(), env.buf_episode[lanes].cpu().numpy()
+    flags, ep_len = env.buf_flags[lanes].cpu().numpy(), env.buf_ep_length[lanes].cpu().numpy()
+    worst, resets = 0.0, 0
+    for j, i in enumerate(lanes):
+        o = QuadOracle(draws=PhiloxEnvDraws(seed, base + i), **kw)
+        o.reset()
+        length = 0
+        for t in range(k):
+            _, _, d, _ = o.step(a_host[t, j])
+            length += 1
+            if d:
+                o.reset()
+                resets += 1
+                length = 0
+        assert int(steps[j]) == o.ctrl_step_counter and int(eps[j]) == o.episode + 1, (i, steps[j], o.ctrl_step_counter)
+        assert bool(flags[j] & 1) == bool(o.cnstr_violation) and int(ep_len[j]) == length, i
+        err = float(np.max(np.abs(state[j] - o.state) / np.maximum(1.0, np.abs(o.state))))
+        worst = max(worst, err)
+        assert err <= 1e-3, (i, err)
+    assert resets >= 5
+    print(f"bench path (fast_intrinsic, SPEC, automatic queue, K = {k}): worst state err {worst:.2e} on {len(lanes)} lanes, {resets} resets")
+    env.close()

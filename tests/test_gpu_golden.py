@@ -1,8 +1,16 @@
 """CUDA path (through the C ABI) against the golden vectors recorded from the reference's own
-code.  fp64 build: free-running, <= 1e-12 relative (unit floor) on every float of every event,
-flags bit-exact.  fp32 build: per-step (teacher-forced from the golden state) <= 1e-5 relative
-(unit floor), flags bit-exact, plus free-running trajectory agreement over the first 100 steps
-of the level0 scenarios."""
+code.  fp64 build: free-running, <= 1e-12 on every float of every event, flags bit-exact.  fp32
+build: per-step (teacher-forced from the golden state) <= 1e-5, flags bit-exact, plus free-running
+trajectory agreement over >= 100 steps (level0_dyn_long: 140 steps without a reset).
+
+"Relative" is defined with a unit floor: err = |got - want| / max(1, |want|), i.e. relative for
+quantities above 1 (positions of several metres, rates of tens of rad/s, +-float32.max bounds) and
+absolute below (the state of a hovering drone is O(1) by construction: metres, m/s, rad).  Each test
+also REPORTS the worst error under the stricter floor 1e-3 (true relative down to millimetres /
+milliradians) and holds it to 100x the bar; every parity line goes to gpurun_out/parity_report.jsonl."""
+import json
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -17,16 +25,35 @@ def _make(g, dtype, attitude):
     from safe_control_gym_b200.envs.quadrotor import BatchedQuadrotor
     cfg = dict(g["cfg"])
     cfg["info_in_reset"] = True
-    return BatchedQuadrotor(num_envs=N_ENVS, dtype=dtype, attitude=attitude, auto_reset=False, **cfg)
+    env = BatchedQuadrotor(num_envs=N_ENVS, dtype=dtype, attitude=attitude, auto_reset=False, **cfg)
+    if "Q" in g:   # benchmark_env.py:237-254, before the first reset
+        env.set_cost_function_param(g["Q"], g["R"])
+    return env
+
+
+STRICT = {"worst": 0.0, "assert": True}   # worst error of the current test under the 1e-3 floor; held to 100x the bar in the
+#                                            per-step tests, reported only in the free-running ones (drift accumulates there)
 
 
 def _cmp(name, got, want, tol, what):
     got = np.asarray(got, dtype=np.float64)
     want = np.asarray(want, dtype=np.float64)
     m = np.isfinite(want)
-    err = np.abs(got[..., m] - want[m]) / np.maximum(1.0, np.abs(want[m]))
+    diff = np.abs(got[..., m] - want[m])
+    err = diff / np.maximum(1.0, np.abs(want[m]))
     assert err.size == 0 or err.max() <= tol, f"{name} {what}: rel err {err.max():.3e} > {tol}"
+    if err.size:
+        strict = float((diff / np.maximum(1e-3, np.abs(want[m]))).max())
+        assert not STRICT["assert"] or strict <= 100.0 * tol, f"{name} {what}: rel err (floor 1e-3) {strict:.3e} > {100.0 * tol}"
+        STRICT["worst"] = max(STRICT["worst"], strict)
     return 0.0 if err.size == 0 else float(err.max())
+
+
+def _report(**row):
+    out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    if os.path.isdir(out):
+        with open(os.path.join(out, "parity_report.jsonl"), "a") as f:
+            f.write(json.dumps(row) + "\n")
 
 
 def _check_event(name, e, g, env, out, tol, is_reset):
@@ -41,6 +68,8 @@ def _check_event(name, e, g, env, out, tol, is_reset):
             assert (info["constraint_violation"].cpu().numpy() == g["ev_viol"][e]).all(), f"{name} ev{e} violation"
         if g["ev_trunc"][e] >= 0:
             assert (info["TimeLimit.truncated"].cpu().numpy().astype(int) == g["ev_trunc"][e]).all(), f"{name} ev{e} trunc"
+        if "ev_goal" in g and g["ev_goal"][e] >= 0:   # stabilisation + cost "quadratic": the previous step's flag (F10)
+            assert (info["goal_reached"].cpu().numpy().astype(int) == g["ev_goal"][e]).all(), f"{name} ev{e} goal_reached"
         worst = max(worst, _cmp(name, info["mse"].cpu().numpy(), np.full(N_ENVS, g["ev_mse"][e]), tol, f"ev{e} mse"))
     worst = max(worst, _cmp(name, obs.cpu().numpy(), g["ev_obs"][e], tol, f"ev{e} obs"))
     worst = max(worst, _cmp(name, env.buf_env_state.t().cpu().numpy(), g["ev_state"][e], tol, f"ev{e} state"))
@@ -60,6 +89,7 @@ def test_fp64_free_running(name, attitude):
     env = _make(g, torch.float64, attitude)
     cur = DrawCursor(g["draws"])
     worst, t = 0.0, 0
+    STRICT["worst"], STRICT["assert"] = 0.0, False
     for e, kind in enumerate(g["ev_type"]):
         if kind == 0:
             out = cuda_reset(env, cur)
@@ -71,6 +101,8 @@ def test_fp64_free_running(name, attitude):
         worst = max(worst, _check_event(name, e, g, env, out, 1e-8 if name == "quad3d_tumble" else 1e-12, kind == 0))
     assert cur.pos == len(g["draws"])
     print(f"{name}[{attitude}] fp64 worst rel err {worst:.2e} over {len(g['ev_type'])} events")
+    _report(test="fp64_free_running", scenario=name, attitude=attitude, events=len(g["ev_type"]), worst_unit_floor=worst,
+            **{"worst_floor_1e-3": STRICT["worst"]})
 
 
 def _near_gimbal(g, e, margin=0.15):
@@ -99,7 +131,8 @@ def _per_step(name, attitude, dtype, tol):
         tol, loose = tol * 10.0, loose * 10.0
     env = _make(g, dtype, attitude)
     cur = DrawCursor(g["draws"])
-    worst, t, resets, steps_in_ep, n_near = 0.0, 0, 0, 0, 0
+    worst, t, resets, steps_in_ep, n_near, worst_near = 0.0, 0, 0, 0, 0, 0.0
+    STRICT["worst"], STRICT["assert"] = 0.0, True
     for e, kind in enumerate(g["ev_type"]):
         if kind == 0:
             out = cuda_reset(env, cur)
@@ -117,8 +150,18 @@ def _per_step(name, attitude, dtype, tol):
         if near and dtype == torch.float32 and attitude == "roundtrip":
             continue   # fp32 rounding of the quaternion can put the literal sequence on the other side of the
             #            |sin(pitch)| = 0.99999 snap: a discrete difference, not an error bound
-        worst = max(worst, _check_event(name, e, g, env, out, loose if near else tol, kind == 0))
-    print(f"{name}[{attitude}] {dtype} per-step worst rel err {worst:.2e} ({n_near} of {len(g['ev_type'])} events near gimbal lock)")
+        if near:   # the conditioning exception: its own bound, reported separately (count + worst error inside it)
+            strict_keep = STRICT["worst"]
+            STRICT_TOL = loose
+            worst_near = max(worst_near, _check_event(name, e, g, env, out, STRICT_TOL, kind == 0))
+            STRICT["worst"] = strict_keep
+        else:
+            worst = max(worst, _check_event(name, e, g, env, out, tol, kind == 0))
+    print(f"{name}[{attitude}] {dtype} per-step worst rel err {worst:.2e} outside, {worst_near:.2e} inside the near-gimbal bound "
+          f"({n_near} of {len(g['ev_type'])} events use it)")
+    _report(test="per_step", scenario=name, attitude=attitude, dtype=str(dtype), events=len(g["ev_type"]), tol=tol,
+            worst_unit_floor=worst, **{"worst_floor_1e-3": STRICT["worst"]}, near_gimbal_events=n_near, near_gimbal_tol=loose,
+            worst_near_gimbal=worst_near)
 
 
 @pytest.mark.parametrize("attitude", ["roundtrip", "fast", "fast_intrinsic"])
@@ -134,15 +177,17 @@ def test_fp64_per_step(name, attitude):
 
 
 @pytest.mark.parametrize("attitude", ["fast", "fast_intrinsic"])
-@pytest.mark.parametrize("name", ["level0_dyn_s4", "level0_dyn_s1"])
+@pytest.mark.parametrize("name", ["level0_dyn_long", "level0_dyn_s4", "level0_dyn_s1"])
 def test_fp32_trajectory_100_steps(name, attitude):
-    """Free-running fp32 vs the fp64 reference over 100 control steps (reported, loose bound)."""
+    """Free-running fp32 vs the fp64 reference (north_star: "trajectory agreement reported over 100 steps").
+    level0_dyn_long holds 140 control steps without a reset; the two older fixtures stop at their first reset
+    (41 / 80 steps) and are kept as additional reports.  Drift is printed every 10 steps."""
     g = load(name)
     env = _make(g, torch.float32, attitude)
     cur = DrawCursor(g["draws"])
-    t, worst = 0, 0.0
+    t, worst, curve = 0, 0.0, []
     for e, kind in enumerate(g["ev_type"]):
-        if t >= 100 or (kind == 0 and e > 0):
+        if kind == 0 and e > 0:
             break
         if kind == 0:
             cuda_reset(env, cur)
@@ -151,5 +196,11 @@ def test_fp32_trajectory_100_steps(name, attitude):
         t += 1
         got = env.buf_env_state.t().cpu().numpy()[0].astype(np.float64)
         worst = max(worst, float(np.max(np.abs(got - g["ev_state"][e]) / np.maximum(1.0, np.abs(g["ev_state"][e])))))
-    print(f"{name}[{attitude}]: fp32 free-running drift after {t} steps: {worst:.2e}")
+        if t % 10 == 0:
+            curve.append(worst)
+    print(f"{name}[{attitude}]: fp32 free-running drift after {t} steps: {worst:.2e}; per 10 steps: " +
+          " ".join(f"{c:.1e}" for c in curve))
+    _report(test="fp32_trajectory", scenario=name, attitude=attitude, steps=t, worst_unit_floor=worst, drift_per_10_steps=curve)
+    if name == "level0_dyn_long":
+        assert t >= 100
     assert worst < 1e-3

@@ -11,7 +11,7 @@ def test_oracle_reproduces_reference(name):
     g = load(name)
     ev, env = replay_oracle(g)
     assert len(ev) == len(g["ev_type"])
-    for k in ["type", "done", "viol", "trunc"]:
+    for k in ["type", "done", "viol", "trunc", "goal"]:
         assert (np.array([e[k] for e in ev]) == g["ev_" + k]).all(), k
     for k in ["obs", "rew", "mse", "cvals", "state", "kin"]:
         a = np.array([e[k] for e in ev], dtype=float)
@@ -22,6 +22,13 @@ def test_oracle_reproduces_reference(name):
             rel = np.abs(a[m] - b[m]) / np.maximum(1.0, np.abs(b[m]))
             assert rel.max() <= 1e-13, (k, rel.max())
     assert env.draws.pos == len(g["draws"])  # every recorded draw consumed, in order
+    # what the reset draws turned into: the poses the reference handed to loadURDF / EFFECTIVE_GATES_POSITIONS and the
+    # overridden inertial properties (pins the draw ORDER obstacles -> gates -> inertia -> init, quadrotor.py:371-488)
+    for k in ["gates", "obstacles", "inertia"]:
+        a, b = np.array(env.reset_log[k], dtype=float), g["reset_" + k]
+        assert a.shape == b.shape, k
+        if a.size:
+            assert np.max(np.abs(a - b)) <= 1e-15, (k, np.max(np.abs(a - b)))
     np.testing.assert_array_equal(env.action_low, g["action_low"])
     np.testing.assert_array_equal(env.state_high, g["state_high"])
     np.testing.assert_allclose(env.X_GOAL, g["X_GOAL"], rtol=0, atol=1e-15)
