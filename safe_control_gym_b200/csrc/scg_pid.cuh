@@ -14,7 +14,7 @@ namespace scg {
 template <int KIND, typename real>
 __device__ __noinline__ void pid_action(const PidP<real>& P, const real* __restrict__ pos, const real* __restrict__ vel,
                                         const real* __restrict__ rpy, const real* __restrict__ tpos, const real* __restrict__ tvel,
-                                        real* __restrict__ mem, int64_t n, int64_t i, real* __restrict__ act) {
+                                        real* __restrict__ mem, int64_t n, int64_t i, real* __restrict__ act, bool write = true) {
     real ipos[3], last[3], irot[3];
 #pragma unroll
     for (int j = 0; j < 3; ++j) { ipos[j] = mem[int64_t(j) * n + i]; last[j] = mem[int64_t(3 + j) * n + i]; irot[j] = mem[int64_t(6 + j) * n + i]; }
@@ -67,8 +67,10 @@ __device__ __noinline__ void pid_action(const PidP<real>& P, const real* __restr
     }
     if constexpr (KIND == SCG_QUAD_3D) { act[0] = f[0]; act[1] = f[1]; act[2] = f[2]; act[3] = f[3]; }
     else { act[0] = f[0] + f[3]; act[1] = f[1] + f[2]; }
+    if (write) {   // false: an out-of-range lane shadowing env n - 1 (rollout_range) -- the memory belongs to the owner lane
 #pragma unroll
-    for (int j = 0; j < 3; ++j) { mem[int64_t(j) * n + i] = ipos[j]; mem[int64_t(3 + j) * n + i] = last[j]; mem[int64_t(6 + j) * n + i] = irot[j]; }
+        for (int j = 0; j < 3; ++j) { mem[int64_t(j) * n + i] = ipos[j]; mem[int64_t(3 + j) * n + i] = last[j]; mem[int64_t(6 + j) * n + i] = irot[j]; }
+    }
 }
 
 }  // namespace scg

@@ -46,6 +46,7 @@ template <int KIND, typename real> struct EnvRegs {
 #ifndef SCG_NO_PAIRS
 #define SCG_NO_PAIRS 0
 #endif
+
 template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN> struct Paired {
     static constexpr bool value = KIND == SCG_QUAD_3D && sizeof(real) == 4 && ATT != SCG_ATT_ROUNDTRIP && LEAN && PLAIN && !SCG_NO_PAIRS;
 };
@@ -199,7 +200,7 @@ template <typename real> SCG_DEV real rand_value(const RandP<real>& rp, real u, 
 template <int KIND, typename real, int ATT>
 SCG_DEV void reset_env_body(const Hot<real>& h, const Cold<real>* __restrict__ cold, const Buf<real>& b,
                             const ResetInject<real>& inj, const RngKey& key, int64_t n, int64_t i,
-                            EnvRegs<KIND, real>& e, real (&st)[Dims<KIND>::NX]) {
+                            EnvRegs<KIND, real>& e, real (&st)[Dims<KIND>::NX], bool write = true) {
     constexpr int NX = Dims<KIND>::NX;
     const uint32_t ep = h.reseed_on_reset ? 0u : uint32_t(e.resets);
     e.resets += 1;
@@ -217,7 +218,7 @@ SCG_DEV void reset_env_body(const Hot<real>& h, const Cold<real>* __restrict__ c
                     const U4 w = philox4x32_10(0u, ep, STREAM_RESET_OFFSETS, uint32_t(D.slot >> 2), key.seed, key.env);
                     off = randint(word_of(w, D.slot & 3), D.max_step);
                 }
-                b.dist_offset[int64_t(D.slot) * n + i] = off;
+                if (write) b.dist_offset[int64_t(D.slot) * n + i] = off;
             }
         }
     }
@@ -233,7 +234,7 @@ SCG_DEV void reset_env_body(const Hot<real>& h, const Cold<real>* __restrict__ c
             real v = h.inertia_nominal[j];
             if (inj.inertia) v += inj.inertia[int64_t(j) * n + i];
             else if (h.any_inertia_rand) v += rand_value(h.inertia_rand[j], u[j], z[j]);
-            b.inertia[int64_t(j) * n + i] = v;
+            if (write) b.inertia[int64_t(j) * n + i] = v;
         }
     }
     load_inertia<KIND, real>(h, b.inertia, n, i, e.in);
@@ -424,8 +425,14 @@ __device__ __noinline__ void draw_spare_general(const Hot<real>& h, const Cold<r
 template <int KIND, typename real, int ATT>
 __device__ __noinline__ void apply_spare_extras(const Hot<real>& h, const Cold<real>* __restrict__ cold, real* __restrict__ inertia,
                                                 int32_t* __restrict__ dist_offset, const real* __restrict__ sp, int64_t n, int64_t i,
-                                                Inertia<real>* in_out) {
+                                                Inertia<real>* in_out, bool write) {
     constexpr int N0 = Spare<KIND, real, ATT>::N;
+    if (!write) {   // an out-of-range lane shadowing env n - 1: the buffers belong to the owner lane
+        Inertia<real> in;
+        load_inertia<KIND, real>(h, inertia, n, i, in);
+        *in_out = in;
+        return;
+    }
     if (inertia) {
 #pragma unroll
         for (int j = 0; j < 4; ++j)
@@ -457,12 +464,13 @@ SCG_DEV void spare_ang0(const real* __restrict__ sp, real (&ang0)[3]) {
 // are not pinned to local memory by the call.
 template <int KIND, typename real, int ATT>
 __device__ __noinline__ void reset_env_cold(const Hot<real>& h, const Cold<real>* __restrict__ cold, const Buf<real>& b,
-                                            RngKey key, int64_t n, int64_t i, EnvRegs<KIND, real>* e_io, real* __restrict__ st_out) {
+                                            RngKey key, int64_t n, int64_t i, EnvRegs<KIND, real>* e_io, real* __restrict__ st_out,
+                                            bool write) {
     constexpr int NX = Dims<KIND>::NX;
     EnvRegs<KIND, real> e = *e_io;
     real st[NX];
     const ResetInject<real> none{nullptr, nullptr, nullptr};
-    reset_env_body<KIND, real, ATT>(h, cold, b, none, key, n, i, e, st);
+    reset_env_body<KIND, real, ATT>(h, cold, b, none, key, n, i, e, st, write);
     *e_io = e;
 #pragma unroll
     for (int d = 0; d < NX; ++d) st_out[d] = st[d];
@@ -780,7 +788,6 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
         mse = real(0);
         constexpr int NM = KIND == SCG_QUAD_3D ? 9 : NX;
         if (KIND == SCG_QUAD_3D && (cfg & CFG_MSE_POS)) {   // same sum: the skipped terms are exact zeros
-#pragma unroll
             const Row4<real> wt = ldc4(h.pos_pack + 12);   // mse_weight[0, 2, 4]
             { const real er = (st[0] - goal_pos_at(0)) * wt.x; mse += er * er; }
             { const real er = (st[2] - goal_pos_at(2)) * wt.y; mse += er * er; }
@@ -972,12 +979,16 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
                            const int64_t i, const int k0, const int k1, float* const ep_acc, double* const mse_acc, real* const sp) {
     constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
     const int64_t n = b.n;
-    // Out-of-range lanes of the last env block take no part: every global side effect of the loop (state, PID memory,
-    // disturbance offsets, per-step outputs) belongs to exactly one lane.  The callers' block barriers and the final
-    // warp reduction sit outside this function, where the warp has reconverged.
-    if (i >= n) return;
+    // Out-of-range lanes of the last env block READ env n - 1 and compute along with the warp, but every global side
+    // effect of the loop -- state, PID memory, disturbance offsets / inertia, per-step outputs, the log -- is predicated on
+    // `valid`: each word of batch memory has exactly one writer.  (Leaving the function early instead makes the whole loop
+    // body potentially divergent code, where the compiler cannot use the uniform datapath for the scenario constants:
+    // measured 6.11e10 -> 5.78e10 env-steps/s on the headline workload, profiles/r2_summary.md.)  What a shadow lane
+    // computes may drift from its owner (it can observe the owner's PID memory / offsets at another step); nothing of it
+    // is stored, and its statistics go to the scratch column.
+    const bool valid = i < n;
     ep_acc[1 * ACC_LD] = 0.f;   // return of the episodes that end in this range: summed in fp32 per range, in fp64 across ranges
-    const int64_t ii = i;
+    const int64_t ii = valid ? i : n - 1;
     const RngKey key{h.seed, h.env_id_base_lo + uint32_t(ii)};
     EnvRegs<KIND, real> e;
 #pragma unroll
@@ -985,6 +996,9 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
     e.t = b.ctrl_step[ii];
     e.resets = b.episode[ii];
     unpack_flags<KIND, real>(e, b.flags[ii]);
+    // SPEC: cost "competition" is a compile-time fact, the goal_reached bit (cost "quadratic" only) cannot change: it is
+    // not carried through the loop (one register less at the 96-register bound) but re-read where the flags are stored
+    if constexpr (SPEC) e.goal_prev = false;
     real st[NX];   // env.state after the last step (LEAN: rebuilt from the registers after the loop)
     load_inertia<KIND, real>(h, PLAIN ? nullptr : b.inertia, n, ii, e.in);
     derive_attitude<KIND, real, ATT>(e);
@@ -1006,7 +1020,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
     const uint32_t cfg_rt = h.cfg | (ro.step_outputs ? (CFG_FULL_STATE | CFG_STEP_OUTPUTS) : 0u);
     const uint32_t cfg = SPEC ? ((cfg_rt & ~CFG_SPEC_MASK) | CFG_SPEC_VAL) : cfg_rt;
     const bool full = (cfg & CFG_FULL_STATE) != 0u;
-    real* const c_out = SPEC ? nullptr : (ro.step_outputs ? b.c_values : nullptr);
+    real* const c_out = SPEC ? nullptr : ((ro.step_outputs && valid) ? b.c_values : nullptr);
     // software prefetch of the next action (one 16-byte load per 3D env per step)
     real raw[NU], nxt[NU];
     const bool closed_loop = !PLAIN && ro.use_pid != 0;   // uniform: actions from the on-device PID (scg_pid.cuh)
@@ -1042,10 +1056,10 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
                     tp[0] = goal_at(0); tp[1] = real(0); tp[2] = goal_at(2);
                     tv[0] = stab ? real(0) : goal_at(1); tv[1] = real(0); tv[2] = stab ? real(0) : goal_at(3);
                 }
-                pid_action<KIND, real>(ro.pid, pos, vel, rpy, tp, tv, ro.pid_mem, n, ii, act);
+                pid_action<KIND, real>(ro.pid, pos, vel, rpy, tp, tv, ro.pid_mem, n, ii, act, valid);
 #pragma unroll
                 for (int j = 0; j < NU; ++j) raw[j] = act[j];
-                if (ro.actions_out) {
+                if (ro.actions_out && valid) {
 #pragma unroll
                     for (int j = 0; j < NU; ++j) ro.actions_out[(int64_t(k) * n + ii) * NU + j] = act[j];
                 }
@@ -1068,9 +1082,9 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
             s_coll += (info & SCG_INFO_COLLISION) ? 1.f : 0.f;
         }
         if (any_out) {
-            if (ro.reward_out) ro.reward_out[int64_t(k) * n + ii] = reward;
-            if (ro.done_out) ro.done_out[int64_t(k) * n + ii] = done ? 1 : 0;
-            if (ro.log_out && (k % ro.log_stride) == 0) {
+            if (ro.reward_out && valid) ro.reward_out[int64_t(k) * n + ii] = reward;
+            if (ro.done_out && valid) ro.done_out[int64_t(k) * n + ii] = done ? 1 : 0;
+            if (ro.log_out && (k % ro.log_stride) == 0 && valid) {
                 if constexpr (PAIRED) {
                     EnvRegs<KIND, real> el = e;   // the record reads the scalar layout
                     scalars_from_pairs(el);
@@ -1103,7 +1117,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
             if (info & SCG_INFO_COMPLETED) ep_acc[4 * ACC_LD] += 1.f;
             if (ep_viol > 0) ep_acc[5 * ACC_LD] += 1.f;
             if (cfg & CFG_AUTO_RESET) {   // DummyVecEnv.step_wait (dummy_vec_env.py:38-49)
-                if ((cfg & CFG_STEP_OUTPUTS) && b.terminal_obs) {
+                if ((cfg & CFG_STEP_OUTPUTS) && b.terminal_obs && valid) {
                     real tl[NX];
 #pragma unroll
                     for (int d = 0; d < NX; ++d) tl[d] = sk[d];
@@ -1113,14 +1127,14 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
                 if constexpr (!LEAN) {
                     EnvRegs<KIND, real> ec = e;
                     real sn[NX];
-                    reset_env_cold<KIND, real, ATT>(h, cold, b, key, n, ii, &ec, sn);
+                    reset_env_cold<KIND, real, ATT>(h, cold, b, key, n, ii, &ec, sn, valid);
                     e = ec;
 #pragma unroll
                     for (int d = 0; d < NX; ++d) st[d] = sn[d];
                 }
                 ep_ret = real(0); ep_len = 0; ep_viol = 0;
                 fresh = true;
-                if (closed_loop) {   // PIDController.reset() with the env (quadrotor_utils.py:124-135)
+                if (closed_loop && valid) {   // PIDController.reset() with the env (quadrotor_utils.py:124-135)
 #pragma unroll
                     for (int j = 0; j < 9; ++j) ro.pid_mem[int64_t(j) * n + ii] = real(0);
                 }
@@ -1128,7 +1142,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
                     reset_from_spare<KIND, real, ATT, PAIRED>(sp, e);
                     if (!PLAIN && (cfg & CFG_RESET_EXTRAS)) {
                         Inertia<real> in;
-                        apply_spare_extras<KIND, real, ATT>(h, cold, b.inertia, b.dist_offset, sp, n, ii, &in);
+                        apply_spare_extras<KIND, real, ATT>(h, cold, b.inertia, b.dist_offset, sp, n, ii, &in, valid);
                         e.in = in;
                     }
                     spare_ok = false;
@@ -1140,10 +1154,13 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
     // a range that ends inside the launch (ticket queue) hands over the state only: observation, env.state and the
     // per-step scalars are rewritten by the range that ends the launch
     const bool last_range = k1 >= ro.k_steps;   // uniform
-    if (!last_range) {
+    if (!valid) {
+        // nothing of a shadow lane is stored
+    } else if (!last_range) {
 #pragma unroll
         for (int d = 0; d < NX; ++d) b.state[int64_t(d) * n + ii] = e.x[d];
-        b.ctrl_step[ii] = e.t; b.episode[ii] = e.resets; b.flags[ii] = pack_flags<KIND, real>(e);
+        b.ctrl_step[ii] = e.t; b.episode[ii] = e.resets;
+        b.flags[ii] = pack_flags<KIND, real>(e) | (SPEC ? (b.flags[ii] & SCG_FLAG_GOAL_REACHED) : 0u);
     } else {
     if constexpr (LEAN) {
         // env.state as observed after the loop: the fresh episode's (PyBullet still holds INIT_ANG_VEL)
@@ -1167,7 +1184,8 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
     }
 #pragma unroll
     for (int d = 0; d < NX; ++d) b.state[int64_t(d) * n + ii] = e.x[d];
-    b.ctrl_step[ii] = e.t; b.episode[ii] = e.resets; b.flags[ii] = pack_flags<KIND, real>(e);
+    b.ctrl_step[ii] = e.t; b.episode[ii] = e.resets;
+    b.flags[ii] = pack_flags<KIND, real>(e) | (SPEC ? (b.flags[ii] & SCG_FLAG_GOAL_REACHED) : 0u);
     if (b.env_state) {
 #pragma unroll
         for (int d = 0; d < NX; ++d) b.env_state[int64_t(d) * n + ii] = st[d];
@@ -1182,9 +1200,9 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
     b.reward[ii] = reward; b.done[ii] = done ? 1 : 0; b.info[ii] = uint8_t(info);
     if (b.mse) b.mse[ii] = mse;
     }
-    if (b.ep_return) b.ep_return[ii] = ep_ret;
-    if (b.ep_length) b.ep_length[ii] = ep_len;
-    if (b.ep_violations) b.ep_violations[ii] = ep_viol;
+    if (b.ep_return && valid) b.ep_return[ii] = ep_ret;
+    if (b.ep_length && valid) b.ep_length[ii] = ep_len;
+    if (b.ep_violations && valid) b.ep_violations[ii] = ep_viol;
     // statistics of this range into the caller's columns (an out-of-range lane was handed the scratch column)
     // (the mse sum goes into a double column: a sum of fp32 terms in fp64 is exact, so the total does not depend on
     // which resident thread ran which chunk; the other statistics are small integers, exact in fp32)
