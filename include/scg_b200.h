@@ -316,6 +316,19 @@ int scg_kernel_variant(const scg_env* env);
  * The environment variables SCG_QUEUE / SCG_QUEUE_CHUNK give the initial values.  Results do not depend on it (a K-step
  * rollout equals any split of it into launches); the episode statistics agree up to the order of their float sums. */
 int scg_set_rollout_queue(scg_env* env, int32_t mode, int32_t chunk_steps);
+/* scg_rollout without any allocation.  No counterpart in the reference; added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments and results as scg_rollout, always through the time-chunk ticket queue, whose scratch (pop counter, push
+ * counter, ready list) lives in a file-scope static device array of SCG_NOALLOC_QUEUE_WORDS int32 (512 KiB, held by every
+ * GPU that loads the library until exit) instead of the handle's cudaMalloc'ed list.  Limits: precision 32 with a fast
+ * attitude mode, k_steps >= 64, and 2 + ceil(k_steps / chunk) * ceil(n / 64) <= SCG_NOALLOC_QUEUE_WORDS (chunk = 64 unless
+ * scg_set_rollout_queue changed it), e.g. 65,536 envs x 8,000 steps or 1 M envs x 448 steps per launch; anything beyond
+ * returns SCG_ERR_SHAPE with the numbers in scg_last_error().  Calls no cudaMalloc / cudaFree / allocating library routine;
+ * the words it uses are cleared on `stream` before the kernel reads them.  ALL handles and calls on one GPU share the
+ * array: calls that overlap on the GPU (different streams, no ordering between them) race -- keep them on one stream or
+ * order them with events.  The kernel's first launch in a process loads its module; warm up once before capturing. */
+#define SCG_NOALLOC_QUEUE_WORDS 131072
+int scg_rollout_noalloc(scg_env* env, const scg_rollout_args* args, void* stream);
 /* 1 when the last fused rollout launch went through the ticket queue, else 0 */
 int scg_last_rollout_queue(const scg_env* env);
 const char* scg_last_error(void);

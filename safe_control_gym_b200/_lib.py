@@ -12,6 +12,7 @@ LIB_PATH = os.environ.get("SCG_LIB", os.path.join(HERE, "libscg_b200.so"))   # S
 
 MAX_NX, MAX_NU, MAX_CONSTRAINTS, MAX_CON_ROWS, MAX_ROWS = 12, 4, 8, 24, 64
 MAX_DIST, MAX_GATES, MAX_OBSTACLES, STATS_LEN = 4, 8, 8, 16
+NOALLOC_QUEUE_WORDS = 131072
 
 QUAD_1D, QUAD_2D, QUAD_3D, CARTPOLE = 1, 2, 3, 10
 TASK_STABILIZATION, TASK_TRAJ_TRACKING = 0, 1
@@ -34,7 +35,7 @@ STAT_NAMES = ["episodes", "return", "length", "violation_steps", "mse", "gates",
 EXPORTS = ["scg_create", "scg_destroy", "scg_bind_buffers", "scg_set_injection", "scg_reset", "scg_step",
            "scg_rollout", "scg_rollout_host", "scg_rollout_pid", "scg_stats_reset", "scg_stats_read", "scg_constraints_eval",
            "scg_symbolic_eval", "scg_symbolic_loss", "scg_gate_info", "scg_measure_fp32_peak", "scg_launch_count", "scg_kernel_variant",
-           "scg_set_rollout_queue", "scg_last_rollout_queue", "scg_set_seed",
+           "scg_set_rollout_queue", "scg_last_rollout_queue", "scg_set_seed", "scg_rollout_noalloc",
            "scg_last_error", "scg_version"]
 
 
@@ -145,6 +146,7 @@ def load():
     lib.scg_step.argtypes = [vp, vp, vp]
     lib.scg_rollout.argtypes = [vp, C.POINTER(RolloutArgs), vp]
     lib.scg_rollout_host.argtypes = [vp, vp, i32, i32, vp]
+    lib.scg_rollout_noalloc.argtypes = [vp, C.POINTER(RolloutArgs), vp]
     lib.scg_rollout_pid.argtypes = [vp, C.POINTER(PidConfig), vp, C.POINTER(RolloutArgs), vp, vp]
     lib.scg_stats_reset.argtypes = [vp, vp]
     lib.scg_stats_read.argtypes = [vp, C.POINTER(C.c_double), vp]

@@ -521,6 +521,55 @@ extern "C" int scg_rollout(scg_env* e, const scg_rollout_args* a, void* stream) 
                      0, static_cast<cudaStream_t>(stream));
 }
 
+// ---------------------------------------------------------------- scg_rollout_noalloc
+// The scratch of the time-chunk ticket queue (pop counter, push counter, ready list) for callers that must not allocate:
+// one file-scope device array per GPU that loads the library, held until exit.  g_queue_scratch is a host-side stand-in
+// in host code -- its device address comes from cudaGetSymbolAddress, once per device, with that device current.
+static __device__ __align__(256) int32_t g_queue_scratch[SCG_NOALLOC_QUEUE_WORDS];
+static int32_t* g_queue_scratch_ptr[64] = {nullptr};
+
+extern "C" int scg_rollout_noalloc(scg_env* e, const scg_rollout_args* a, void* stream) {
+    if (!e || !a || !a->actions) return fail(SCG_ERR_NULL, "scg_rollout_noalloc: null argument");
+    if (!e->bound) return fail(SCG_ERR_STATE, "scg_rollout_noalloc: buffers not bound");
+    if (!e->did_reset) return fail(SCG_ERR_STATE, "[ERROR] You must call env.reset() at least once before using env.step().");
+    if (a->log_out && a->log_stride < 1) return fail(SCG_ERR_SHAPE, "log_stride must be >= 1");
+    const bool quad_att = e->cfg.env_kind == SCG_QUAD_3D || e->cfg.env_kind == SCG_QUAD_2D;
+    if (e->cfg.precision != 32 || (quad_att && e->cfg.attitude_mode == SCG_ATT_ROUNDTRIP))
+        return fail(SCG_ERR_BAD_CONFIG, "scg_rollout_noalloc: the queued rollout kernel exists for precision 32 with a fast attitude mode only");
+    if (a->k_steps < 64) return fail(SCG_ERR_SHAPE, "scg_rollout_noalloc: k_steps must be >= 64 (shorter launches take the static grid, which needs no scratch: use scg_rollout)");
+    // the ranges of this launch, as launch_queued (scg_inst.cuh) will cut them
+    const int64_t env_blocks = (e->buf.n + 63) / 64;
+    int chunk = e->queue_chunk > 0 ? e->queue_chunk : 64;
+    if (chunk > a->k_steps) chunk = a->k_steps;
+    const int64_t tickets = int64_t((a->k_steps + chunk - 1) / chunk) * env_blocks;
+    if (2 + tickets > SCG_NOALLOC_QUEUE_WORDS) {
+        char msg[256];
+        snprintf(msg, sizeof(msg), "scg_rollout_noalloc: %lld (64-env block, %d-step chunk) ranges need %lld words of queue scratch, the static array holds "
+                 "%d: use fewer envs / steps per launch, a longer chunk (scg_set_rollout_queue), or scg_rollout", (long long)tickets, chunk,
+                 (long long)(2 + tickets), SCG_NOALLOC_QUEUE_WORDS);
+        return fail(SCG_ERR_SHAPE, msg);
+    }
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(SCG_ERR_BAD_CONFIG, "scg_rollout_noalloc: device ordinal out of range");
+    if (!g_queue_scratch_ptr[dev]) {
+        int32_t* p = nullptr;
+        CU(cudaGetSymbolAddress((void**)&p, g_queue_scratch));
+        g_queue_scratch_ptr[dev] = p;
+    }
+    // For this call the handle's queue scratch IS the static array, large enough by the check above, so the launcher neither
+    // frees nor allocates; it clears the words it uses (cudaMemsetAsync on `stream`) before the kernel reads them.
+    int32_t* const keep_mem = e->q_mem; const int64_t keep_cap = e->q_cap; const int keep_mode = e->queue_mode;
+    e->q_mem = g_queue_scratch_ptr[dev]; e->q_cap = SCG_NOALLOC_QUEUE_WORDS; e->queue_mode = 1;
+    const int rc = run_steps(e, a->actions, a->k_steps, a->reward_out, a->done_out, a->log_out, a->log_stride > 0 ? a->log_stride : 1, 0,
+                             static_cast<cudaStream_t>(stream));
+    const bool queued = e->last_queue == 1 && e->q_mem == g_queue_scratch_ptr[dev];
+    e->q_mem = keep_mem; e->q_cap = keep_cap; e->queue_mode = keep_mode;
+    if (rc != SCG_OK) return rc;
+    if (!queued) return fail(SCG_ERR_STATE, "scg_rollout_noalloc: the launcher did not take the queued kernel (the rollout ran on the static grid, which uses no scratch)");
+    return SCG_OK;
+}
+
 // Closed loop: K fused control steps whose actions come from the on-device DSL PID tracking the env's X_GOAL
 // (quadrotor_utils.py:70-278; competition_utils.py:338-356 / controllers/pid/pid.py:97-141).
 extern "C" int scg_rollout_pid(scg_env* e, const scg_pid_config* pid, void* pid_mem, const scg_rollout_args* a, void* actions_out,

@@ -281,6 +281,23 @@ class BatchedEnvBase:
             L.check(self.lib.scg_rollout(self._h, C.byref(args), self._stream()))
         return self.buf_obs.t()
 
+    def rollout_noalloc(self, actions, reward_out=None, done_out=None, log_out=None, log_stride=1):
+        """``rollout`` through scg_rollout_noalloc: the library allocates nothing (the ticket queue's scratch is a static
+        device array, see include/scg_b200.h for the limits).  ``actions`` must already be the [K, N, nu] device tensor of
+        the env's dtype -- nothing is converted or copied here either."""
+        if not self.initial_reset:
+            raise RuntimeError("[ERROR] You must call env.reset() at least once before using env.step().")
+        a = actions
+        assert a.is_cuda and a.dtype == self.dtype and a.is_contiguous() and a.shape[1:] == (self.num_envs, self.action_dim)
+        args = L.RolloutArgs()
+        args.actions, args.k_steps, args.log_stride = a.data_ptr(), a.shape[0], int(log_stride)
+        args.reward_out = reward_out.data_ptr() if reward_out is not None else None
+        args.done_out = done_out.data_ptr() if done_out is not None else None
+        args.log_out = log_out.data_ptr() if log_out is not None else None
+        with torch.cuda.device(self.device):
+            L.check(self.lib.scg_rollout_noalloc(self._h, C.byref(args), self._stream()))
+        return self._obs_view
+
     def rollout_pid(self, k_steps, pid=None, pid_mem=None, actions_out=None, reward_out=None, done_out=None, log_out=None,
                     log_stride=1):
         """K fused CLOSED-LOOP control steps: the action of every step comes from the on-device DSL PID
