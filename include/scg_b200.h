@@ -331,6 +331,11 @@ int scg_set_rollout_queue(scg_env* env, int32_t mode, int32_t chunk_steps);
 int scg_rollout_noalloc(scg_env* env, const scg_rollout_args* args, void* stream);
 /* 1 when the last fused rollout launch went through the ticket queue, else 0 */
 int scg_last_rollout_queue(const scg_env* env);
+/* 1 when the last fused rollout launch wrote its trajectory log (scg_rollout_args.log_out: the Logger record,
+ * envs/gym_pybullet_drones/Logger.py:50-66) through the TMA unit -- records staged in shared memory, one bulk tensor store
+ * per warp and pair of logged steps -- else 0 (plain strided stores).  Taken for quad_type 3, precision 32, a fast attitude
+ * mode, n % 4 == 0 and a 16-byte aligned log tensor, unless the queue is forced on or SCG_TLOG=0.  Same bytes either way. */
+int scg_last_rollout_tlog(const scg_env* env);
 const char* scg_last_error(void);
 const char* scg_version(void);
 

@@ -35,7 +35,7 @@ STAT_NAMES = ["episodes", "return", "length", "violation_steps", "mse", "gates",
 EXPORTS = ["scg_create", "scg_destroy", "scg_bind_buffers", "scg_set_injection", "scg_reset", "scg_step",
            "scg_rollout", "scg_rollout_host", "scg_rollout_pid", "scg_stats_reset", "scg_stats_read", "scg_constraints_eval",
            "scg_symbolic_eval", "scg_symbolic_loss", "scg_gate_info", "scg_measure_fp32_peak", "scg_launch_count", "scg_kernel_variant",
-           "scg_set_rollout_queue", "scg_last_rollout_queue", "scg_set_seed", "scg_rollout_noalloc",
+           "scg_set_rollout_queue", "scg_last_rollout_queue", "scg_set_seed", "scg_rollout_noalloc", "scg_last_rollout_tlog",
            "scg_last_error", "scg_version"]
 
 
@@ -161,6 +161,7 @@ def load():
     lib.scg_set_rollout_queue.argtypes = [vp, C.c_int32, C.c_int32]
     lib.scg_last_rollout_queue.argtypes = [vp]
     lib.scg_set_seed.argtypes = [vp, C.c_uint32]
+    lib.scg_last_rollout_tlog.argtypes = [vp]
     lib.scg_last_error.restype = C.c_char_p
     lib.scg_version.restype = C.c_char_p
     for name in EXPORTS:

@@ -313,6 +313,7 @@ extern "C" int scg_set_rollout_queue(scg_env* env, int32_t mode, int32_t chunk_s
     return SCG_OK;
 }
 extern "C" int scg_last_rollout_queue(const scg_env* env) { return env ? env->last_queue : 0; }
+extern "C" int scg_last_rollout_tlog(const scg_env* env) { return env ? env->last_tlog : 0; }
 // BenchmarkEnv.seed (benchmark_env.py:220-235): the Philox key of every later draw.  The constant block travels by value
 // with each launch, so the host copy is all there is to patch.
 extern "C" int scg_set_seed(scg_env* env, uint32_t seed) {

@@ -34,6 +34,7 @@ struct scg_env {
     unsigned queue_sleep_ns = 500; // poll interval of a block that waits for its ticket's predecessor (SCG_QUEUE_SLEEP)
     int queue_blocks_per_sm = 8;   // workers of a queued launch per SM (0: every resident slot); 8 x 148 for 1,024 env blocks measured best
     int last_queue = 0;            // the last rollout launch went through the queue (scg_last_rollout_queue)
+    int last_tlog = 0;             // ... wrote its trajectory log through the TMA unit (scg_last_rollout_tlog)
 };
 
 int scg_fail(int code, const std::string& msg);
@@ -59,6 +60,8 @@ template <typename real> inline Buf<real> typed_buf(const scg_buffers& b) {
 // defined (and explicitly instantiated) in scg_inst.cuh / scg_k_*.cu
 template <int KIND, typename real> int launch_reset(scg_env* e, const ResetInject<real>& inj, const uint8_t* mask, cudaStream_t st);
 template <int KIND, typename real> int launch_rollout(scg_env* e, const Roll<real>& ro, cudaStream_t st);
+// scg_k_3d_f_tlog.cu: logged 3D fp32 rollouts with the TMA-staged log store; 1 = launched, 0 = not eligible
+int launch_rollout_tlog_3d_f(scg_env* e, const Roll<float>& ro, cudaStream_t st);
 template <int KIND, typename real> int launch_constraints(scg_env* e, const real* state, const real* action, int64_t n,
                                                           real* out_values, uint8_t* out_flags, cudaStream_t st);
 

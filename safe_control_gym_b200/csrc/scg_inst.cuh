@@ -99,6 +99,14 @@ int launch_rollout(scg_env* e, const Roll<real>& ro, cudaStream_t st) {
     const unsigned blocks = unsigned((b.n + ENV_BLOCK - 1) / ENV_BLOCK);
     const Cold<real>* cold = static_cast<const Cold<real>*>(e->cold_dev);
     const int att = e->cfg.attitude_mode;
+    e->last_tlog = 0;
+    if constexpr (KIND == SCG_QUAD_3D && sizeof(real) == 4) {
+        if (ro.log_out && e->queue_mode != 1 && launch_rollout_tlog_3d_f(e, ro, st)) {   // staged (TMA) trajectory log
+            e->launches += 1;
+            SCG_CU(cudaGetLastError());
+            return SCG_OK;
+        }
+    }
     if constexpr (KIND == SCG_QUAD_3D || KIND == SCG_QUAD_2D) {
         if (att == SCG_ATT_ROUNDTRIP) { e->last_queue = 0; k_rollout<KIND, real, SCG_ATT_ROUNDTRIP, false, false><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro); }
         else if (att == SCG_ATT_FAST_INTRINSIC && sizeof(real) == 4 && KIND == SCG_QUAD_3D)

@@ -5,6 +5,8 @@
 // Cold<real> : library-owned device memory; read with uniform loads only when a feature
 //              that needs it is enabled (dense constraint rows, disturbances, goal table, gates).
 #pragma once
+#include <cuda.h>   // CUtensorMap (types only: the encode entry point is fetched through the runtime, no -lcuda)
+
 #include "scg_math.cuh"
 #include "../../include/scg_b200.h"
 
@@ -182,6 +184,22 @@ template <typename real> struct Roll {
     // q_tickets = chunks * q_env_blocks ranges of q_chunk control steps each
     int32_t* q_mem; int32_t q_chunk; int32_t q_env_blocks; int32_t q_tickets; uint32_t q_sleep_ns;
 };
+
+// Staged trajectory log (k_rollout_tlog, scg_step.cuh): two TMA descriptors over the caller's log tensor viewed as the 2-D
+// array [rows = logged steps x 16][n] of floats -- `full` stores a box of LOG_T logged steps x 16 fields x 32 envs (what one
+// warp stages), `one` a single logged step (the tail of a launch).  Encoded on the host per launch (scg_k_3d_f_tlog.cu).
+struct alignas(64) LogMaps { CUtensorMap full; CUtensorMap one; };
+#ifndef SCG_LOG_T
+#define SCG_LOG_T 2
+#endif
+constexpr int LOG_T = SCG_LOG_T;             // logged steps per TMA store
+#ifndef SCG_LOG_STAGES
+#define SCG_LOG_STAGES 1
+#endif
+constexpr int LOG_STAGES = SCG_LOG_STAGES;   // stages per warp.  One is enough: a stage is rewritten a whole control step after it was handed to the TMA
+                                             // unit (the wait before the rewrite never blocks), and 8 KB per block keep nine blocks per SM resident --
+                                             // measured 53.0 G env-steps/s against 49.9 G with two stages / eight blocks (profiles/r2_summary.md)
+constexpr int LOG_STAGE = LOG_T * 16 * 32;   // floats of one stage of one warp (two warps per block)
 
 template <typename real> struct ResetInject { const real* init; const real* inertia; const int32_t* offsets; };
 

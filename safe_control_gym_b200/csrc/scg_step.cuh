@@ -871,8 +871,7 @@ SCG_DEV float warp_sum(float v) {
 
 // the Logger record (Logger.py:50-66): pos3 vel3 rpy3 ang_vel3 rpm4, [16][n] per logged step
 template <int KIND, typename real, bool FASTMATH>
-SCG_DEV void write_log(const Hot<real>& h, const EnvRegs<KIND, real>& e, const Motors<real>& mot, real* __restrict__ L, int64_t n) {
-    real rec[16];
+SCG_DEV void log_record(const Hot<real>& h, const EnvRegs<KIND, real>& e, const Motors<real>& mot, real (&rec)[16]) {
     if constexpr (KIND == SCG_QUAD_3D) {
         rec[0] = e.x[0]; rec[1] = e.x[2]; rec[2] = e.x[4]; rec[3] = e.x[1]; rec[4] = e.x[3]; rec[5] = e.x[5];
         rec[6] = e.a3.rpy[0]; rec[7] = e.a3.rpy[1]; rec[8] = e.a3.rpy[2];
@@ -889,9 +888,27 @@ SCG_DEV void write_log(const Hot<real>& h, const EnvRegs<KIND, real>& e, const M
     }
 #pragma unroll
     for (int j = 0; j < 4; ++j) rec[12 + j] = motor_rpm<real, FASTMATH>(h, mot, j);
+}
+template <int KIND, typename real, bool FASTMATH>
+SCG_DEV void write_log(const Hot<real>& h, const EnvRegs<KIND, real>& e, const Motors<real>& mot, real* __restrict__ L, int64_t n) {
+    real rec[16];
+    log_record<KIND, real, FASTMATH>(h, e, mot, rec);
 #pragma unroll
     for (int j = 0; j < 16; ++j) L[int64_t(j) * n] = rec[j];
 }
+
+// ---- staged log store (TLOG): shared memory -> global through the TMA unit (cp.async.bulk.tensor, SASS UTMASTG).
+// Every lane parks its 16-float record in its warp's stage ([LOG_T][16][32] floats, conflict-free); after LOG_T logged steps
+// ONE lane issues ONE bulk tensor store of the [LOG_T * 16][32] box -- 16 STS per env-step instead of 16 strided STG with
+// their 64-bit address arithmetic.  The hardware clips the box at the tensor's edges (ragged last warp: columns >= n).
+SCG_DEV void tma_fence_smem_writes() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+SCG_DEV void tma_store_2d(const CUtensorMap* map, const float* smem, int32_t col, int32_t row) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];"
+                 :: "l"(reinterpret_cast<uint64_t>(map)), "r"(col), "r"(row), "r"(uint32_t(__cvta_generic_to_shared(smem))) : "memory");
+}
+SCG_DEV void tma_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N> SCG_DEV void tma_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" :: "n"(N) : "memory"); }
+SCG_DEV void tma_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
 template <int NU, typename real> struct ActVec;
 template <> struct ActVec<4, float> { using type = float4; };
@@ -974,9 +991,10 @@ k_reset(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold
 constexpr int SPARE_CADENCE = SCG_SPARE_CADENCE;   // control steps between the warp-wide spare refills (power of two)
 constexpr int ACC_LD = ENV_BLOCK + 1;   // column ENV_BLOCK is the scratch column of out-of-range lanes
 constexpr int N_ACC = 11;   // episodes, return, length, truncated, completed, violated episodes, violation steps, (mse: double column), env steps, gates, collisions
-template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN, bool SPEC>
+template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN, bool SPEC, bool TLOG = false>
 SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ cold, const Buf<real>& b, const Roll<real>& ro,
-                           const int64_t i, const int k0, const int k1, float* const ep_acc, double* const mse_acc, real* const sp) {
+                           const int64_t i, const int k0, const int k1, float* const ep_acc, double* const mse_acc, real* const sp,
+                           const LogMaps* const lg_maps = nullptr, float* const lg_warp = nullptr) {
     constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
     const int64_t n = b.n;
     // Out-of-range lanes of the last env block READ env n - 1 and compute along with the warp, but every global side
@@ -1030,6 +1048,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
 #pragma unroll
         for (int j = 0; j < NU; ++j) nxt[j] = real(0);
     }
+    int lg_slot = 0, lg_stage = 0, lg_row0 = 0;   // TLOG (warp-uniform): records in the open stage, which stage, its first logged step
     bool fresh = false;   // obs must come from a reset this step
     // LEAN: spare initial state for the next episode (drawn ahead, see draw_init_lean)
     bool spare_ok = false;
@@ -1084,6 +1103,31 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
         if (any_out) {
             if (ro.reward_out && valid) ro.reward_out[int64_t(k) * n + ii] = reward;
             if (ro.done_out && valid) ro.done_out[int64_t(k) * n + ii] = done ? 1 : 0;
+            if constexpr (TLOG) {
+                if (k % ro.log_stride == 0) {   // uniform: the whole warp (shadow lanes included -- their columns are clipped) stages
+                    float rec[16];
+                    if constexpr (PAIRED) {
+                        EnvRegs<KIND, real> el = e;
+                        scalars_from_pairs(el);
+                        log_record<KIND, real, true>(h, el, mot, rec);
+                    } else log_record<KIND, real, true>(h, e, mot, rec);
+                    const int lane = threadIdx.x & 31;
+                    if (lg_slot == 0) {   // this stage's previous store (two stores ago) must have finished reading it
+                        if (lane == 0) tma_wait_read<LOG_STAGES - 1>();
+                        __syncwarp();
+                        lg_row0 = k / ro.log_stride;
+                    }
+                    float* const stg = lg_warp + lg_stage * LOG_STAGE;
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) stg[(lg_slot * 16 + j) * 32 + lane] = rec[j];
+                    if (++lg_slot == LOG_T) {
+                        tma_fence_smem_writes();
+                        __syncwarp();
+                        if (lane == 0) { tma_store_2d(&lg_maps->full, stg, int32_t(i) - lane, lg_row0 * 16); tma_commit(); }
+                        lg_slot = 0; lg_stage = lg_stage + 1 == LOG_STAGES ? 0 : lg_stage + 1;
+                    }
+                }
+            } else
             if (ro.log_out && (k % ro.log_stride) == 0 && valid) {
                 if constexpr (PAIRED) {
                     EnvRegs<KIND, real> el = e;   // the record reads the scalar layout
@@ -1150,6 +1194,17 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
             }
         }
     }
+    if constexpr (TLOG) {   // the records of an incomplete stage go out one logged step at a time; then drain
+        const int lane = threadIdx.x & 31;
+        if (lg_slot > 0) { tma_fence_smem_writes(); __syncwarp(); }
+        if (lane == 0) {
+            for (int s = 0; s < lg_slot; ++s)
+                tma_store_2d(&lg_maps->one, lg_warp + lg_stage * LOG_STAGE + s * 16 * 32, int32_t(i) - lane, (lg_row0 + s) * 16);
+            tma_commit();
+            tma_wait_all();
+        }
+        __syncwarp();
+    }
     if constexpr (PAIRED) scalars_from_pairs(e);
     // a range that ends inside the launch (ticket queue) hands over the state only: observation, env.state and the
     // per-step scalars are rewritten by the range that ends the launch
@@ -1209,6 +1264,35 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
     ep_acc[6 * ACC_LD] += s_viol; ep_acc[8 * ACC_LD] += float(k1 - k0);
     mse_acc[0] += double(s_mse); mse_acc[ACC_LD] += double(ep_acc[1 * ACC_LD]);
     if (!PLAIN) { ep_acc[9 * ACC_LD] += s_gates; ep_acc[10 * ACC_LD] += s_coll; }
+}
+
+// episode statistics of a block: warp-shuffle reduction, one atomic per warp per statistic
+template <bool PLAIN>
+SCG_DEV void reduce_stats(double* __restrict__ stats, const float* __restrict__ acc_buf, const double* __restrict__ mse_buf) {
+    if (stats) {
+        constexpr int NS = PLAIN ? 9 : 11;
+        const float* const a = acc_buf + threadIdx.x;
+        float v[11] = {a[0 * ACC_LD], a[1 * ACC_LD], a[2 * ACC_LD], a[6 * ACC_LD], a[7 * ACC_LD], a[3 * ACC_LD],
+                       a[4 * ACC_LD], a[5 * ACC_LD], a[8 * ACC_LD], a[9 * ACC_LD], a[10 * ACC_LD]};
+        const int slot[11] = {SCG_STAT_EPISODES, SCG_STAT_RETURN, SCG_STAT_LENGTH, SCG_STAT_VIOLATION_STEPS,
+                              SCG_STAT_MSE, SCG_STAT_TRUNCATED, SCG_STAT_COMPLETED, SCG_STAT_VIOLATED_EPISODES, SCG_STAT_ENV_STEPS,
+                              SCG_STAT_GATES, SCG_STAT_COLLISIONS};
+        // per-thread counts are exact in fp32 (<= 2^24 control steps per launch and thread); their sum over a warp is
+        // formed in fp64 so that it stays exact for any launch length
+#pragma unroll
+        for (int j = 0; j < NS; ++j) {
+            if (slot[j] == SCG_STAT_MSE || slot[j] == SCG_STAT_RETURN) continue;
+            double r = double(v[j]);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+            if ((threadIdx.x & 31) == 0 && r != 0.0) atomicAdd(stats + slot[j], r);
+        }
+        double m = mse_buf[threadIdx.x], r = mse_buf[ACC_LD + threadIdx.x];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { m += __shfl_xor_sync(0xffffffffu, m, o); r += __shfl_xor_sync(0xffffffffu, r, o); }
+        if ((threadIdx.x & 31) == 0 && m != 0.0) atomicAdd(stats + SCG_STAT_MSE, m);
+        if ((threadIdx.x & 31) == 0 && r != 0.0) atomicAdd(stats + SCG_STAT_RETURN, r);
+    }
 }
 
 SCG_DEV int32_t ld_acquire_gpu(const int32_t* p) {
@@ -1272,30 +1356,32 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
             push = k1 < ro.k_steps ? item + ro.q_env_blocks : 0;
         }
     }
-    if (b.stats) {   // warp-shuffle reduction, one atomic per warp per statistic
-        constexpr int NS = PLAIN ? 9 : 11;
-        const float* const a = acc_buf + threadIdx.x;
-        float v[11] = {a[0 * ACC_LD], a[1 * ACC_LD], a[2 * ACC_LD], a[6 * ACC_LD], a[7 * ACC_LD], a[3 * ACC_LD],
-                       a[4 * ACC_LD], a[5 * ACC_LD], a[8 * ACC_LD], a[9 * ACC_LD], a[10 * ACC_LD]};
-        const int slot[11] = {SCG_STAT_EPISODES, SCG_STAT_RETURN, SCG_STAT_LENGTH, SCG_STAT_VIOLATION_STEPS,
-                              SCG_STAT_MSE, SCG_STAT_TRUNCATED, SCG_STAT_COMPLETED, SCG_STAT_VIOLATED_EPISODES, SCG_STAT_ENV_STEPS,
-                              SCG_STAT_GATES, SCG_STAT_COLLISIONS};
-        // per-thread counts are exact in fp32 (<= 2^24 control steps per launch and thread); their sum over a warp is
-        // formed in fp64 so that it stays exact for any launch length
-#pragma unroll
-        for (int j = 0; j < NS; ++j) {
-            if (slot[j] == SCG_STAT_MSE || slot[j] == SCG_STAT_RETURN) continue;
-            double r = double(v[j]);
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
-            if ((threadIdx.x & 31) == 0 && r != 0.0) atomicAdd(b.stats + slot[j], r);
-        }
-        double m = mse_buf[threadIdx.x], r = mse_buf[ACC_LD + threadIdx.x];
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) { m += __shfl_xor_sync(0xffffffffu, m, o); r += __shfl_xor_sync(0xffffffffu, r, o); }
-        if ((threadIdx.x & 31) == 0 && m != 0.0) atomicAdd(b.stats + SCG_STAT_MSE, m);
-        if ((threadIdx.x & 31) == 0 && r != 0.0) atomicAdd(b.stats + SCG_STAT_RETURN, r);
-    }
+    reduce_stats<PLAIN>(b.stats, acc_buf, mse_buf);
 }
+
+// The same launch shape as k_rollout<..., QUEUE = false> with the trajectory log staged in shared memory and written by the
+// TMA unit (rollout_range<..., TLOG = true>; 3D fp32, launched from scg_k_3d_f_tlog.cu when the log tensor qualifies).
+template <int ATT, bool PLAIN, bool SPEC>
+#ifndef SCG_TLOG_BLOCKS
+#define SCG_TLOG_BLOCKS 9   // 96 registers, like the SPEC rollout kernels (SCG_BLOCKS_PER_SM)
+#endif
+__global__ void __launch_bounds__(ENV_BLOCK, SPEC ? SCG_TLOG_BLOCKS : 8)   // (the PLAIN kernel spills at 96 registers)
+k_rollout_tlog(const __grid_constant__ Hot<float> h, const Cold<float>* __restrict__ cold, const Buf<float> b, const Roll<float> ro,
+               const __grid_constant__ LogMaps maps) {
+    constexpr int KIND = SCG_QUAD_3D;
+    __shared__ float acc_buf[N_ACC * ACC_LD];
+    __shared__ double mse_buf[2 * ACC_LD];
+    __shared__ float sp_buf[(Spare<KIND, float, ATT>::N + (PLAIN ? 0 : SPARE_EXTRA)) * ENV_BLOCK];
+    __shared__ __align__(128) float lg_buf[2 * LOG_STAGES * LOG_STAGE];   // [warp][stage][LOG_T][16][32]
+    mse_buf[threadIdx.x] = 0.0; mse_buf[ACC_LD + threadIdx.x] = 0.0;
+#pragma unroll
+    for (int j = 0; j < N_ACC; ++j) acc_buf[j * ACC_LD + threadIdx.x] = 0.f;
+    const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    rollout_range<KIND, float, ATT, true, PLAIN, SPEC, true>(h, cold, b, ro, i, 0, ro.k_steps, acc_buf + (i < b.n ? threadIdx.x : ENV_BLOCK),
+                                                            mse_buf + (i < b.n ? threadIdx.x : ENV_BLOCK), sp_buf + threadIdx.x, &maps,
+                                                            lg_buf + (threadIdx.x >> 5) * LOG_STAGES * LOG_STAGE);
+    reduce_stats<PLAIN>(b.stats, acc_buf, mse_buf);
+}
+
 
 }  // namespace scg

@@ -160,6 +160,11 @@ class BatchedEnvBase:
         """True when the last fused rollout launch went through the ticket queue."""
         return bool(self.lib.scg_last_rollout_queue(self._h))
 
+    @property
+    def last_rollout_tlog(self):
+        """True when the last fused rollout wrote its trajectory log through the TMA unit (scg_last_rollout_tlog)."""
+        return bool(self.lib.scg_last_rollout_tlog(self._h))
+
     def set_injection(self, channel, k, tensor):
         """Feed pre-drawn noise for disturbance ``k`` of ``channel`` ([dim, N]); None = Philox."""
         ch = {"observation": L.CH_OBSERVATION, "action": L.CH_ACTION, "dynamics": L.CH_DYNAMICS}[channel]

@@ -307,3 +307,34 @@ def test_bench_path_matches_oracle_on_sampled_lanes(k):
     assert resets >= 5
     print(f"bench path (fast_intrinsic, SPEC, automatic queue, K = {k}): worst state err {worst:.2e} on {len(lanes)} lanes, {resets} resets")
     env.close()
+
+
+@pytest.mark.parametrize("variant", ["spec", "plain", "lean_gates"])
+@pytest.mark.parametrize("n,k,stride", [(4100, 37, 1), (4100, 40, 3), (64 * 1184 + 8, 9, 1)])
+def test_tma_staged_log_equals_plain_log(variant, n, k, stride):
+    """Row X1: the trajectory log written through the TMA unit (records staged in shared memory, one bulk tensor store per
+    warp and LOG_T logged steps, scg_step.cuh: rollout_range<..., TLOG>) carries the same bytes as the plain strided
+    stores -- ragged last warp (columns clipped by the hardware), an odd number of logged steps (the tail goes out one
+    step at a time), log strides, more than one wave of blocks, and all three kernel variants."""
+    over = {"spec": {}, "plain": dict(done_on_violation=False), "lean_gates": dict(gate_geometry=True)}[variant]
+    a, b = _quad(n, attitude="fast_intrinsic", **over), _quad(n, attitude="fast_intrinsic", **over)
+    assert int(a.lib.scg_kernel_variant(a._h)) == {"spec": 3, "plain": 2, "lean_gates": 1}[variant]
+    b.set_rollout_queue(1)   # a forced queue keeps the plain store path (k < 64: static grid, plain stores)
+    acts = _actions(n, k, std=0.01)
+    rows = (k + stride - 1) // stride
+    la = torch.full((rows, 16, n), float("nan"), device="cuda"); lb = torch.full((rows, 16, n), float("nan"), device="cuda")
+    a.reset(); b.reset()
+    for _ in range(2):
+        a.rollout(acts, log_out=la, log_stride=stride); b.rollout(acts, log_out=lb, log_stride=stride)
+        torch.cuda.synchronize()
+        assert a.last_rollout_tlog == (variant != "lean_gates") and not b.last_rollout_tlog   # the LEAN kernels keep plain stores
+        assert not torch.isnan(la).any() and torch.equal(la, lb)
+        for name in ("state", "ctrl_step", "episode", "flags", "obs", "ep_length"):
+            assert torch.equal(getattr(a, "buf_" + name), getattr(b, "buf_" + name)), name
+    assert a.stats()["episodes"] == b.stats()["episodes"]
+    # a log tensor the TMA unit cannot address (row pitch not a multiple of 16 bytes) takes the plain path
+    c = _quad(4099, attitude="fast_intrinsic", **over)
+    c.reset()
+    c.rollout(_actions(4099, 8), log_out=torch.empty(8, 16, 4099, device="cuda"))
+    assert not c.last_rollout_tlog
+    a.close(); b.close(); c.close()

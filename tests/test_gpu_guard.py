@@ -57,7 +57,7 @@ def _extra(shape, dtype=torch.float32):
     return big, mid
 
 
-@pytest.mark.parametrize("n", [5037, 64 * 3 + 1, 2 * 1184 * 64 + 5])
+@pytest.mark.parametrize("n", [5037, 5036, 64 * 3 + 1, 2 * 1184 * 64 + 4])
 def test_guard_bands_config2(n):
     from safe_control_gym_b200.envs.quadrotor import BatchedQuadrotor
     env = BatchedQuadrotor(num_envs=n, dtype=torch.float32, attitude="fast_intrinsic", **bench.env_kwargs())
@@ -73,6 +73,7 @@ def test_guard_bands_config2(n):
         rbig, rew = _extra((k, n)); dbig, dn = _extra((k, n), torch.uint8)
         lbig, log = _extra(((k + 2) // 3, 16, n))
         env.rollout(acts, reward_out=rew, done_out=dn, log_out=log, log_stride=3)
+        assert env.last_rollout_tlog == (mode == 0 and n % 4 == 0)   # TMA-staged log store on the static grid
         env.rollout(acts)
         torch.cuda.synchronize()
         _check(bigs + [("reward_out", rbig), ("done_out", dbig), ("log_out", lbig)], f"rollout queue={mode}")
