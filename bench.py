@@ -55,6 +55,53 @@ def env_kwargs():
                 normalized_rl_action_space=False, seed=1337)
 
 
+def config3_kwargs():
+    """BASELINE configs[2]: the cartpole_config of tests/scripts/verbose_api.yaml:1-91 -- 50 / 50 Hz,
+    10 s episodes (T = 500), true pole length 1.0 with randomised inertial properties, randomised init, default input +
+    state constraints (10 values), cost quadratic, done_on_violation -- with the white-noise disturbance (std 0.1) on the
+    ACTION channel, drawn from Philox per env and step."""
+    u = lambda lo, hi: dict(distrib="uniform", low=lo, high=hi)
+    return dict(ctrl_freq=50, pyb_freq=50, episode_len_sec=10, cost="quadratic", task="traj_tracking",
+                task_info=dict(stabilization_goal=[0], stabilization_goal_tolerance=0.01, trajectory_type="circle", num_cycles=1,
+                               trajectory_plane="zx", trajectory_position_offset=[0, 0], trajectory_scale=0.2),
+                init_state=dict(init_x=0, init_x_dot=0, init_theta=0, init_theta_dot=0), randomized_init=True,
+                init_state_randomization_info={k: u(-0.05, 0.05) for k in ["init_x", "init_x_dot", "init_theta", "init_theta_dot"]},
+                inertial_prop=dict(pole_length=1.0, pole_mass=0.1, cart_mass=1.0), randomized_inertial_prop=True,
+                inertial_prop_randomization_info=dict(pole_length=u(-0.25, 0.0), cart_mass=u(0.5, 1.5), pole_mass=u(0.05, 0.15)),
+                constraints=[dict(constraint_form="default_constraint", constrained_variable="input", strict=False),
+                             dict(constraint_form="default_constraint", constrained_variable="state")],
+                disturbances=dict(action=[dict(disturbance_func="white_noise", std=0.1)]),
+                done_on_violation=True, done_on_out_of_bound=True, info_in_reset=True, seed=1337)
+
+
+def config4_kwargs():
+    """BASELINE configs[3]: Quadrotor 2D, 60 / 240 Hz (S = 4), 10 s episodes (T = 600); per-episode
+    mass = nominal +- 0.01 kg and Iyy +- 1e-6 that REACH the integrator (dyn_uses_episode_inertia: extension, F9); action
+    channel: impulse (0.02 N, duration 10, decay 0.9, random offset) + step (0.01 N, random offset); default input + state
+    constraints (16 values); stabilisation, cost rl_reward, out-of-bound termination."""
+    u = lambda lo, hi: dict(distrib="uniform", low=lo, high=hi)
+    return dict(quad_type=2, ctrl_freq=60, pyb_freq=240, episode_len_sec=10, task="stabilization", cost="rl_reward",
+                task_info=dict(stabilization_goal=[0, 1], stabilization_goal_tolerance=0.05),
+                init_state=dict(init_x=0, init_x_dot=0, init_z=1.0, init_z_dot=0, init_theta=0, init_theta_dot=0), randomized_init=True,
+                init_state_randomization_info={"init_x": u(-0.3, 0.3), "init_z": u(-0.3, 0.3), "init_theta": u(-0.2, 0.2),
+                                               "init_theta_dot": u(-0.5, 0.5)},
+                randomized_inertial_prop=True, dyn_uses_episode_inertia=True,
+                inertial_prop_randomization_info={"M": u(-0.01, 0.01), "Iyy": u(-1e-6, 1e-6)},
+                disturbances={"action": [dict(disturbance_func="impulse", magnitude=0.02, step_offset=None, duration=10, decay_rate=0.9),
+                                         dict(disturbance_func="step", magnitude=0.01, step_offset=None)]},
+                constraints=[dict(constraint_form="default_constraint", constrained_variable="input"),
+                             dict(constraint_form="default_constraint", constrained_variable="state")],
+                done_on_violation=False, done_on_out_of_bound=True, rew_exponential=True, seed=1337)
+
+
+def config5_kwargs():
+    """BASELINE configs[4]: the headline 3D scenario (level0's gates + obstacles) with the analytic
+    gate-pass / contact geometry ON (extension, F5); every env logs the 16-float Logger record every control step."""
+    kw = env_kwargs()
+    kw["gate_geometry"] = True
+    return kw
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
 
@@ -130,6 +177,173 @@ def cpu_reference(sample_envs, sample_steps, repeats, threads=0):
         co.rollout(acts)
         times.append(time.perf_counter() - t0)
     return sample_envs * sample_steps / (sum(times) / len(times)), co.num_threads(), times
+
+
+# --------------------------------------------------------------------------------------------------------------------
+# The other BASELINE configs and the two other modes of config 2 (host-driven step(), closed
+# loop), each measured the same way: warm-up launch, then `reps` back-to-back launches between CUDA events on the launching
+# stream, barrier + synchronize on both sides, MAX over ranks.  Inputs are larger than L2 (config 3: 8.4 GB, 4: 5 GB,
+# 5: 27 GB of actions) except where noted.
+def cpu_port(kind, sample_envs, sample_steps, threads=0):
+    """env-steps/s of the C/OpenMP port of config `kind` (oracle/scg_oracle.c) on the host cores, one rollout of the sample."""
+    import numpy as np
+    from oracle import c_oracle as co
+    threads = threads or host_threads()
+    rng = np.random.default_rng(1337)
+    if kind == "3":
+        from oracle.cartpole_oracle import CartPoleOracle
+        kw = config3_kwargs(); seed = kw.pop("seed")
+        port = co.COracleCartPole(CartPoleOracle(**kw), n=sample_envs, seed=seed, threads=threads)
+        acts, extra = rng.normal(0, 3.0, size=(sample_steps, sample_envs, 1)), {}
+    else:
+        from oracle.quad_oracle import QuadOracle
+        kw = config4_kwargs() if kind == "4" else config5_kwargs(); seed = kw.pop("seed")
+        port = co.COracleQuadExt(QuadOracle(**kw), n=sample_envs, seed=seed, threads=threads)
+        if kind == "4":
+            hover = 0.03454 * 9.8 / 2
+            acts, extra = np.clip(hover + rng.normal(0, 0.005, size=(sample_steps, sample_envs, 2)), 0, 4 * hover), {}
+        else:
+            acts = np.clip(0.03454 * 9.8 / 4 + rng.normal(0, 0.005, size=(sample_steps, sample_envs, 4)), 0.0281616878, 0.1483414471)
+            extra = dict(log_out=np.zeros((sample_steps, 16, sample_envs)))
+    port.reset()
+    port.rollout(acts[:max(1, sample_steps // 10)])
+    t0 = time.perf_counter()
+    port.rollout(acts, **extra)
+    dt = time.perf_counter() - t0
+    return {"value": sample_envs * sample_steps / dt, "unit": "env-steps/s", "cores": port.num_threads(), "kind": "port",
+            "sample": f"{sample_envs} envs x {sample_steps} ctrl steps, C/OpenMP port (oracle/scg_oracle.c), fp64"}
+
+
+def timed_launches(torch, dist, world, dev, fn, reps, sampler=None):
+    """Average seconds per call of fn over `reps` back-to-back calls, device-timed, max over ranks."""
+    fn()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    marks = []
+    for _ in range(reps):
+        fn()
+        if sampler is not None:   # long runs: keep a few launches queued so that neither side waits for the other
+            m = torch.cuda.Event(); m.record(); marks.append(m)
+            if len(marks) > 4:
+                marks.pop(0).synchronize()
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t = torch.tensor([e0.elapsed_time(e1) * 1e-3 / reps], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def run_configs(torch, dist, world, rank, dev, args, fp32_peak, hbm_peak):
+    """BASELINE configs[2..4] + the host-driven and closed-loop modes of config 2 -> the `configs` array of the JSON line."""
+    from safe_control_gym_b200.envs.cartpole import BatchedCartPole
+    from safe_control_gym_b200.envs.quadrotor import BatchedQuadrotor
+    out = []
+    sc = args.config_scale
+
+    def entry(cid, workload, n, k, dt, bound, per_step, cpu, parity, **more):
+        value = world * n * k / dt
+        per_gpu = n * k / dt
+        ach = per_gpu * per_step / (1e12 if bound == "fp32" else 1e9)
+        peak = fp32_peak if bound == "fp32" else hbm_peak
+        e = {"id": cid, "workload": workload, "envs_per_gpu": n, "ctrl_steps_per_launch": k, "value": value, "unit": "env-steps/s",
+             "ms_per_launch": dt * 1e3, "scaling": "weak",
+             "roofline": {"bound": bound, "achieved": ach, "peak": peak, "unit": "TFLOP/s" if bound == "fp32" else "GB/s", "frac": ach / peak,
+                          ("flops_per_env_step" if bound == "fp32" else "bytes_per_env_step"): per_step, "traffic": None},
+             "cpu_baseline": cpu, "parity_test": parity}
+        e.update(more)
+        return e
+
+    def cpu(kind, envs, steps):
+        return cpu_port(kind, envs, steps) if (rank == 0 and world == 1 and not args.no_cpu) else None
+
+    if "3" in args.configs:
+        n, k = max(64, int(4 * 1024 * 1024 * sc)), 500
+        kw = config3_kwargs(); kw.pop("info_in_reset")
+        env = BatchedCartPole(num_envs=n, device=dev, dtype=torch.float32, auto_reset=True, seed_offset=rank * n, **kw)
+        g = torch.Generator(device=dev); g.manual_seed(3 + rank)
+        a = torch.empty(k, n, 1, dtype=torch.float32, device=dev).normal_(0.0, 3.0, generator=g).clamp_(-10.0, 10.0)
+        env.reset()
+        dt = timed_launches(torch, dist, world, dev, lambda: env.rollout(a), 8)
+        out.append(entry("3", "cartpole_4Mx500_white_noise_action_default_constraints", n, k, dt, "fp32", 240, cpu("3", 262144, 200),
+                         "tests/test_gpu_teacher_forced.py::test_config3_cartpole_teacher_forced (1e-5 per step vs the fp64 oracle; parity "
+                         "unpinned: the env is absent from the reference fork, SURVEY.md F2)",
+                         kernel_variant=int(env.lib.scg_kernel_variant(env._h)), episodes=env.stats()["episodes"]))
+        env.close(); del env, a
+        torch.cuda.empty_cache()
+    if "4" in args.configs:
+        n, k = max(64, int(1024 * 1024 * sc)), 600
+        kw = config4_kwargs()
+        env = BatchedQuadrotor(num_envs=n, device=dev, dtype=torch.float32, auto_reset=True, seed_offset=rank * n, **kw)
+        hover = env.MASS * 9.8 / 2
+        g = torch.Generator(device=dev); g.manual_seed(4 + rank)
+        a = torch.empty(k, n, 2, dtype=torch.float32, device=dev).normal_(hover, 0.005, generator=g).clamp_(0.0, 4 * hover)
+        env.reset()
+        dt = timed_launches(torch, dist, world, dev, lambda: env.rollout(a), 16)
+        out.append(entry("4", "quadrotor2d_1Mx600_impulse_step_per_env_inertia", n, k, dt, "fp32", 120 + 60 * SUBSTEPS, cpu("4", 65536, 200),
+                         "tests/test_gpu_teacher_forced.py::test_config4_quad2d_teacher_forced (1e-5 per step vs the fp64 oracle; per-env "
+                         "inertia in the integrator is an extension over the reference's DYN behaviour, SURVEY.md F9)",
+                         kernel_variant=int(env.lib.scg_kernel_variant(env._h)), episodes=env.stats()["episodes"]))
+        env.close(); del env, a
+        torch.cuda.empty_cache()
+    if "5" in args.configs:
+        # weak: 16 M envs on one GPU, 2 M per GPU on N > 1 (SURVEY.md 8d: "N fixed per GPU"); strong: 16 M in total
+        k = 100
+        shapes = [("5", max(64, int((16 if world == 1 else 2) * 1024 * 1024 * sc)), "weak")]
+        if world > 1:
+            shapes.append(("5-strong", max(64, int(16 * 1024 * 1024 * sc) // world), "strong"))
+        for cid, n, scaling in shapes:
+            for gates in (True, False):
+                kw = config5_kwargs(); kw["gate_geometry"] = gates
+                env = BatchedQuadrotor(num_envs=n, device=dev, dtype=torch.float32, attitude=args.attitude, auto_reset=True,
+                                       seed_offset=rank * n, **kw)
+                a = make_actions(torch, n, k, dev, 5 + rank, args.action_std)
+                log = torch.empty(k, 16, n, dtype=torch.float32, device=dev)
+                env.reset()
+                dt = timed_launches(torch, dist, world, dev, lambda: env.rollout(a, log_out=log, log_stride=1), 8 if gates else 24)
+                st = env.stats()
+                e = entry(cid if gates else cid + "-gates-off", "quadrotor3d_%dx100_logged_every_step_gate_geometry_%s" % (n * world, "on" if gates else "off"),
+                          n, k, dt, "hbm", 80, cpu("5", 32768, 100) if (gates and cid == "5") else None,
+                          "tests/test_gpu_gates.py (gate / contact geometry vs oracle/gate_geometry.py: an extension, parity unpinned -- PyBullet's "
+                          "queries are dead in DYN, SURVEY.md F5); tests/test_gpu_batch.py::test_logged_rollout_record, "
+                          "::test_tma_staged_log_equals_plain_log (the Logger record, bit-exact)",
+                          log_store="tma" if env.last_rollout_tlog else "plain", gates_passed=st["gates"], collisions=st["collisions"])
+                e["scaling"] = scaling
+                out.append(e)
+                env.close(); del env, a, log
+                torch.cuda.empty_cache()
+    if "2h" in args.configs:
+        n, k = args.envs, 500
+        env = BatchedQuadrotor(num_envs=n, device=dev, dtype=torch.float32, attitude=args.attitude, auto_reset=True, seed_offset=rank * n, **env_kwargs())
+        a = make_actions(torch, n, k, dev, 7 + rank, args.action_std)
+        env.reset()
+
+        def loop():
+            for t in range(k):
+                env.step(a[t])
+        dt = timed_launches(torch, dist, world, dev, loop, 2)
+        out.append(entry("2-host-driven", "quadrotor3d_dyn_65536_host_driven_step", n, k, dt, "hbm", 180, None,
+                         "tests/test_gpu_batch.py::test_fused_rollout_equals_host_driven_steps; tests/test_gpu_golden.py (every golden scenario steps "
+                         "through scg_step)", us_per_step=dt / k * 1e6,
+                         note="one scg_step launch per control step from Python (facade + launch latency included); state is L2-resident"))
+        env.close(); del env, a
+    if "2c" in args.configs:
+        n, k = args.envs, 1000
+        env = BatchedQuadrotor(num_envs=n, device=dev, dtype=torch.float32, attitude=args.attitude, auto_reset=True, seed_offset=rank * n, **env_kwargs())
+        env.reset()
+        dt = timed_launches(torch, dist, world, dev, lambda: env.rollout_pid(k), 8)
+        out.append(entry("2-closed-loop", "quadrotor3d_dyn_65536x1000_on_device_pid", n, k, dt, "fp32", FLOPS_PER_STEP, None,
+                         "tests/test_gpu_pid.py (actions vs oracle/pid_oracle.py, itself pinned on the reference's PIDController)",
+                         note="actions computed on the device by the DSL PID (quadrotor_utils.py:70-278): no action table, no H2D traffic; the PID's own "
+                              "~330 flop per step are not counted"))
+        env.close(); del env
+    torch.cuda.empty_cache()
+    return out
 
 
 def run_reference(args):
@@ -245,34 +459,81 @@ def run_gpu(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = world * n * k * e2e_steps / float(t.item())
+    h2d_bytes = int(host_actions.numel() * 4)
+
+    # ---- sustained: >= 2 s of back-to-back headline launches with the clocks / power sampled inside that window
+    class _PowerSampler(ClockSampler):
+        def __init__(self, idx):
+            super().__init__(idx)
+            self.q += ",power.draw"
+
+        def power_max(self):
+            p = [float(r[6]) for r in self.rows if len(r) > 6 and r[6].replace(".", "", 1).isdigit()]
+            return max(p) if p else None
+    sus_reps = max(10, int(args.sustain_seconds / (total_ms * 1e-3 / args.steps)))
+    with _PowerSampler(local) as sclk:
+        sus_dt = timed_launches(torch, dist, world, dev, one_step, sus_reps, sampler=sclk)
+        drain()
+        torch.cuda.synchronize()
+    value_sustained = world * n * k / sus_dt
+    sustained = {"value": value_sustained, "unit": "env-steps/s", "seconds": sus_dt * sus_reps, "launches": sus_reps,
+                 "clocks": sclk.summary(), "power_w_max": sclk.power_max()}
+
+    # ---- end to end, closed loop: what the reference's own loops do (competition/getting_started.py:142-316, tests/scripts/tracking.py)
+    # -- a controller turns observations into actions.  Here the DSL PID runs on the device (scg_rollout_pid): nothing goes to the GPU
+    # per step, the final observations and the statistics come back.
+    env.reset()
+
+    def one_e2e_pid():
+        env.rollout_pid(k)
+        obs_host.copy_(env.buf_obs, non_blocking=True)
+        st = env.buf_stats.cpu()
+        torch.cuda.synchronize()
+        return st
+    one_e2e_pid()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        one_e2e_pid()
+    t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_pid_value = world * n * k * e2e_steps / float(t.item())
+    variant_id = int(env.lib.scg_kernel_variant(env._h))
+    del actions, host_actions
+    env.close()
+    torch.cuda.empty_cache()
+    peak = C.c_double()
+    L.check(L.load().scg_measure_fp32_peak(C.byref(peak)))
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        hbm_peak, hbm_src = float(peaks["hbm_gbs"]), "MEASURED_PEAKS.json"
+    except Exception:
+        hbm_peak, hbm_src = 6650.0, "fallback (B200_PROFILING.md)"
+    configs = run_configs(torch, dist, world, rank, dev, args, peak.value, hbm_peak) if args.configs else []
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
     # ---- roofline of the dominant kernel (k_rollout<3, float, ATT, ...>): one launch per step
-    variant = {0: "GENERAL", 1: "LEAN", 2: "LEAN,PLAIN", 3: "LEAN,PLAIN,SPEC"}[int(env.lib.scg_kernel_variant(env._h))]
+    variant = {0: "GENERAL", 1: "LEAN", 2: "LEAN,PLAIN", 3: "LEAN,PLAIN,SPEC"}[variant_id]
     if queued:
         variant += ",QUEUE"
-    peak = C.c_double()
-    L.check(L.load().scg_measure_fp32_peak(C.byref(peak)))
     kernel_ms = sum(per) / len(per)   # one launch per step; stats all-reduce excluded at N = 1
     flops = float(n) * k * FLOPS_PER_STEP
     achieved_tf = flops / (kernel_ms * 1e-3) / 1e12
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        hbm_peak, hbm_src = float(peaks["hbm_gbs"]), "MEASURED_PEAKS.json"
-    except Exception:
-        hbm_peak, hbm_src = 6650.0, "fallback (B200_PROFILING.md)"
     hbm_bytes = float(n) * k * BYTES_PER_STEP_FUSED + n * (12 * 4 * 3 + 24)
-    traffic = None
+    traffic, fma_pipe = None, None
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
         try:
-            traffic = json.load(open(tp)).get("k_env_rollout_dram_bytes_per_launch")
+            tj = json.load(open(tp))
+            traffic, fma_pipe = tj.get("k_env_rollout_dram_bytes_per_launch"), tj.get("k_env_rollout_fma_pipe_frac")
         except Exception:
             traffic = None
-    cpu_v, cores, _ = cpu_reference(4096, 200, 3)
+    cpu_v, cores, _ = cpu_reference(4096, 200, 3) if not args.no_cpu else (None, 0, None)
     line = {
         "metric": METRIC, "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -282,7 +543,12 @@ def run_gpu(args):
                    "schedule": "ticket queue over (64-step chunk, 64-env block) units, one persistent launch" if queued else "one block per 64 envs",
                    "attitude": args.attitude, "action_std": args.action_std,
                    "l2_policy": "inputs larger than L2 (1.05 GB action table re-streamed each step)"},
+        "value_sustained": sustained,
         "roofline": {"bound": "fp32", "achieved": achieved_tf, "peak": peak.value, "unit": "TFLOP/s", "frac": achieved_tf / peak.value,
+                     "frac_meaning": "ALGORITHMIC flops of the literal reference sequence (632 per env-step, SURVEY.md 8d) over the measured FFMA peak; the "
+                                     "fast attitude path does not execute the quaternion round trip it is credited for.  The hardware view (ncu "
+                                     "sm__inst_executed_pipe_fma of the same kernel) is `fma_pipe_frac`.",
+                     "fma_pipe_frac": fma_pipe,
                      "traffic": traffic, "kernel": "scg::k_rollout<3,float,%s,%s>" % (args.attitude, variant), "kernel_ms": kernel_ms,
                      "flops_per_env_step": FLOPS_PER_STEP,
                      "peak_source": "measured live: register-only FFMA kernel (scg_measure_fp32_peak); MEASURED_PEAKS.json has no non-tensor fp32 figure",
@@ -291,8 +557,15 @@ def run_gpu(args):
                              "bytes_per_env_step": BYTES_PER_STEP_FUSED}},
         "cpu_baseline": {"value": cpu_v, "unit": "env-steps/s", "cores": cores, "kind": "port",
                          "sample": "4096 envs x 200 ctrl steps x 3, C/OpenMP oracle (oracle/scg_oracle.c), fp64"},
-        "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": int(host_actions.numel() * 4),
-                "d2h_bytes_per_step": int(obs_host.numel() * 4 + L.STATS_LEN * 8), "steps": e2e_steps, "chunk_ctrl_steps": args.chunk},
+        "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": h2d_bytes,
+                "d2h_bytes_per_step": int(obs_host.numel() * 4 + L.STATS_LEN * 8), "steps": e2e_steps, "chunk_ctrl_steps": args.chunk,
+                "mode": "open loop: a [1000, N, 4] fp32 action table in pinned host memory is streamed to the device every step (16 B per env-step "
+                        "over PCIe: %.1f GB/s per GPU)" % (h2d_bytes * e2e_value / (world * n * k) / 1e9),
+                "closed_loop": {"value": e2e_pid_value, "unit": "env-steps/s", "h2d_bytes_per_step": 0,
+                                "d2h_bytes_per_step": int(obs_host.numel() * 4 + L.STATS_LEN * 8),
+                                "mode": "actions from the on-device DSL PID (scg_rollout_pid), final observations + statistics read back: the shape of "
+                                        "the reference's own loops (controller in the loop, competition/getting_started.py:142-316)"}},
+        "configs": configs,
         "gpu_launches": launches, "clocks": clk.summary(),
         "episode_stats": {kk: stats[kk] for kk in ("episodes", "return", "length", "violation_steps", "env_steps")},
     }
@@ -324,6 +597,11 @@ def main():
     ap.add_argument("--chunk", type=int, default=50)
     ap.add_argument("--attitude", default="fast_intrinsic", help="fast_intrinsic (MUFU sin/cos) | fast (polynomial sin/cos) | roundtrip (literal)")
     ap.add_argument("--action-std", type=float, default=0.005)
+    ap.add_argument("--configs", default="3,4,5,2h,2c", type=lambda v: [c for c in v.split(",") if c],
+                    help="extra BASELINE configs measured after the headline: 3, 4, 5, 2h (host-driven step), 2c (closed loop); '' = none")
+    ap.add_argument("--config-scale", type=float, default=1.0, help="scale the env counts of the extra configs (smoke runs)")
+    ap.add_argument("--sustain-seconds", type=float, default=2.0)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline legs")
     args = ap.parse_args()
     # stdout carries exactly one JSON line: anything a library prints there (NCCL's version banner under torchrun) goes
     # to stderr instead -- fd 1 is pointed at fd 2 for the run and the line is written to the saved descriptor
