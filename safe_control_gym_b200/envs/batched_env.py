@@ -263,6 +263,9 @@ class BatchedEnvBase:
         if self._squeeze:
             i = {k: (v[0].cpu().numpy() if v.dim() > 1 else v[0].item()) for k, v in info.items()}
             i["constraint_values"] = np.asarray(i["constraint_values"], dtype=np.float64)
+            i["collision"] = (None, bool(i["collision"]))   # (object id, flag) (quadrotor.py:1046-1057; ids are PyBullet's)
+            if isinstance(i.get("current_target_gate_pos"), np.ndarray):
+                i["current_target_gate_pos"] = i["current_target_gate_pos"].tolist() if i["current_target_gate_id"] >= 0 else []
             return obs[0].cpu().numpy().astype(np.float64), float(rew[0].item()), bool(done[0].item()), i
         return obs, rew, done, info
 

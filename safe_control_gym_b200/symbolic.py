@@ -10,7 +10,8 @@ tensors, one sample ``[nx]`` / ``[nu]`` or a batch ``[N, nx]`` / ``[N, nu]``; th
 
 ``fd_func`` is fixed-step RK4 over ``dt`` (controllers/mpc/mpc_utils.py:79-101), not CasADi's CVODES
 integrator (symbolic_systems.py:70-73; adaptive BDF -- unreproducible bit-for-bit).
-``x_sym`` / ``u_sym`` / ``x_dot`` are kept as label lists for introspection; there is no expression graph.
+``fd_linear_func`` likewise (RK4 over the linearised field).  ``x_sym`` / ``u_sym`` / ``x_dot`` / ``cost_func`` are kept as
+labels for introspection (tests/scripts/verbose_api.py prints them); there is no expression graph.
 """
 import ctypes as C
 
@@ -31,6 +32,9 @@ class SymbolicModel:
         self.u_sym = list(input_labels or getattr(env, "ACTION_LABELS", [f"u{i}" for i in range(self.nu)]))
         self.y_sym = self.x_sym
         self.x_dot = [s + "_dot" for s in self.x_sym]
+        # cost (quadrotor.py:676-682): labels only, like x_sym -- `loss` evaluates it
+        self.cost_func = "0.5 * (X - Xr)' Q (X - Xr) + 0.5 * (U - Ur)' R (U - Ur)"
+        self.Q, self.R, self.Xr, self.Ur = "Q", "R", "Xr", "Ur"
 
     # ------------------------------------------------------------------ plumbing
     def _prep(self, x, u):
@@ -104,6 +108,30 @@ class SymbolicModel:
             dx, du = np.asarray(x_eval, float) - np.asarray(x, float), np.asarray(u_eval, float) - np.asarray(u, float)
             return f + np.einsum("...ij,...j->...i", A, dx) + np.einsum("...ij,...j->...i", B, du)
         return f + torch.einsum("...ij,...j->...i", A, x_eval - x) + torch.einsum("...ij,...j->...i", B, u_eval - u)
+
+    def fd_linear_func(self, x0=None, p=None, dt=None):
+        """Discrete LINEARISED dynamics (symbolic_systems.py:100-106): the ODE x_eval' = f(x, u) + A (x_eval - x) + B (u_eval - u),
+        linearised at (x, u), integrated over ``dt`` from x_eval = x0; CasADi call style ``fd_linear_func(x0=x_eval,
+        p=vertcat(u_eval, x, u))['xf']`` -- p is the concatenation [u_eval (nu), x (nx), u (nu)] along the last axis.
+        Fixed-step RK4 like ``fd_func`` (the reference integrates with CVODES); f, A, B come from the device (fc_func, df_func),
+        the four stages of the affine field are composed on the caller's side."""
+        dt = self.dt if dt is None else dt
+        as_numpy = not isinstance(x0, torch.Tensor)
+        xe = np.asarray(x0, dtype=np.float64) if as_numpy else x0
+        pp = np.asarray(p, dtype=np.float64) if not isinstance(p, torch.Tensor) else p
+        ue, x, u = pp[..., :self.nu], pp[..., self.nu:self.nu + self.nx], pp[..., self.nu + self.nx:]
+        f = self.fc_func(x, u)
+        A, B = self.df_func(x, u)
+        ein = np.einsum if as_numpy else torch.einsum
+        c = f + ein("...ij,...j->...i", B, ue - u) - ein("...ij,...j->...i", A, x)   # field(y) = A y + c
+
+        def field(y):
+            return ein("...ij,...j->...i", A, y) + c
+        k1 = field(xe)
+        k2 = field(xe + 0.5 * dt * k1)
+        k3 = field(xe + 0.5 * dt * k2)
+        k4 = field(xe + dt * k3)
+        return {"xf": xe + dt / 6.0 * (k1 + 2.0 * k2 + 2.0 * k3 + k4)}
 
     def g_linear_func(self, x_eval, u_eval, x, u):
         return x_eval

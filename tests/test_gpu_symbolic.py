@@ -88,3 +88,30 @@ def test_device_tensors_stay_on_device():
     f = env.symbolic.fc_func(x, u)
     assert f.is_cuda and f.shape == (8, 12) and float(f.abs().max()) < 1e-5   # hover equilibrium
     env.close()
+
+
+@pytest.mark.parametrize("kind", [2, 3])
+def test_fd_linear_func(kind):
+    """SymbolicModel.fd_linear_func (symbolic_systems.py:100-106): at the linearisation point with u_eval = u it is the exact
+    flow of the affine field x' = f + A (x_eval - x): one RK4 step of it against the matrix-exponential solution, and it
+    agrees with the non-linear fd_func to second order in dt."""
+    from scipy.linalg import expm
+    env, prm = _env(kind, torch.float64)
+    nx, nu = so.DIMS[kind]
+    rng = np.random.default_rng(40 + kind)
+    x = rng.normal(0, 0.2, size=(5, nx)); u = rng.uniform(0.05, 0.1, size=(5, nu))
+    xe = x + rng.normal(0, 0.01, size=x.shape); ue = u + rng.normal(0, 0.002, size=u.shape)
+    dt = 1.0 / 240
+    got = env.symbolic.fd_linear_func(x0=xe, p=np.concatenate([ue, x, u], axis=-1), dt=dt)["xf"]
+    f = env.symbolic.fc_func(x, u)
+    A, B = env.symbolic.df_func(x, u)
+    for i in range(5):
+        c = f[i] + B[i] @ (ue[i] - u[i]) - A[i] @ x[i]
+        M = np.zeros((nx + 1, nx + 1)); M[:nx, :nx] = A[i]; M[:nx, nx] = c   # d/dt [y; 1] = M [y; 1]
+        want = (expm(M * dt) @ np.append(xe[i], 1.0))[:nx]
+        assert _rel(got[i], want) <= 1e-10
+    nonlin = env.symbolic.fd_func(x0=xe, p=ue, dt=dt)["xf"]
+    assert _rel(got, nonlin) <= 1e-4
+    single = env.symbolic.fd_linear_func(x0=xe[0], p=np.concatenate([ue[0], x[0], u[0]]), dt=dt)["xf"]
+    assert single.shape == (nx,) and _rel(single, got[0]) <= 1e-14
+    env.close()
