@@ -283,6 +283,25 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
     if (h.need_cold_constraints || !same_strict) h.cfg |= CFG_COLD_CONSTRAINTS;
     if (c.n_dist[1] > 0 || c.n_dist[2] > 0 || c.adversary_channel == SCG_CH_ACTION || c.adversary_channel == SCG_CH_DYNAMICS)
         h.cfg |= CFG_DISTURBED;
+    {   // inline evaluation of the action-channel disturbances (Hot::ds_*)
+        bool simple = c.n_dist[1] > 0 && c.adversary_channel < 0 && !(c.n_dist[2] > 0 && c.dyn_applies_force);
+        for (int q = 0; q < c.n_dist[1] && simple; ++q) {
+            const scg_disturbance& s = c.dist[1][q];
+            simple = (s.kind == SCG_DIST_IMPULSE || s.kind == SCG_DIST_STEP || s.kind == SCG_DIST_WHITE) && !s.has_mask && !s.inject;
+        }
+        h.ds_n = 0;
+        if (simple) {
+            h.ds_n = c.n_dist[1];
+            for (int q = 0; q < c.n_dist[1]; ++q) {
+                const scg_disturbance& s = c.dist[1][q];
+                h.ds_kind[q] = s.kind; h.ds_off[q] = s.step_offset; h.ds_slot[q] = s.slot;
+                h.ds_mag[q] = real(s.magnitude); h.ds_half[q] = real(s.duration / 2.0); h.ds_decay[q] = real(s.decay_rate);
+                h.ds_l2decay[q] = real(std::log2(s.decay_rate > 0.0 ? s.decay_rate : 1.0));
+                for (int j = 0; j < SCG_MAX_NU; ++j) h.ds_std[q][j] = real(s.std[j]);
+            }
+            h.cfg |= CFG_DIST_SIMPLE;
+        }
+    }
     if (!h.quadratic_diag) h.cfg |= CFG_QR_DENSE;
     if (c.cost == SCG_COST_RL_REWARD && c.use_constraint_penalty) h.cfg |= CFG_PENALTY;
     // ---- LEAN kernel (scg_step.cuh): the auto-reset can take a spare initial state drawn ahead of time, i.e. reset()
@@ -295,6 +314,15 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
             if ((s.kind == SCG_DIST_IMPULSE || s.kind == SCG_DIST_STEP) && s.step_offset < 0) reset_draws = true;
         }
     if (reset_draws) h.cfg |= CFG_RESET_EXTRAS;
+    {
+        bool outside = false;
+        for (int ch = 0; ch < 3; ch += 2)
+            for (int q = 0; q < c.n_dist[ch]; ++q) {
+                const scg_disturbance& s = c.dist[ch][q];
+                if ((s.kind == SCG_DIST_IMPULSE || s.kind == SCG_DIST_STEP) && s.step_offset < 0) outside = true;
+            }
+        if (!outside) h.cfg |= CFG_SPARE_SIMPLE;
+    }
     h.step_row[0] = h.dt; h.step_row[1] = h.arm_s2; h.step_row[2] = h.km_over_kf; h.step_row[3] = h.inv_mass;
     h.step_row[4] = -h.dJ[1]; h.step_row[5] = h.kJ[1]; h.step_row[6] = -(h.gravity_force * h.inv_mass); h.step_row[7] = real(0);
     for (int j = 0; j < 3; ++j) {
@@ -422,6 +450,16 @@ extern "C" int scg_set_injection(scg_env* e, int channel, int k, const void* dev
     if (!e) return fail(SCG_ERR_NULL, "scg_set_injection: null env");
     if (channel == -1) { e->buf.adv_action = dev_ptr; return SCG_OK; }   // adversary action for the next step
     if (channel < 0 || channel > 2 || k < 0 || k >= e->cfg.n_dist[channel]) return fail(SCG_ERR_SHAPE, "no such disturbance");
+    if (channel == SCG_CH_ACTION) {
+        // injected draws are read by the general (out-of-line) evaluation only: the inline path is taken while no
+        // action-channel disturbance has a pointer set.  The constant block travels by value with every launch.
+        e->cfg.dist[channel][k].inject = dev_ptr;
+        bool any = false;
+        for (int q = 0; q < e->cfg.n_dist[SCG_CH_ACTION]; ++q) any = any || e->cfg.dist[SCG_CH_ACTION][q].inject != nullptr;
+        const bool simple = !any && e->hf.ds_n + e->hd.ds_n > 0;
+        if (simple) { e->hf.cfg |= CFG_DIST_SIMPLE; e->hd.cfg |= CFG_DIST_SIMPLE; }
+        else { e->hf.cfg &= ~CFG_DIST_SIMPLE; e->hd.cfg &= ~CFG_DIST_SIMPLE; }
+    }
     if (e->cfg.precision == 32) {
         Cold<float>* c = static_cast<Cold<float>*>(e->cold_host);
         c->dist[channel][k].inject = static_cast<const float*>(dev_ptr);

@@ -162,13 +162,13 @@ template <typename real> struct Att2 { real theta; real r3x, r3z; uint32_t flipp
 template <typename real>
 SCG_DEV void attitude2(real alpha_pre, uint32_t flipped_in, Att2<real>& a) {
     if (!flipped_in && m_abs(alpha_pre) < real(1.5663)) {
-        m_sincos(alpha_pre, &a.r3x, &a.r3z);
+        sincos_pi(alpha_pre, &a.r3x, &a.r3z);   // |alpha| < pi / 2: the compact ~1-ulp pair (fp64: sincos)
         a.theta = alpha_pre; a.flipped = 0u;
         return;
     }
     const real phys = flipped_in ? Consts<real>::pi - alpha_pre : alpha_pre;
     real s, c;
-    m_sincos(phys, &s, &c);
+    sincos_any(phys, &s, &c);
     a.r3x = s; a.r3z = c;
     if (s <= real(-0.99999)) { a.theta = -Consts<real>::half_pi; a.flipped = 0u; }
     else if (s >= real(0.99999)) { a.theta = Consts<real>::half_pi; a.flipped = 0u; }

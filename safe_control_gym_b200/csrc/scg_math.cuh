@@ -149,6 +149,41 @@ template <typename real> SCG_DEV void normal_pair(uint32_t w0, uint32_t w1, real
     *n0 = r * c;
     *n1 = r * s;
 }
+// Box-Muller for the fp32 fast paths: MUFU.LG2 / MUFU.SQRT / MUFU.SIN / MUFU.COS instead of libdevice's logf / sqrtf / sincosf
+// (~100 instructions with their slow-path branches).  The angle is taken in [-pi, pi): cos(2 pi u) = -cos(2 pi (u - 1/2)).
+// Same draws as normal_pair up to ~1e-6 relative (|ln u| >= 6e-8 keeps the MUFU.LG2 error relative to the radius small).
+template <typename real, bool FAST> SCG_DEV void normal_pair_f(uint32_t w0, uint32_t w1, real* n0, real* n1) {
+    if constexpr (FAST && sizeof(real) == 4) {
+        const float r = sqrt_fast(-2.f * __logf(u01<float>(w0)));
+        float s, c;
+        __sincosf(Consts<float>::two_pi * (u01<float>(w1) - 0.5f), &s, &c);
+        *n0 = -(r * c);
+        *n1 = -(r * s);
+    } else normal_pair<real>(w0, w1, n0, n1);
+}
+template <typename real, int DIM, bool FAST> SCG_DEV void draw_normals_f(const uint32_t seed, const uint32_t env, uint32_t index, uint32_t episode,
+                                                                         uint32_t stream, real (&z)[DIM]) {
+#pragma unroll
+    for (int b = 0; b < (DIM + 3) / 4; ++b) {
+        const U4 w = philox4x32_10(index, episode, stream, b, seed, env);
+        real n[4];
+        normal_pair_f<real, FAST>(w.x, w.y, &n[0], &n[1]);
+        if (4 * b + 2 < DIM) normal_pair_f<real, FAST>(w.z, w.w, &n[2], &n[3]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (4 * b + j < DIM) z[4 * b + j] = n[j];
+    }
+}
+// sin / cos of any angle for the fp32 fast paths: wrap + ~1-ulp polynomial pair (no libdevice slow path)
+SCG_DEV void sincos_any(float x, float* s, float* c) {
+    const float k = fast_rint(x * 0.15915494309189535f);
+    sincos_pi(fmaf(-k, -1.7484555e-07f, fmaf(-k, 6.2831855f, x)), s, c);
+}
+SCG_DEV void sincos_any(double x, double* s, double* c) { sincos(x, s, c); }
+// decay^k for a small non-negative integer k (impulse disturbances, disturbances.py:133-139): exp2(k log2 decay) in fp32
+SCG_DEV float pow_int(float decay, float l2decay, int k) { (void)decay; return exp2f(float(k) * l2decay); }
+SCG_DEV double pow_int(double decay, double l2decay, int k) { (void)l2decay; return pow(decay, double(k)); }
+
 SCG_DEV int32_t randint(uint32_t w, int32_t n) { return static_cast<int32_t>(__umulhi(w, static_cast<uint32_t>(n))); }
 
 // value i (of a vector draw) lives in word i % 4 of block i / 4

@@ -91,6 +91,11 @@ template <typename real> struct Hot {
     uint32_t init_block_mask;       // Philox blocks (4 labels each) holding a randomised init label
     uint32_t seed;
     uint32_t env_id_base_lo;
+    // CFG_DIST_SIMPLE: the action-channel disturbances the control-step loop evaluates INLINE -- impulse / step / white noise
+    // without mask or injected draws, no adversary, no external force (BASELINE configs 3 and 4, competition/level1-3.yaml):
+    // parameters as constant-bank operands instead of generic loads from Cold::dist behind an out-of-line call
+    int32_t ds_n, ds_kind[SCG_MAX_DIST], ds_off[SCG_MAX_DIST] /* >= 0 fixed, -1: this episode's draw */, ds_slot[SCG_MAX_DIST];
+    real ds_mag[SCG_MAX_DIST], ds_half[SCG_MAX_DIST], ds_decay[SCG_MAX_DIST], ds_l2decay[SCG_MAX_DIST], ds_std[SCG_MAX_DIST][SCG_MAX_NU];
     // the uniform switches the control-step loop tests, packed (CFG_*): one constant-bank word feeds all of
     // them, where a separate field per switch costs a dependent load -> compare -> branch chain each
     uint32_t cfg;
@@ -116,6 +121,8 @@ enum : uint32_t {
     CFG_MSE_POS = 1u << 20,         // 3D: info["mse"] weighs nothing but the positions x, y, z (the default)
     CFG_BOX_POS = 1u << 21,         // 3D: the merged state box bounds nothing but x, y, z
     CFG_CLIP_ONCE = 1u << 22,       // 3D: the action bounds lie inside the rotor force bounds, the motor map needs no second clip
+    CFG_DIST_SIMPLE = 1u << 23,     // (with CFG_DISTURBED) every per-step disturbance is one of Hot::ds_*: evaluated inline
+    CFG_SPARE_SIMPLE = 1u << 24,    // no impulse / step disturbance with a per-episode offset outside the action channel: apply_spare_simple
     CFG_RESET_EXTRAS = 1u << 19,    // reset() draws more than uniform init offsets: inertial properties, disturbance offsets, normal draws
 };
 // SPEC kernels (scg_step.cuh): the switches of the competition scenario family (competition/level0-3.yaml: stabilisation

@@ -34,6 +34,8 @@ template <int KIND, typename real> struct EnvRegs {
     bool goal_prev;      // goal_reached of the previous _get_done (info["goal_reached"] lags one step, F10); survives reset
     uint32_t gate, hold;
     Inertia<real> in;
+    real* offc;          // CFG_DIST_SIMPLE: this episode's impulse / step offsets (Hot::ds_off < 0), mirrored from Buf::dist_offset into a
+                         // per-thread shared-memory column [k * ENV_BLOCK] (exact small integers; registers are what the loop is short of)
     Att3<real> a3;       // 3D
     Att2<real> a2;       // 2D
     // PAIRED loops (3D fp32 PLAIN, see step_env): the state of the control-step loop in packed pairs -- (x, y), (vx, vy),
@@ -81,6 +83,25 @@ template <int KIND, typename real> SCG_DEV uint32_t pack_flags(const EnvRegs<KIN
     return f;
 }
 
+// the integrator's per-episode constants from this episode's (M, Ixx, Iyy, Izz) (extension F9; KIND != cart-pole)
+template <int KIND, typename real> SCG_DEV void inertia_from_values(const Hot<real>& h, const real (&v)[4], Inertia<real>& in) {
+    in.inv_mass = real(1) / v[0];
+    in.g_over_m = h.gravity_force * h.inv_mass;   // g * m_env / m_env == GRAVITY_ACC
+#pragma unroll
+    for (int j = 0; j < 3; ++j) { in.J[j] = v[j + 1]; in.J_inv[j] = real(1) / in.J[j]; }
+#pragma unroll
+    for (int j = 0; j < 3; ++j) { in.dJ[j] = in.J[(j + 2) % 3] - in.J[(j + 1) % 3]; in.kJ[j] = h.dt * in.J_inv[j]; }
+}
+
+// CFG_DIST_SIMPLE: the episode's impulse / step offsets into registers
+template <int KIND, typename real> SCG_DEV void load_offsets(const Hot<real>& h, const int32_t* __restrict__ dist_offset, int64_t n, int64_t i,
+                                                             EnvRegs<KIND, real>& e) {
+#pragma unroll
+    for (int k = 0; k < SCG_MAX_DIST; ++k) {
+        if (k < h.ds_n && h.ds_off[k] < 0 && h.ds_kind[k] != SCG_DIST_WHITE) e.offc[k * ENV_BLOCK] = real(dist_offset[int64_t(h.ds_slot[k]) * n + i]);
+    }
+}
+
 template <int KIND, typename real> SCG_DEV void load_inertia(const Hot<real>& h, const real* __restrict__ inertia, int64_t n, int64_t i,
                                                    Inertia<real>& in) {
     in.cp_l = h.cp_length; in.cp_mp = h.cp_pole_mass; in.cp_mc = h.cp_cart_mass;
@@ -88,13 +109,8 @@ template <int KIND, typename real> SCG_DEV void load_inertia(const Hot<real>& h,
         if (inertia && h.any_inertia_rand) { in.cp_l = inertia[i]; in.cp_mp = inertia[n + i]; in.cp_mc = inertia[2 * n + i]; }
     }
     if (KIND != SCG_CARTPOLE && h.dyn_uses_episode_inertia && inertia) {   // extension (F9)
-        const real m = inertia[i];
-        in.inv_mass = real(1) / m;
-        in.g_over_m = h.gravity_force * h.inv_mass;   // g * m_env / m_env == GRAVITY_ACC
-#pragma unroll
-        for (int j = 0; j < 3; ++j) { in.J[j] = inertia[int64_t(j + 1) * n + i]; in.J_inv[j] = real(1) / in.J[j]; }
-#pragma unroll
-        for (int j = 0; j < 3; ++j) { in.dJ[j] = in.J[(j + 2) % 3] - in.J[(j + 1) % 3]; in.kJ[j] = h.dt * in.J_inv[j]; }
+        const real v[4] = {inertia[i], inertia[n + i], inertia[2 * n + i], inertia[3 * n + i]};
+        inertia_from_values<KIND, real>(h, v, in);
     } else {
         in.inv_mass = h.inv_mass;
         in.g_over_m = h.gravity_force * h.inv_mass;
@@ -382,7 +398,7 @@ SCG_DEV void reset_from_spare(const real* __restrict__ sp, EnvRegs<KIND, real>& 
 // uniform or normal offsets, inertial properties, impulse / step disturbance offsets -- with the same Philox
 // counters as reset_env_body.  Slots after the state / attitude block: 4 inertial properties, then one per
 // disturbance slot.  Out of line: it runs for all lanes together at the refill cadence.
-constexpr int SPARE_EXTRA = 4 + 3 * SCG_MAX_DIST;
+constexpr int SPARE_EXTRA = 4 + 3 * SCG_MAX_DIST + SCG_MAX_DIST;   // (+ the CURRENT episode's action-channel offsets, EnvRegs::offc)
 
 template <int KIND, typename real, int ATT>
 __device__ __noinline__ void draw_spare_general(const Hot<real>& h, const Cold<real>* __restrict__ cold, RngKey key, uint32_t ep,
@@ -447,6 +463,35 @@ __device__ __noinline__ void apply_spare_extras(const Hot<real>& h, const Cold<r
             const DistP<real>& D = cold->dist[ch][k];
             if ((D.kind == SCG_DIST_IMPULSE || D.kind == SCG_DIST_STEP) && D.step_offset < 0 && D.slot < 3 * SCG_MAX_DIST)
                 dist_offset[int64_t(D.slot) * n + i] = int32_t(sp[(N0 + 4 + D.slot) * ENV_BLOCK]);
+        }
+    }
+}
+
+// The same for configs whose per-step disturbances are all inline (CFG_DIST_SIMPLE) or absent: no table walks, no read-back --
+// the restarting lane stores the episode's inertial properties and offsets (owner lane only) and forms its constants from the
+// spare's values directly.  Inline: with ~1 % of env-steps ending an episode a third of all warp-steps pass through here.
+template <int KIND, typename real, int ATT>
+SCG_DEV void apply_spare_simple(const Hot<real>& h, real* __restrict__ inertia, int32_t* __restrict__ dist_offset, const real* __restrict__ sp,
+                                int64_t n, int64_t i, EnvRegs<KIND, real>& e, bool write) {
+    constexpr int N0 = Spare<KIND, real, ATT>::N;
+    if (inertia) {
+        real v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[j] = h.any_inertia_rand ? sp[(N0 + j) * ENV_BLOCK] : h.inertia_nominal[j];
+        if (write) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) inertia[int64_t(j) * n + i] = v[j];
+        }
+        if constexpr (KIND == SCG_CARTPOLE) {
+            if (h.any_inertia_rand) { e.in.cp_l = v[0]; e.in.cp_mp = v[1]; e.in.cp_mc = v[2]; }
+        } else if (h.dyn_uses_episode_inertia) inertia_from_values<KIND, real>(h, v, e.in);
+    }
+#pragma unroll
+    for (int k = 0; k < SCG_MAX_DIST; ++k) {
+        if (k < h.ds_n && h.ds_off[k] < 0 && h.ds_kind[k] != SCG_DIST_WHITE) {
+            const real o = sp[(N0 + 4 + h.ds_slot[k]) * ENV_BLOCK];
+            e.offc[k * ENV_BLOCK] = o;
+            if (write) dist_offset[int64_t(h.ds_slot[k]) * n + i] = int32_t(o);
         }
     }
 }
@@ -546,7 +591,31 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
         thr[j] = pre[j];
     }
     real fx = real(0), fy = real(0), fz = real(0);
-    if (!PLAIN && (cfg & CFG_DISTURBED)) {   // uniform; one out-of-line call on private copies
+    if (!PLAIN && (cfg & CFG_DIST_SIMPLE)) {   // uniform: impulse / step / white noise on the action channel, inline (Hot::ds_*)
+#pragma unroll
+        for (int k = 0; k < SCG_MAX_DIST; ++k) {
+            if (k >= h.ds_n) break;
+            if (h.ds_kind[k] == SCG_DIST_WHITE) {   // disturbances.py:237-248; draw = (index t, episode, stream of this disturbance)
+                real z[NU];
+                draw_normals_f<real, NU, FASTMATH>(key.seed, key.env, uint32_t(t), ep, STREAM_DISTURB_BASE + 8u * SCG_CH_ACTION + uint32_t(k), z);
+#pragma unroll
+                for (int j = 0; j < NU; ++j) thr[j] = m_fma(z[j], h.ds_std[k][j], thr[j]);
+            } else {                                // disturbances.py:128-143, 174-184
+                const real off = h.ds_off[k] >= 0 ? real(h.ds_off[k]) : e.offc[k * ENV_BLOCK];
+                real sn = real(0);
+                if (real(t) >= off) {
+                    if (h.ds_kind[k] == SCG_DIST_STEP) sn = h.ds_mag[k];
+                    else {
+                        const int32_t peak = static_cast<int32_t>(off + h.ds_half[k]);
+                        const int32_t kk = t >= peak ? t - peak : peak - t;
+                        if (real(kk) < h.ds_half[k]) sn = h.ds_mag[k] * pow_int(h.ds_decay[k], h.ds_l2decay[k], kk);
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < NU; ++j) thr[j] += sn;
+            }
+        }
+    } else if (!PLAIN && (cfg & CFG_DISTURBED)) {   // uniform; one out-of-line call on private copies
         real tl[NU], fl[3];
 #pragma unroll
         for (int j = 0; j < NU; ++j) tl[j] = thr[j];
@@ -682,8 +751,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
         }
     } else if constexpr (KIND == SCG_QUAD_2D) {
         const real axf = fx * e.in.inv_mass, azf = fz * e.in.inv_mass - e.in.g_over_m;
-#pragma unroll 1
-        for (int s = 0; s < h.substeps; ++s) {
+        auto substep2d = [&]() {
             const real ax = e.a2.r3x * Tm + axf, az = e.a2.r3z * Tm + azf;
             const real dw = e.in.J_inv[1] * mot.ty;
             e.x[1] += dt * ax; e.x[3] += dt * az;
@@ -691,6 +759,11 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             e.x[0] += dt * e.x[1]; e.x[2] += dt * e.x[3];
             attitude2<real>(e.a2.theta + dt * e.x[5], e.a2.flipped, e.a2);
             e.x[4] = e.a2.theta;
+        };
+        if (LEAN && h.substeps == 4) { substep2d(); substep2d(); substep2d(); substep2d(); }   // the usual PYB_FREQ / CTRL_FREQ: straight-line
+        else {
+#pragma unroll 1
+            for (int s = 0; s < h.substeps; ++s) substep2d();
         }
     } else if constexpr (KIND == SCG_CARTPOLE) {
         // RK4 over the cart-pole ODE at the simulation rate; a dynamics-channel disturbance acts as an
@@ -1014,11 +1087,13 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
     e.t = b.ctrl_step[ii];
     e.resets = b.episode[ii];
     unpack_flags<KIND, real>(e, b.flags[ii]);
+    e.offc = PLAIN ? nullptr : (LEAN ? sp + (Spare<KIND, real, ATT>::N + 4 + 3 * SCG_MAX_DIST) * ENV_BLOCK : sp);
     // SPEC: cost "competition" is a compile-time fact, the goal_reached bit (cost "quadratic" only) cannot change: it is
     // not carried through the loop (one register less at the 96-register bound) but re-read where the flags are stored
     if constexpr (SPEC) e.goal_prev = false;
     real st[NX];   // env.state after the last step (LEAN: rebuilt from the registers after the loop)
     load_inertia<KIND, real>(h, PLAIN ? nullptr : b.inertia, n, ii, e.in);
+    if constexpr (!PLAIN) { if (h.cfg & CFG_DIST_SIMPLE) load_offsets<KIND, real>(h, b.dist_offset, n, ii, e); }
     derive_attitude<KIND, real, ATT>(e);
     constexpr bool PAIRED = Paired<KIND, real, ATT, LEAN, PLAIN>::value;
     if constexpr (PAIRED) pairs_from_scalars(e);
@@ -1173,6 +1248,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
                     real sn[NX];
                     reset_env_cold<KIND, real, ATT>(h, cold, b, key, n, ii, &ec, sn, valid);
                     e = ec;
+                    if (cfg & CFG_DIST_SIMPLE) load_offsets<KIND, real>(h, b.dist_offset, n, ii, e);
 #pragma unroll
                     for (int d = 0; d < NX; ++d) st[d] = sn[d];
                 }
@@ -1185,9 +1261,18 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
                 if constexpr (LEAN) {
                     reset_from_spare<KIND, real, ATT, PAIRED>(sp, e);
                     if (!PLAIN && (cfg & CFG_RESET_EXTRAS)) {
-                        Inertia<real> in;
-                        apply_spare_extras<KIND, real, ATT>(h, cold, b.inertia, b.dist_offset, sp, n, ii, &in, valid);
-                        e.in = in;
+                        if ((cfg & CFG_SPARE_SIMPLE) && ((cfg & CFG_DIST_SIMPLE) || h.n_dist_act == 0)) apply_spare_simple<KIND, real, ATT>(h, b.inertia, b.dist_offset, sp, n, ii, e, valid);
+                        else {
+                            Inertia<real> in;
+                            apply_spare_extras<KIND, real, ATT>(h, cold, b.inertia, b.dist_offset, sp, n, ii, &in, valid);
+                            e.in = in;
+                            if (cfg & CFG_DIST_SIMPLE) {   // (offsets of this episode as apply_spare_extras published them)
+#pragma unroll
+                                for (int q = 0; q < SCG_MAX_DIST; ++q)
+                                    if (q < h.ds_n && h.ds_off[q] < 0 && h.ds_kind[q] != SCG_DIST_WHITE)
+                                        e.offc[q * ENV_BLOCK] = sp[(Spare<KIND, real, ATT>::N + 4 + h.ds_slot[q]) * ENV_BLOCK];
+                            }
+                        }
                     }
                     spare_ok = false;
                 }
@@ -1316,7 +1401,7 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     __shared__ float acc_buf[N_ACC * ACC_LD];
     __shared__ double mse_buf[2 * ACC_LD];   // fp64 columns: mse sum, return sum
     mse_buf[threadIdx.x] = 0.0; mse_buf[ACC_LD + threadIdx.x] = 0.0;
-    __shared__ real sp_buf[LEAN ? (Spare<KIND, real, ATT>::N + (PLAIN ? 0 : SPARE_EXTRA)) * ENV_BLOCK : 1];
+    __shared__ real sp_buf[LEAN ? (Spare<KIND, real, ATT>::N + (PLAIN ? 0 : SPARE_EXTRA)) * ENV_BLOCK : SCG_MAX_DIST * ENV_BLOCK];
     real* const sp = sp_buf + threadIdx.x;
 #pragma unroll
     for (int j = 0; j < N_ACC; ++j) acc_buf[j * ACC_LD + threadIdx.x] = 0.f;
