@@ -305,7 +305,10 @@ int64_t scg_launch_count(const scg_env* env);
  * or R, constraint penalty, gate geometry), so all of that is compiled out; 3 = PLAIN + SPEC: a Quadrotor 3D config of
  * the competition family (stabilisation task, cost "competition", done on violation and completion, position box +
  * input bounds, positions-only mse, auto-reset) whose fused launches without per-step outputs run with those switches
- * as compile-time constants (scg_step and launches with per-step outputs take variant 2); 0 = GENERAL: SCG_ATT_ROUNDTRIP only
+ * as compile-time constants (scg_step and launches with per-step outputs take variant 2); 4 = PLAIN + DS (fp32, quad_type 2 and
+ * the cart-pole): like 2, but the config's extras are the cheap ones -- action-channel impulse / step / white-noise disturbances
+ * evaluated inline and / or per-episode inertial properties and offsets taken from the spare -- so the rest of the LEAN kernel
+ * is compiled out (BASELINE configs 3 and 4); 0 = GENERAL: SCG_ATT_ROUNDTRIP only
  * (validation: literal quaternion round trip, reset one lane at a time).  Same results in every variant. */
 int scg_kernel_variant(const scg_env* env);
 /* Scheduling of the fused rollout launches (scg_rollout / scg_rollout_host / scg_rollout_pid; no reference counterpart:

@@ -59,24 +59,35 @@ static bool launch_queued(scg_env* e, K kernel, bool plain, const int64_t n, int
     return true;
 }
 
-template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN, bool SPEC>
+template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN, bool SPEC, bool DS = false>
 static void launch_rollout_v(scg_env* e, const Hot<real>& h, const Cold<real>* cold, const Buf<real>& b, const Roll<real>& ro,
                              unsigned blocks, cudaStream_t st) {
     if constexpr (LEAN && sizeof(real) == 4) {
         Roll<real> rq = ro;
         unsigned grid = 0;
-        if (!ro.step_outputs && launch_queued(e, k_rollout<KIND, real, ATT, LEAN, PLAIN, SPEC, true>, PLAIN, b.n, ro.k_steps, &rq.q_chunk,
+        if (!ro.step_outputs && launch_queued(e, k_rollout<KIND, real, ATT, LEAN, PLAIN, SPEC, true, DS>, PLAIN && !DS, b.n, ro.k_steps, &rq.q_chunk,
                                               &rq.q_env_blocks, &rq.q_tickets, &grid)) {
             rq.q_mem = e->q_mem; rq.q_sleep_ns = e->queue_sleep_ns;
             if (cudaMemsetAsync(e->q_mem, 0, sizeof(int32_t) * (2 + size_t(rq.q_tickets)), st) == cudaSuccess) {
-                k_rollout<KIND, real, ATT, LEAN, PLAIN, SPEC, true><<<grid, ENV_BLOCK, 0, st>>>(h, cold, b, rq);
+                k_rollout<KIND, real, ATT, LEAN, PLAIN, SPEC, true, DS><<<grid, ENV_BLOCK, 0, st>>>(h, cold, b, rq);
                 e->last_queue = 1;
                 return;
             }
         }
     }
     e->last_queue = 0;
-    k_rollout<KIND, real, ATT, LEAN, PLAIN, SPEC, false><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro);
+    k_rollout<KIND, real, ATT, LEAN, PLAIN, SPEC, false, DS><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro);
+}
+
+// The PLAIN + DS kernel applies (scg_step.cuh: step_env): none of the general extras, disturbances (if any) all inline, the
+// restart (if it draws more than uniform init offsets) through apply_spare_simple.  Evaluated per launch: injected draws switch
+// CFG_DIST_SIMPLE off (scg_set_injection).
+template <typename real> static bool ds_kernel_ok(const Hot<real>& h) {
+    const uint32_t c = h.cfg;
+    if ((c & (CFG_COLD_CONSTRAINTS | CFG_QR_DENSE | CFG_PENALTY | CFG_GATE_GEOMETRY)) || h.normalized_action) return false;
+    if ((c & CFG_DISTURBED) && !(c & CFG_DIST_SIMPLE)) return false;
+    if ((c & CFG_RESET_EXTRAS) && !((c & CFG_SPARE_SIMPLE) && ((c & CFG_DIST_SIMPLE) || h.n_dist_act == 0))) return false;
+    return true;
 }
 
 template <int KIND, typename real, int ATT>
@@ -88,6 +99,8 @@ static void launch_rollout_att(scg_env* e, const Hot<real>& h, const Cold<real>*
             launch_rollout_v<KIND, real, ATT, true, F32, (F32 && KIND == SCG_QUAD_3D)>(e, h, cold, b, ro, blocks, st);
         else launch_rollout_v<KIND, real, ATT, true, F32, false>(e, h, cold, b, ro, blocks, st);
     }
+    else if (e->lean && F32 && (KIND == SCG_QUAD_2D || KIND == SCG_CARTPOLE) && !ro.use_pid && ds_kernel_ok(h))
+        launch_rollout_v<KIND, real, ATT, true, F32, false, (F32 && (KIND == SCG_QUAD_2D || KIND == SCG_CARTPOLE))>(e, h, cold, b, ro, blocks, st);
     else if (e->lean) launch_rollout_v<KIND, real, ATT, true, false, false>(e, h, cold, b, ro, blocks, st);
     else launch_rollout_v<KIND, real, ATT, false, false, false>(e, h, cold, b, ro, blocks, st);
 }

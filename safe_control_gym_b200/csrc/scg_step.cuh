@@ -569,7 +569,10 @@ __device__ __noinline__ real dense_form(const real* __restrict__ M, const real* 
 
 // One Quadrotor.step(): returns reward / done / info bits, leaves env.state in st
 // (3D: p, q, r only when `full`).
-template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN>
+// DS (PLAIN kernels only): the config's extras are exactly the ones that stay cheap inline -- CFG_DIST_SIMPLE disturbances and / or
+// per-episode inertia / offsets through apply_spare_simple -- so everything else a LEAN kernel carries (out-of-line disturbance and
+// constraint evaluation, dense costs, gate geometry, the PID) is compiled out: a third of the code size of the LEAN kernel.
+template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN, bool DS = false>
 SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, const Buf<real>& b,
                       const RngKey& key, int64_t n, int64_t i, EnvRegs<KIND, real>& e,
                       const real (&raw)[Dims<KIND>::NU], uint32_t cfg, real (&st)[Dims<KIND>::NX], real& reward, bool& done,
@@ -591,7 +594,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
         thr[j] = pre[j];
     }
     real fx = real(0), fy = real(0), fz = real(0);
-    if (!PLAIN && (cfg & CFG_DIST_SIMPLE)) {   // uniform: impulse / step / white noise on the action channel, inline (Hot::ds_*)
+    if ((!PLAIN || DS) && (cfg & CFG_DIST_SIMPLE)) {   // uniform: impulse / step / white noise on the action channel, inline (Hot::ds_*)
 #pragma unroll
         for (int k = 0; k < SCG_MAX_DIST; ++k) {
             if (k >= h.ds_n) break;
@@ -624,10 +627,10 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
         for (int j = 0; j < NU; ++j) thr[j] = tl[j];
         fx = fl[0]; fy = fl[1]; fz = fl[2];
     }
-    if constexpr (KIND != SCG_CARTPOLE) motors_from_thrust<KIND, real, FASTMATH>(h, thr, mot, !(PLAIN && (cfg & CFG_CLIP_ONCE)));
+    if constexpr (KIND != SCG_CARTPOLE) motors_from_thrust<KIND, real, FASTMATH>(h, thr, mot, !(PLAIN && !DS && (cfg & CFG_CLIP_ONCE)));
     else { mot.T = mot.tx = mot.ty = mot.tz = real(0); mot.rpm[0] = mot.rpm[1] = mot.rpm[2] = mot.rpm[3] = real(0); }
     // ---- _advance_simulation: S explicit substeps (base_aviary.py:266-322, 522-576)
-    constexpr bool ROWS = PLAIN && KIND == SCG_QUAD_3D && sizeof(real) == 4 && ATT != SCG_ATT_ROUNDTRIP;   // nominal inertia: constants from Hot::step_row
+    constexpr bool ROWS = PLAIN && !DS && KIND == SCG_QUAD_3D && sizeof(real) == 4 && ATT != SCG_ATT_ROUNDTRIP;   // nominal inertia: constants from Hot::step_row
     const real Tm = mot.T * (ROWS ? ldc4(h.step_row).w : e.in.inv_mass);
     const real dt = ROWS ? ldc4(h.step_row).x : h.dt;
     if constexpr (KIND == SCG_QUAD_3D) {
@@ -666,7 +669,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             if constexpr (LAST) { e.x[6] = pre3[0]; e.x[7] = pre3[1]; e.x[8] = pre3[2]; }
             attitude3<real, ATT>(pre3, e.a3);
         };
-        if constexpr (Paired<KIND, real, ATT, LEAN, PLAIN>::value) {
+        if constexpr (Paired<KIND, real, ATT, LEAN, (PLAIN && !DS)>::value) {
             // The same substep on packed pairs (FFMA2 / FADD2, scg_math.cuh): every half is the scalar operation of
             // `substep` above, bit for bit; the loop is issue-bound and a pair takes one issue slot instead of two.
             // Pairing: (x, y) of position and velocity; (roll, yaw) of angles and rates, so that the two wraps that
@@ -778,7 +781,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
         for (int s = 0; s < h.substeps; ++s) { e.x[1] += dt * az; e.x[0] += dt * e.x[1]; }
     }
     // ---- _get_observation: env.state (obs itself is written by the caller, it may be replaced on reset)
-    constexpr bool PAIRED = Paired<KIND, real, ATT, LEAN, PLAIN>::value;
+    constexpr bool PAIRED = Paired<KIND, real, ATT, LEAN, (PLAIN && !DS)>::value;
     real ang[3];
     if constexpr (PAIRED) { ang[0] = lo2(e.Wxz); ang[1] = hi2(e.ZB); ang[2] = hi2(e.Wxz); }
     else if constexpr (KIND == SCG_QUAD_3D) { ang[0] = e.x[9]; ang[1] = e.x[10]; ang[2] = e.x[11]; }
@@ -1064,7 +1067,7 @@ k_reset(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold
 constexpr int SPARE_CADENCE = SCG_SPARE_CADENCE;   // control steps between the warp-wide spare refills (power of two)
 constexpr int ACC_LD = ENV_BLOCK + 1;   // column ENV_BLOCK is the scratch column of out-of-range lanes
 constexpr int N_ACC = 11;   // episodes, return, length, truncated, completed, violated episodes, violation steps, (mse: double column), env steps, gates, collisions
-template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN, bool SPEC, bool TLOG = false>
+template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN, bool SPEC, bool TLOG = false, bool DS = false>
 SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ cold, const Buf<real>& b, const Roll<real>& ro,
                            const int64_t i, const int k0, const int k1, float* const ep_acc, double* const mse_acc, real* const sp,
                            const LogMaps* const lg_maps = nullptr, float* const lg_warp = nullptr) {
@@ -1087,15 +1090,15 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
     e.t = b.ctrl_step[ii];
     e.resets = b.episode[ii];
     unpack_flags<KIND, real>(e, b.flags[ii]);
-    e.offc = PLAIN ? nullptr : (LEAN ? sp + (Spare<KIND, real, ATT>::N + 4 + 3 * SCG_MAX_DIST) * ENV_BLOCK : sp);
+    e.offc = (PLAIN && !DS) ? nullptr : (LEAN ? sp + (Spare<KIND, real, ATT>::N + 4 + 3 * SCG_MAX_DIST) * ENV_BLOCK : sp);
     // SPEC: cost "competition" is a compile-time fact, the goal_reached bit (cost "quadratic" only) cannot change: it is
     // not carried through the loop (one register less at the 96-register bound) but re-read where the flags are stored
     if constexpr (SPEC) e.goal_prev = false;
     real st[NX];   // env.state after the last step (LEAN: rebuilt from the registers after the loop)
-    load_inertia<KIND, real>(h, PLAIN ? nullptr : b.inertia, n, ii, e.in);
-    if constexpr (!PLAIN) { if (h.cfg & CFG_DIST_SIMPLE) load_offsets<KIND, real>(h, b.dist_offset, n, ii, e); }
+    load_inertia<KIND, real>(h, (PLAIN && !DS) ? nullptr : b.inertia, n, ii, e.in);
+    if constexpr (!PLAIN || DS) { if (h.cfg & CFG_DIST_SIMPLE) load_offsets<KIND, real>(h, b.dist_offset, n, ii, e); }
     derive_attitude<KIND, real, ATT>(e);
-    constexpr bool PAIRED = Paired<KIND, real, ATT, LEAN, PLAIN>::value;
+    constexpr bool PAIRED = Paired<KIND, real, ATT, LEAN, (PLAIN && !DS)>::value;
     if constexpr (PAIRED) pairs_from_scalars(e);
     real ep_ret = b.ep_return ? b.ep_return[ii] : real(0);
     int32_t ep_len = b.ep_length ? b.ep_length[ii] : 0;
@@ -1165,7 +1168,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
         // after the loop is rebuilt from e there
         real sl[LEAN ? NX : 1];
         real (&sk)[NX] = *reinterpret_cast<real (*)[NX]>(LEAN ? sl : st);
-        step_env<KIND, real, ATT, LEAN, PLAIN>(h, cold, b, key, n, ii, e, raw, cfg, sk, reward, done, info, mse, mot, c_out);
+        step_env<KIND, real, ATT, LEAN, PLAIN, DS>(h, cold, b, key, n, ii, e, raw, cfg, sk, reward, done, info, mse, mot, c_out);
         ep_ret += reward; ep_len += 1;
         const bool viol = (info & SCG_INFO_VIOLATION) != 0u;
         ep_viol += viol ? 1 : 0;
@@ -1221,7 +1224,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
             const bool cadence = ahead && ((k - k0) & (SPARE_CADENCE - 1)) == 0;   // uniform
             if (bool(int(!spare_ok) & (int(restart) | int(cadence)))) {
                 const uint32_t next_ep = (cfg & CFG_RESEED) ? 0u : uint32_t(e.resets);
-                if (!PLAIN && (cfg & CFG_RESET_EXTRAS)) draw_spare_general<KIND, real, ATT>(h, cold, key, next_ep, sp);
+                if ((!PLAIN || DS) && (cfg & CFG_RESET_EXTRAS)) draw_spare_general<KIND, real, ATT>(h, cold, key, next_ep, sp);
                 else {
                     real init[NX];
                     draw_init_lean<KIND, real>(h, key, next_ep, init);
@@ -1260,7 +1263,9 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
                 }
                 if constexpr (LEAN) {
                     reset_from_spare<KIND, real, ATT, PAIRED>(sp, e);
-                    if (!PLAIN && (cfg & CFG_RESET_EXTRAS)) {
+                    if constexpr (DS) {
+                        if (cfg & CFG_RESET_EXTRAS) apply_spare_simple<KIND, real, ATT>(h, b.inertia, b.dist_offset, sp, n, ii, e, valid);
+                    } else if (!PLAIN && (cfg & CFG_RESET_EXTRAS)) {
                         if ((cfg & CFG_SPARE_SIMPLE) && ((cfg & CFG_DIST_SIMPLE) || h.n_dist_act == 0)) apply_spare_simple<KIND, real, ATT>(h, b.inertia, b.dist_offset, sp, n, ii, e, valid);
                         else {
                             Inertia<real> in;
@@ -1395,19 +1400,19 @@ SCG_DEV void st_release_gpu(int32_t* p, int32_t v) { asm volatile("st.release.gp
 // four-warp ones set the makespan; through the queue every scheduler hosts four warps, the ~14 % that wait for a range
 // sleep, and a scheduler that runs ahead simply takes more ranges (same result: the split into ranges is invisible, see
 // rollout_range).
-template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN = false, bool SPEC = false, bool QUEUE = false>
+template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN = false, bool SPEC = false, bool QUEUE = false, bool DS = false>
 __global__ void __launch_bounds__(ENV_BLOCK, sizeof(real) == 4 ? (SPEC ? SCG_BLOCKS_PER_SM : 8) : 1)
 k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, const Buf<real> b, const Roll<real> ro) {
     __shared__ float acc_buf[N_ACC * ACC_LD];
     __shared__ double mse_buf[2 * ACC_LD];   // fp64 columns: mse sum, return sum
     mse_buf[threadIdx.x] = 0.0; mse_buf[ACC_LD + threadIdx.x] = 0.0;
-    __shared__ real sp_buf[LEAN ? (Spare<KIND, real, ATT>::N + (PLAIN ? 0 : SPARE_EXTRA)) * ENV_BLOCK : SCG_MAX_DIST * ENV_BLOCK];
+    __shared__ real sp_buf[LEAN ? (Spare<KIND, real, ATT>::N + ((PLAIN && !DS) ? 0 : SPARE_EXTRA)) * ENV_BLOCK : SCG_MAX_DIST * ENV_BLOCK];
     real* const sp = sp_buf + threadIdx.x;
 #pragma unroll
     for (int j = 0; j < N_ACC; ++j) acc_buf[j * ACC_LD + threadIdx.x] = 0.f;
     if constexpr (!QUEUE) {
         const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-        rollout_range<KIND, real, ATT, LEAN, PLAIN, SPEC>(h, cold, b, ro, i, 0, ro.k_steps, acc_buf + (i < b.n ? threadIdx.x : ENV_BLOCK),
+        rollout_range<KIND, real, ATT, LEAN, PLAIN, SPEC, false, DS>(h, cold, b, ro, i, 0, ro.k_steps, acc_buf + (i < b.n ? threadIdx.x : ENV_BLOCK),
                                                           mse_buf + (i < b.n ? threadIdx.x : ENV_BLOCK), sp);
     } else {
         // q_mem: [0] pop counter, [1] push counter, [2 + s] the ready list: item s = 1 + env block + env_blocks * chunk.
@@ -1436,7 +1441,7 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
             const int32_t chunk = (item - 1) / ro.q_env_blocks, eb = (item - 1) - chunk * ro.q_env_blocks;
             const int64_t i = int64_t(eb) * ENV_BLOCK + threadIdx.x;
             const int k0 = chunk * ro.q_chunk, k1 = k0 + ro.q_chunk < ro.k_steps ? k0 + ro.q_chunk : ro.k_steps;
-            rollout_range<KIND, real, ATT, LEAN, PLAIN, SPEC>(h, cold, b, ro, i, k0, k1, acc_buf + (i < b.n ? threadIdx.x : ENV_BLOCK),
+            rollout_range<KIND, real, ATT, LEAN, PLAIN, SPEC, false, DS>(h, cold, b, ro, i, k0, k1, acc_buf + (i < b.n ? threadIdx.x : ENV_BLOCK),
                                                               mse_buf + (i < b.n ? threadIdx.x : ENV_BLOCK), sp);
             push = k1 < ro.k_steps ? item + ro.q_env_blocks : 0;
         }

@@ -30,7 +30,7 @@ def test_config4_matches_oracle(dtype, tol):
     from safe_control_gym_b200.envs.quadrotor import BatchedQuadrotor
     n, steps, base = 64, 150, 500
     env = BatchedQuadrotor(num_envs=n, dtype=dtype, auto_reset=True, seed_offset=base, info_in_reset=True, **CFG)
-    assert int(env.lib.scg_kernel_variant(env._h)) == 1   # spare reset carrying inertia + offsets
+    assert int(env.lib.scg_kernel_variant(env._h)) == (4 if dtype == torch.float32 else 1)   # fp32: PLAIN + DS (inline impulse / step, spare restart carrying inertia + offsets)
     kw = {k: v for k, v in CFG.items() if k != "seed"}
     lanes = [0, 7, 31, 32, 63]
     refs = {i: QuadOracle(draws=PhiloxEnvDraws(CFG["seed"], base + i), info_in_reset=True, **kw) for i in lanes}
@@ -81,4 +81,43 @@ def test_config4_queued_rollout_equals_static_rollout():
             assert torch.equal(getattr(a, "buf_" + name), getattr(b, "buf_" + name)), name
     sa, sb = a.stats(), b.stats()
     assert sa["env_steps"] == 2 * n * k and sa["episodes"] == sb["episodes"] > 0
+    a.close(); b.close()
+
+
+@pytest.mark.parametrize("kind", ["quad2d", "cartpole"])
+def test_ds_kernel_equals_lean_kernel(kind):
+    """The PLAIN + DS specialisation (variant 4: inline impulse / step / white-noise disturbances, cheap restart) against the LEAN
+    kernel of the same config -- reached by handing the env a constraint tolerance it never uses (CFG_COLD_CONSTRAINTS is
+    a LEAN-only feature; the tolerance only feeds is_almost_active, which this cost does not read): bit-identical."""
+    from test_gpu_cartpole import CFG as CFG3
+    n, k = 3000, 150
+    if kind == "quad2d":
+        from safe_control_gym_b200.envs.quadrotor import BatchedQuadrotor as Env
+        cfg, nu = dict(CFG), 2
+        acts = (0.16 + 0.01 * torch.randn(k, n, nu, generator=torch.Generator().manual_seed(3))).cuda()
+        ntol = 4
+    else:
+        from safe_control_gym_b200.envs.cartpole import BatchedCartPole as Env
+        cfg, nu = dict(CFG3), 1
+        acts = torch.randn(k, n, nu, generator=torch.Generator().manual_seed(3)).mul_(3.0).cuda()
+        ntol = 2
+    lean = dict(cfg)
+    lean["constraints"] = [dict(c) for c in cfg["constraints"]]
+    lean["constraints"][0]["tolerance"] = [1e-3] * ntol
+    a, b = Env(num_envs=n, dtype=torch.float32, auto_reset=True, **cfg), Env(num_envs=n, dtype=torch.float32, auto_reset=True, **lean)
+    assert int(a.lib.scg_kernel_variant(a._h)) == 4 and int(b.lib.scg_kernel_variant(b._h)) == 1
+    a.reset(); b.reset()
+    ra, rb = torch.empty(k, n, device="cuda"), torch.empty(k, n, device="cuda")
+    for queue in (0, 1):
+        a.set_rollout_queue(queue, 32); b.set_rollout_queue(queue, 32)
+        a.rollout(acts, reward_out=ra); b.rollout(acts, reward_out=rb)
+        torch.cuda.synchronize()
+        assert torch.equal(ra, rb)
+        for name in ("state", "ctrl_step", "episode", "flags", "obs", "ep_return", "ep_length", "inertia", "dist_offset"):
+            assert torch.equal(getattr(a, "buf_" + name), getattr(b, "buf_" + name)), name
+    # single steps take the same kernels (K = 1)
+    oa, *_ = a.step(acts[0]); ob, *_ = b.step(acts[0])
+    assert torch.equal(oa, ob)
+    sa, sb = a.stats(), b.stats()
+    assert sa["episodes"] == sb["episodes"] > 0 and sa["violation_steps"] == sb["violation_steps"]
     a.close(); b.close()
