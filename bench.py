@@ -279,7 +279,7 @@ def run_configs(torch, dist, world, rank, dev, args, fp32_peak, hbm_peak):
     if "4" in args.configs:
         n, k = max(64, int(1024 * 1024 * sc)), 600
         kw = config4_kwargs()
-        env = BatchedQuadrotor(num_envs=n, device=dev, dtype=torch.float32, auto_reset=True, seed_offset=rank * n, **kw)
+        env = BatchedQuadrotor(num_envs=n, device=dev, dtype=torch.float32, attitude=args.attitude, auto_reset=True, seed_offset=rank * n, **kw)
         hover = env.MASS * 9.8 / 2
         g = torch.Generator(device=dev); g.manual_seed(4 + rank)
         a = torch.empty(k, n, 2, dtype=torch.float32, device=dev).normal_(hover, 0.005, generator=g).clamp_(0.0, 4 * hover)

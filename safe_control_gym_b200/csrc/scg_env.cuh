@@ -159,10 +159,12 @@ template <typename real> SCG_DEV void attitude3_complete(Att3<real>& a) {
 // physical pitch.
 template <typename real> struct Att2 { real theta; real r3x, r3z; uint32_t flipped; };
 
-template <typename real>
+template <typename real, int ATT = SCG_ATT_FAST>
 SCG_DEV void attitude2(real alpha_pre, uint32_t flipped_in, Att2<real>& a) {
     if (!flipped_in && m_abs(alpha_pre) < real(1.5663)) {
-        sincos_pi(alpha_pre, &a.r3x, &a.r3z);   // |alpha| < pi / 2: the compact ~1-ulp pair (fp64: sincos)
+        // |alpha| < pi / 2: the compact ~1-ulp pair (fp64: sincos); SCG_ATT_FAST_INTRINSIC (fp32): MUFU.SIN / MUFU.COS
+        if (ATT == SCG_ATT_FAST_INTRINSIC && sizeof(real) == 4) att_sincos<ATT>(alpha_pre, &a.r3x, &a.r3z);
+        else sincos_pi(alpha_pre, &a.r3x, &a.r3z);
         a.theta = alpha_pre; a.flipped = 0u;
         return;
     }

@@ -15,8 +15,8 @@ int launch_reset(scg_env* e, const ResetInject<real>& inj, const uint8_t* mask, 
     const int att = e->cfg.attitude_mode;
     if constexpr (KIND == SCG_QUAD_3D || KIND == SCG_QUAD_2D) {
         if (att == SCG_ATT_ROUNDTRIP) k_reset<KIND, real, SCG_ATT_ROUNDTRIP><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, inj, mask);
-        else if (att == SCG_ATT_FAST_INTRINSIC && sizeof(real) == 4 && KIND == SCG_QUAD_3D)
-            k_reset<KIND, real, (sizeof(real) == 4 && KIND == SCG_QUAD_3D) ? SCG_ATT_FAST_INTRINSIC : SCG_ATT_FAST><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, inj, mask);
+        else if (att == SCG_ATT_FAST_INTRINSIC && sizeof(real) == 4)
+            k_reset<KIND, real, sizeof(real) == 4 ? SCG_ATT_FAST_INTRINSIC : SCG_ATT_FAST><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, inj, mask);
         else k_reset<KIND, real, SCG_ATT_FAST><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, inj, mask);
     } else {
         k_reset<KIND, real, SCG_ATT_FAST><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, inj, mask);
@@ -122,8 +122,8 @@ int launch_rollout(scg_env* e, const Roll<real>& ro, cudaStream_t st) {
     }
     if constexpr (KIND == SCG_QUAD_3D || KIND == SCG_QUAD_2D) {
         if (att == SCG_ATT_ROUNDTRIP) { e->last_queue = 0; k_rollout<KIND, real, SCG_ATT_ROUNDTRIP, false, false><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro); }
-        else if (att == SCG_ATT_FAST_INTRINSIC && sizeof(real) == 4 && KIND == SCG_QUAD_3D)
-            launch_rollout_att<KIND, real, (sizeof(real) == 4 && KIND == SCG_QUAD_3D) ? SCG_ATT_FAST_INTRINSIC : SCG_ATT_FAST>(e, h, cold, b, ro, blocks, st);
+        else if (att == SCG_ATT_FAST_INTRINSIC && sizeof(real) == 4)
+            launch_rollout_att<KIND, real, sizeof(real) == 4 ? SCG_ATT_FAST_INTRINSIC : SCG_ATT_FAST>(e, h, cold, b, ro, blocks, st);
         else launch_rollout_att<KIND, real, SCG_ATT_FAST>(e, h, cold, b, ro, blocks, st);
     } else {
         launch_rollout_att<KIND, real, SCG_ATT_FAST>(e, h, cold, b, ro, blocks, st);

@@ -124,7 +124,7 @@ template <int KIND, typename real, int ATT> SCG_DEV void derive_attitude(EnvRegs
         const real pre[3] = {e.x[6], e.x[7], e.x[8]};
         attitude3<real, ATT>(pre, e.a3);
     } else if constexpr (KIND == SCG_QUAD_2D) {
-        attitude2<real>(e.x[4], e.a2.flipped, e.a2);
+        attitude2<real, ATT>(e.x[4], e.a2.flipped, e.a2);
         e.x[4] = e.a2.theta;
     }
 }
@@ -344,7 +344,7 @@ SCG_DEV void spare_store(const real (&init)[Dims<KIND>::NX], real* __restrict__ 
         sp[(NX + 9) * ENV_BLOCK] = a.R[2]; sp[(NX + 10) * ENV_BLOCK] = a.R[5]; sp[(NX + 11) * ENV_BLOCK] = a.R[8];
     } else if constexpr (KIND == SCG_QUAD_2D) {
         Att2<real> a;
-        attitude2<real>(init[4], 0u, a);
+        attitude2<real, ATT>(init[4], 0u, a);
         sp[(NX + 0) * ENV_BLOCK] = a.theta; sp[(NX + 1) * ENV_BLOCK] = a.r3x; sp[(NX + 2) * ENV_BLOCK] = a.r3z;
         sp[(NX + 3) * ENV_BLOCK] = a.flipped ? real(1) : real(0);
     }
@@ -760,7 +760,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             e.x[1] += dt * ax; e.x[3] += dt * az;
             e.x[5] += dt * dw;
             e.x[0] += dt * e.x[1]; e.x[2] += dt * e.x[3];
-            attitude2<real>(e.a2.theta + dt * e.x[5], e.a2.flipped, e.a2);
+            attitude2<real, ATT>(e.a2.theta + dt * e.x[5], e.a2.flipped, e.a2);
             e.x[4] = e.a2.theta;
         };
         if (LEAN && h.substeps == 4) { substep2d(); substep2d(); substep2d(); substep2d(); }   // the usual PYB_FREQ / CTRL_FREQ: straight-line
@@ -1060,6 +1060,9 @@ k_reset(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold
 #ifndef SCG_BLOCKS_PER_SM
 #define SCG_BLOCKS_PER_SM 9   // resident 64-thread blocks per SM the SPEC rollout kernels are bounded for (96 registers, no spill); the other fp32
                               // kernels: 8 (128 registers) -- at 96 the PLAIN kernel with per-step outputs spills and the single step goes 21 -> 29 us
+#endif
+#ifndef SCG_DS_BLOCKS
+#define SCG_DS_BLOCKS 8       // resident blocks per SM the PLAIN + DS kernels are bounded for
 #endif
 #ifndef SCG_SPARE_CADENCE
 #define SCG_SPARE_CADENCE 16
@@ -1401,7 +1404,7 @@ SCG_DEV void st_release_gpu(int32_t* p, int32_t v) { asm volatile("st.release.gp
 // sleep, and a scheduler that runs ahead simply takes more ranges (same result: the split into ranges is invisible, see
 // rollout_range).
 template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN = false, bool SPEC = false, bool QUEUE = false, bool DS = false>
-__global__ void __launch_bounds__(ENV_BLOCK, sizeof(real) == 4 ? (SPEC ? SCG_BLOCKS_PER_SM : 8) : 1)
+__global__ void __launch_bounds__(ENV_BLOCK, sizeof(real) == 4 ? (SPEC ? SCG_BLOCKS_PER_SM : (DS ? SCG_DS_BLOCKS : 8)) : 1)
 k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, const Buf<real> b, const Roll<real> ro) {
     __shared__ float acc_buf[N_ACC * ACC_LD];
     __shared__ double mse_buf[2 * ACC_LD];   // fp64 columns: mse sum, return sum

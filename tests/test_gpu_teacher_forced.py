@@ -97,10 +97,11 @@ def test_config3_cartpole_teacher_forced():
     env.close()
 
 
-def test_config4_quad2d_teacher_forced():
+@pytest.mark.parametrize("attitude", ["fast", "fast_intrinsic"])
+def test_config4_quad2d_teacher_forced(attitude):
     from safe_control_gym_b200.envs.quadrotor import BatchedQuadrotor
     n, steps, base = 64, 200, 500
-    env = BatchedQuadrotor(num_envs=n, dtype=torch.float32, auto_reset=True, seed_offset=base, info_in_reset=True, **CFG4)
+    env = BatchedQuadrotor(num_envs=n, dtype=torch.float32, attitude=attitude, auto_reset=True, seed_offset=base, info_in_reset=True, **CFG4)
     kw = {k: v for k, v in CFG4.items() if k != "seed"}
     lanes = [0, 7, 31, 32, 63]
     refs = {i: QuadOracle(draws=PhiloxEnvDraws(CFG4["seed"], base + i), info_in_reset=True, **kw) for i in lanes}
@@ -109,7 +110,7 @@ def test_config4_quad2d_teacher_forced():
     worst, _, _, resets = _run(env, refs, lanes, acts, 2)
     assert resets >= 8
     print(f"config 4 (2D, impulse + step, per-episode inertia) fp32 teacher-forced: worst per-step err {worst:.2e}, {resets} resets")
-    _report(test="teacher_forced", scenario="config4_quad2d", dtype="fp32", tol=TOL, worst_unit_floor=worst, steps=steps, resets=resets)
+    _report(test="teacher_forced", scenario="config4_quad2d", attitude=attitude, dtype="fp32", tol=TOL, worst_unit_floor=worst, steps=steps, resets=resets)
     env.close()
 
 

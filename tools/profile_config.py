@@ -28,7 +28,7 @@ if a.config == "3":
     run = lambda: env.rollout(acts)
 elif a.config == "4":
     n = int(1024 * 1024 * a.scale)
-    env = BatchedQuadrotor(num_envs=n, device=dev, dtype=torch.float32, auto_reset=True, **bench.config4_kwargs())
+    env = BatchedQuadrotor(num_envs=n, device=dev, dtype=torch.float32, attitude="fast_intrinsic", auto_reset=True, **bench.config4_kwargs())
     hover = env.MASS * 9.8 / 2
     acts = torch.empty(a.k, n, 2, device=dev).normal_(hover, 0.005, generator=g).clamp_(0, 4 * hover)
     run = lambda: env.rollout(acts)
