@@ -265,7 +265,7 @@ def run_configs(torch, dist, world, rank, dev, args, fp32_peak, hbm_peak):
     if "3" in args.configs:
         n, k = max(64, int(4 * 1024 * 1024 * sc)), 500
         kw = config3_kwargs(); kw.pop("info_in_reset")
-        env = BatchedCartPole(num_envs=n, device=dev, dtype=torch.float32, auto_reset=True, seed_offset=rank * n, **kw)
+        env = BatchedCartPole(num_envs=n, device=dev, dtype=torch.float32, attitude=args.attitude, auto_reset=True, seed_offset=rank * n, **kw)
         g = torch.Generator(device=dev); g.manual_seed(3 + rank)
         a = torch.empty(k, n, 1, dtype=torch.float32, device=dev).normal_(0.0, 3.0, generator=g).clamp_(-10.0, 10.0)
         env.reset()

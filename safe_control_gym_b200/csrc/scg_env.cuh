@@ -245,7 +245,7 @@ template <typename real> struct Inertia { real inv_mass, g_over_m, J[3], J_inv[3
 // Frictionless cart-pole (Barto et al.), x = [x, x_dot, theta, theta_dot], theta = 0 upright,
 // l = effective (half) pole length.  The env is absent from the reference fork:
 // contract inferred from tests/scripts/verbose_api.yaml:1-91 -- parity unpinned.
-template <typename real>
+template <typename real, int ATT = SCG_ATT_FAST>
 SCG_DEV void cartpole_f(const Inertia<real>& in, real g, const real (&x)[4], real F, real (&dx)[4]) {
     real s, c;
     const real Mm = in.cp_mc + in.cp_mp, ml = in.cp_mp * in.cp_l;
@@ -254,7 +254,8 @@ SCG_DEV void cartpole_f(const Inertia<real>& in, real g, const real (&x)[4], rea
         // compiler), sin / cos by the wrap + ~1-ulp polynomial pair instead of libdevice's slow-path sincosf: ~45 instead
         // of ~90 instructions per stage, a few ulp from the literal order below (fp32 bar of the CartPole tests: 2e-4)
         const float inv_Mm = 1.f / Mm;
-        sincos_pi(wrap_pi(x[2]), &s, &c);
+        if (ATT == SCG_ATT_FAST_INTRINSIC) __sincosf(att_wrap<ATT>(x[2]), &s, &c);   // MUFU.SIN / MUFU.COS: |err| <= 2^-21.4 on [-pi, pi]
+        else sincos_pi(wrap_pi(x[2]), &s, &c);
         const float tmp = (F + ml * x[3] * x[3] * s) * inv_Mm;
         const float thdd = (g * s - c * tmp) / (in.cp_l * (float(4.0 / 3.0) - in.cp_mp * c * c * inv_Mm));
         dx[0] = x[1]; dx[1] = tmp - ml * thdd * c * inv_Mm; dx[2] = x[3]; dx[3] = thdd;
@@ -265,19 +266,19 @@ SCG_DEV void cartpole_f(const Inertia<real>& in, real g, const real (&x)[4], rea
     const real thdd = (g * s - c * tmp) / (in.cp_l * (real(4.0 / 3.0) - in.cp_mp * c * c / Mm));
     dx[0] = x[1]; dx[1] = tmp - ml * thdd * c / Mm; dx[2] = x[3]; dx[3] = thdd;
 }
-template <typename real>
+template <typename real, int ATT = SCG_ATT_FAST>
 SCG_DEV void cartpole_rk4(const Inertia<real>& in, real g, real (&x)[4], real F, real dt) {   // mpc_utils.py:79-101
     real k1[4], k2[4], k3[4], k4[4], y[4];
-    cartpole_f(in, g, x, F, k1);
+    cartpole_f<real, ATT>(in, g, x, F, k1);
 #pragma unroll
     for (int d = 0; d < 4; ++d) y[d] = x[d] + dt * real(0.5) * k1[d];
-    cartpole_f(in, g, y, F, k2);
+    cartpole_f<real, ATT>(in, g, y, F, k2);
 #pragma unroll
     for (int d = 0; d < 4; ++d) y[d] = x[d] + dt * real(0.5) * k2[d];
-    cartpole_f(in, g, y, F, k3);
+    cartpole_f<real, ATT>(in, g, y, F, k3);
 #pragma unroll
     for (int d = 0; d < 4; ++d) y[d] = x[d] + dt * k3[d];
-    cartpole_f(in, g, y, F, k4);
+    cartpole_f<real, ATT>(in, g, y, F, k4);
 #pragma unroll
     for (int d = 0; d < 4; ++d) x[d] += dt / real(6) * (k1[d] + real(2) * k2[d] + real(2) * k3[d] + k4[d]);
 }

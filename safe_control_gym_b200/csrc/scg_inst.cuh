@@ -125,6 +125,8 @@ int launch_rollout(scg_env* e, const Roll<real>& ro, cudaStream_t st) {
         else if (att == SCG_ATT_FAST_INTRINSIC && sizeof(real) == 4)
             launch_rollout_att<KIND, real, sizeof(real) == 4 ? SCG_ATT_FAST_INTRINSIC : SCG_ATT_FAST>(e, h, cold, b, ro, blocks, st);
         else launch_rollout_att<KIND, real, SCG_ATT_FAST>(e, h, cold, b, ro, blocks, st);
+    } else if (KIND == SCG_CARTPOLE && sizeof(real) == 4 && att == SCG_ATT_FAST_INTRINSIC) {
+        launch_rollout_att<KIND, real, (KIND == SCG_CARTPOLE && sizeof(real) == 4) ? SCG_ATT_FAST_INTRINSIC : SCG_ATT_FAST>(e, h, cold, b, ro, blocks, st);
     } else {
         launch_rollout_att<KIND, real, SCG_ATT_FAST>(e, h, cold, b, ro, blocks, st);
     }

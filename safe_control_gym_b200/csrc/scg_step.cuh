@@ -774,7 +774,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
         const real F = thr[0] + fx;
         (void)fy; (void)fz; (void)Tm;
 #pragma unroll 1
-        for (int s = 0; s < h.substeps; ++s) cartpole_rk4<real>(e.in, h.gravity_acc, e.x, F, dt);
+        for (int s = 0; s < h.substeps; ++s) cartpole_rk4<real, ATT>(e.in, h.gravity_acc, e.x, F, dt);
     } else {
         const real az = Tm + (fz * e.in.inv_mass - e.in.g_over_m);
 #pragma unroll 1

@@ -40,7 +40,7 @@ class BatchedCartPole(BatchedEnvBase):
     TASK_INFO = {"stabilization_goal": [0], "stabilization_goal_tolerance": 0.05, "trajectory_type": "circle",
                  "num_cycles": 1, "trajectory_plane": "zx", "trajectory_position_offset": [0, 0], "trajectory_scale": 0.2}
 
-    def __init__(self, num_envs=1, device="cuda", dtype=torch.float32, auto_reset=True, squeeze=False, seed_offset=0,
+    def __init__(self, num_envs=1, device="cuda", dtype=torch.float32, attitude="fast", auto_reset=True, squeeze=False, seed_offset=0,
                  output_dir=None, seed=None, info_in_reset=False, gui=False, verbose=False,
                  normalized_rl_action_space=False, task="stabilization", task_info=None, cost="rl_reward",
                  pyb_freq=50, ctrl_freq=50, episode_len_sec=5, init_state=None, randomized_init=True,
@@ -52,6 +52,10 @@ class BatchedCartPole(BatchedEnvBase):
                  done_on_out_of_bound=True, info_mse_metric_state_weight=None, dyn_applies_force=False, **kwargs):
         if gui:
             raise NotImplementedError("gui / rendering: unavailable on this box (no graphics stack)")
+        # how the fp32 kernels evaluate sin / cos of the pole angle: "fast" = ~1-ulp polynomial pair, "fast_intrinsic" = MUFU.SIN / MUFU.COS
+        self._attitude = {"fast": L.ATT_FAST, "fast_intrinsic": L.ATT_FAST_INTRINSIC}[attitude]
+        if self._attitude == L.ATT_FAST_INTRINSIC and dtype != torch.float32:
+            raise ValueError("attitude='fast_intrinsic' is an fp32-only mode")
         nx, nu = 4, 1
         self.GRAVITY_ACC = 9.8
         self.x_threshold, self.theta_threshold_radians = 2.4, 90 * math.pi / 180
@@ -209,7 +213,7 @@ class BatchedCartPole(BatchedEnvBase):
     def _make_config(self, precision, prior):
         c = L.Config()
         nx, nu = 4, 1
-        c.env_kind, c.precision, c.attitude_mode = L.CARTPOLE, precision, L.ATT_FAST
+        c.env_kind, c.precision, c.attitude_mode = L.CARTPOLE, precision, self._attitude
         c.substeps, c.ctrl_steps = self.PYB_STEPS_PER_CTRL, int(self.CTRL_STEPS)
         c.ctrl_freq, c.pyb_freq, c.pyb_dt = int(self.CTRL_FREQ), int(self.PYB_FREQ), self.PYB_TIMESTEP
         c.mass, c.gravity_acc, c.gravity_force = 1.0, self.GRAVITY_ACC, self.GRAVITY_ACC

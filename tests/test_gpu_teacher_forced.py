@@ -80,10 +80,11 @@ def _run(env, refs, lanes, acts, kind, near_gimbal=None):
     return worst, worst_near, n_near, resets
 
 
-def test_config3_cartpole_teacher_forced():
+@pytest.mark.parametrize("attitude", ["fast", "fast_intrinsic"])
+def test_config3_cartpole_teacher_forced(attitude):
     from safe_control_gym_b200.envs.cartpole import BatchedCartPole
     n, steps, base = 96, 260, 1000
-    env = BatchedCartPole(num_envs=n, dtype=torch.float32, auto_reset=True, seed_offset=base, **CFG3)
+    env = BatchedCartPole(num_envs=n, dtype=torch.float32, attitude=attitude, auto_reset=True, seed_offset=base, **CFG3)
     rng = np.random.default_rng(5)
     acts = rng.normal(0, 4.0, size=(steps, n, 1))
     acts[17, 3, 0] = 25.0
@@ -93,7 +94,7 @@ def test_config3_cartpole_teacher_forced():
     worst, _, _, resets = _run(env, refs, lanes, acts, "cartpole")
     assert resets >= 8
     print(f"config 3 (CartPole) fp32 teacher-forced: worst per-step err {worst:.2e} over {steps} steps x {len(lanes)} lanes, {resets} resets")
-    _report(test="teacher_forced", scenario="config3_cartpole", dtype="fp32", tol=TOL, worst_unit_floor=worst, steps=steps, resets=resets)
+    _report(test="teacher_forced", scenario="config3_cartpole", attitude=attitude, dtype="fp32", tol=TOL, worst_unit_floor=worst, steps=steps, resets=resets)
     env.close()
 
 

@@ -23,7 +23,7 @@ g = torch.Generator(device=dev); g.manual_seed(1)
 if a.config == "3":
     n = int(4 * 1024 * 1024 * a.scale)
     kw = bench.config3_kwargs(); kw.pop("info_in_reset")
-    env = BatchedCartPole(num_envs=n, device=dev, dtype=torch.float32, auto_reset=True, **kw)
+    env = BatchedCartPole(num_envs=n, device=dev, dtype=torch.float32, attitude="fast_intrinsic", auto_reset=True, **kw)
     acts = torch.empty(a.k, n, 1, device=dev).normal_(0.0, 3.0, generator=g).clamp_(-10, 10)
     run = lambda: env.rollout(acts)
 elif a.config == "4":
