@@ -55,6 +55,17 @@ def env_kwargs():
                 normalized_rl_action_space=False, seed=1337)
 
 
+def level2_like_kwargs():
+    """Config 2 with competition/level2.yaml's randomisation (level2.yaml:40-100): inertial properties, gate and obstacle poses
+    redrawn per episode besides the initial state.  The DYN integrator keeps the nominal inertia, as the reference's does (F9)."""
+    u = lambda lo, hi: dict(distrib="uniform", low=lo, high=hi)
+    kw = env_kwargs()
+    kw.update(randomized_inertial_prop=True,
+              inertial_prop_randomization_info={"M": u(-0.01, 0.01), "Ixx": u(-1e-6, 1e-6), "Iyy": u(-1e-6, 1e-6), "Izz": u(-1e-6, 1e-6)},
+              randomized_gates_and_obstacles=True, gates_and_obstacles_randomization_info=dict(gates=u(-0.1, 0.1), obstacles=u(-0.2, 0.2)))
+    return kw
+
+
 def config3_kwargs():
     """BASELINE configs[2]: the cartpole_config of tests/scripts/verbose_api.yaml:1-91 -- 50 / 50 Hz,
     10 s episodes (T = 500), true pole length 1.0 with randomised inertial properties, randomised init, default input +
@@ -332,6 +343,19 @@ def run_configs(torch, dist, world, rank, dev, args, fp32_peak, hbm_peak):
                          "through scg_step)", us_per_step=dt / k * 1e6,
                          note="one scg_step launch per control step from Python (facade + launch latency included); state is L2-resident"))
         env.close(); del env, a
+    if "2l" in args.configs:
+        # competition/level2.yaml's randomisation set on config 2: per-episode inertial properties, initial state, gate / obstacle poses
+        n, k = args.envs, 1000
+        kw = level2_like_kwargs()
+        env = BatchedQuadrotor(num_envs=n, device=dev, dtype=torch.float32, attitude=args.attitude, auto_reset=True, seed_offset=rank * n, **kw)
+        a = make_actions(torch, n, k, dev, 9 + rank, args.action_std)
+        env.reset()
+        dt = timed_launches(torch, dist, world, dev, lambda: env.rollout(a), 8)
+        out.append(entry("2-level2-like", "quadrotor3d_dyn_65536x1000_randomised_inertia_init_gates_obstacles", n, k, dt, "fp32", FLOPS_PER_STEP, None,
+                         "tests/test_gpu_golden.py (level2_dyn fixture from the reference's own Quadrotor); tests/test_gpu_config4.py::"
+                         "test_ds_kernel_3d_level2_like_matches_lean_kernel; tests/test_gpu_batch.py::test_spare_reset_with_inertia_and_offsets_equals_stepping",
+                         kernel_variant=int(env.lib.scg_kernel_variant(env._h)), episodes=env.stats()["episodes"]))
+        env.close(); del env, a
     if "2c" in args.configs:
         n, k = args.envs, 1000
         env = BatchedQuadrotor(num_envs=n, device=dev, dtype=torch.float32, attitude=args.attitude, auto_reset=True, seed_offset=rank * n, **env_kwargs())
@@ -597,8 +621,8 @@ def main():
     ap.add_argument("--chunk", type=int, default=50)
     ap.add_argument("--attitude", default="fast_intrinsic", help="fast_intrinsic (MUFU sin/cos) | fast (polynomial sin/cos) | roundtrip (literal)")
     ap.add_argument("--action-std", type=float, default=0.005)
-    ap.add_argument("--configs", default="3,4,5,2h,2c", type=lambda v: [c for c in v.split(",") if c],
-                    help="extra BASELINE configs measured after the headline: 3, 4, 5, 2h (host-driven step), 2c (closed loop); '' = none")
+    ap.add_argument("--configs", default="3,4,5,2h,2l,2c", type=lambda v: [c for c in v.split(",") if c],
+                    help="extra BASELINE configs measured after the headline: 3, 4, 5, 2h (host-driven step), 2l (level2-like randomisation), 2c (closed loop); '' = none")
     ap.add_argument("--config-scale", type=float, default=1.0, help="scale the env counts of the extra configs (smoke runs)")
     ap.add_argument("--sustain-seconds", type=float, default=2.0)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline legs")

@@ -356,7 +356,8 @@ extern "C" int scg_kernel_variant(const scg_env* env) {
     if (!env || !env->lean) return 0;
     const bool quad_att = env->cfg.env_kind == SCG_QUAD_3D || env->cfg.env_kind == SCG_QUAD_2D;
     if (quad_att && env->cfg.attitude_mode == SCG_ATT_ROUNDTRIP) return 0;   // validation mode: GENERAL kernel (scg_inst.cuh)
-    if (!env->plain && env->cfg.precision == 32 && (env->cfg.env_kind == SCG_QUAD_2D || env->cfg.env_kind == SCG_CARTPOLE)) {
+    if (!env->plain && env->cfg.precision == 32 && env->cfg.env_kind != SCG_QUAD_1D &&
+        !(env->cfg.env_kind == SCG_QUAD_3D && env->cfg.dyn_uses_episode_inertia)) {
         // PLAIN + DS (scg_inst.cuh: ds_kernel_ok; closed-loop launches and launches with injected draws still take variant 1)
         const uint32_t c = env->hf.cfg;
         const bool general = (c & (CFG_COLD_CONSTRAINTS | CFG_QR_DENSE | CFG_PENALTY | CFG_GATE_GEOMETRY)) || env->hf.normalized_action;

@@ -572,6 +572,8 @@ __device__ __noinline__ real dense_form(const real* __restrict__ M, const real* 
 // DS (PLAIN kernels only): the config's extras are exactly the ones that stay cheap inline -- CFG_DIST_SIMPLE disturbances and / or
 // per-episode inertia / offsets through apply_spare_simple -- so everything else a LEAN kernel carries (out-of-line disturbance and
 // constraint evaluation, dense costs, gate geometry, the PID) is compiled out: a third of the code size of the LEAN kernel.
+// (quad_type 3 takes a DS kernel only with nominal inertia in the integrator -- the reference's own DYN behaviour, F9 -- so that the
+// packed substep with its constant-bank inertia rows stays valid; per-episode inertia in the 3D integrator takes the LEAN kernel.)
 template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN, bool DS = false>
 SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, const Buf<real>& b,
                       const RngKey& key, int64_t n, int64_t i, EnvRegs<KIND, real>& e,
@@ -630,7 +632,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
     if constexpr (KIND != SCG_CARTPOLE) motors_from_thrust<KIND, real, FASTMATH>(h, thr, mot, !(PLAIN && !DS && (cfg & CFG_CLIP_ONCE)));
     else { mot.T = mot.tx = mot.ty = mot.tz = real(0); mot.rpm[0] = mot.rpm[1] = mot.rpm[2] = mot.rpm[3] = real(0); }
     // ---- _advance_simulation: S explicit substeps (base_aviary.py:266-322, 522-576)
-    constexpr bool ROWS = PLAIN && !DS && KIND == SCG_QUAD_3D && sizeof(real) == 4 && ATT != SCG_ATT_ROUNDTRIP;   // nominal inertia: constants from Hot::step_row
+    constexpr bool ROWS = PLAIN && KIND == SCG_QUAD_3D && sizeof(real) == 4 && ATT != SCG_ATT_ROUNDTRIP;   // nominal inertia: constants from Hot::step_row
     const real Tm = mot.T * (ROWS ? ldc4(h.step_row).w : e.in.inv_mass);
     const real dt = ROWS ? ldc4(h.step_row).x : h.dt;
     if constexpr (KIND == SCG_QUAD_3D) {
@@ -669,7 +671,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             if constexpr (LAST) { e.x[6] = pre3[0]; e.x[7] = pre3[1]; e.x[8] = pre3[2]; }
             attitude3<real, ATT>(pre3, e.a3);
         };
-        if constexpr (Paired<KIND, real, ATT, LEAN, (PLAIN && !DS)>::value) {
+        if constexpr (Paired<KIND, real, ATT, LEAN, PLAIN>::value) {
             // The same substep on packed pairs (FFMA2 / FADD2, scg_math.cuh): every half is the scalar operation of
             // `substep` above, bit for bit; the loop is issue-bound and a pair takes one issue slot instead of two.
             // Pairing: (x, y) of position and velocity; (roll, yaw) of angles and rates, so that the two wraps that
@@ -781,7 +783,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
         for (int s = 0; s < h.substeps; ++s) { e.x[1] += dt * az; e.x[0] += dt * e.x[1]; }
     }
     // ---- _get_observation: env.state (obs itself is written by the caller, it may be replaced on reset)
-    constexpr bool PAIRED = Paired<KIND, real, ATT, LEAN, (PLAIN && !DS)>::value;
+    constexpr bool PAIRED = Paired<KIND, real, ATT, LEAN, PLAIN>::value;
     real ang[3];
     if constexpr (PAIRED) { ang[0] = lo2(e.Wxz); ang[1] = hi2(e.ZB); ang[2] = hi2(e.Wxz); }
     else if constexpr (KIND == SCG_QUAD_3D) { ang[0] = e.x[9]; ang[1] = e.x[10]; ang[2] = e.x[11]; }
@@ -1101,7 +1103,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
     load_inertia<KIND, real>(h, (PLAIN && !DS) ? nullptr : b.inertia, n, ii, e.in);
     if constexpr (!PLAIN || DS) { if (h.cfg & CFG_DIST_SIMPLE) load_offsets<KIND, real>(h, b.dist_offset, n, ii, e); }
     derive_attitude<KIND, real, ATT>(e);
-    constexpr bool PAIRED = Paired<KIND, real, ATT, LEAN, (PLAIN && !DS)>::value;
+    constexpr bool PAIRED = Paired<KIND, real, ATT, LEAN, PLAIN>::value;
     if constexpr (PAIRED) pairs_from_scalars(e);
     real ep_ret = b.ep_return ? b.ep_return[ii] : real(0);
     int32_t ep_len = b.ep_length ? b.ep_length[ii] : 0;
@@ -1404,7 +1406,7 @@ SCG_DEV void st_release_gpu(int32_t* p, int32_t v) { asm volatile("st.release.gp
 // sleep, and a scheduler that runs ahead simply takes more ranges (same result: the split into ranges is invisible, see
 // rollout_range).
 template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN = false, bool SPEC = false, bool QUEUE = false, bool DS = false>
-__global__ void __launch_bounds__(ENV_BLOCK, sizeof(real) == 4 ? (SPEC ? SCG_BLOCKS_PER_SM : (DS ? SCG_DS_BLOCKS : 8)) : 1)
+__global__ void __launch_bounds__(ENV_BLOCK, sizeof(real) == 4 ? (DS ? SCG_DS_BLOCKS : (SPEC ? SCG_BLOCKS_PER_SM : 8)) : 1)
 k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, const Buf<real> b, const Roll<real> ro) {
     __shared__ float acc_buf[N_ACC * ACC_LD];
     __shared__ double mse_buf[2 * ACC_LD];   // fp64 columns: mse sum, return sum

@@ -155,24 +155,27 @@ def test_kernel_variant_selection():
     """scg_kernel_variant: 3 = PLAIN + SPEC for the headline workload (competition switches compiled in), 2 = PLAIN for
     other extra-free fp32 configs, 1 = LEAN as soon as a per-step extra or a
     reset-time draw beyond uniform init offsets is configured (the spare reset carries those too), 0 = GENERAL for the
-    literal round-trip attitude (validation), 4 = PLAIN + DS for fp32 2D / cart-pole configs whose extras are inline disturbances and
-    spare-carried reset draws."""
+    literal round-trip attitude (validation), 4 = PLAIN + DS for fp32 configs whose extras are inline action disturbances and
+    spare-carried reset draws (3D: with the nominal inertia in the integrator)."""
     from safe_control_gym_b200.envs.cartpole import BatchedCartPole
     lib_variant = lambda env: int(env.lib.scg_kernel_variant(env._h))
     imp = lambda off: {"action": [dict(disturbance_func="impulse", magnitude=0.01, step_offset=off, duration=2, decay_rate=0.9)]}
     cases = [(_quad(64), 3), (_quad(64, done_on_completion=False), 2), (_quad(64, cost="rl_reward"), 2), (_quad(64, gate_geometry=True), 1),
-             (_quad(64, disturbances={"action": [dict(disturbance_func="white_noise", std=0.01)]}), 1),
-             (_quad(64, disturbances=imp(None)), 1), (_quad(64, disturbances=imp(3)), 1),
-             (_quad(64, randomized_inertial_prop=True), 1), (_quad(64, attitude="roundtrip"), 0),
+             (_quad(64, disturbances={"action": [dict(disturbance_func="white_noise", std=0.01)]}), 4),
+             (_quad(64, disturbances=imp(None)), 4), (_quad(64, disturbances=imp(3)), 4),
+             (_quad(64, disturbances={"observation": [dict(disturbance_func="white_noise", std=0.01)]}), 3),   # applied where obs is written
+             (_quad(64, randomized_inertial_prop=True), 4), (_quad(64, randomized_inertial_prop=True, dyn_uses_episode_inertia=True), 1),
+             (_quad(64, attitude="roundtrip"), 0),
              (_quad(64, dtype=torch.float64), 1),
              (BatchedCartPole(num_envs=64, disturbances={"action": [dict(disturbance_func="white_noise", std=0.2)]}), 4),
              (BatchedCartPole(num_envs=64, dtype=torch.float64, disturbances={"action": [dict(disturbance_func="white_noise", std=0.2)]}), 1),
              (BatchedCartPole(num_envs=64, disturbances={"action": [dict(disturbance_func="uniform", low=-0.1, high=0.1)]}), 1),
              (_quad(64, quad_type=2, task_info=dict(stabilization_goal=[0, 1], stabilization_goal_tolerance=0.05), cost="rl_reward",
                     init_state=None, init_state_randomization_info=None, constraints=None, disturbances=imp(None)), 4)]
-    for env, want in cases:
-        assert lib_variant(env) == want, (want, lib_variant(env))
+    got = [lib_variant(env) for env, _ in cases]
+    for env, _ in cases:
         env.close()
+    assert got == [want for _, want in cases], got
 
 
 def test_spare_reset_with_inertia_and_offsets_equals_stepping():

@@ -121,3 +121,44 @@ def test_ds_kernel_equals_lean_kernel(kind):
     sa, sb = a.stats(), b.stats()
     assert sa["episodes"] == sb["episodes"] > 0 and sa["violation_steps"] == sb["violation_steps"]
     a.close(); b.close()
+
+
+def test_ds_kernel_3d_level2_like_matches_lean_kernel():
+    """quad_type 3 takes the PLAIN + DS kernel too (variant 4: the packed substep on nominal inertia -- the reference's DYN integrator
+    never reads the per-episode draws, SURVEY.md F9 -- plus inline white noise / impulse on the action channel and the cheap restart
+    that carries the per-episode inertia and offset draws): competition/level2.yaml's randomisation set.  Checked against the LEAN
+    kernel of the same config (forced by an unused constraint tolerance).  The packed substep folds -g dt into one fma where the
+    LEAN kernel multiplies and adds, so states agree to fp32 rounding accumulated over the rollout, not bit for bit; the integer
+    state (episode, step counter, per-episode draws) must be identical on every lane that did not sit on a termination edge."""
+    import bench
+    from safe_control_gym_b200.envs.quadrotor import BatchedQuadrotor as Env
+    n, k = 4096, 120
+    cfg = bench.env_kwargs()
+    cfg.update(episode_len_sec=1, randomized_inertial_prop=True,
+               inertial_prop_randomization_info={"M": U(-0.01, 0.01), "Ixx": U(-1e-6, 1e-6), "Iyy": U(-1e-6, 1e-6), "Izz": U(-1e-6, 1e-6)},
+               randomized_gates_and_obstacles=True, gates_and_obstacles_randomization_info=dict(gates=U(-0.1, 0.1), obstacles=U(-0.2, 0.2)),
+               disturbances={"action": [dict(disturbance_func="white_noise", std=0.001),
+                                        dict(disturbance_func="impulse", magnitude=0.01, step_offset=None, duration=2, decay_rate=0.9)]})
+    lean = dict(cfg)
+    lean["constraints"] = [dict(c) for c in cfg["constraints"]]
+    lean["constraints"][0]["tolerance"] = [1e-3] * 8
+    a = Env(num_envs=n, dtype=torch.float32, attitude="fast_intrinsic", auto_reset=True, **cfg)
+    b = Env(num_envs=n, dtype=torch.float32, attitude="fast_intrinsic", auto_reset=True, **lean)
+    assert int(a.lib.scg_kernel_variant(a._h)) == 4 and int(b.lib.scg_kernel_variant(b._h)) == 1
+    a.reset(); b.reset()
+    acts = bench.make_actions(torch, n, k, torch.device("cuda:0"), 5, 0.005)
+    ra, rb = torch.empty(k, n, device="cuda"), torch.empty(k, n, device="cuda")
+    for queue in (0, 1):
+        a.set_rollout_queue(queue, 32); b.set_rollout_queue(queue, 32)
+        a.rollout(acts, reward_out=ra); b.rollout(acts, reward_out=rb)
+        torch.cuda.synchronize()
+        same = (a.buf_episode == b.buf_episode) & (a.buf_ctrl_step == b.buf_ctrl_step)
+        assert float(same.float().mean()) > 0.999, float(same.float().mean())
+        assert int(a.buf_episode.max()) >= 2          # restarts happened inside the launch
+        for name in ("inertia", "dist_offset"):
+            x, y = getattr(a, "buf_" + name), getattr(b, "buf_" + name)
+            assert torch.equal(x[..., same], y[..., same]), name
+        err = (a.buf_state[:, same] - b.buf_state[:, same]).abs().max()
+        assert float(err) < 2e-3, float(err)
+        assert float((ra[:, same] - rb[:, same]).abs().max()) < 2e-3
+    a.close(); b.close()

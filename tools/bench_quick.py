@@ -1,10 +1,10 @@
-"""Quick device-timed numbers of the bench configs (no CPU baselines, short): python tools/bench_quick.py [--configs 3,4,5,2h,2c]"""
+"""Quick device-timed numbers of the bench configs (no CPU baselines, short): python tools/bench_quick.py [--configs 3,4,5,2h,2l,2c]"""
 import json
 import subprocess
 import sys
 import os
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-cfgs = sys.argv[sys.argv.index("--configs") + 1] if "--configs" in sys.argv else "3,4,5,2h,2c"
+cfgs = sys.argv[sys.argv.index("--configs") + 1] if "--configs" in sys.argv else "3,4,5,2h,2l,2c"
 out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "50", "--no-cpu", "--sustain-seconds", "0.3", "--configs", cfgs],
                      capture_output=True, text=True)
 try:

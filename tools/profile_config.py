@@ -1,5 +1,5 @@
 """Small driver for ncu captures of the other BASELINE configs (the bench shapes at reduced K).
-    python tools/profile_config.py --config 3|4|5|5g|pid|step [--k 64] [--launches 3] [--scale 0.25]"""
+    python tools/profile_config.py --config 2|3|4|5|5g|2l|pid|step [--k 64] [--launches 3] [--scale 0.25]"""
 import argparse
 import os
 import sys
@@ -33,13 +33,15 @@ elif a.config == "4":
     acts = torch.empty(a.k, n, 2, device=dev).normal_(hover, 0.005, generator=g).clamp_(0, 4 * hover)
     run = lambda: env.rollout(acts)
 else:
-    n = int((65536 if a.config in ("pid", "step") else 4 * 1024 * 1024) * (1.0 if a.config in ("pid", "step") else a.scale))
-    kw = bench.config5_kwargs() if a.config == "5g" else bench.env_kwargs()
+    n = int((65536 if a.config in ("pid", "step", "2l", "2") else 4 * 1024 * 1024) * (1.0 if a.config in ("pid", "step", "2l", "2") else a.scale))
+    kw = bench.config5_kwargs() if a.config == "5g" else (bench.level2_like_kwargs() if a.config == "2l" else bench.env_kwargs())
     env = BatchedQuadrotor(num_envs=n, device=dev, dtype=torch.float32, attitude="fast_intrinsic", auto_reset=True, **kw)
     acts = bench.make_actions(torch, n, a.k, dev, 1, 0.005)
     if a.config in ("5", "5g"):
         log = torch.empty(a.k, 16, n, device=dev)
         run = lambda: env.rollout(acts, log_out=log)
+    elif a.config in ("2l", "2"):
+        run = lambda: env.rollout(acts)
     elif a.config == "pid":
         run = lambda: env.rollout_pid(a.k)
     else:
