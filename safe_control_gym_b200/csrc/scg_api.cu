@@ -204,6 +204,16 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
             return double(INFINITY);
         };
         k.gate_broad2 = real(broad2(c.gate_rand)); k.obstacle_broad2 = real(broad2(c.obstacle_rand));
+        // the inline copy of the same test (Hot::geo): fp32, radius widened by 1e-4 relative so that it never rejects what the scan accepts
+        h.geo_n = 0;
+        for (int g = 0; g < c.n_gates; ++g, ++h.geo_n) {
+            h.geo_neg[h.geo_n][0] = -float(c.gates[g][0]); h.geo_neg[h.geo_n][1] = -float(c.gates[g][1]);
+            h.geo_r2[h.geo_n] = float(broad2(c.gate_rand) * 1.0002 + 1e-6);
+        }
+        for (int g = 0; g < c.n_obstacles; ++g, ++h.geo_n) {
+            h.geo_neg[h.geo_n][0] = -float(c.obstacles[g][0]); h.geo_neg[h.geo_n][1] = -float(c.obstacles[g][1]);
+            h.geo_r2[h.geo_n] = float(broad2(c.obstacle_rand) * 1.0002 + 1e-6);
+        }
     }
     k.n_obstacles = c.n_obstacles;
     h.seed = c.seed; h.env_id_base_lo = uint32_t(c.env_id_base & 0xFFFFFFFFll);
@@ -217,7 +227,6 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
         for (int q = 0; q < nd; ++q) if (k.dense[q].var == SCG_VAR_STATE) rates = true;
         if (c.cost == SCG_COST_RL_REWARD) for (int d = 9; d < 12; ++d) if (c.rew_state_weight[d] != 0.0) rates = true;
         if (c.cost == SCG_COST_QUADRATIC) rates = true;   // Q weighs the rates (identity by default); goal_reached norms the full state
-        if (c.gate_geometry) rates = true;                // the gate rays need the whole rotation matrix
     }
     h.need_full_state = rates ? 1 : 0;
     h.cfg = (c.task == SCG_TASK_STABILIZATION ? CFG_STAB : 0u) | (c.cost == SCG_COST_RL_REWARD ? CFG_COST_RL : 0u) |
@@ -360,7 +369,7 @@ extern "C" int scg_kernel_variant(const scg_env* env) {
         !(env->cfg.env_kind == SCG_QUAD_3D && env->cfg.dyn_uses_episode_inertia)) {
         // PLAIN + DS (scg_inst.cuh: ds_kernel_ok; closed-loop launches and launches with injected draws still take variant 1)
         const uint32_t c = env->hf.cfg;
-        const bool general = (c & (CFG_COLD_CONSTRAINTS | CFG_QR_DENSE | CFG_PENALTY | CFG_GATE_GEOMETRY)) || env->hf.normalized_action;
+        const bool general = (c & (CFG_COLD_CONSTRAINTS | CFG_QR_DENSE | CFG_PENALTY)) || env->hf.normalized_action;
         const bool dist_ok = !(c & CFG_DISTURBED) || (c & CFG_DIST_SIMPLE);
         const bool reset_ok = !(c & CFG_RESET_EXTRAS) || ((c & CFG_SPARE_SIMPLE) && ((c & CFG_DIST_SIMPLE) || env->hf.n_dist_act == 0));
         if (!general && dist_ok && reset_ok) return 4;

@@ -509,7 +509,13 @@ SCG_DEV void pose_offsets(const RandP<real>& rp, uint32_t stream, uint32_t idx, 
     }
 }
 
-// returns bit 0: a ray of the current gate hit the drone; bit 1: the drone touches a gate, an obstacle or the ground.
+// ground plane against the drone's collision cylinder: its support along -z
+template <typename real> SCG_DEV bool ground_contact(real pz, real r8) {
+    const real support = Geo<real>::drone_hl * m_abs(r8) + Geo<real>::drone_r * m_sqrt(m_max(real(0), real(1) - r8 * r8));
+    return pz - support < real(0);
+}
+
+// returns bit 0: a ray of the current gate hit the drone; bit 1: the drone touches a gate or an obstacle.
 // Broad phase first: an object whose NOMINAL axis is farther than `broad2` (0.35 m + the largest pose offset) from the
 // drone is skipped before its pose offsets are even drawn -- almost every (env, object) pair of a step.
 template <typename real>
@@ -529,7 +535,10 @@ __device__ __noinline__ uint32_t gate_scan(const Hot<real>& h, const Cold<real>*
             m_sincos(G[5] + off[2], &sy, &cy);
         }
         const real height = G[6] == real(0) ? real(1.0) : real(0.525);
-        if (check_gate && uint32_t(g) == cur_gate) {   // quadrotor.py:1060-1092
+        // (narrow phase of the rays first: they span +-0.15 m along the gate and +-0.1875 m in height around its centre, the drone's
+        //  cylinder lies inside a sphere of radius sqrt(0.06^2 + 0.0125^2) < 0.0615 -- farther than that nothing can hit)
+        const real cgx = px - gx, cgy = py - gy, cgz = pz - height;
+        if (check_gate && uint32_t(g) == cur_gate && cgx * cgx + cgy * cgy <= real(0.2116 * 0.2116) && m_abs(cgz) <= real(0.2491)) {   // quadrotor.py:1060-1092
             const real dx = real(0.05) * cy, dy = real(0.05) * sy;
             const real zl = height - real(0.1875) - pz, zh = height + real(0.1875) - pz;
 #pragma unroll 1
@@ -569,10 +578,7 @@ __device__ __noinline__ uint32_t gate_scan(const Hot<real>& h, const Cold<real>*
         collided |= sphere_vcyl<real>(p, real(0), real(0.05), real(0.4)) |
                     sphere_box<real>(p, 0, 0, real(-0.4), real(0.075), real(0.075), real(0.125));
     }
-    // ground plane against the collision cylinder: its support along -z
-    const real support = Geo<real>::drone_hl * m_abs(r8) + Geo<real>::drone_r * m_sqrt(m_max(real(0), real(1) - r8 * r8));
-    collided |= pz - support < real(0);
-    return (passed ? 1u : 0u) | (collided ? 2u : 0u);
+    return (passed ? 1u : 0u) | (collided ? 2u : 0u);   // (the ground plane is the caller's: ground_contact)
 }
 
 // ------------------------------------------------------------------ disturbances (row A5)

@@ -65,4 +65,13 @@ int launch_rollout_tlog_3d_f(scg_env* e, const Roll<float>& ro, cudaStream_t st)
 template <int KIND, typename real> int launch_constraints(scg_env* e, const real* state, const real* action, int64_t n,
                                                           real* out_values, uint8_t* out_flags, cudaStream_t st);
 
+// (see scg_inst.cuh: launch_rollout_att)
+template <typename real> inline bool ds_kernel_ok(const Hot<real>& h) {
+    const uint32_t c = h.cfg;
+    if ((c & (CFG_COLD_CONSTRAINTS | CFG_QR_DENSE | CFG_PENALTY)) || h.normalized_action) return false;   // (gate geometry: quad_type 3 only, inline broad phase)
+    if ((c & CFG_DISTURBED) && !(c & CFG_DIST_SIMPLE)) return false;
+    if ((c & CFG_RESET_EXTRAS) && !((c & CFG_SPARE_SIMPLE) && ((c & CFG_DIST_SIMPLE) || h.n_dist_act == 0))) return false;
+    return true;
+}
+
 }  // namespace scg

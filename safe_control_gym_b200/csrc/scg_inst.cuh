@@ -82,14 +82,6 @@ static void launch_rollout_v(scg_env* e, const Hot<real>& h, const Cold<real>* c
 // The PLAIN + DS kernel applies (scg_step.cuh: step_env): none of the general extras, disturbances (if any) all inline, the
 // restart (if it draws more than uniform init offsets) through apply_spare_simple.  Evaluated per launch: injected draws switch
 // CFG_DIST_SIMPLE off (scg_set_injection).
-template <typename real> static bool ds_kernel_ok(const Hot<real>& h) {
-    const uint32_t c = h.cfg;
-    if ((c & (CFG_COLD_CONSTRAINTS | CFG_QR_DENSE | CFG_PENALTY | CFG_GATE_GEOMETRY)) || h.normalized_action) return false;
-    if ((c & CFG_DISTURBED) && !(c & CFG_DIST_SIMPLE)) return false;
-    if ((c & CFG_RESET_EXTRAS) && !((c & CFG_SPARE_SIMPLE) && ((c & CFG_DIST_SIMPLE) || h.n_dist_act == 0))) return false;
-    return true;
-}
-
 template <int KIND, typename real, int ATT>
 static void launch_rollout_att(scg_env* e, const Hot<real>& h, const Cold<real>* cold, const Buf<real>& b, const Roll<real>& ro,
                                unsigned blocks, cudaStream_t st) {

@@ -96,6 +96,11 @@ template <typename real> struct Hot {
     // parameters as constant-bank operands instead of generic loads from Cold::dist behind an out-of-line call
     int32_t ds_n, ds_kind[SCG_MAX_DIST], ds_off[SCG_MAX_DIST] /* >= 0 fixed, -1: this episode's draw */, ds_slot[SCG_MAX_DIST];
     real ds_mag[SCG_MAX_DIST], ds_half[SCG_MAX_DIST], ds_decay[SCG_MAX_DIST], ds_l2decay[SCG_MAX_DIST], ds_std[SCG_MAX_DIST][SCG_MAX_NU];
+    // gate_geometry: the first broad phase of the contact scan, inline (step_env): nominal axis (x, y) and widened squared radius of every
+    // gate, then every obstacle.  A drone outside all of them -- almost every env-step -- never enters gate_scan (scg_env.cuh).
+    int32_t geo_n;
+    alignas(8) float geo_neg[SCG_MAX_GATES + SCG_MAX_OBSTACLES][2];   // (-x, -y): one packed add per object
+    float geo_r2[SCG_MAX_GATES + SCG_MAX_OBSTACLES];
     // the uniform switches the control-step loop tests, packed (CFG_*): one constant-bank word feeds all of
     // them, where a separate field per switch costs a dependent load -> compare -> branch chain each
     uint32_t cfg;

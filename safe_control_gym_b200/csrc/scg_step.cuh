@@ -789,7 +789,6 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
     else if constexpr (KIND == SCG_QUAD_3D) { ang[0] = e.x[9]; ang[1] = e.x[10]; ang[2] = e.x[11]; }
     else if constexpr (KIND == SCG_QUAD_2D) { ang[0] = real(0); ang[1] = e.x[5]; ang[2] = real(0); }
     else { ang[0] = ang[1] = ang[2] = real(0); }
-    real Rw[KIND == SCG_QUAD_3D ? 9 : 1];   // body-to-world rotation for the gate geometry (dead otherwise)
     if constexpr (KIND == SCG_QUAD_3D) {
         make_state<KIND, real, false, PAIRED>(e, ang, st);
         st[9] = st[10] = st[11] = real(0);
@@ -798,8 +797,6 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             if constexpr (PAIRED) { c.R[2] = lo2(e.Rxy); c.R[5] = hi2(e.Rxy); c.R[8] = e.R8; }
             attitude3_complete<real>(c);
             const real* R = c.R;
-#pragma unroll
-            for (int j = 0; j < 9; ++j) Rw[j] = R[j];
             st[9] = (R[0] * ang[0] + R[3] * ang[1]) + R[6] * ang[2];
             st[10] = (R[1] * ang[0] + R[4] * ang[1]) + R[7] * ang[2];
             st[11] = (R[2] * ang[0] + R[5] * ang[1]) + R[8] * ang[2];
@@ -807,15 +804,33 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
     } else make_state<KIND, real>(e, ang, st);
     // ---- _get_info (quadrotor.py:1004-1134): goal hold (collision scan is dead in DYN, F5)
     bool gate_passed = false, collided = false;
-    if constexpr (KIND == SCG_QUAD_3D && !PLAIN) {
-        if (cfg & CFG_GATE_GEOMETRY) {   // extension: the contact scan and the gate rays on the integrated pose (implies `full`)
-            // pyb_step_counter > 0.5 PYB_FREQ, the counter still at t * S (it advances in after_step, benchmark_env.py:427)
-            //   <=>  2 t > CTRL_FREQ (quadrotor.py:1060)
-            const bool check_gate = 2 * t > h.ctrl_freq && e.gate < uint32_t(h.n_gates);
-            const uint32_t bits = gate_scan<real>(h, cold, key, ep, st[0], st[2], st[4], Rw[0], Rw[1], Rw[2], Rw[3], Rw[4], Rw[5],
-                                                  Rw[6], Rw[7], Rw[8], e.gate, check_gate);
-            if (bits & 1u) { e.gate += 1u; gate_passed = true; }
-            collided = (bits & 2u) != 0u;
+    if constexpr (KIND == SCG_QUAD_3D && (!PLAIN || DS)) {
+        if (cfg & CFG_GATE_GEOMETRY) {   // extension: the contact scan and the gate rays on the integrated pose
+            real r8;
+            if constexpr (PAIRED) r8 = e.R8; else r8 = e.a3.R[8];
+            collided = ground_contact<real>(st[4], r8);
+            // first broad phase, inline on constant-bank operands (Hot::geo): is the drone near ANY gate / obstacle axis?
+            bool near = false;
+            const f32x2 P = pk2(float(st[0]), float(st[2]));
+#pragma unroll
+            for (int j = 0; j < SCG_MAX_GATES + SCG_MAX_OBSTACLES; ++j) {
+                if (j >= h.geo_n) break;   // uniform
+                const f32x2 D = add2(P, *reinterpret_cast<const f32x2*>(h.geo_neg[j]));
+                const f32x2 S = mul2(D, D);
+                near |= lo2(S) + hi2(S) <= h.geo_r2[j];
+            }
+            if (near) {   // rare: the whole rotation matrix (the gate rays work in the body frame) and the exact scan, out of line
+                Att3<real> c = e.a3;
+                if constexpr (PAIRED) { c.R[2] = lo2(e.Rxy); c.R[5] = hi2(e.Rxy); c.R[8] = e.R8; }
+                attitude3_complete<real>(c);
+                // pyb_step_counter > 0.5 PYB_FREQ, the counter still at t * S (it advances in after_step, benchmark_env.py:427)
+                //   <=>  2 t > CTRL_FREQ (quadrotor.py:1060)
+                const bool check_gate = 2 * t > h.ctrl_freq && e.gate < uint32_t(h.n_gates);
+                const uint32_t bits = gate_scan<real>(h, cold, key, ep, st[0], st[2], st[4], c.R[0], c.R[1], c.R[2], c.R[3], c.R[4], c.R[5],
+                                                      c.R[6], c.R[7], c.R[8], e.gate, check_gate);
+                if (bits & 1u) { e.gate += 1u; gate_passed = true; }
+                collided |= (bits & 2u) != 0u;
+            }
         }
     }
     e.at_goal = false;
@@ -1179,7 +1194,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
         ep_viol += viol ? 1 : 0;
         s_viol += viol ? 1.f : 0.f;
         s_mse += float(mse);
-        if (!PLAIN && (cfg & CFG_GATE_GEOMETRY)) {
+        if ((!PLAIN || DS) && (cfg & CFG_GATE_GEOMETRY)) {
             s_gates += (info & SCG_INFO_GATE_PASSED) ? 1.f : 0.f;
             s_coll += (info & SCG_INFO_COLLISION) ? 1.f : 0.f;
         }
@@ -1358,7 +1373,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
     // which resident thread ran which chunk; the other statistics are small integers, exact in fp32)
     ep_acc[6 * ACC_LD] += s_viol; ep_acc[8 * ACC_LD] += float(k1 - k0);
     mse_acc[0] += double(s_mse); mse_acc[ACC_LD] += double(ep_acc[1 * ACC_LD]);
-    if (!PLAIN) { ep_acc[9 * ACC_LD] += s_gates; ep_acc[10 * ACC_LD] += s_coll; }
+    if (!PLAIN || DS) { ep_acc[9 * ACC_LD] += s_gates; ep_acc[10 * ACC_LD] += s_coll; }
 }
 
 // episode statistics of a block: warp-shuffle reduction, one atomic per warp per statistic
@@ -1451,31 +1466,32 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
             push = k1 < ro.k_steps ? item + ro.q_env_blocks : 0;
         }
     }
-    reduce_stats<PLAIN>(b.stats, acc_buf, mse_buf);
+    reduce_stats<(PLAIN && !DS)>(b.stats, acc_buf, mse_buf);
 }
 
 // The same launch shape as k_rollout<..., QUEUE = false> with the trajectory log staged in shared memory and written by the
 // TMA unit (rollout_range<..., TLOG = true>; 3D fp32, launched from scg_k_3d_f_tlog.cu when the log tensor qualifies).
-template <int ATT, bool PLAIN, bool SPEC>
+// DS: the PLAIN + DS loop (inline disturbances, gate geometry behind its inline broad phase, cheap restart) -- BASELINE config 5.
+template <int ATT, bool DS, bool SPEC>
 #ifndef SCG_TLOG_BLOCKS
 #define SCG_TLOG_BLOCKS 9   // 96 registers, like the SPEC rollout kernels (SCG_BLOCKS_PER_SM)
 #endif
-__global__ void __launch_bounds__(ENV_BLOCK, SPEC ? SCG_TLOG_BLOCKS : 8)   // (the PLAIN kernel spills at 96 registers)
+__global__ void __launch_bounds__(ENV_BLOCK, (SPEC && !DS) ? SCG_TLOG_BLOCKS : 8)   // (the other kernels spill at 96 registers)
 k_rollout_tlog(const __grid_constant__ Hot<float> h, const Cold<float>* __restrict__ cold, const Buf<float> b, const Roll<float> ro,
                const __grid_constant__ LogMaps maps) {
     constexpr int KIND = SCG_QUAD_3D;
     __shared__ float acc_buf[N_ACC * ACC_LD];
     __shared__ double mse_buf[2 * ACC_LD];
-    __shared__ float sp_buf[(Spare<KIND, float, ATT>::N + (PLAIN ? 0 : SPARE_EXTRA)) * ENV_BLOCK];
+    __shared__ float sp_buf[(Spare<KIND, float, ATT>::N + (DS ? SPARE_EXTRA : 0)) * ENV_BLOCK];
     __shared__ __align__(128) float lg_buf[2 * LOG_STAGES * LOG_STAGE];   // [warp][stage][LOG_T][16][32]
     mse_buf[threadIdx.x] = 0.0; mse_buf[ACC_LD + threadIdx.x] = 0.0;
 #pragma unroll
     for (int j = 0; j < N_ACC; ++j) acc_buf[j * ACC_LD + threadIdx.x] = 0.f;
     const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-    rollout_range<KIND, float, ATT, true, PLAIN, SPEC, true>(h, cold, b, ro, i, 0, ro.k_steps, acc_buf + (i < b.n ? threadIdx.x : ENV_BLOCK),
-                                                            mse_buf + (i < b.n ? threadIdx.x : ENV_BLOCK), sp_buf + threadIdx.x, &maps,
-                                                            lg_buf + (threadIdx.x >> 5) * LOG_STAGES * LOG_STAGE);
-    reduce_stats<PLAIN>(b.stats, acc_buf, mse_buf);
+    rollout_range<KIND, float, ATT, true, true, SPEC, true, DS>(h, cold, b, ro, i, 0, ro.k_steps, acc_buf + (i < b.n ? threadIdx.x : ENV_BLOCK),
+                                                               mse_buf + (i < b.n ? threadIdx.x : ENV_BLOCK), sp_buf + threadIdx.x, &maps,
+                                                               lg_buf + (threadIdx.x >> 5) * LOG_STAGES * LOG_STAGE);
+    reduce_stats<!DS>(b.stats, acc_buf, mse_buf);
 }
 
 

@@ -160,7 +160,7 @@ def test_kernel_variant_selection():
     from safe_control_gym_b200.envs.cartpole import BatchedCartPole
     lib_variant = lambda env: int(env.lib.scg_kernel_variant(env._h))
     imp = lambda off: {"action": [dict(disturbance_func="impulse", magnitude=0.01, step_offset=off, duration=2, decay_rate=0.9)]}
-    cases = [(_quad(64), 3), (_quad(64, done_on_completion=False), 2), (_quad(64, cost="rl_reward"), 2), (_quad(64, gate_geometry=True), 1),
+    cases = [(_quad(64), 3), (_quad(64, done_on_completion=False), 2), (_quad(64, cost="rl_reward"), 2), (_quad(64, gate_geometry=True), 4),
              (_quad(64, disturbances={"action": [dict(disturbance_func="white_noise", std=0.01)]}), 4),
              (_quad(64, disturbances=imp(None)), 4), (_quad(64, disturbances=imp(3)), 4),
              (_quad(64, disturbances={"observation": [dict(disturbance_func="white_noise", std=0.01)]}), 3),   # applied where obs is written
@@ -317,16 +317,17 @@ def test_bench_path_matches_oracle_on_sampled_lanes(k):
     env.close()
 
 
-@pytest.mark.parametrize("variant", ["spec", "plain", "lean_gates"])
+@pytest.mark.parametrize("variant", ["spec", "plain", "ds_gates", "lean"])
 @pytest.mark.parametrize("n,k,stride", [(4100, 37, 1), (4100, 40, 3), (64 * 1184 + 8, 9, 1)])
 def test_tma_staged_log_equals_plain_log(variant, n, k, stride):
     """Row X1: the trajectory log written through the TMA unit (records staged in shared memory, one bulk tensor store per
     warp and LOG_T logged steps, scg_step.cuh: rollout_range<..., TLOG>) carries the same bytes as the plain strided
     stores -- ragged last warp (columns clipped by the hardware), an odd number of logged steps (the tail goes out one
-    step at a time), log strides, more than one wave of blocks, and all three kernel variants."""
-    over = {"spec": {}, "plain": dict(done_on_violation=False), "lean_gates": dict(gate_geometry=True)}[variant]
+    step at a time), log strides, more than one wave of blocks, and the PLAIN, SPEC, PLAIN + DS (BASELINE config 5: gate geometry) and LEAN loops."""
+    over = {"spec": {}, "plain": dict(done_on_violation=False), "ds_gates": dict(gate_geometry=True),
+            "lean": dict(randomized_inertial_prop=True, dyn_uses_episode_inertia=True)}[variant]
     a, b = _quad(n, attitude="fast_intrinsic", **over), _quad(n, attitude="fast_intrinsic", **over)
-    assert int(a.lib.scg_kernel_variant(a._h)) == {"spec": 3, "plain": 2, "lean_gates": 1}[variant]
+    assert int(a.lib.scg_kernel_variant(a._h)) == {"spec": 3, "plain": 2, "ds_gates": 4, "lean": 1}[variant]
     b.set_rollout_queue(1)   # a forced queue keeps the plain store path (k < 64: static grid, plain stores)
     acts = _actions(n, k, std=0.01)
     rows = (k + stride - 1) // stride
@@ -335,7 +336,7 @@ def test_tma_staged_log_equals_plain_log(variant, n, k, stride):
     for _ in range(2):
         a.rollout(acts, log_out=la, log_stride=stride); b.rollout(acts, log_out=lb, log_stride=stride)
         torch.cuda.synchronize()
-        assert a.last_rollout_tlog == (variant != "lean_gates") and not b.last_rollout_tlog   # the LEAN kernels keep plain stores
+        assert a.last_rollout_tlog == (variant != "lean") and not b.last_rollout_tlog   # the LEAN kernels keep plain stores
         assert not torch.isnan(la).any() and torch.equal(la, lb)
         for name in ("state", "ctrl_step", "episode", "flags", "obs", "ep_length"):
             assert torch.equal(getattr(a, "buf_" + name), getattr(b, "buf_" + name)), name

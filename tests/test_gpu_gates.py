@@ -89,3 +89,33 @@ def test_gate_progress_and_collisions_match_oracle(dtype, randomized):
     if not dropped:
         assert st["gates"] == passed and st["collisions"] == collided
     env.close()
+
+
+def test_gate_geometry_ds_kernel_matches_lean_kernel():
+    """The fused fp32 rollout with gate geometry takes the PLAIN + DS loop (inline broad phase over Hot::geo, gate_scan only for
+    drones near an object; variant 4) -- against the LEAN loop of the same config (forced by an unused constraint tolerance) on
+    drones that fly through / into the gates: same gates passed, collisions and episodes on every lane whose contact / ray
+    decisions did not fall within fp32 rounding of a threshold (the packed substep rounds -g dt differently, see
+    tests/test_gpu_config4.py::test_ds_kernel_3d_level2_like_matches_lean_kernel)."""
+    from safe_control_gym_b200.envs.quadrotor import BatchedQuadrotor
+    n, k = 8192, 150
+    for randomized in (False, True):
+        kw = _kwargs(randomized)
+        lean = dict(kw)
+        lean["constraints"] = [dict(kw["constraints"][0], tolerance=[1e-3] * 8)]
+        a = BatchedQuadrotor(num_envs=n, dtype=torch.float32, attitude="fast_intrinsic", auto_reset=True, **kw)
+        b = BatchedQuadrotor(num_envs=n, dtype=torch.float32, attitude="fast_intrinsic", auto_reset=True, **lean)
+        assert int(a.lib.scg_kernel_variant(a._h)) == 4 and int(b.lib.scg_kernel_variant(b._h)) == 1
+        a.reset(); b.reset()
+        acts = torch.full((k, n, 4), M * G / 4, device="cuda")
+        a.rollout(acts); b.rollout(acts)
+        torch.cuda.synchronize()
+        same = (a.buf_episode == b.buf_episode) & (a.buf_ctrl_step == b.buf_ctrl_step) & (a.buf_flags == b.buf_flags)
+        assert float(same.float().mean()) > 0.995, float(same.float().mean())
+        sa, sb = a.stats(), b.stats()
+        assert sa["gates"] > n // 16 and sa["collisions"] > n // 16, sa
+        for key in ("gates", "collisions", "episodes"):
+            assert abs(sa[key] - sb[key]) <= 0.005 * max(sa[key], sb[key]), (key, sa[key], sb[key])
+        err = (a.buf_state[:, same] - b.buf_state[:, same]).abs().max()
+        assert float(err) < 2e-3, float(err)
+        a.close(); b.close()
