@@ -290,7 +290,11 @@ SCG_DEV void cartpole_rk4(const Inertia<real>& in, real g, real (&x)[4], real F,
 template <typename real> SCG_DEV real round8(real c) { return m_rint(c * real(1e8)) / real(1e8); }
 template <> SCG_DEV float round8<float>(float c) {
     // fp32 carries fewer than 8 decimals above |c| ~ 0.08: rounding is then the identity
-    return m_abs(c) < 0.08f ? m_rint(c * 1e8f) / 1e8f : c;
+    // k / 1e8 as a product and one Newton step on its residual (k is an integer below 2^23: the residual fma is exact) --
+    // the division subroutine was 250 instructions per host-driven step for the 14 rows of the level0 family
+    const float k = m_rint(c * 1e8f);
+    const float q = k * 1e-8f;
+    return m_abs(c) < 0.08f ? fmaf(fmaf(-q, 1e8f, k), 1e-8f, q) : c;
 }
 template <typename real> SCG_DEV bool viol_test(real c, int strict) {
     const real y = c * real(1e8);
@@ -379,17 +383,25 @@ __device__ __noinline__ uint32_t constraint_values_cold(const Hot<real>& h, cons
 // The same values for configs whose rows all come from plain bounded constraints (Hot::crow_*): one pass over the output
 // rows instead of the object / dim / kind loops above (the host-driven step of the level0 family spent 40 % of its
 // instructions there).  Same arithmetic per row: c = lo - x or x - hi, round8, viol_test.
+// Inline: the row table is then read from the constant bank (through a reference handed to an out-of-line function the same
+// loads are generic ones: 38 instructions per row, 25 % of the host-driven step's time).
 template <int KIND, typename real>
-__device__ __noinline__ uint32_t constraint_values_flat(const Hot<real>& h, const real* __restrict__ st, const real* __restrict__ raw,
-                                                        bool state_only, real* __restrict__ c_out, int64_t n, int64_t i) {
-    constexpr int NX = Dims<KIND>::NX;
+SCG_DEV uint32_t constraint_values_flat(const Hot<real>& h, const real (&st)[Dims<KIND>::NX], const real (&raw)[Dims<KIND>::NU],
+                                        bool state_only, real* __restrict__ c_out, int64_t n, int64_t i) {
+    constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
+    real v[NX + NU];   // indexed by the row's source: a small local-memory array
+#pragma unroll
+    for (int d = 0; d < NX; ++d) v[d] = st[d];
+#pragma unroll
+    for (int d = 0; d < NU; ++d) v[NX + d] = raw[d];
     bool violated = false;
     real* p = c_out + i;
     const int strict = h.crow_strict;
+#pragma unroll 1
     for (int r = 0; r < h.n_crows; ++r, p += n) {
         const int src = h.crow_src[r];
         if (src >= NX && state_only) continue;
-        const real x = src < NX ? st[src] : raw[src - NX];
+        const real x = v[src];
         const real b = h.crow_bound[r];
         const real c = h.crow_sgn[r] > 0 ? x - b : b - x;
         *p = round8(c);
@@ -408,14 +420,17 @@ SCG_DEV void eval_constraints(const Hot<real>& h, const Cold<real>* __restrict__
                               bool& violated, bool& almost, uint32_t cfg) {
     constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
     violated = false; almost = false;
+    if (c_out != nullptr && h.n_crows > 0) {
+        violated = constraint_values_flat<KIND, real>(h, st, raw, state_only, c_out, n, i) != 0u;
+        return;
+    }
     if (c_out != nullptr || (!PLAIN && (cfg & CFG_COLD_CONSTRAINTS))) {
         real sl[NX], rl[NU];   // the out-of-line call takes copies, the caller's registers stay registers
 #pragma unroll
         for (int d = 0; d < NX; ++d) sl[d] = st[d];
 #pragma unroll
         for (int d = 0; d < NU; ++d) rl[d] = raw[d];
-        const uint32_t bits = (c_out != nullptr && h.n_crows > 0) ? constraint_values_flat<KIND, real>(h, sl, rl, state_only, c_out, n, i)
-                                                                 : constraint_values_cold<KIND, real>(h, cold, sl, rl, state_only, c_out, n, i);
+        const uint32_t bits = constraint_values_cold<KIND, real>(h, cold, sl, rl, state_only, c_out, n, i);
         violated = (bits & 1u) != 0u; almost = (bits & 2u) != 0u;
         return;
     }

@@ -1392,10 +1392,9 @@ SCG_DEV void reduce_stats(double* __restrict__ stats, const float* __restrict__ 
 #pragma unroll
         for (int j = 0; j < NS; ++j) {
             if (slot[j] == SCG_STAT_MSE || slot[j] == SCG_STAT_RETURN) continue;
-            double r = double(v[j]);
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
-            if ((threadIdx.x & 31) == 0 && r != 0.0) atomicAdd(stats + slot[j], r);
+            // (counts: integers below 2^24 per thread, so the warp sum is one exact integer reduction)
+            const int r = __reduce_add_sync(0xffffffffu, __float2int_rn(v[j]));
+            if ((threadIdx.x & 31) == 0 && r != 0) atomicAdd(stats + slot[j], double(r));
         }
         double m = mse_buf[threadIdx.x], r = mse_buf[ACC_LD + threadIdx.x];
 #pragma unroll
