@@ -422,7 +422,7 @@ def run_gpu(args):
             # The only collective of the path: merge the episode statistics.  It runs on NCCL's
             # stream behind a snapshot of the 16 doubles, two buffers in turn, so the next launch does not wait for it;
             # drain() makes the timed region end only after the last merge has completed.
-            merger.submit(env.buf_stats)
+            merger.submit(env.stats_vector())
 
     def drain():
         merger.drain()
@@ -469,7 +469,7 @@ def run_gpu(args):
     def one_e2e():
         env.rollout_host(host_actions, chunk_steps=args.chunk)
         obs_host.copy_(env.buf_obs, non_blocking=True)
-        st = env.buf_stats.cpu()
+        st = env.stats_vector().cpu()
         torch.cuda.synchronize()
         return st
     one_e2e()
@@ -511,7 +511,7 @@ def run_gpu(args):
     def one_e2e_pid():
         env.rollout_pid(k)
         obs_host.copy_(env.buf_obs, non_blocking=True)
-        st = env.buf_stats.cpu()
+        st = env.stats_vector().cpu()
         torch.cuda.synchronize()
         return st
     one_e2e_pid()

@@ -44,6 +44,10 @@ extern "C" {
 #define SCG_MAX_GATES 8
 #define SCG_MAX_OBSTACLES 8
 #define SCG_STATS_LEN 16
+/* The device accumulators are SCG_STAT_REPLICAS copies of the statistics vector; a warp adds to the copy its index selects and the
+ * totals are the sums over the copies (scg_stats_read returns them).  One copy made every warp of a launch queue on the same
+ * few L2 words: 6 us of a 15 us host-driven step at 65,536 envs. */
+#define SCG_STAT_REPLICAS 64
 
 /* env_kind: QuadType (quadrotor_utils.py:11-18) or the cart-pole */
 enum { SCG_QUAD_1D = 1, SCG_QUAD_2D = 2, SCG_QUAD_3D = 3, SCG_CARTPOLE = 10 };
@@ -210,7 +214,7 @@ typedef struct {
     void* ep_return;          /* [n] real running return */
     int32_t* ep_length;       /* [n] */
     int32_t* ep_violations;   /* [n] */
-    double* stats;            /* [SCG_STATS_LEN] device accumulators */
+    double* stats;            /* [SCG_STAT_REPLICAS][SCG_STATS_LEN] device accumulators (totals: sum over the replicas) */
     /* adversary action for the next step, [n][dim] env-major (optional) */
     const void* adv_action;
 } scg_buffers;
@@ -251,7 +255,7 @@ int scg_rollout(scg_env* env, const scg_rollout_args* args, void* stream);
 /* same, actions in pinned HOST memory [K][n][nu]; copies are chunked and overlapped
  * with compute on an internal copy stream; final obs / reward sums land in the bound buffers */
 int scg_rollout_host(scg_env* env, const void* host_actions, int32_t k_steps, int32_t chunk_steps, void* stream);
-/* zero / read the float64[SCG_STATS_LEN] statistics vector (async copy to host_out) */
+/* zero the accumulators / read their totals, float64[SCG_STATS_LEN] (summed over the replicas on the device, async copy to host_out) */
 int scg_stats_reset(scg_env* env, void* stream);
 int scg_stats_read(scg_env* env, double* host_out, void* stream);
 /* ConstraintList.get_values / is_violated (constraints.py:503-563) on caller-given

@@ -12,6 +12,7 @@ LIB_PATH = os.environ.get("SCG_LIB", os.path.join(HERE, "libscg_b200.so"))   # S
 
 MAX_NX, MAX_NU, MAX_CONSTRAINTS, MAX_CON_ROWS, MAX_ROWS = 12, 4, 8, 24, 64
 MAX_DIST, MAX_GATES, MAX_OBSTACLES, STATS_LEN = 4, 8, 8, 16
+STAT_REPLICAS = 64   # SCG_STAT_REPLICAS: the device accumulators are [STAT_REPLICAS][STATS_LEN], totals = sum over axis 0
 NOALLOC_QUEUE_WORDS = 131072
 
 QUAD_1D, QUAD_2D, QUAD_3D, CARTPOLE = 1, 2, 3, 10

@@ -437,6 +437,7 @@ extern "C" int scg_create(const scg_config* cfg, scg_env** out) {
 extern "C" int scg_destroy(scg_env* e) {
     if (!e) return SCG_OK;
     if (e->cold_dev) cudaFree(e->cold_dev);
+    if (e->stats_total_dev) cudaFree(e->stats_total_dev);
     if (e->q_mem) cudaFree(e->q_mem);
     if (e->x_goal_dev) cudaFree(e->x_goal_dev);
     for (int j = 0; j < 2; ++j) {
@@ -537,6 +538,8 @@ static int run_steps_t(scg_env* e, const void* actions, int k_steps, void* rewar
     Roll<real> ro{};
     ro.actions = (const real*)actions; ro.k_steps = k_steps; ro.reward_out = (real*)reward_out; ro.done_out = done_out;
     ro.log_out = (real*)log_out; ro.log_stride = log_stride; ro.step_outputs = step_outputs;
+    static const bool pdl = [] { const char* v = getenv("SCG_PDL"); return !(v && atoi(v) == 0); }();
+    ro.pdl = (pdl && k_steps == 1 && step_outputs) ? 1 : 0;   // scg_step: the next step's launch overlaps this one's tail
     if (pid) {
         ro.use_pid = 1; ro.pid_mem = (real*)pid_mem; ro.actions_out = (real*)actions_out;
         PidP<real>& P = ro.pid;
@@ -692,13 +695,22 @@ extern "C" int scg_rollout_host(scg_env* e, const void* host_actions, int32_t k_
 
 extern "C" int scg_stats_reset(scg_env* e, void* stream) {
     if (!e || !e->bound || !e->buf.stats) return fail(SCG_ERR_NULL, "scg_stats_reset: no stats buffer bound");
-    CU(cudaMemsetAsync(e->buf.stats, 0, sizeof(double) * SCG_STATS_LEN, static_cast<cudaStream_t>(stream)));
+    CU(cudaMemsetAsync(e->buf.stats, 0, sizeof(double) * SCG_STAT_REPLICAS * SCG_STATS_LEN, static_cast<cudaStream_t>(stream)));
     return SCG_OK;
+}
+
+static __global__ void k_stats_fold(const double* __restrict__ rep, double* __restrict__ total) {
+    double s = 0.0;
+    for (int r = 0; r < SCG_STAT_REPLICAS; ++r) s += rep[r * SCG_STATS_LEN + threadIdx.x];
+    total[threadIdx.x] = s;
 }
 
 extern "C" int scg_stats_read(scg_env* e, double* host_out, void* stream) {
     if (!e || !host_out || !e->bound || !e->buf.stats) return fail(SCG_ERR_NULL, "scg_stats_read: no stats buffer bound");
-    CU(cudaMemcpyAsync(host_out, e->buf.stats, sizeof(double) * SCG_STATS_LEN, cudaMemcpyDeviceToHost, static_cast<cudaStream_t>(stream)));
+    if (!e->stats_total_dev) CU(cudaMalloc(&e->stats_total_dev, sizeof(double) * SCG_STATS_LEN));
+    k_stats_fold<<<1, SCG_STATS_LEN, 0, static_cast<cudaStream_t>(stream)>>>(e->buf.stats, e->stats_total_dev);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(host_out, e->stats_total_dev, sizeof(double) * SCG_STATS_LEN, cudaMemcpyDeviceToHost, static_cast<cudaStream_t>(stream)));
     return SCG_OK;
 }
 

@@ -14,6 +14,7 @@ struct scg_env {
     scg::Hot<float> hf;
     scg::Hot<double> hd;
     void* cold_dev = nullptr;      // Cold<float> or Cold<double>
+    double* stats_total_dev = nullptr;   // [SCG_STATS_LEN]: scg_stats_read folds the replicas here
     void* cold_host = nullptr;     // host mirror (for injection pointer updates)
     void* x_goal_dev = nullptr;
     scg_buffers buf;

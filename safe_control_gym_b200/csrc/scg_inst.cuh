@@ -76,6 +76,19 @@ static void launch_rollout_v(scg_env* e, const Hot<real>& h, const Cold<real>* c
         }
     }
     e->last_queue = 0;
+    if (ro.pdl) {
+        // Host-driven single steps (scg_step): programmatic dependent launch.  The kernel signals at its first instruction that
+        // its dependents may be scheduled and then waits (griddepcontrol.wait) for the grid before it to complete and flush,
+        // so launch latency, parameter upload and block ramp-up of step t + 1 overlap the body of step t.  Work submitted by
+        // others behind it on the stream is ordered as usual (a launch without the attribute waits for full completion).
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cudaLaunchConfig_t lc{};
+        lc.gridDim = dim3(blocks); lc.blockDim = dim3(ENV_BLOCK); lc.dynamicSmemBytes = 0; lc.stream = st; lc.attrs = attr; lc.numAttrs = 1;
+        if (cudaLaunchKernelEx(&lc, k_rollout<KIND, real, ATT, LEAN, PLAIN, SPEC, false, DS>, h, cold, b, ro) == cudaSuccess) return;
+        (void)cudaGetLastError();   // not supported here: the plain launch below
+    }
     k_rollout<KIND, real, ATT, LEAN, PLAIN, SPEC, false, DS><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro);
 }
 

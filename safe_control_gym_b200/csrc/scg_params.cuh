@@ -195,6 +195,7 @@ template <typename real> struct Roll {
     // time-chunk queue (k_rollout<..., QUEUE>): q_mem[0] = pop counter, q_mem[1] = push counter, q_mem[2 + s] = ready list;
     // q_tickets = chunks * q_env_blocks ranges of q_chunk control steps each
     int32_t* q_mem; int32_t q_chunk; int32_t q_env_blocks; int32_t q_tickets; uint32_t q_sleep_ns;
+    int32_t pdl;                    // host-driven single steps: launched with programmatic stream serialization (see k_rollout)
 };
 
 // Staged trajectory log (k_rollout_tlog, scg_step.cuh): two TMA descriptors over the caller's log tensor viewed as the 2-D

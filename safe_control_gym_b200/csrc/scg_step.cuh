@@ -1379,7 +1379,11 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
 // episode statistics of a block: warp-shuffle reduction, one atomic per warp per statistic
 template <bool PLAIN>
 SCG_DEV void reduce_stats(double* __restrict__ stats, const float* __restrict__ acc_buf, const double* __restrict__ mse_buf) {
+#ifdef SCG_EXP_NO_STATS
+    return;
+#endif
     if (stats) {
+        stats += ((blockIdx.x * (ENV_BLOCK / 32) + (threadIdx.x >> 5)) & (SCG_STAT_REPLICAS - 1)) * SCG_STATS_LEN;   // this warp's replica
         constexpr int NS = PLAIN ? 9 : 11;
         const float* const a = acc_buf + threadIdx.x;
         float v[11] = {a[0 * ACC_LD], a[1 * ACC_LD], a[2 * ACC_LD], a[6 * ACC_LD], a[7 * ACC_LD], a[3 * ACC_LD],
@@ -1422,6 +1426,12 @@ SCG_DEV void st_release_gpu(int32_t* p, int32_t v) { asm volatile("st.release.gp
 template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN = false, bool SPEC = false, bool QUEUE = false, bool DS = false>
 __global__ void __launch_bounds__(ENV_BLOCK, sizeof(real) == 4 ? (DS ? SCG_DS_BLOCKS : (SPEC ? SCG_BLOCKS_PER_SM : 8)) : 1)
 k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, const Buf<real> b, const Roll<real> ro) {
+    if constexpr (!QUEUE) {
+        if (ro.pdl) {   // uniform; scg_inst.cuh: launch_rollout_v.  Nothing above this line reads batch memory.
+            asm volatile("griddepcontrol.launch_dependents;");
+            asm volatile("griddepcontrol.wait;" ::: "memory");
+        }
+    }
     __shared__ float acc_buf[N_ACC * ACC_LD];
     __shared__ double mse_buf[2 * ACC_LD];   // fp64 columns: mse sum, return sum
     mse_buf[threadIdx.x] = 0.0; mse_buf[ACC_LD + threadIdx.x] = 0.0;

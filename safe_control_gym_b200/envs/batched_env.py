@@ -117,7 +117,7 @@ class BatchedEnvBase:
         self.buf_ep_return = z(n)
         self.buf_ep_length = z(n, dt=torch.int32)
         self.buf_ep_violations = z(n, dt=torch.int32)
-        self.buf_stats = z(L.STATS_LEN, dt=torch.float64)
+        self.buf_stats = z(L.STAT_REPLICAS, L.STATS_LEN, dt=torch.float64)   # per-warp-group copies; totals: stats_vector()
         self._adv = None
         self._obs_view = self.buf_obs.t()
         self._done_view = self.buf_done.view(torch.bool)
@@ -373,9 +373,13 @@ class BatchedEnvBase:
             L.check(self.lib.scg_rollout_host(self._h, C.c_void_p(host_actions.data_ptr()), k, int(chunk_steps), self._stream()))
         return self.buf_obs.t()
 
+    def stats_vector(self):
+        """float64[STATS_LEN] device tensor: the accumulators summed over their replicas (include/scg_b200.h: SCG_STAT_REPLICAS)."""
+        return self.buf_stats.sum(0)
+
     def stats(self, reset=False):
         """Episode statistics accumulated on the device (VecRecordEpisodeStatistics semantics)."""
-        out = self.buf_stats.cpu().numpy().copy()
+        out = self.stats_vector().cpu().numpy().copy()
         if reset:
             self.buf_stats.zero_()
         return {name: float(out[i]) for i, name in enumerate(L.STAT_NAMES)}
