@@ -309,10 +309,13 @@ int64_t scg_launch_count(const scg_env* env);
  * or R, constraint penalty, gate geometry), so all of that is compiled out; 3 = PLAIN + SPEC: a Quadrotor 3D config of
  * the competition family (stabilisation task, cost "competition", done on violation and completion, position box +
  * input bounds, positions-only mse, auto-reset) whose fused launches without per-step outputs run with those switches
- * as compile-time constants (scg_step and launches with per-step outputs take variant 2); 4 = PLAIN + DS (fp32, quad_type 2 and
+ * as compile-time constants (scg_step and launches with per-step outputs take variant 2); 4 = PLAIN + DS (fp32; quad_type 2, 3 and
  * the cart-pole): like 2, but the config's extras are the cheap ones -- action-channel impulse / step / white-noise disturbances
- * evaluated inline and / or per-episode inertial properties and offsets taken from the spare -- so the rest of the LEAN kernel
- * is compiled out (BASELINE configs 3 and 4); 0 = GENERAL: SCG_ATT_ROUNDTRIP only
+ * evaluated inline, per-episode inertial properties and offsets taken from the spare (quad_type 3: with the nominal inertia in
+ * the integrator, the reference's own DYN behaviour), gate geometry behind its inline broad phase -- so the rest of the LEAN
+ * kernel is compiled out (BASELINE configs 3, 4, 5 and the level1-3 randomisation sets; competition-family configs run with the
+ * switches of variant 3 compiled in as well; closed-loop launches, scg_rollout_pid, of a variant 2 / 3 config take this loop
+ * too); 0 = GENERAL: SCG_ATT_ROUNDTRIP only
  * (validation: literal quaternion round trip, reset one lane at a time).  Same results in every variant. */
 int scg_kernel_variant(const scg_env* env);
 /* Scheduling of the fused rollout launches (scg_rollout / scg_rollout_host / scg_rollout_pid; no reference counterpart:

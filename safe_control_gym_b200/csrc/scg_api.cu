@@ -367,7 +367,7 @@ extern "C" int scg_kernel_variant(const scg_env* env) {
     if (quad_att && env->cfg.attitude_mode == SCG_ATT_ROUNDTRIP) return 0;   // validation mode: GENERAL kernel (scg_inst.cuh)
     if (!env->plain && env->cfg.precision == 32 && env->cfg.env_kind != SCG_QUAD_1D &&
         !(env->cfg.env_kind == SCG_QUAD_3D && env->cfg.dyn_uses_episode_inertia)) {
-        // PLAIN + DS (scg_inst.cuh: ds_kernel_ok; closed-loop launches and launches with injected draws still take variant 1)
+        // PLAIN + DS (scg_inst.cuh: ds_kernel_ok; launches with injected draws still take variant 1; closed-loop launches of a PLAIN config take the PLAIN + DS loop too)
         const uint32_t c = env->hf.cfg;
         const bool general = (c & (CFG_COLD_CONSTRAINTS | CFG_QR_DENSE | CFG_PENALTY)) || env->hf.normalized_action;
         const bool dist_ok = !(c & CFG_DISTURBED) || (c & CFG_DIST_SIMPLE);

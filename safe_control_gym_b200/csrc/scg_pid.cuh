@@ -6,21 +6,26 @@
 #pragma once
 #include "scg_params.cuh"
 #include "scg_math.cuh"
+#include "scg_env.cuh"
 
 namespace scg {
 
 // pos / vel / rpy: the env's current state (world frame; rpy = the canonical angles the reference reads back from
 // PyBullet); tpos / tvel: the reference point.  act: 4 rotor thrusts (3D) or the two pair sums (2D).
-template <int KIND, typename real>
-__device__ __noinline__ void pid_action(const PidP<real>& P, const real* __restrict__ pos, const real* __restrict__ vel,
-                                        const real* __restrict__ rpy, const real* __restrict__ tpos, const real* __restrict__ tvel,
-                                        real* __restrict__ mem, int64_t n, int64_t i, real* __restrict__ act, bool write = true) {
+// mem: this env's nine values at stride `ld` -- a per-thread column of shared memory inside a fused rollout (rollout_range loads
+// it from the caller's [9][N] buffer when a range starts and stores it back when it ends).  Inline: the gains are then
+// constant-bank operands (through a reference handed to an out-of-line function they are generic loads).
+// ATT: the env's attitude mode -- the fast modes take their sin / cos (|rpy| <= pi) like the integrator does.
+template <int KIND, typename real, int ATT>
+SCG_DEV void pid_action(const PidP<real>& P, const real (&pos)[3], const real (&vel)[3], const real (&rpy)[3], const real (&tpos)[3],
+                        const real (&tvel)[3], real* __restrict__ mem, int ld, real (&act)[Dims<KIND>::NU]) {
     real ipos[3], last[3], irot[3];
 #pragma unroll
-    for (int j = 0; j < 3; ++j) { ipos[j] = mem[int64_t(j) * n + i]; last[j] = mem[int64_t(3 + j) * n + i]; irot[j] = mem[int64_t(6 + j) * n + i]; }
+    for (int j = 0; j < 3; ++j) { ipos[j] = mem[j * ld]; last[j] = mem[(3 + j) * ld]; irot[j] = mem[(6 + j) * ld]; }
     // body-to-world rotation of the current attitude: getMatrixFromQuaternion(getQuaternionFromEuler(rpy)) = Rz Ry Rx
     real sph, cph, sth, cth, sps, cps;
-    m_sincos(rpy[0], &sph, &cph); m_sincos(rpy[1], &sth, &cth); m_sincos(rpy[2], &sps, &cps);
+    if constexpr (ATT == SCG_ATT_ROUNDTRIP) { m_sincos(rpy[0], &sph, &cph); m_sincos(rpy[1], &sth, &cth); m_sincos(rpy[2], &sps, &cps); }
+    else { att_sincos<ATT>(rpy[0], &sph, &cph); att_sincos<ATT>(rpy[1], &sth, &cth); att_sincos<ATT>(rpy[2], &sps, &cps); }
     const real R[9] = {cps * cth, cps * sth * sph - sps * cph, cps * sth * cph + sps * sph,
                        sps * cth, sps * sth * sph + cps * cph, sps * sth * cph - cps * sph,
                        -sth, cth * sph, cth * cph};
@@ -67,10 +72,8 @@ __device__ __noinline__ void pid_action(const PidP<real>& P, const real* __restr
     }
     if constexpr (KIND == SCG_QUAD_3D) { act[0] = f[0]; act[1] = f[1]; act[2] = f[2]; act[3] = f[3]; }
     else { act[0] = f[0] + f[3]; act[1] = f[1] + f[2]; }
-    if (write) {   // false: an out-of-range lane shadowing env n - 1 (rollout_range) -- the memory belongs to the owner lane
 #pragma unroll
-        for (int j = 0; j < 3; ++j) { mem[int64_t(j) * n + i] = ipos[j]; mem[int64_t(3 + j) * n + i] = last[j]; mem[int64_t(6 + j) * n + i] = irot[j]; }
-    }
+    for (int j = 0; j < 3; ++j) { mem[j * ld] = ipos[j]; mem[(3 + j) * ld] = last[j]; mem[(6 + j) * ld] = irot[j]; }
 }
 
 }  // namespace scg

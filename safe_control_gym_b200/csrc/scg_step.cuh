@@ -1090,7 +1090,7 @@ constexpr int N_ACC = 11;   // episodes, return, length, truncated, completed, v
 template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN, bool SPEC, bool TLOG = false, bool DS = false>
 SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ cold, const Buf<real>& b, const Roll<real>& ro,
                            const int64_t i, const int k0, const int k1, float* const ep_acc, double* const mse_acc, real* const sp,
-                           const LogMaps* const lg_maps = nullptr, float* const lg_warp = nullptr) {
+                           const LogMaps* const lg_maps = nullptr, float* const lg_warp = nullptr, real* const pm = nullptr) {
     constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
     const int64_t n = b.n;
     // Out-of-range lanes of the last env block READ env n - 1 and compute along with the warp, but every global side
@@ -1139,7 +1139,14 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
     real* const c_out = SPEC ? nullptr : ((ro.step_outputs && valid) ? b.c_values : nullptr);
     // software prefetch of the next action (one 16-byte load per 3D env per step)
     real raw[NU], nxt[NU];
-    const bool closed_loop = !PLAIN && ro.use_pid != 0;   // uniform: actions from the on-device PID (scg_pid.cuh)
+    // uniform: actions from the on-device PID (scg_pid.cuh); its memory rides in the shared-memory column pm[j * ENV_BLOCK]
+    const bool closed_loop = (!PLAIN || DS) && !TLOG && ro.use_pid != 0;
+    if constexpr ((!PLAIN || DS) && !TLOG) {
+        if (closed_loop) {
+#pragma unroll
+            for (int j = 0; j < 9; ++j) pm[j * ENV_BLOCK] = ro.pid_mem[int64_t(j) * n + ii];
+        }
+    }
     const real* ap = ro.actions + (int64_t(k0) * n + ii) * NU;   // action row of this env at the step being prefetched
     if (!closed_loop) load_action<NU, real>(ap, nxt);
     else {
@@ -1156,15 +1163,20 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
     for (int k = k0; k < k1; ++k) {
 #pragma unroll
         for (int j = 0; j < NU; ++j) raw[j] = nxt[j];
-        if constexpr (!PLAIN && (KIND == SCG_QUAD_3D || KIND == SCG_QUAD_2D)) {
+        if constexpr ((!PLAIN || DS) && !TLOG && (KIND == SCG_QUAD_3D || KIND == SCG_QUAD_2D)) {
             if (closed_loop) {   // action = PID(state before the step, reference point of this step)
                 real pos[3], vel[3], rpy[3], tp[3], tv[3], act[NU];
                 const int32_t gi = e.t < h.n_goal_rows - 1 ? e.t : h.n_goal_rows - 1;
                 const bool stab = (cfg & CFG_STAB) != 0u;
                 auto goal_at = [&](int d) { return stab ? h.x_goal0[d] : cold->x_goal[int64_t(gi) * NX + d]; };
                 if constexpr (KIND == SCG_QUAD_3D) {
-                    pos[0] = e.x[0]; pos[1] = e.x[2]; pos[2] = e.x[4]; vel[0] = e.x[1]; vel[1] = e.x[3]; vel[2] = e.x[5];
-                    rpy[0] = e.a3.rpy[0]; rpy[1] = e.a3.rpy[1]; rpy[2] = e.a3.rpy[2];
+                    if constexpr (PAIRED) {   // the loop-carried pairs (EnvRegs): no conversion, the halves are registers
+                        pos[0] = lo2(e.Pxy); pos[1] = hi2(e.Pxy); pos[2] = lo2(e.ZA); vel[0] = lo2(e.Vxy); vel[1] = hi2(e.Vxy); vel[2] = lo2(e.ZB);
+                        rpy[0] = lo2(e.Axz); rpy[1] = hi2(e.ZA); rpy[2] = hi2(e.Axz);
+                    } else {
+                        pos[0] = e.x[0]; pos[1] = e.x[2]; pos[2] = e.x[4]; vel[0] = e.x[1]; vel[1] = e.x[3]; vel[2] = e.x[5];
+                        rpy[0] = e.a3.rpy[0]; rpy[1] = e.a3.rpy[1]; rpy[2] = e.a3.rpy[2];
+                    }
                     tp[0] = goal_at(0); tp[1] = goal_at(2); tp[2] = goal_at(4);
                     tv[0] = stab ? real(0) : goal_at(1); tv[1] = stab ? real(0) : goal_at(3); tv[2] = stab ? real(0) : goal_at(5);
                 } else {
@@ -1173,7 +1185,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
                     tp[0] = goal_at(0); tp[1] = real(0); tp[2] = goal_at(2);
                     tv[0] = stab ? real(0) : goal_at(1); tv[1] = real(0); tv[2] = stab ? real(0) : goal_at(3);
                 }
-                pid_action<KIND, real>(ro.pid, pos, vel, rpy, tp, tv, ro.pid_mem, n, ii, act, valid);
+                pid_action<KIND, real, ATT>(ro.pid, pos, vel, rpy, tp, tv, pm, ENV_BLOCK, act);
 #pragma unroll
                 for (int j = 0; j < NU; ++j) raw[j] = act[j];
                 if (ro.actions_out && valid) {
@@ -1277,9 +1289,11 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
                 }
                 ep_ret = real(0); ep_len = 0; ep_viol = 0;
                 fresh = true;
-                if (closed_loop && valid) {   // PIDController.reset() with the env (quadrotor_utils.py:124-135)
+                if constexpr ((!PLAIN || DS) && !TLOG) {
+                    if (closed_loop) {   // PIDController.reset() with the env (quadrotor_utils.py:124-135)
 #pragma unroll
-                    for (int j = 0; j < 9; ++j) ro.pid_mem[int64_t(j) * n + ii] = real(0);
+                        for (int j = 0; j < 9; ++j) pm[j * ENV_BLOCK] = real(0);
+                    }
                 }
                 if constexpr (LEAN) {
                     reset_from_spare<KIND, real, ATT, PAIRED>(sp, e);
@@ -1314,6 +1328,12 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
             tma_wait_all();
         }
         __syncwarp();
+    }
+    if constexpr ((!PLAIN || DS) && !TLOG) {
+        if (closed_loop && valid) {   // (a shadow lane's copy is dropped: the memory belongs to the owner lane)
+#pragma unroll
+            for (int j = 0; j < 9; ++j) ro.pid_mem[int64_t(j) * n + ii] = pm[j * ENV_BLOCK];
+        }
     }
     if constexpr (PAIRED) scalars_from_pairs(e);
     // a range that ends inside the launch (ticket queue) hands over the state only: observation, env.state and the
@@ -1437,12 +1457,13 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     mse_buf[threadIdx.x] = 0.0; mse_buf[ACC_LD + threadIdx.x] = 0.0;
     __shared__ real sp_buf[LEAN ? (Spare<KIND, real, ATT>::N + ((PLAIN && !DS) ? 0 : SPARE_EXTRA)) * ENV_BLOCK : SCG_MAX_DIST * ENV_BLOCK];
     real* const sp = sp_buf + threadIdx.x;
+    __shared__ real pid_buf[(PLAIN && !DS) ? 1 : 9 * ENV_BLOCK];   // the closed loop's controller memory, one column per thread (scg_pid.cuh)
 #pragma unroll
     for (int j = 0; j < N_ACC; ++j) acc_buf[j * ACC_LD + threadIdx.x] = 0.f;
     if constexpr (!QUEUE) {
         const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
         rollout_range<KIND, real, ATT, LEAN, PLAIN, SPEC, false, DS>(h, cold, b, ro, i, 0, ro.k_steps, acc_buf + (i < b.n ? threadIdx.x : ENV_BLOCK),
-                                                          mse_buf + (i < b.n ? threadIdx.x : ENV_BLOCK), sp);
+                                                          mse_buf + (i < b.n ? threadIdx.x : ENV_BLOCK), sp, nullptr, nullptr, pid_buf + threadIdx.x);
     } else {
         // q_mem: [0] pop counter, [1] push counter, [2 + s] the ready list: item s = 1 + env block + env_blocks * chunk.
         // Items 0 .. env_blocks - 1 are implicit (chunk 0 of every env block is ready at launch); every finished chunk
@@ -1471,7 +1492,7 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
             const int64_t i = int64_t(eb) * ENV_BLOCK + threadIdx.x;
             const int k0 = chunk * ro.q_chunk, k1 = k0 + ro.q_chunk < ro.k_steps ? k0 + ro.q_chunk : ro.k_steps;
             rollout_range<KIND, real, ATT, LEAN, PLAIN, SPEC, false, DS>(h, cold, b, ro, i, k0, k1, acc_buf + (i < b.n ? threadIdx.x : ENV_BLOCK),
-                                                              mse_buf + (i < b.n ? threadIdx.x : ENV_BLOCK), sp);
+                                                              mse_buf + (i < b.n ? threadIdx.x : ENV_BLOCK), sp, nullptr, nullptr, pid_buf + threadIdx.x);
             push = k1 < ro.k_steps ? item + ro.q_env_blocks : 0;
         }
     }
