@@ -266,15 +266,15 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
     h.n_crows = 0; h.crow_strict = nb > 0 ? h.bounded[0].strict : 0;
     if (nb > 0 && nd == 0 && !h.any_tolerance && !symmetric && same_strict && h.n_rows <= SCG_MAX_ROWS) {
         int filled = 0;
-        for (int r = 0; r < SCG_MAX_ROWS; ++r) { h.crow_src[r] = -1; h.crow_sgn[r] = 0; h.crow_bound[r] = real(0); }
+        for (int r = 0; r < SCG_MAX_ROWS; ++r) { k.crow_src[r] = -1; k.crow_sgn[r] = 0; k.crow_bound[r] = real(0); }
         for (int q = 0; q < nb; ++q) {
             const BoundedCon<real>& bc = h.bounded[q];
             const int full = bc.var == SCG_VAR_STATE ? nx : nu, off = bc.var == SCG_VAR_STATE ? 0 : nx;
             for (int d = 0; d < full; ++d) {
                 if (!((bc.mask >> d) & 1u)) continue;
                 const int rl = bc.row_lo[d], rh = bc.row_hi[d];
-                h.crow_src[rl] = int8_t(off + d); h.crow_sgn[rl] = -1; h.crow_bound[rl] = bc.lo[d];
-                h.crow_src[rh] = int8_t(off + d); h.crow_sgn[rh] = 1; h.crow_bound[rh] = bc.hi[d];
+                k.crow_src[rl] = off + d; k.crow_sgn[rl] = -1; k.crow_bound[rl] = bc.lo[d];
+                k.crow_src[rh] = off + d; k.crow_sgn[rh] = 1; k.crow_bound[rh] = bc.hi[d];
                 filled += 2;
             }
         }

@@ -383,27 +383,22 @@ __device__ __noinline__ uint32_t constraint_values_cold(const Hot<real>& h, cons
 // The same values for configs whose rows all come from plain bounded constraints (Hot::crow_*): one pass over the output
 // rows instead of the object / dim / kind loops above (the host-driven step of the level0 family spent 40 % of its
 // instructions there).  Same arithmetic per row: c = lo - x or x - hi, round8, viol_test.
-// Inline: the row table is then read from the constant bank (through a reference handed to an out-of-line function the same
-// loads are generic ones: 38 instructions per row, 25 % of the host-driven step's time).
+// Out of line, with the row table in the cold block: it read the table through a reference to the kernel's parameter block once
+// (generic loads: 38 instructions per row, 25 % of the host-driven step's time) and sat inline in every loop once (2 % of
+// BASELINE config 3, which never calls it).
 template <int KIND, typename real>
-SCG_DEV uint32_t constraint_values_flat(const Hot<real>& h, const real (&st)[Dims<KIND>::NX], const real (&raw)[Dims<KIND>::NU],
-                                        bool state_only, real* __restrict__ c_out, int64_t n, int64_t i) {
-    constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
-    real v[NX + NU];   // indexed by the row's source: a small local-memory array
-#pragma unroll
-    for (int d = 0; d < NX; ++d) v[d] = st[d];
-#pragma unroll
-    for (int d = 0; d < NU; ++d) v[NX + d] = raw[d];
+__device__ __noinline__ uint32_t constraint_values_flat(const Cold<real>* __restrict__ cold, int n_crows, int strict, const real* __restrict__ v,
+                                                        bool state_only, real* __restrict__ c_out, int64_t n, int64_t i) {
+    constexpr int NX = Dims<KIND>::NX;
     bool violated = false;
     real* p = c_out + i;
-    const int strict = h.crow_strict;
 #pragma unroll 1
-    for (int r = 0; r < h.n_crows; ++r, p += n) {
-        const int src = h.crow_src[r];
+    for (int r = 0; r < n_crows; ++r, p += n) {
+        const int src = __ldg(&cold->crow_src[r]);
         if (src >= NX && state_only) continue;
         const real x = v[src];
-        const real b = h.crow_bound[r];
-        const real c = h.crow_sgn[r] > 0 ? x - b : b - x;
+        const real b = __ldg(&cold->crow_bound[r]);
+        const real c = __ldg(&cold->crow_sgn[r]) > 0 ? x - b : b - x;
         *p = round8(c);
         violated |= viol_test(c, strict);
     }
@@ -421,7 +416,12 @@ SCG_DEV void eval_constraints(const Hot<real>& h, const Cold<real>* __restrict__
     constexpr int NX = Dims<KIND>::NX, NU = Dims<KIND>::NU;
     violated = false; almost = false;
     if (c_out != nullptr && h.n_crows > 0) {
-        violated = constraint_values_flat<KIND, real>(h, st, raw, state_only, c_out, n, i) != 0u;
+        real v[NX + NU];   // indexed by the row's source: a local-memory array, private to the call
+#pragma unroll
+        for (int d = 0; d < NX; ++d) v[d] = st[d];
+#pragma unroll
+        for (int d = 0; d < NU; ++d) v[NX + d] = raw[d];
+        violated = constraint_values_flat<KIND, real>(cold, h.n_crows, h.crow_strict, v, state_only, c_out, n, i) != 0u;
         return;
     }
     if (c_out != nullptr || (!PLAIN && (cfg & CFG_COLD_CONSTRAINTS))) {

@@ -65,12 +65,9 @@ template <typename real> struct Hot {
     int32_t n_bounded, n_dense_rows, n_rows, any_tolerance;
     int32_t need_cold_constraints;  // tolerances, symmetric or dense rows: the flags alone need constraint_values_cold
     BoundedCon<real> bounded[MAX_BOUNDED];
-    // the rows of the non-symmetric bounded constraints as a flat table indexed by output row (per-step constraint VALUES of
-    // configs without tolerances / dense rows: constraint_values_flat): source (< nx: state dim, else nx + input dim),
-    // sign (+1: x - bound, -1: bound - x), bound; n_crows = 0 when some row is not of that kind
+    // the rows of the non-symmetric bounded constraints as a flat table indexed by output row (Cold::crow_*; per-step constraint
+    // VALUES of configs without tolerances / dense rows: constraint_values_flat); n_crows = 0 when some row is not of that kind
     int32_t n_crows, crow_strict;
-    int8_t crow_src[SCG_MAX_ROWS], crow_sgn[SCG_MAX_ROWS];
-    real crow_bound[SCG_MAX_ROWS];
     real viol_thr;                  // fp32: 5e-9 (== round(c, 8) > 0 in exact arithmetic)
     // LEAN configs: all bounded constraints merged into one box per state / input dim (violation flag only)
     real box_lo[SCG_MAX_NX], box_hi[SCG_MAX_NX];
@@ -168,6 +165,10 @@ template <typename real> struct Cold {
     real gate_broad2, obstacle_broad2;   // squared horizontal distance from the NOMINAL axis beyond which nothing can touch (inf: unbounded draws)
     int32_t n_obstacles;
     const real* x_goal;             // [n_goal_rows][nx] device
+    // flat constraint rows (Hot::n_crows): source (< nx: state dim, else nx + input dim), sign (+1: x - bound, -1: bound - x), bound.
+    // In the cold block: only launches with per-step outputs (scg_step) read them, through the L1.
+    int32_t crow_src[SCG_MAX_ROWS], crow_sgn[SCG_MAX_ROWS];
+    real crow_bound[SCG_MAX_ROWS];
 };
 
 // caller-owned batch memory, typed

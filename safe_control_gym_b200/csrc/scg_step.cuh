@@ -1140,8 +1140,10 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
     // software prefetch of the next action (one 16-byte load per 3D env per step)
     real raw[NU], nxt[NU];
     // uniform: actions from the on-device PID (scg_pid.cuh); its memory rides in the shared-memory column pm[j * ENV_BLOCK]
-    const bool closed_loop = (!PLAIN || DS) && !TLOG && ro.use_pid != 0;
-    if constexpr ((!PLAIN || DS) && !TLOG) {
+    // (which loops carry the controller: the LEAN / GENERAL ones of the quadrotors and the 3D PLAIN + DS loop)
+    constexpr bool PIDK = (!PLAIN || (DS && KIND == SCG_QUAD_3D)) && !TLOG && (KIND == SCG_QUAD_3D || KIND == SCG_QUAD_2D);
+    const bool closed_loop = PIDK && ro.use_pid != 0;
+    if constexpr (PIDK) {
         if (closed_loop) {
 #pragma unroll
             for (int j = 0; j < 9; ++j) pm[j * ENV_BLOCK] = ro.pid_mem[int64_t(j) * n + ii];
@@ -1163,7 +1165,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
     for (int k = k0; k < k1; ++k) {
 #pragma unroll
         for (int j = 0; j < NU; ++j) raw[j] = nxt[j];
-        if constexpr ((!PLAIN || DS) && !TLOG && (KIND == SCG_QUAD_3D || KIND == SCG_QUAD_2D)) {
+        if constexpr (PIDK) {
             if (closed_loop) {   // action = PID(state before the step, reference point of this step)
                 real pos[3], vel[3], rpy[3], tp[3], tv[3], act[NU];
                 const int32_t gi = e.t < h.n_goal_rows - 1 ? e.t : h.n_goal_rows - 1;
@@ -1289,7 +1291,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
                 }
                 ep_ret = real(0); ep_len = 0; ep_viol = 0;
                 fresh = true;
-                if constexpr ((!PLAIN || DS) && !TLOG) {
+                if constexpr (PIDK) {
                     if (closed_loop) {   // PIDController.reset() with the env (quadrotor_utils.py:124-135)
 #pragma unroll
                         for (int j = 0; j < 9; ++j) pm[j * ENV_BLOCK] = real(0);
@@ -1329,7 +1331,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
         }
         __syncwarp();
     }
-    if constexpr ((!PLAIN || DS) && !TLOG) {
+    if constexpr (PIDK) {
         if (closed_loop && valid) {   // (a shadow lane's copy is dropped: the memory belongs to the owner lane)
 #pragma unroll
             for (int j = 0; j < 9; ++j) ro.pid_mem[int64_t(j) * n + ii] = pm[j * ENV_BLOCK];
@@ -1399,9 +1401,6 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
 // episode statistics of a block: warp-shuffle reduction, one atomic per warp per statistic
 template <bool PLAIN>
 SCG_DEV void reduce_stats(double* __restrict__ stats, const float* __restrict__ acc_buf, const double* __restrict__ mse_buf) {
-#ifdef SCG_EXP_NO_STATS
-    return;
-#endif
     if (stats) {
         stats += ((blockIdx.x * (ENV_BLOCK / 32) + (threadIdx.x >> 5)) & (SCG_STAT_REPLICAS - 1)) * SCG_STATS_LEN;   // this warp's replica
         constexpr int NS = PLAIN ? 9 : 11;
@@ -1457,7 +1456,7 @@ k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ co
     mse_buf[threadIdx.x] = 0.0; mse_buf[ACC_LD + threadIdx.x] = 0.0;
     __shared__ real sp_buf[LEAN ? (Spare<KIND, real, ATT>::N + ((PLAIN && !DS) ? 0 : SPARE_EXTRA)) * ENV_BLOCK : SCG_MAX_DIST * ENV_BLOCK];
     real* const sp = sp_buf + threadIdx.x;
-    __shared__ real pid_buf[(PLAIN && !DS) ? 1 : 9 * ENV_BLOCK];   // the closed loop's controller memory, one column per thread (scg_pid.cuh)
+    __shared__ real pid_buf[((PLAIN && !(DS && KIND == SCG_QUAD_3D)) || KIND == SCG_CARTPOLE || KIND == SCG_QUAD_1D) ? 1 : 9 * ENV_BLOCK];   // the closed loop's controller memory, one column per thread (scg_pid.cuh)
 #pragma unroll
     for (int j = 0; j < N_ACC; ++j) acc_buf[j * ACC_LD + threadIdx.x] = 0.f;
     if constexpr (!QUEUE) {
