@@ -117,3 +117,34 @@ class VecRecordEpisodeStatistics(VecEnvWrapper):
                 acc[idx] = 0
             info["episode"] = ep
         return obs, reward, done, info
+
+
+def info_n(info, done, keys=("constraint_violation", "TimeLimit.truncated", "mse", "constraint_values")):
+    """The reference's list-of-dicts form of a step's ``info`` (DummyVecEnv.step_wait, dummy_vec_env.py:38-49): ``out["n"][i]`` is
+    env i's dict; an env that finished this step carries ``terminal_observation`` and ``terminal_info`` (its last step's info),
+    which is what the PPO rollout loop reads (controllers/ppo/ppo.py:263-273).  One D2H copy per key: for small ``num_envs``."""
+    host = {k: info[k].cpu().numpy() for k in keys if k in info}
+    d = done.cpu().numpy()
+    term = info["terminal_observation"].cpu().numpy() if bool(d.any()) else None
+    out = []
+    for i in range(len(d)):
+        own = {k: v[i] for k, v in host.items()}
+        own["TimeLimit.truncated"] = bool(own.get("TimeLimit.truncated", False))
+        out.append({"terminal_observation": term[i], "terminal_info": own} if d[i] else own)
+    return {"n": out}
+
+
+class ListInfoVecEnv(VecEnvWrapper):
+    """A batched env behind DummyVecEnv's exact return types: numpy ``obs [N, obs_dim]``, ``rew [N]``, ``done [N]`` and
+    ``info = {"n": [dict per env]}`` -- for reference code that must run unmodified (e.g. ``PPO.train_step``) on a handful of envs.
+    Throughput code keeps the tensors and takes the masked form."""
+
+    def reset(self, **kwargs):
+        out = self.venv.reset(**kwargs)
+        if isinstance(out, tuple):
+            return out[0].cpu().numpy(), {"n": [dict() for _ in range(self.num_envs)]}
+        return out.cpu().numpy()
+
+    def step_wait(self):
+        obs, rew, done, info = self.venv.step(torch.as_tensor(self._actions))
+        return obs.cpu().numpy(), rew.cpu().numpy(), done.cpu().numpy(), info_n(info, done)

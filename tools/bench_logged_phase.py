@@ -1,3 +1,5 @@
+"""Logged rollouts at 16 M envs: throughput of consecutive phases of a long run (burst -> power-limited steady state).
+    python tools/bench_logged_phase.py"""
 import sys, os, torch
 sys.path.insert(0, '/root/repo')
 import bench
