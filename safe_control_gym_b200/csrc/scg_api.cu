@@ -266,15 +266,15 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
     h.n_crows = 0; h.crow_strict = nb > 0 ? h.bounded[0].strict : 0;
     if (nb > 0 && nd == 0 && !h.any_tolerance && !symmetric && same_strict && h.n_rows <= SCG_MAX_ROWS) {
         int filled = 0;
-        for (int r = 0; r < SCG_MAX_ROWS; ++r) { k.crow_src[r] = -1; k.crow_sgn[r] = 0; k.crow_bound[r] = real(0); }
+        for (int r = 0; r < SCG_MAX_ROWS; ++r) { k.crow[r][0] = real(0); k.crow[r][1] = real(0); k.crow[r][2] = real(0); k.crow[r][3] = real(0); }
         for (int q = 0; q < nb; ++q) {
             const BoundedCon<real>& bc = h.bounded[q];
             const int full = bc.var == SCG_VAR_STATE ? nx : nu, off = bc.var == SCG_VAR_STATE ? 0 : nx;
             for (int d = 0; d < full; ++d) {
                 if (!((bc.mask >> d) & 1u)) continue;
                 const int rl = bc.row_lo[d], rh = bc.row_hi[d];
-                k.crow_src[rl] = off + d; k.crow_sgn[rl] = -1; k.crow_bound[rl] = bc.lo[d];
-                k.crow_src[rh] = off + d; k.crow_sgn[rh] = 1; k.crow_bound[rh] = bc.hi[d];
+                k.crow[rl][0] = real(off + d); k.crow[rl][1] = real(-1); k.crow[rl][2] = bc.lo[d];
+                k.crow[rh][0] = real(off + d); k.crow[rh][1] = real(1); k.crow[rh][2] = bc.hi[d];
                 filled += 2;
             }
         }

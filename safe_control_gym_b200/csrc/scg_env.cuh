@@ -392,14 +392,14 @@ __device__ __noinline__ uint32_t constraint_values_flat(const Cold<real>* __rest
     constexpr int NX = Dims<KIND>::NX;
     bool violated = false;
     real* p = c_out + i;
-#pragma unroll 1
-    for (int r = 0; r < n_crows; ++r, p += n) {
-        const int src = __ldg(&cold->crow_src[r]);
+    // one 16-byte load per row, four rows in flight (the launch is latency-bound: a rolled loop serialised load -> index -> store)
+#pragma unroll 4
+    for (int r = 0; r < n_crows; ++r) {
+        const Row4<real> q = ldg4(cold->crow[r]);
+        const int src = int(q.x);
         if (src >= NX && state_only) continue;
-        const real x = v[src];
-        const real b = __ldg(&cold->crow_bound[r]);
-        const real c = __ldg(&cold->crow_sgn[r]) > 0 ? x - b : b - x;
-        *p = round8(c);
+        const real c = q.y * (v[src] - q.z);   // sign * (x - bound): bound - x == -(x - bound) exactly
+        p[int64_t(r) * n] = round8(c);
         violated |= viol_test(c, strict);
     }
     return violated ? 1u : 0u;

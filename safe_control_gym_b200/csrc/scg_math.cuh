@@ -99,6 +99,12 @@ template <typename real> SCG_DEV real m_clip(real x, real lo, real hi) { return 
 template <typename real> struct Row4 { real x, y, z, w; };
 SCG_DEV Row4<float> ldc4(const float* p) { const float4 v = *reinterpret_cast<const float4*>(p); return {v.x, v.y, v.z, v.w}; }
 SCG_DEV Row4<double> ldc4(const double* p) { return {p[0], p[1], p[2], p[3]}; }
+// the same row from global memory through the read-only path
+SCG_DEV Row4<float> ldg4(const float* p) { const float4 v = __ldg(reinterpret_cast<const float4*>(p)); return {v.x, v.y, v.z, v.w}; }
+SCG_DEV Row4<double> ldg4(const double* p) {
+    const double2 a = __ldg(reinterpret_cast<const double2*>(p)), b = __ldg(reinterpret_cast<const double2*>(p) + 1);
+    return {a.x, a.y, b.x, b.y};
+}
 typedef unsigned long long f32x2;
 SCG_DEV f32x2 pk2(float lo, float hi) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
 SCG_DEV f32x2 bc2(float v) { return pk2(v, v); }

@@ -167,8 +167,8 @@ template <typename real> struct Cold {
     const real* x_goal;             // [n_goal_rows][nx] device
     // flat constraint rows (Hot::n_crows): source (< nx: state dim, else nx + input dim), sign (+1: x - bound, -1: bound - x), bound.
     // In the cold block: only launches with per-step outputs (scg_step) read them, through the L1.
-    int32_t crow_src[SCG_MAX_ROWS], crow_sgn[SCG_MAX_ROWS];
-    real crow_bound[SCG_MAX_ROWS];
+    // one 16-byte entry per row: {source index, sign, bound, 0}, the index stored as a real (exact: < 32)
+    alignas(16) real crow[SCG_MAX_ROWS][4];
 };
 
 // caller-owned batch memory, typed
