@@ -4,10 +4,13 @@ Follows safe_control_gym/envs/gym_pybullet_drones/quadrotor.py:581-697 (_setup_s
 ODEs, written with the explicit Rz @ Ry @ Rx product of math_and_models/transformations.py:125-182) and
 safe_control_gym/math_and_models/symbolic_systems.py:63-123 (fc / df / loss).  The CasADi expression graph is
 plain arithmetic; its Jacobians are reproduced here by complex-step differentiation of the restated f
-(accurate to rounding, and independent of the closed-form derivatives in csrc/scg_symbolic.cu).  The discrete
-model is fixed-step RK4 (controllers/mpc/mpc_utils.py:79-101); CasADi's CVODES ``fd_func`` (adaptive BDF,
-symbolic_systems.py:70-73) is not reproducible to 1e-12 -- parity unpinned for it, loose cross-check only
-(tests/test_oracle_symbolic.py integrates with scipy at rtol 1e-10).  The cart-pole model is absent from the
+(accurate to rounding, and independent of the closed-form derivatives in csrc/scg_symbolic.cu).  PINNED: fc, both
+Jacobians, the linearised field and the loss with all derivatives equal, to 1e-12, what the reference's OWN
+``_setup_symbolic`` + ``SymbolicModel`` code evaluates to when CasADi is replaced by an expression-graph stand-in
+(tests/golden/symbolic_model.npz, make_symbolic_golden.py, mini_casadi.py; tests/test_oracle_symbolic_golden.py).  The
+discrete model is fixed-step RK4 (controllers/mpc/mpc_utils.py:79-101); CasADi's CVODES ``fd_func`` (adaptive BDF at
+reltol 1e-6, symbolic_systems.py:70-73) is not reproducible bit for bit by anything else -- RK4 is held to the ODE's
+integrated flow within its truncation error (2.5e-6 / 6.3e-6 relative for 2D / 3D over 1 / 60 s at the fixture's points).  The cart-pole model is absent from the
 reference fork: standard frictionless cart-pole, parity unpinned.
 """
 import numpy as np

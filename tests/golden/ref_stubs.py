@@ -157,7 +157,8 @@ class _NumpyCompat:
         return np.array(*a, **k)
 
 
-def install(reference_root="/root/reference"):
+def install(reference_root="/root/reference", casadi=None):
+    """``casadi``: a module to install in place of the MagicMock (tests/golden/mini_casadi.py, make_symbolic_golden.py)."""
     if not hasattr(np, "round_"):
         np.round_ = np.round  # removed in numpy 2.x (SURVEY.md F4)
     gym = types.ModuleType("gym")
@@ -176,6 +177,8 @@ def install(reference_root="/root/reference"):
     sys.modules["pybullet_data"] = pd
     for name in ("casadi", "matplotlib", "matplotlib.pyplot"):
         sys.modules[name] = mock.MagicMock()
+    if casadi is not None:
+        sys.modules["casadi"] = casadi
     # Import the reference's sub-packages without running safe_control_gym/__init__.py
     # (which pulls in every controller: torch, cvxpy, gpytorch, ...).
     pkg = types.ModuleType("safe_control_gym")
@@ -205,6 +208,8 @@ def install(reference_root="/root/reference"):
 
         def _setup_symbolic(self):
             super()._setup_symbolic()   # builds MagicMock expressions
+            if casadi is not None:      # a working casadi stand-in: the reference's own SymbolicModel.loss evaluates
+                return
 
             def loss(x, u, Xr, Ur, Q, R):
                 """cost_func of quadrotor.py:682 evaluated on numbers (casadi would do the same arithmetic):

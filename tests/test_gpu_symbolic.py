@@ -115,3 +115,36 @@ def test_fd_linear_func(kind):
     single = env.symbolic.fd_linear_func(x0=xe[0], p=np.concatenate([ue[0], x[0], u[0]]), dt=dt)["xf"]
     assert single.shape == (nx,) and _rel(single, got[0]) <= 1e-14
     env.close()
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float64, 1e-12), (torch.float32, 2e-5)])
+@pytest.mark.parametrize("kind", [1, 2, 3])
+def test_device_model_matches_the_reference_expressions(kind, dtype, tol):
+    """The device functions against golden vectors produced by the reference's OWN ``_setup_symbolic`` + ``SymbolicModel``
+    (tests/golden/symbolic_model.npz, make_symbolic_golden.py: CasADi replaced by an expression-graph stand-in): fc_func, both
+    Jacobians of df_func, fc_linear_func, loss with its gradients / Hessians; fd_func / fd_linear_func (RK4 over dt) against
+    the integrated flow within RK4's truncation error (see tests/test_oracle_symbolic_golden.py for the measured values)."""
+    import os
+    from safe_control_gym_b200.envs.quadrotor import BatchedQuadrotor
+    G = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "symbolic_model.npz"))
+    p = f"q{kind}_"
+    ti = dict(stabilization_goal=[0, 0, 1][:max(kind, 2)], stabilization_goal_tolerance=0.05)
+    env = BatchedQuadrotor(num_envs=4, dtype=dtype, quad_type=kind, ctrl_freq=60, pyb_freq=240, task_info=ti)   # nominal URDF constants
+    sm = env.symbolic
+    assert abs(sm.dt - float(G[p + "dt"])) < 1e-15
+    X, U, Xe, Ue = G[p + "X"], G[p + "U"], G[p + "Xe"], G[p + "Ue"]
+    scale = 1.0 if dtype == torch.float64 else 300.0     # fp32: |f| reaches 200 rad/s^2 at these points (unit floor in _rel)
+    assert _rel(sm.fc_func(X, U), G[p + "fc"]) <= tol * scale
+    A, B = sm.df_func(X, U)
+    assert _rel(A, G[p + "dfdx"]) <= tol * scale and _rel(B, G[p + "dfdu"]) <= tol * scale
+    assert _rel(sm.fc_linear_func(Xe, Ue, X, U), G[p + "fc_lin"]) <= tol * scale
+    for Qn, pre in (("Q", "l"), ("Qa", "la")):
+        out = sm.loss(X, U, G[p + "Xr"], G[p + "Ur"], G[p + Qn], G[p + "R"])
+        assert _rel(out["l"], G[p + pre].reshape(-1)) <= tol * 10
+        assert _rel(out["l_x"], G[p + pre + "_x"].reshape(len(X), -1)) <= tol * 10
+        assert _rel(out["l_xx"], G[p + pre + "_xx"][0]) <= 1e-12
+    assert _rel(out["l_u"], G[p + "l_u"].reshape(len(X), -1)) <= tol * 10 and _rel(out["l_uu"], G[p + "l_uu"][0]) <= 1e-12
+    rk4 = {1: 1e-12, 2: 1e-5, 3: 2e-5}[kind]
+    assert _rel(sm.fd_func(x0=X, p=U)["xf"], G[p + "fd"]) <= max(rk4, tol * scale)
+    assert _rel(sm.fd_linear_func(x0=Xe, p=np.concatenate([Ue, X, U], axis=-1))["xf"], G[p + "fd_lin"]) <= max(rk4, tol * scale)
+    env.close()
