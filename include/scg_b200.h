@@ -318,6 +318,9 @@ int64_t scg_launch_count(const scg_env* env);
  * too); 0 = GENERAL: SCG_ATT_ROUNDTRIP only
  * (validation: literal quaternion round trip, reset one lane at a time).  Same results in every variant. */
 int scg_kernel_variant(const scg_env* env);
+/* Diagnostic: the packed word of uniform scenario switches the kernels branch on (csrc/scg_params.cuh: CFG_*); the SPEC
+ * kernels are the ones compiled for particular values of it.  No reference counterpart. */
+uint32_t scg_config_word(const scg_env* env);
 /* Scheduling of the fused rollout launches (scg_rollout / scg_rollout_host / scg_rollout_pid; no reference counterpart:
  * the reference steps one env at a time).  mode -1 (default) = automatic: launches of >= 64 control steps whose env
  * blocks fill the resident block slots of the GPU unevenly (between half a wave and six waves) are cut into chunks of

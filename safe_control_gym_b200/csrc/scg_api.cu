@@ -361,6 +361,7 @@ extern "C" int scg_set_seed(scg_env* env, uint32_t seed) {
 extern "C" const char* scg_last_error(void) { return g_err.c_str(); }
 extern "C" const char* scg_version(void) { return "scg_b200 0.1 (sm_100a)"; }
 extern "C" int64_t scg_launch_count(const scg_env* env) { return env ? env->launches : 0; }
+extern "C" uint32_t scg_config_word(const scg_env* env) { return env ? (env->cfg.precision == 32 ? env->hf.cfg : env->hd.cfg) : 0u; }
 extern "C" int scg_kernel_variant(const scg_env* env) {
     if (!env || !env->lean) return 0;
     const bool quad_att = env->cfg.env_kind == SCG_QUAD_3D || env->cfg.env_kind == SCG_QUAD_2D;

@@ -106,8 +106,8 @@ static void launch_rollout_att(scg_env* e, const Hot<real>& h, const Cold<real>*
     }
     else if (e->lean && F32 && KIND != SCG_QUAD_1D && (KIND == SCG_QUAD_3D || !ro.use_pid) && ds_kernel_ok(h) &&
              !(KIND == SCG_QUAD_3D && h.dyn_uses_episode_inertia)) {   // (quad_type 3: closed-loop launches too)
-        if (KIND == SCG_QUAD_3D && !ro.step_outputs && (h.cfg & CFG_SPEC_MASK) == CFG_SPEC_VAL)   // the competition switches compiled in (level1-3.yaml)
-            launch_rollout_v<KIND, real, ATT, true, F32, (F32 && KIND == SCG_QUAD_3D), (F32 && KIND != SCG_QUAD_1D)>(e, h, cold, b, ro, blocks, st);
+        if (KIND != SCG_QUAD_1D && !ro.step_outputs && (h.cfg & SpecCfg<KIND>::MASK) == SpecCfg<KIND>::VAL)   // this kind's family switches compiled in (SpecCfg)
+            launch_rollout_v<KIND, real, ATT, true, F32, (F32 && KIND != SCG_QUAD_1D), (F32 && KIND != SCG_QUAD_1D)>(e, h, cold, b, ro, blocks, st);
         else launch_rollout_v<KIND, real, ATT, true, F32, false, (F32 && KIND != SCG_QUAD_1D)>(e, h, cold, b, ro, blocks, st);
     }
     else if (e->lean) launch_rollout_v<KIND, real, ATT, true, false, false>(e, h, cold, b, ro, blocks, st);

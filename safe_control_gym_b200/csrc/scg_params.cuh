@@ -137,6 +137,20 @@ constexpr uint32_t CFG_SPEC_MASK = CFG_STAB | CFG_COST_RL | CFG_COST_QUAD | CFG_
 constexpr uint32_t CFG_SPEC_VAL = CFG_STAB | CFG_DONE_COMPLETION | CFG_DONE_VIOLATION | CFG_HAS_ROWS | CFG_AUTO_RESET | CFG_UBOX |
                                   CFG_MSE_POS | CFG_BOX_POS | CFG_CLIP_ONCE;
 
+// Per env kind: which value of the switch word the SPEC instantiation of that kind is compiled for.  quad_type 3: the competition
+// family above.  quad_type 2 (PLAIN + DS loop only): the RL family of BASELINE config 4 -- stabilisation, cost rl_reward with the
+// exponential, out-of-bound termination, default constraints, auto-reset.  Cart-pole (PLAIN + DS only): BASELINE config 3 -- trajectory
+// tracking, cost quadratic, done on violation and out of bound.  The launcher compares and falls back, as for quad_type 3.
+template <int KIND> struct SpecCfg { static constexpr uint32_t MASK = CFG_SPEC_MASK, VAL = CFG_SPEC_VAL; };
+template <> struct SpecCfg<SCG_QUAD_2D> {
+    static constexpr uint32_t MASK = CFG_SPEC_MASK | CFG_REW_EXP;
+    static constexpr uint32_t VAL = CFG_STAB | CFG_COST_RL | CFG_REW_EXP | CFG_OOB | CFG_HAS_ROWS | CFG_AUTO_RESET | CFG_FULL_STATE | CFG_UBOX;
+};
+template <> struct SpecCfg<SCG_CARTPOLE> {
+    static constexpr uint32_t MASK = CFG_SPEC_MASK;
+    static constexpr uint32_t VAL = CFG_COST_QUAD | CFG_OOB | CFG_DONE_VIOLATION | CFG_HAS_ROWS | CFG_AUTO_RESET | CFG_FULL_STATE | CFG_UBOX;
+};
+
 
 template <typename real> struct DenseRow {     // linear: c = a . x - b ; quadratic: c = x' P x - b
     real a[SCG_MAX_NX];

@@ -1113,7 +1113,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
     e.offc = (PLAIN && !DS) ? nullptr : (LEAN ? sp + (Spare<KIND, real, ATT>::N + 4 + 3 * SCG_MAX_DIST) * ENV_BLOCK : sp);
     // SPEC: cost "competition" is a compile-time fact, the goal_reached bit (cost "quadratic" only) cannot change: it is
     // not carried through the loop (one register less at the 96-register bound) but re-read where the flags are stored
-    if constexpr (SPEC) e.goal_prev = false;
+    if constexpr (SPEC && KIND == SCG_QUAD_3D) e.goal_prev = false;
     real st[NX];   // env.state after the last step (LEAN: rebuilt from the registers after the loop)
     load_inertia<KIND, real>(h, (PLAIN && !DS) ? nullptr : b.inertia, n, ii, e.in);
     if constexpr (!PLAIN || DS) { if (h.cfg & CFG_DIST_SIMPLE) load_offsets<KIND, real>(h, b.dist_offset, n, ii, e); }
@@ -1134,7 +1134,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
     Motors<real> mot;
     // the uniform switches of the loop in one word (see CFG_*)
     const uint32_t cfg_rt = h.cfg | (ro.step_outputs ? (CFG_FULL_STATE | CFG_STEP_OUTPUTS) : 0u);
-    const uint32_t cfg = SPEC ? ((cfg_rt & ~CFG_SPEC_MASK) | CFG_SPEC_VAL) : cfg_rt;
+    const uint32_t cfg = SPEC ? ((cfg_rt & ~SpecCfg<KIND>::MASK) | SpecCfg<KIND>::VAL) : cfg_rt;
     const bool full = (cfg & CFG_FULL_STATE) != 0u;
     real* const c_out = SPEC ? nullptr : ((ro.step_outputs && valid) ? b.c_values : nullptr);
     // software prefetch of the next action (one 16-byte load per 3D env per step)
@@ -1347,7 +1347,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
 #pragma unroll
         for (int d = 0; d < NX; ++d) b.state[int64_t(d) * n + ii] = e.x[d];
         b.ctrl_step[ii] = e.t; b.episode[ii] = e.resets;
-        b.flags[ii] = pack_flags<KIND, real>(e) | (SPEC ? (b.flags[ii] & SCG_FLAG_GOAL_REACHED) : 0u);
+        b.flags[ii] = pack_flags<KIND, real>(e) | ((SPEC && KIND == SCG_QUAD_3D) ? (b.flags[ii] & SCG_FLAG_GOAL_REACHED) : 0u);
     } else {
     if constexpr (LEAN) {
         // env.state as observed after the loop: the fresh episode's (PyBullet still holds INIT_ANG_VEL)
@@ -1372,7 +1372,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
 #pragma unroll
     for (int d = 0; d < NX; ++d) b.state[int64_t(d) * n + ii] = e.x[d];
     b.ctrl_step[ii] = e.t; b.episode[ii] = e.resets;
-    b.flags[ii] = pack_flags<KIND, real>(e) | (SPEC ? (b.flags[ii] & SCG_FLAG_GOAL_REACHED) : 0u);
+    b.flags[ii] = pack_flags<KIND, real>(e) | ((SPEC && KIND == SCG_QUAD_3D) ? (b.flags[ii] & SCG_FLAG_GOAL_REACHED) : 0u);
     if (b.env_state) {
 #pragma unroll
         for (int d = 0; d < NX; ++d) b.env_state[int64_t(d) * n + ii] = st[d];
