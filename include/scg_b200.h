@@ -188,6 +188,15 @@ typedef struct {
     int32_t dyn_applies_force;             /* F5 */
     int32_t gate_geometry;                 /* analytic gate-pass / collision tests */
     int32_t auto_reset;                    /* DummyVecEnv.step_wait semantics (dummy_vec_env.py:38-49) */
+    /* extension (quad_type 3): the aerodynamic terms of the reference's PYB_* modes (base_aviary.py:437-497) folded
+     * into DYN as one more external force / body torque per substep.  Bit 0: _drag, bit 1: _ground_effect (_downwash is zero for
+     * one drone per env).  Coefficients as _parse_urdf_parameters reads them (base_aviary.py:637-644, :145-147). */
+    int32_t dyn_aero;
+    double aero_drag_coeff[3];             /* DRAG_COEFF = (xy, xy, z) */
+    double aero_gnd_eff_coeff;             /* GND_EFF_COEFF */
+    double aero_prop_radius;               /* PROP_RADIUS */
+    double aero_gnd_eff_h_clip;            /* GND_EFF_H_CLIP */
+    double aero_prop_xy[4][2];             /* propeller link positions in the body frame (cf2x.urdf) */
 } scg_config;
 
 /* caller-owned batch memory (device pointers; NULL = not wanted where marked optional) */
@@ -217,6 +226,8 @@ typedef struct {
     double* stats;            /* [SCG_STAT_REPLICAS][SCG_STATS_LEN] device accumulators (totals: sum over the replicas) */
     /* adversary action for the next step, [n][dim] env-major (optional) */
     const void* adv_action;
+    /* dyn_aero drag: sum(2 pi rpm / 60) of the previous substep's action (base_aviary.py:224, :297, :320), [n] real; required then */
+    void* aero_mem;
 } scg_buffers;
 
 /* K-step fused rollout (state stays in registers for all K * substeps integrator steps) */

@@ -26,6 +26,9 @@ CF2X = dict(M=0.03454, L=0.0397, THRUST2WEIGHT=2.25, IXX=1.4e-5, IYY=1.4e-5, IZZ
             MIN_PWM=20000.0, MAX_PWM=65535.0, COLLISION_R=0.06, COLLISION_H=0.025)
 GRAVITY_ACC = 9.8  # base_aviary.py:90
 F32MAX = float(np.finfo(np.float32).max)
+# cf2x.urdf <properties> (aerodynamic coefficients) and the propeller links' positions in the body frame
+AERO = dict(GND_EFF_COEFF=11.36859, PROP_RADIUS=2.31348e-2, DRAG_COEFF=(9.1785e-7, 9.1785e-7, 10.311e-7),
+            PROP_XY=((0.028, 0.028), (-0.028, 0.028), (-0.028, -0.028), (0.028, -0.028)))
 
 STATE_LABELS = {
     1: ["init_x", "init_x_dot"],
@@ -348,7 +351,9 @@ class QuadOracle:
                  info_mse_metric_state_weight=None, gates=None, obstacles=None,
                  randomized_gates_and_obstacles=False, gates_and_obstacles_randomization_info=None,
                  done_on_collision=False, done_on_completion=False, reseed_on_reset=False,
-                 dyn_uses_episode_inertia=False, gate_geometry=False, **_ignored):
+                 dyn_uses_episode_inertia=False, gate_geometry=False, dyn_aero=(), **_ignored):
+        # extension: the drag / ground-effect terms of the PYB_* modes folded into DYN (see _aero)
+        self.dyn_aero = tuple(dyn_aero)
         # ---- Quadrotor.__init__ pre-super part (quadrotor.py:176-201)
         self.QUAD_TYPE = int(quad_type)
         self.norm_act_scale = norm_act_scale
@@ -596,6 +601,7 @@ class QuadOracle:
         # _reset_simulation: zero kinematics, rpy_rates = 0.
         self.rpy_rates = np.zeros(3)
         self.last_clipped_action = np.zeros(4)
+        self.last_substep_rpm = np.zeros(4)
         # Gates / obstacles (quadrotor.py:371-434): x, y, yaw offsets, 3 draws each.
         self.EFFECTIVE_OBSTACLES = []
         for i, ob in enumerate(self.OBSTACLES):
@@ -688,6 +694,34 @@ class QuadOracle:
         pwm = np.clip(pwm, self.MIN_PWM, self.MAX_PWM)
         return self.PWM2RPM_SCALE * pwm + self.PWM2RPM_CONST
 
+    def _aero(self, rpm):
+        """Extension (opt-in, off in parity mode): the aerodynamic terms the reference's PYB_* modes add with
+        applyExternalForce (base_aviary.py:437-497), as world force and body torque for the explicit integrator.
+
+        ``_ground_effect`` (:437-470): per propeller, height of its link (URDF offset rotated into the world) clipped at
+        GND_EFF_H_CLIP (:145-147), force rpm^2 KF GND_EFF_COEFF (PROP_RADIUS / (4 h))^2 along the link's z axis, applied at
+        the link, only while |roll| and |pitch| are below pi / 2.  ``_drag`` (:472-497): R (k * v) with k = -DRAG_COEFF *
+        sum(2 pi rpm / 60) of ``last_clipped_action`` (the PREVIOUS substep's RPMs: zeros after a reset, :224, :297, :320),
+        handed to applyExternalForce with LINK_FRAME, i.e. rotated into the world once more.  ``_downwash`` (:499-520) is
+        zero for one drone per env."""
+        R = np.array(bm.matrix_from_quat(self.quat)).reshape(3, 3)
+        force, torque = np.zeros(3), np.zeros(3)
+        if "ground_effect" in self.dyn_aero:
+            max_rpm = np.sqrt((CF2X["THRUST2WEIGHT"] * self.GRAVITY) / (4 * self.KF))      # base_aviary.py:140-141
+            max_thrust = 4 * self.KF * max_rpm ** 2
+            h_clip = 0.25 * AERO["PROP_RADIUS"] * np.sqrt((15 * max_rpm ** 2 * self.KF * AERO["GND_EFF_COEFF"]) / max_thrust)
+            heights = np.array([self.pos[2] + (R @ np.array([x, y, 0.0]))[2] for x, y in AERO["PROP_XY"]])
+            heights = np.clip(heights, h_clip, np.inf)
+            gnd = np.array(rpm ** 2) * self.KF * AERO["GND_EFF_COEFF"] * (AERO["PROP_RADIUS"] / (4 * heights)) ** 2
+            if abs(self.rpy[0]) < np.pi / 2 and abs(self.rpy[1]) < np.pi / 2:
+                for (x, y), g in zip(AERO["PROP_XY"], gnd):
+                    force = force + R @ np.array([0.0, 0.0, g])
+                    torque = torque + np.cross(np.array([x, y, 0.0]), np.array([0.0, 0.0, g]))
+        if "drag" in self.dyn_aero:
+            k = -1 * np.array(AERO["DRAG_COEFF"]) * np.sum(np.array(2 * np.pi * self.last_substep_rpm / 60))
+            force = force + R @ (R @ (k * self.vel))
+        return force, torque
+
     def _dynamics(self, rpm, ext_force=None):
         """base_aviary.py:522-576, TIMESTEP := PYB_TIMESTEP (F3).  One explicit substep followed
         by the PyBullet store/readback that re-derives rpy from the quaternion (:565-574, :362-374)."""
@@ -709,6 +743,11 @@ class QuadOracle:
         x_torque = (forces[0] + forces[1] - forces[2] - forces[3]) * (self.L / np.sqrt(2))
         y_torque = (-forces[0] + forces[1] + forces[2] - forces[3]) * (self.L / np.sqrt(2))
         torques = np.array([x_torque, y_torque, z_torque])
+        if self.dyn_aero:
+            f_aero, t_aero = self._aero(rpm)
+            force_world = force_world + f_aero
+            torques = torques + t_aero
+            self.last_substep_rpm = np.array(rpm, dtype=float)     # base_aviary.py:320
         torques = torques - np.cross(self.rpy_rates, np.dot(J, self.rpy_rates))
         rates_deriv = np.dot(J_inv, torques)
         acc = force_world / mass

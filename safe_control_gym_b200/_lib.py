@@ -91,7 +91,9 @@ class Config(C.Structure):
         ("gate_rand", Rand), ("obstacle_rand", Rand),
         ("seed", C.c_uint32), ("env_id_base", C.c_int64),
         ("dyn_uses_episode_inertia", C.c_int32), ("dyn_applies_force", C.c_int32), ("gate_geometry", C.c_int32),
-        ("auto_reset", C.c_int32)]
+        ("auto_reset", C.c_int32),
+        ("dyn_aero", C.c_int32), ("aero_drag_coeff", C.c_double * 3), ("aero_gnd_eff_coeff", C.c_double),
+        ("aero_prop_radius", C.c_double), ("aero_gnd_eff_h_clip", C.c_double), ("aero_prop_xy", (C.c_double * 2) * 4)]
 
 
 class Buffers(C.Structure):
@@ -100,7 +102,7 @@ class Buffers(C.Structure):
                 ("obs", C.c_void_p), ("env_state", C.c_void_p), ("reward", C.c_void_p), ("done", C.c_void_p),
                 ("info", C.c_void_p), ("mse", C.c_void_p), ("c_values", C.c_void_p), ("terminal_obs", C.c_void_p),
                 ("ep_return", C.c_void_p), ("ep_length", C.c_void_p), ("ep_violations", C.c_void_p),
-                ("stats", C.c_void_p), ("adv_action", C.c_void_p)]
+                ("stats", C.c_void_p), ("adv_action", C.c_void_p), ("aero_mem", C.c_void_p)]
 
 
 class RolloutArgs(C.Structure):

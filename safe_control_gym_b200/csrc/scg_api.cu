@@ -234,7 +234,12 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
             (c.done_on_out_of_bound ? CFG_OOB : 0u) | (c.done_on_completion ? CFG_DONE_COMPLETION : 0u) |
             (c.done_on_violation ? CFG_DONE_VIOLATION : 0u) | (c.auto_reset ? CFG_AUTO_RESET : 0u) |
             (rates ? CFG_FULL_STATE : 0u) | (c.reseed_on_reset ? CFG_RESEED : 0u) | ((h.mse_mask & 0xE00u) ? CFG_MSE_RATES : 0u) |
-            ((c.gate_geometry && c.env_kind == SCG_QUAD_3D) ? CFG_GATE_GEOMETRY : 0u);
+            ((c.gate_geometry && c.env_kind == SCG_QUAD_3D) ? CFG_GATE_GEOMETRY : 0u) |
+            ((c.dyn_aero && c.env_kind == SCG_QUAD_3D) ? CFG_AERO : 0u);
+    h.aero = c.env_kind == SCG_QUAD_3D ? c.dyn_aero : 0;
+    for (int j = 0; j < 3; ++j) h.aero_drag[j] = real(c.aero_drag_coeff[j]);
+    h.aero_gnd_coeff = real(c.aero_gnd_eff_coeff); h.aero_prop_radius = real(c.aero_prop_radius); h.aero_h_clip = real(c.aero_gnd_eff_h_clip);
+    for (int j = 0; j < 4; ++j) { h.aero_prop_xy[j][0] = real(c.aero_prop_xy[j][0]); h.aero_prop_xy[j][1] = real(c.aero_prop_xy[j][1]); }
     // ---- LEAN kernel specialisation (scg_step.cuh): none of the rare features is configured
     bool symmetric = false;
     for (int q = 0; q < nb; ++q) symmetric |= h.bounded[q].symmetric != 0;
@@ -370,7 +375,7 @@ extern "C" int scg_kernel_variant(const scg_env* env) {
         !(env->cfg.env_kind == SCG_QUAD_3D && env->cfg.dyn_uses_episode_inertia)) {
         // PLAIN + DS (scg_inst.cuh: ds_kernel_ok; launches with injected draws still take variant 1; closed-loop launches of a PLAIN config take the PLAIN + DS loop too)
         const uint32_t c = env->hf.cfg;
-        const bool general = (c & (CFG_COLD_CONSTRAINTS | CFG_QR_DENSE | CFG_PENALTY)) || env->hf.normalized_action;
+        const bool general = (c & (CFG_COLD_CONSTRAINTS | CFG_QR_DENSE | CFG_PENALTY | CFG_AERO)) || env->hf.normalized_action;
         const bool dist_ok = !(c & CFG_DISTURBED) || (c & CFG_DIST_SIMPLE);
         const bool reset_ok = !(c & CFG_RESET_EXTRAS) || ((c & CFG_SPARE_SIMPLE) && ((c & CFG_DIST_SIMPLE) || env->hf.n_dist_act == 0));
         if (!general && dist_ok && reset_ok) return 4;
@@ -384,7 +389,7 @@ template <typename real> static int upload_params(scg_env* e) {
     if (!k) return fail(SCG_ERR_BAD_CONFIG, "out of host memory");
     Hot<real>& h = *reinterpret_cast<Hot<real>*>(sizeof(real) == 4 ? (void*)&e->hf : (void*)&e->hd);
     int rc = build_params<real>(e->cfg, e->nx, e->nu, h, *k, &e->n_rows, &e->n_slots, &e->lean);
-    e->plain = e->lean && !(h.cfg & (CFG_DISTURBED | CFG_COLD_CONSTRAINTS | CFG_QR_DENSE | CFG_PENALTY | CFG_GATE_GEOMETRY | CFG_RESET_EXTRAS)) &&
+    e->plain = e->lean && !(h.cfg & (CFG_DISTURBED | CFG_COLD_CONSTRAINTS | CFG_QR_DENSE | CFG_PENALTY | CFG_GATE_GEOMETRY | CFG_RESET_EXTRAS | CFG_AERO)) &&
                !h.normalized_action;
     if (rc != SCG_OK) { delete k; return rc; }
     const int rows = e->cfg.n_goal_rows > 0 ? e->cfg.n_goal_rows : 1;
@@ -459,6 +464,7 @@ extern "C" int scg_bind_buffers(scg_env* e, const scg_buffers* b) {
         return fail(SCG_ERR_NULL, "scg_bind_buffers: state, ctrl_step, episode, flags, obs, reward, done, info are required");
     if (e->n_slots > 0 && !b->dist_offset) return fail(SCG_ERR_NULL, "dist_offset required when disturbances carry step offsets");
     if (e->cfg.dyn_uses_episode_inertia && !b->inertia) return fail(SCG_ERR_NULL, "inertia buffer required for dyn_uses_episode_inertia");
+    if (e->cfg.env_kind == SCG_QUAD_3D && (e->cfg.dyn_aero & 1) && !b->aero_mem) return fail(SCG_ERR_NULL, "aero_mem buffer required for dyn_aero drag");
     if (e->cfg.adversary_channel >= 0 && e->cfg.adversary_channel != SCG_CH_ACTION && e->cfg.adversary_channel != SCG_CH_DYNAMICS)
         return fail(SCG_ERR_BAD_CONFIG, "adversary channel must be action or dynamics");
     e->buf = *b;

@@ -530,6 +530,42 @@ template <typename real> SCG_DEV bool ground_contact(real pz, real r8) {
     return pz - support < real(0);
 }
 
+// ------------------------------------------------------------------ aerodynamic terms (row N4, dyn_aero extension)
+// What the reference's PYB_* modes add through applyExternalForce (base_aviary.py:437-497), for the explicit integrator: world
+// force and body torque (x, y) of one substep.  _ground_effect (:437-470): per propeller, height of its link (URDF offset rotated
+// into the world) clipped at GND_EFF_H_CLIP, rpm^2 KF GND_EFF_COEFF (PROP_RADIUS / (4 h))^2 along the link's z axis, applied at
+// the link, only while |roll| and |pitch| are below pi / 2.  _drag (:472-497): R (k * v), k = -DRAG_COEFF sum(2 pi rpm / 60) of
+// the PREVIOUS substep's RPMs (`omega_prev`: last_clipped_action, zeros after a reset), handed over as a LINK_FRAME force, i.e.
+// rotated into the world once more.  _downwash is zero for one drone per env.  Out of line, on copies: a rare extension.
+template <typename real, bool FASTMATH>
+__device__ __noinline__ void aero_terms(const Hot<real>& h, real pz, real vx, real vy, real vz, Att3<real> a, real m0, real m1, real m2,
+                                        real m3, real omega_prev, real* __restrict__ out) {
+    attitude3_complete<real>(a);
+    const real* R = a.R;
+    real fx = real(0), fy = real(0), fz = real(0), tx = real(0), ty = real(0);
+    if (h.aero & 2) {
+        const real mr[4] = {m0, m1, m2, m3};   // the rotor forces (fast motor map) or the RPMs (literal map), see Motors
+        const bool upright = m_abs(a.rpy[0]) < Consts<real>::half_pi && m_abs(a.rpy[1]) < Consts<real>::half_pi;
+        real fb = real(0);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const real x = h.aero_prop_xy[i][0], y = h.aero_prop_xy[i][1];
+            const real hgt = m_max(pz + (R[6] * x + R[7] * y), h.aero_h_clip);
+            const real thrust = FASTMATH ? mr[i] : mr[i] * mr[i] * h.kf;
+            const real q = h.aero_prop_radius / (real(4) * hgt);
+            const real g = thrust * h.aero_gnd_coeff * (q * q);
+            if (upright) { fb += g; tx += y * g; ty -= x * g; }
+        }
+        fx += R[2] * fb; fy += R[5] * fb; fz += R[8] * fb;
+    }
+    if (h.aero & 1) {
+        const real d0 = -h.aero_drag[0] * omega_prev * vx, d1 = -h.aero_drag[1] * omega_prev * vy, d2 = -h.aero_drag[2] * omega_prev * vz;
+        const real b0 = (R[0] * d0 + R[1] * d1) + R[2] * d2, b1 = (R[3] * d0 + R[4] * d1) + R[5] * d2, b2 = (R[6] * d0 + R[7] * d1) + R[8] * d2;
+        fx += (R[0] * b0 + R[1] * b1) + R[2] * b2; fy += (R[3] * b0 + R[4] * b1) + R[5] * b2; fz += (R[6] * b0 + R[7] * b1) + R[8] * b2;
+    }
+    out[0] = fx; out[1] = fy; out[2] = fz; out[3] = tx; out[4] = ty;
+}
+
 // returns bit 0: a ray of the current gate hit the drone; bit 1: the drone touches a gate or an obstacle.
 // Broad phase first: an object whose NOMINAL axis is farther than `broad2` (0.35 m + the largest pose offset) from the
 // drone is skipped before its pose offsets are even drawn -- almost every (env, object) pair of a step.

@@ -55,6 +55,7 @@ template <typename real> inline Buf<real> typed_buf(const scg_buffers& b) {
     t.reward = (real*)b.reward; t.done = b.done; t.info = b.info; t.mse = (real*)b.mse; t.c_values = (real*)b.c_values;
     t.terminal_obs = (real*)b.terminal_obs; t.ep_return = (real*)b.ep_return; t.ep_length = b.ep_length;
     t.ep_violations = b.ep_violations; t.stats = b.stats; t.adv_action = (const real*)b.adv_action;
+    t.aero_mem = (real*)b.aero_mem;
     return t;
 }
 
@@ -69,7 +70,7 @@ template <int KIND, typename real> int launch_constraints(scg_env* e, const real
 // (see scg_inst.cuh: launch_rollout_att)
 template <typename real> inline bool ds_kernel_ok(const Hot<real>& h) {
     const uint32_t c = h.cfg;
-    if ((c & (CFG_COLD_CONSTRAINTS | CFG_QR_DENSE | CFG_PENALTY)) || h.normalized_action) return false;   // (gate geometry: quad_type 3 only, inline broad phase)
+    if ((c & (CFG_COLD_CONSTRAINTS | CFG_QR_DENSE | CFG_PENALTY | CFG_AERO)) || h.normalized_action) return false;   // (gate geometry: quad_type 3 only, inline broad phase)
     if ((c & CFG_DISTURBED) && !(c & CFG_DIST_SIMPLE)) return false;
     if ((c & CFG_RESET_EXTRAS) && !((c & CFG_SPARE_SIMPLE) && ((c & CFG_DIST_SIMPLE) || h.n_dist_act == 0))) return false;
     return true;

@@ -95,6 +95,9 @@ template <typename real> struct Hot {
     real ds_mag[SCG_MAX_DIST], ds_half[SCG_MAX_DIST], ds_decay[SCG_MAX_DIST], ds_l2decay[SCG_MAX_DIST], ds_std[SCG_MAX_DIST][SCG_MAX_NU];
     // gate_geometry: the first broad phase of the contact scan, inline (step_env): nominal axis (x, y) and widened squared radius of every
     // gate, then every obstacle.  A drone outside all of them -- almost every env-step -- never enters gate_scan (scg_env.cuh).
+    // dyn_aero (extension): see aero_terms (scg_env.cuh)
+    int32_t aero;
+    real aero_drag[3], aero_gnd_coeff, aero_prop_radius, aero_h_clip, aero_prop_xy[4][2];
     int32_t geo_n;
     alignas(8) float geo_neg[SCG_MAX_GATES + SCG_MAX_OBSTACLES][2];   // (-x, -y): one packed add per object
     float geo_r2[SCG_MAX_GATES + SCG_MAX_OBSTACLES];
@@ -125,6 +128,7 @@ enum : uint32_t {
     CFG_CLIP_ONCE = 1u << 22,       // 3D: the action bounds lie inside the rotor force bounds, the motor map needs no second clip
     CFG_DIST_SIMPLE = 1u << 23,     // (with CFG_DISTURBED) every per-step disturbance is one of Hot::ds_*: evaluated inline
     CFG_SPARE_SIMPLE = 1u << 24,    // no impulse / step disturbance with a per-episode offset outside the action channel: apply_spare_simple
+    CFG_AERO = 1u << 25,            // 3D: drag / ground-effect terms per substep (extension; LEAN / GENERAL kernels only)
     CFG_RESET_EXTRAS = 1u << 19,    // reset() draws more than uniform init offsets: inertial properties, disturbance offsets, normal draws
 };
 // SPEC kernels (scg_step.cuh): the switches of the competition scenario family (competition/level0-3.yaml: stabilisation
@@ -192,6 +196,7 @@ template <typename real> struct Buf {
     real* obs; real* env_state; real* reward; uint8_t* done; uint8_t* info; real* mse; real* c_values;
     real* terminal_obs; real* ep_return; int32_t* ep_length; int32_t* ep_violations; double* stats;
     const real* adv_action;
+    real* aero_mem;
 };
 
 // the DSL PID's gains and motor constants (quadrotor_utils.py:76-122), for closed-loop rollouts (scg_pid.cuh)

@@ -43,6 +43,7 @@ template <int KIND, typename real> struct EnvRegs {
     // live, x[0..5], x[9..11], a3.rpy and a3.R[2 / 5 / 8] are not (x[6..8] and a3.sc stay scalar).
     f32x2 Pxy, Vxy, Wxz, ZA, ZB, Axz, Rxy;
     real R8;
+    real aero_prev;      // dyn_aero drag: sum(2 pi rpm / 60) of the previous substep's action (LEAN / GENERAL kernels only)
 };
 
 #ifndef SCG_NO_PAIRS
@@ -639,11 +640,31 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
         const real axf = fx * e.in.inv_mass, ayf = fy * e.in.inv_mass, azf = fz * e.in.inv_mass - e.in.g_over_m;
         const real Tdt = Tm * dt, gdt = e.in.g_over_m * dt;
         (void)Tdt; (void)gdt;
+        // dyn_aero (extension, uniform): the rotor speed sum _drag reads -- the previous substep's, then this step's
+        real om_sub = real(0), om_now = real(0);
+        if constexpr (!PLAIN) {
+            if (cfg & CFG_AERO) {
+                om_sub = e.aero_prev;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) om_now += real(2) * Consts<real>::pi * motor_rpm<real, FASTMATH>(h, mot, j) / real(60);
+            }
+        }
+        (void)om_sub; (void)om_now;
         // One substep.  LAST = false (all but the final substep of a control step, LEAN kernels): the pre-round-trip
         // angles are not copied into e.x[6..8] -- only the final ones are ever read (derive_attitude, the next launch).
         auto substep = [&](auto last_tag) {
             constexpr bool LAST = decltype(last_tag)::value;
             const real w0 = e.x[9], w1 = e.x[10], w2 = e.x[11];
+            real fax = real(0), fay = real(0), faz = real(0), tax = real(0), tay = real(0);
+            if constexpr (!PLAIN) {
+                if (cfg & CFG_AERO) {
+                    real o[5];
+                    aero_terms<real, FASTMATH>(h, e.x[4], e.x[1], e.x[3], e.x[5], e.a3, mot.rpm[0], mot.rpm[1], mot.rpm[2], mot.rpm[3], om_sub, o);
+                    fax = o[0] * e.in.inv_mass; fay = o[1] * e.in.inv_mass; faz = o[2] * e.in.inv_mass; tax = o[3]; tay = o[4];
+                    om_sub = om_now;   // base_aviary.py:320
+                }
+            }
+            (void)fax; (void)fay; (void)faz; (void)tax; (void)tay;
             if constexpr (FASTMATH) {
                 // same update with the constants folded (fp32 fast modes; a few ulp from the literal order below):
                 // w x Jw = (w1 w2 (Izz - Iyy), w2 w0 (Ixx - Izz), w0 w1 (Iyy - Ixx)) for a diagonal J; dt / J and dt T / m premultiplied
@@ -651,17 +672,17 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
                     e.x[1] = m_fma(e.a3.R[2], Tdt, e.x[1]); e.x[3] = m_fma(e.a3.R[5], Tdt, e.x[3]);
                     e.x[5] = m_fma(e.a3.R[8], Tdt, e.x[5] - gdt);
                 } else {
-                    e.x[1] = m_fma(e.a3.R[2], Tdt, e.x[1] + axf * dt); e.x[3] = m_fma(e.a3.R[5], Tdt, e.x[3] + ayf * dt);
-                    e.x[5] = m_fma(e.a3.R[8], Tdt, e.x[5] + azf * dt);
+                    e.x[1] = m_fma(e.a3.R[2], Tdt, e.x[1] + (axf + fax) * dt); e.x[3] = m_fma(e.a3.R[5], Tdt, e.x[3] + (ayf + fay) * dt);
+                    e.x[5] = m_fma(e.a3.R[8], Tdt, e.x[5] + (azf + faz) * dt);
                 }
-                e.x[9] = m_fma(m_fma(-(w1 * w2), e.in.dJ[0], mot.tx), e.in.kJ[0], e.x[9]);
-                e.x[10] = m_fma(m_fma(-(w2 * w0), e.in.dJ[1], mot.ty), e.in.kJ[1], e.x[10]);
+                e.x[9] = m_fma(m_fma(-(w1 * w2), e.in.dJ[0], mot.tx + tax), e.in.kJ[0], e.x[9]);
+                e.x[10] = m_fma(m_fma(-(w2 * w0), e.in.dJ[1], mot.ty + tay), e.in.kJ[1], e.x[10]);
                 e.x[11] = m_fma(m_fma(-(w0 * w1), e.in.dJ[2], mot.tz), e.in.kJ[2], e.x[11]);
             } else {
-                const real ax = e.a3.R[2] * Tm + axf, ay = e.a3.R[5] * Tm + ayf, az = e.a3.R[8] * Tm + azf;
+                const real ax = e.a3.R[2] * Tm + axf + fax, ay = e.a3.R[5] * Tm + ayf + fay, az = e.a3.R[8] * Tm + azf + faz;
                 const real jw0 = e.in.J[0] * w0, jw1 = e.in.J[1] * w1, jw2 = e.in.J[2] * w2;
-                const real d0 = e.in.J_inv[0] * (mot.tx - (w1 * jw2 - w2 * jw1));
-                const real d1 = e.in.J_inv[1] * (mot.ty - (w2 * jw0 - w0 * jw2));
+                const real d0 = e.in.J_inv[0] * ((mot.tx + tax) - (w1 * jw2 - w2 * jw1));
+                const real d1 = e.in.J_inv[1] * ((mot.ty + tay) - (w2 * jw0 - w0 * jw2));
                 const real d2 = e.in.J_inv[2] * (mot.tz - (w0 * jw1 - w1 * jw0));
                 e.x[1] += dt * ax; e.x[3] += dt * ay; e.x[5] += dt * az;          // vel first
                 e.x[9] += dt * d0; e.x[10] += dt * d1; e.x[11] += dt * d2;         // then rates
@@ -754,6 +775,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
 #pragma unroll 1
             for (int s = 0; s < h.substeps; ++s) substep(std::true_type{});
         }
+        if constexpr (!PLAIN) { if (cfg & CFG_AERO) e.aero_prev = om_now; }
     } else if constexpr (KIND == SCG_QUAD_2D) {
         const real axf = fx * e.in.inv_mass, azf = fz * e.in.inv_mass - e.in.g_over_m;
         auto substep2d = [&]() {
@@ -1053,6 +1075,7 @@ k_reset(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold
     }
     write_obs<KIND, real>(h, cold, b.dist_offset, b.obs, st, 0, 0u, key, h.reseed_on_reset ? 0u : uint32_t(e.resets - 1), n, i);
     if (b.ep_return) b.ep_return[i] = real(0);
+    if (b.aero_mem) b.aero_mem[i] = real(0);   // last_clipped_action = 0 (base_aviary.py:224)
     if (b.ep_length) b.ep_length[i] = 0;
     if (b.ep_violations) b.ep_violations[i] = 0;
     if (h.n_rows > 0 && b.c_values) {   // after_reset: state constraints only (benchmark_env.py:376-383)
@@ -1118,6 +1141,8 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
     load_inertia<KIND, real>(h, (PLAIN && !DS) ? nullptr : b.inertia, n, ii, e.in);
     if constexpr (!PLAIN || DS) { if (h.cfg & CFG_DIST_SIMPLE) load_offsets<KIND, real>(h, b.dist_offset, n, ii, e); }
     derive_attitude<KIND, real, ATT>(e);
+    e.aero_prev = real(0);
+    if constexpr (!PLAIN && KIND == SCG_QUAD_3D) { if ((h.cfg & CFG_AERO) && b.aero_mem) e.aero_prev = b.aero_mem[ii]; }
     constexpr bool PAIRED = Paired<KIND, real, ATT, LEAN, PLAIN>::value;
     if constexpr (PAIRED) pairs_from_scalars(e);
     real ep_ret = b.ep_return ? b.ep_return[ii] : real(0);
@@ -1291,6 +1316,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
                 }
                 ep_ret = real(0); ep_len = 0; ep_viol = 0;
                 fresh = true;
+                if constexpr (!PLAIN) e.aero_prev = real(0);   // (after reset_env_cold copied the registers back; the LEAN restart below keeps it)
                 if constexpr (PIDK) {
                     if (closed_loop) {   // PIDController.reset() with the env (quadrotor_utils.py:124-135)
 #pragma unroll
@@ -1338,6 +1364,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
         }
     }
     if constexpr (PAIRED) scalars_from_pairs(e);
+    if constexpr (!PLAIN && KIND == SCG_QUAD_3D) { if ((h.cfg & CFG_AERO) && b.aero_mem && valid) b.aero_mem[ii] = e.aero_prev; }
     // a range that ends inside the launch (ticket queue) hands over the state only: observation, env.state and the
     // per-step scalars are rewritten by the range that ends the launch
     const bool last_range = k1 >= ro.k_steps;   // uniform

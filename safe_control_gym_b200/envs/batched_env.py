@@ -117,6 +117,7 @@ class BatchedEnvBase:
         self.buf_ep_return = z(n)
         self.buf_ep_length = z(n, dt=torch.int32)
         self.buf_ep_violations = z(n, dt=torch.int32)
+        self.buf_aero = z(n)   # dyn_aero drag: rotor speed sum of the previous substep's action
         self.buf_stats = z(L.STAT_REPLICAS, L.STATS_LEN, dt=torch.float64)   # per-warp-group copies; totals: stats_vector()
         self._adv = None
         self._obs_view = self.buf_obs.t()
@@ -141,6 +142,7 @@ class BatchedEnvBase:
             b.ep_return, b.ep_length, b.ep_violations = (self.buf_ep_return.data_ptr(), self.buf_ep_length.data_ptr(),
                                                          self.buf_ep_violations.data_ptr())
         b.stats = self.buf_stats.data_ptr()
+        b.aero_mem = self.buf_aero.data_ptr()
         b.adv_action = self._adv.data_ptr() if self._adv is not None else None
         self._buffers = b
         L.check(self.lib.scg_bind_buffers(self._h, C.byref(b)))

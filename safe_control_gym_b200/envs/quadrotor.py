@@ -95,7 +95,7 @@ class BatchedQuadrotor(BatchedEnvBase):
                  # BaseAviary kwargs
                  physics="dyn",
                  # extensions (off = reference behaviour)
-                 dyn_uses_episode_inertia=False, dyn_applies_force=False, gate_geometry=False,
+                 dyn_uses_episode_inertia=False, dyn_applies_force=False, gate_geometry=False, dyn_aero=(),
                  **kwargs):
         if str(getattr(physics, "value", physics)) != "dyn":
             raise NotImplementedError("only physics='dyn' is implemented (the PYB_* modes need Bullet's solver; "
@@ -263,6 +263,11 @@ class BatchedQuadrotor(BatchedEnvBase):
         self._dyn_uses_episode_inertia = bool(dyn_uses_episode_inertia)
         self._dyn_applies_force = bool(dyn_applies_force)
         self._gate_geometry = bool(gate_geometry)
+        # quad_type 3: the PYB_* modes' aerodynamic terms folded into DYN (include/scg_b200.h: dyn_aero): "drag", "ground_effect"
+        unknown = set(dyn_aero) - {"drag", "ground_effect"}
+        if unknown:
+            raise ValueError(f"dyn_aero: unknown term(s) {sorted(unknown)} (downwash is zero for one drone per env)")
+        self._dyn_aero = (1 if "drag" in dyn_aero else 0) | (2 if "ground_effect" in dyn_aero else 0)
         self._auto_reset = bool(auto_reset)
         self._attitude = {"fast": L.ATT_FAST, "roundtrip": L.ATT_ROUNDTRIP, "fast_intrinsic": L.ATT_FAST_INTRINSIC}[attitude]
         if self._attitude == L.ATT_FAST_INTRINSIC and dtype != torch.float32:
@@ -536,4 +541,12 @@ class BatchedQuadrotor(BatchedEnvBase):
         c.dyn_applies_force = int(self._dyn_applies_force)
         c.gate_geometry = int(self._gate_geometry)
         c.auto_reset = int(self._auto_reset)
+        c.dyn_aero = int(self._dyn_aero) if self.QUAD_TYPE == 3 else 0
+        for j, v in enumerate((CF2X["DRAG_COEFF_XY"], CF2X["DRAG_COEFF_XY"], CF2X["DRAG_COEFF_Z"])):   # base_aviary.py:639-641
+            c.aero_drag_coeff[j] = v
+        c.aero_gnd_eff_coeff, c.aero_prop_radius = CF2X["GND_EFF_COEFF"], CF2X["PROP_RADIUS"]
+        c.aero_gnd_eff_h_clip = float(0.25 * CF2X["PROP_RADIUS"] * np.sqrt((15 * self.MAX_RPM ** 2 * self.KF * CF2X["GND_EFF_COEFF"])
+                                                                          / self.MAX_THRUST))                       # base_aviary.py:145-147
+        for j, (x, y) in enumerate(((0.028, 0.028), (-0.028, 0.028), (-0.028, -0.028), (0.028, -0.028))):   # cf2x.urdf prop links
+            c.aero_prop_xy[j][0], c.aero_prop_xy[j][1] = x, y
         return c

@@ -29,7 +29,7 @@ def test_struct_sizes_match_the_header():
     assert C.sizeof(L.Rand) == 24
     assert C.sizeof(L.Constraint) == 4 * 5 + 4 * 12 + 4 + 8 * (12 + 12 + 144 + 24) + 8 + 8 * 24   # with padding to 8
     assert C.sizeof(L.RolloutArgs) == 48
-    assert C.sizeof(L.Buffers) == 8 * 20
+    assert C.sizeof(L.Buffers) == 8 * 21
 
 
 def test_version_and_error_codes_without_a_gpu():
