@@ -570,9 +570,9 @@ __device__ __noinline__ void aero_terms(const Hot<real>& h, real pz, real vx, re
 // Broad phase first: an object whose NOMINAL axis is farther than `broad2` (0.35 m + the largest pose offset) from the
 // drone is skipped before its pose offsets are even drawn -- almost every (env, object) pair of a step.
 template <typename real>
-__device__ __noinline__ uint32_t gate_scan(const Hot<real>& h, const Cold<real>* __restrict__ cold, RngKey key, uint32_t ep,
-                                           real px, real py, real pz, real r0, real r1, real r2, real r3, real r4, real r5,
-                                           real r6, real r7, real r8, uint32_t cur_gate, bool check_gate) {
+SCG_DEV uint32_t gate_scan_body(const Hot<real>& h, const Cold<real>* __restrict__ cold, RngKey key, uint32_t ep,
+                                real px, real py, real pz, real r0, real r1, real r2, real r3, real r4, real r5,
+                                real r6, real r7, real r8, uint32_t cur_gate, bool check_gate) {
     bool collided = false, passed = false;
     for (int g = 0; g < h.n_gates; ++g) {
         const real* G = cold->gates[g];
@@ -630,6 +630,13 @@ __device__ __noinline__ uint32_t gate_scan(const Hot<real>& h, const Cold<real>*
                     sphere_box<real>(p, 0, 0, real(-0.4), real(0.075), real(0.075), real(0.125));
     }
     return (passed ? 1u : 0u) | (collided ? 2u : 0u);   // (the ground plane is the caller's: ground_contact)
+}
+// out of line for the LEAN / GENERAL kernels; the PLAIN + DS loop inlines the body (no call inside the packed loop)
+template <typename real>
+__device__ __noinline__ uint32_t gate_scan(const Hot<real>& h, const Cold<real>* __restrict__ cold, RngKey key, uint32_t ep,
+                                           real px, real py, real pz, real r0, real r1, real r2, real r3, real r4, real r5,
+                                           real r6, real r7, real r8, uint32_t cur_gate, bool check_gate) {
+    return gate_scan_body<real>(h, cold, key, ep, px, py, pz, r0, r1, r2, r3, r4, r5, r6, r7, r8, cur_gate, check_gate);
 }
 
 // ------------------------------------------------------------------ disturbances (row A5)

@@ -402,8 +402,8 @@ SCG_DEV void reset_from_spare(const real* __restrict__ sp, EnvRegs<KIND, real>& 
 constexpr int SPARE_EXTRA = 4 + 3 * SCG_MAX_DIST + SCG_MAX_DIST;   // (+ the CURRENT episode's action-channel offsets, EnvRegs::offc)
 
 template <int KIND, typename real, int ATT>
-__device__ __noinline__ void draw_spare_general(const Hot<real>& h, const Cold<real>* __restrict__ cold, RngKey key, uint32_t ep,
-                                                real* __restrict__ sp) {
+SCG_DEV void draw_spare_general_body(const Hot<real>& h, const Cold<real>* __restrict__ cold, RngKey key, uint32_t ep,
+                                     real* __restrict__ sp) {
     constexpr int NX = Dims<KIND>::NX, N0 = Spare<KIND, real, ATT>::N;
     real init[NX];
 #pragma unroll
@@ -435,6 +435,14 @@ __device__ __noinline__ void draw_spare_general(const Hot<real>& h, const Cold<r
             }
         }
     }
+}
+
+// The LEAN kernels call it out of line (rare code, kept out of their loop); the PLAIN + DS loop inlines it: a call inside the packed
+// loop pushes the loop-carried pairs through the ABI's few callee-saved registers.
+template <int KIND, typename real, int ATT>
+__device__ __noinline__ void draw_spare_general(const Hot<real>& h, const Cold<real>* __restrict__ cold, RngKey key, uint32_t ep,
+                                                real* __restrict__ sp) {
+    draw_spare_general_body<KIND, real, ATT>(h, cold, key, ep, sp);
 }
 
 // ... and what the restarting lane does with it beyond reset_from_spare: publish the episode's inertial properties
@@ -848,8 +856,11 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
                 // pyb_step_counter > 0.5 PYB_FREQ, the counter still at t * S (it advances in after_step, benchmark_env.py:427)
                 //   <=>  2 t > CTRL_FREQ (quadrotor.py:1060)
                 const bool check_gate = 2 * t > h.ctrl_freq && e.gate < uint32_t(h.n_gates);
-                const uint32_t bits = gate_scan<real>(h, cold, key, ep, st[0], st[2], st[4], c.R[0], c.R[1], c.R[2], c.R[3], c.R[4], c.R[5],
-                                                      c.R[6], c.R[7], c.R[8], e.gate, check_gate);
+                uint32_t bits;
+                if constexpr (DS) bits = gate_scan_body<real>(h, cold, key, ep, st[0], st[2], st[4], c.R[0], c.R[1], c.R[2], c.R[3], c.R[4], c.R[5],
+                                                              c.R[6], c.R[7], c.R[8], e.gate, check_gate);
+                else bits = gate_scan<real>(h, cold, key, ep, st[0], st[2], st[4], c.R[0], c.R[1], c.R[2], c.R[3], c.R[4], c.R[5],
+                                            c.R[6], c.R[7], c.R[8], e.gate, check_gate);
                 if (bits & 1u) { e.gate += 1u; gate_passed = true; }
                 collided |= (bits & 2u) != 0u;
             }
@@ -1283,7 +1294,10 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
             const bool cadence = ahead && ((k - k0) & (SPARE_CADENCE - 1)) == 0;   // uniform
             if (bool(int(!spare_ok) & (int(restart) | int(cadence)))) {
                 const uint32_t next_ep = (cfg & CFG_RESEED) ? 0u : uint32_t(e.resets);
-                if ((!PLAIN || DS) && (cfg & CFG_RESET_EXTRAS)) draw_spare_general<KIND, real, ATT>(h, cold, key, next_ep, sp);
+                if ((!PLAIN || DS) && (cfg & CFG_RESET_EXTRAS)) {
+                    if constexpr (DS) draw_spare_general_body<KIND, real, ATT>(h, cold, key, next_ep, sp);
+                    else draw_spare_general<KIND, real, ATT>(h, cold, key, next_ep, sp);
+                }
                 else {
                     real init[NX];
                     draw_init_lean<KIND, real>(h, key, next_ep, init);
