@@ -1,5 +1,5 @@
 """profiles/<tag>_ncu_digests.md from the full ncu captures of tools/capture_all.sh (read here, no GPU):
-    python tools/make_digests.py r2y
+    python tools/make_digests.py r2z
 Per config: kernel, duration, registers, instructions per warp-step, issue / pipe utilisation, threads per instruction,
 DRAM bytes, stall mix, and the source lines that cost the most instructions (joined with the line table of the build)."""
 import os
