@@ -383,11 +383,12 @@ __device__ __noinline__ uint32_t constraint_values_cold(const Hot<real>& h, cons
 // The same values for configs whose rows all come from plain bounded constraints (Hot::crow_*): one pass over the output
 // rows instead of the object / dim / kind loops above (the host-driven step of the level0 family spent 40 % of its
 // instructions there).  Same arithmetic per row: c = lo - x or x - hi, round8, viol_test.
-// Out of line, with the row table in the cold block: it read the table through a reference to the kernel's parameter block once
-// (generic loads: 38 instructions per row, 25 % of the host-driven step's time) and sat inline in every loop once (2 % of
-// BASELINE config 3, which never calls it).
+// The row table sits in the cold block (through a reference to the kernel's parameter block handed to an out-of-line function it
+// was read with generic loads: 38 instructions per row, 25 % of the host-driven step's time).  Inline: the SPEC instantiations,
+// which every fused BASELINE config takes, compile the whole per-step-output path away (c_out == nullptr at compile time), and the
+// kernels that keep it -- the host-driven step above all -- save the ABI call (the caller's live state spilled around it).
 template <int KIND, typename real>
-__device__ __noinline__ uint32_t constraint_values_flat(const Cold<real>* __restrict__ cold, int n_crows, int strict, const real* __restrict__ v,
+SCG_DEV uint32_t constraint_values_flat(const Cold<real>* __restrict__ cold, int n_crows, int strict, const real* __restrict__ v,
                                                         bool state_only, real* __restrict__ c_out, int64_t n, int64_t i) {
     constexpr int NX = Dims<KIND>::NX;
     bool violated = false;

@@ -179,9 +179,12 @@ SCG_DEV void goal_row(const Hot<real>& h, const Cold<real>* __restrict__ cold, i
 }
 
 // obs = state + observation disturbances, then extend_obs (quadrotor.py:878-884, benchmark_env.py:406-420).
-// Out of line: called once per launch (final obs) or on done steps (terminal obs), never in the substep loop.
+// write_obs_body inline / write_obs out of line, chosen per instantiation by measurement (profiles/r2_summary.md): inline for the
+// kernels that write per-step outputs (the host-driven step saves the ABI call and reads the scenario constants from the constant
+// bank: 10.16 -> 9.75 us per step) and for the cart-pole (config 3 +10 %); out of line for the 3D SPEC loops, whose register
+// allocation the inlined epilogue disturbs (level2-like -16 %, headline -1.4 %).  Observation disturbances stay out of line.
 template <int KIND, typename real>
-__device__ __noinline__ void write_obs(const Hot<real>& h, const Cold<real>* __restrict__ cold, const int32_t* __restrict__ dist_offset,
+SCG_DEV void write_obs_body(const Hot<real>& h, const Cold<real>* __restrict__ cold, const int32_t* __restrict__ dist_offset,
                                        real* __restrict__ dst, const real* __restrict__ st, int32_t t_pre, uint32_t obs_index,
                                        RngKey key, uint32_t episode, int64_t n, int64_t i) {
     constexpr int NX = Dims<KIND>::NX;
@@ -204,6 +207,20 @@ __device__ __noinline__ void write_obs(const Hot<real>& h, const Cold<real>* __r
             for (int d = 0; d < NX; ++d) dst[int64_t((r + 1) * NX + d) * n + i] = g[d];
         }
     }
+}
+
+template <int KIND, typename real>
+__device__ __noinline__ void write_obs(const Hot<real>& h, const Cold<real>* __restrict__ cold, const int32_t* __restrict__ dist_offset,
+                                       real* __restrict__ dst, const real* __restrict__ st, int32_t t_pre, uint32_t obs_index,
+                                       RngKey key, uint32_t episode, int64_t n, int64_t i) {
+    write_obs_body<KIND, real>(h, cold, dist_offset, dst, st, t_pre, obs_index, key, episode, n, i);
+}
+template <int KIND, typename real, bool INL>
+SCG_DEV void write_obs_sel(const Hot<real>& h, const Cold<real>* __restrict__ cold, const int32_t* __restrict__ dist_offset,
+                           real* __restrict__ dst, const real* __restrict__ st, int32_t t_pre, uint32_t obs_index,
+                           RngKey key, uint32_t episode, int64_t n, int64_t i) {
+    if constexpr (INL) write_obs_body<KIND, real>(h, cold, dist_offset, dst, st, t_pre, obs_index, key, episode, n, i);
+    else write_obs<KIND, real>(h, cold, dist_offset, dst, st, t_pre, obs_index, key, episode, n, i);
 }
 
 template <typename real> SCG_DEV real rand_value(const RandP<real>& rp, real u, real z) {
@@ -1316,8 +1333,8 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
                     real tl[NX];
 #pragma unroll
                     for (int d = 0; d < NX; ++d) tl[d] = sk[d];
-                    write_obs<KIND, real>(h, cold, b.dist_offset, b.terminal_obs, tl, e.t - 1, uint32_t(e.t), key,
-                                          (cfg & CFG_RESEED) ? 0u : uint32_t(e.resets - 1), n, ii);
+                    write_obs_sel<KIND, real, (!SPEC || KIND == SCG_CARTPOLE)>(h, cold, b.dist_offset, b.terminal_obs, tl, e.t - 1, uint32_t(e.t), key,
+                                                                              (cfg & CFG_RESEED) ? 0u : uint32_t(e.resets - 1), n, ii);
                 }
                 if constexpr (!LEAN) {
                     EnvRegs<KIND, real> ec = e;
@@ -1423,7 +1440,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
         real fl[NX];
 #pragma unroll
         for (int d = 0; d < NX; ++d) fl[d] = st[d];
-        write_obs<KIND, real>(h, cold, b.dist_offset, b.obs, fl, fresh ? 0 : e.t - 1, fresh ? 0u : uint32_t(e.t), key, ep, n, ii);
+        write_obs_sel<KIND, real, (!SPEC || KIND == SCG_CARTPOLE)>(h, cold, b.dist_offset, b.obs, fl, fresh ? 0 : e.t - 1, fresh ? 0u : uint32_t(e.t), key, ep, n, ii);
     }
     b.reward[ii] = reward; b.done[ii] = done ? 1 : 0; b.info[ii] = uint8_t(info);
     if (b.mse) b.mse[ii] = mse;
