@@ -332,6 +332,10 @@ int scg_kernel_variant(const scg_env* env);
 /* Diagnostic: the packed word of uniform scenario switches the kernels branch on (csrc/scg_params.cuh: CFG_*); the SPEC
  * kernels are the ones compiled for particular values of it.  No reference counterpart. */
 uint32_t scg_config_word(const scg_env* env);
+/* Diagnostics: whether the last fused launch ran a SPEC instantiation; keep every launch of this handle on the non-SPEC kernels
+ * (enabled = 0) -- same results, used by the parity tests and for A/B measurements.  No reference counterpart. */
+int scg_last_rollout_spec(const scg_env* env);
+int scg_set_spec_enabled(scg_env* env, int enabled);
 /* Scheduling of the fused rollout launches (scg_rollout / scg_rollout_host / scg_rollout_pid; no reference counterpart:
  * the reference steps one env at a time).  mode -1 (default) = automatic: launches of >= 64 control steps whose env
  * blocks fill the resident block slots of the GPU unevenly (between half a wave and six waves) are cut into chunks of

@@ -34,7 +34,7 @@ STAT_NAMES = ["episodes", "return", "length", "violation_steps", "mse", "gates",
               "completed", "env_steps", "violated_episodes"]
 
 EXPORTS = ["scg_create", "scg_destroy", "scg_bind_buffers", "scg_set_injection", "scg_reset", "scg_step",
-           "scg_rollout", "scg_rollout_host", "scg_rollout_pid", "scg_stats_reset", "scg_stats_read", "scg_config_word", "scg_constraints_eval",
+           "scg_rollout", "scg_rollout_host", "scg_rollout_pid", "scg_stats_reset", "scg_stats_read", "scg_config_word", "scg_last_rollout_spec", "scg_set_spec_enabled", "scg_constraints_eval",
            "scg_symbolic_eval", "scg_symbolic_loss", "scg_gate_info", "scg_measure_fp32_peak", "scg_launch_count", "scg_kernel_variant",
            "scg_set_rollout_queue", "scg_last_rollout_queue", "scg_set_seed", "scg_rollout_noalloc", "scg_last_rollout_tlog",
            "scg_last_error", "scg_version"]
@@ -151,6 +151,8 @@ def load():
     lib.scg_rollout_host.argtypes = [vp, vp, i32, i32, vp]
     lib.scg_rollout_noalloc.argtypes = [vp, C.POINTER(RolloutArgs), vp]
     lib.scg_rollout_pid.argtypes = [vp, C.POINTER(PidConfig), vp, C.POINTER(RolloutArgs), vp, vp]
+    lib.scg_last_rollout_spec.argtypes = [vp]
+    lib.scg_set_spec_enabled.argtypes = [vp, C.c_int]
     lib.scg_config_word.argtypes = [vp]
     lib.scg_config_word.restype = C.c_uint32
     lib.scg_stats_reset.argtypes = [vp, vp]

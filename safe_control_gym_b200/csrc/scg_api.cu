@@ -356,6 +356,12 @@ extern "C" int scg_set_rollout_queue(scg_env* env, int32_t mode, int32_t chunk_s
 }
 extern "C" int scg_last_rollout_queue(const scg_env* env) { return env ? env->last_queue : 0; }
 extern "C" int scg_last_rollout_tlog(const scg_env* env) { return env ? env->last_tlog : 0; }
+extern "C" int scg_last_rollout_spec(const scg_env* env) { return env ? env->last_spec : 0; }
+extern "C" int scg_set_spec_enabled(scg_env* env, int enabled) {
+    if (!env) return fail(SCG_ERR_NULL, "scg_set_spec_enabled: null handle");
+    env->spec_enabled = enabled ? 1 : 0;
+    return SCG_OK;
+}
 // BenchmarkEnv.seed (benchmark_env.py:220-235): the Philox key of every later draw.  The constant block travels by value
 // with each launch, so the host copy is all there is to patch.
 extern "C" int scg_set_seed(scg_env* env, uint32_t seed) {

@@ -35,6 +35,8 @@ struct scg_env {
     unsigned queue_sleep_ns = 500; // poll interval of a block that waits for its ticket's predecessor (SCG_QUEUE_SLEEP)
     int queue_blocks_per_sm = 8;   // workers of a queued launch per SM (0: every resident slot); 8 x 148 for 1,024 env blocks measured best
     int last_queue = 0;            // the last rollout launch went through the queue (scg_last_rollout_queue)
+    int last_spec = 0;             // ... ran a SPEC instantiation (scg_last_rollout_spec)
+    int spec_enabled = 1;          // scg_set_spec_enabled: 0 keeps every launch on the non-SPEC kernels (A/B runs, parity tests)
     int last_tlog = 0;             // ... wrote its trajectory log through the TMA unit (scg_last_rollout_tlog)
 };
 

@@ -99,16 +99,19 @@ template <int KIND, typename real, int ATT>
 static void launch_rollout_att(scg_env* e, const Hot<real>& h, const Cold<real>* cold, const Buf<real>& b, const Roll<real>& ro,
                                unsigned blocks, cudaStream_t st) {
     constexpr bool F32 = sizeof(real) == 4;
+    e->last_spec = 0;
     if (e->lean && e->plain && !ro.use_pid && F32) {
-        if (KIND == SCG_QUAD_3D && !ro.step_outputs && (h.cfg & CFG_SPEC_MASK) == CFG_SPEC_VAL)
+        if (KIND == SCG_QUAD_3D && !ro.step_outputs && e->spec_enabled && (h.cfg & CFG_SPEC_MASK) == CFG_SPEC_VAL) {
+            e->last_spec = 1;
             launch_rollout_v<KIND, real, ATT, true, F32, (F32 && KIND == SCG_QUAD_3D)>(e, h, cold, b, ro, blocks, st);
-        else launch_rollout_v<KIND, real, ATT, true, F32, false>(e, h, cold, b, ro, blocks, st);
+        } else launch_rollout_v<KIND, real, ATT, true, F32, false>(e, h, cold, b, ro, blocks, st);
     }
     else if (e->lean && F32 && KIND != SCG_QUAD_1D && (KIND == SCG_QUAD_3D || !ro.use_pid) && ds_kernel_ok(h) &&
              !(KIND == SCG_QUAD_3D && h.dyn_uses_episode_inertia)) {   // (quad_type 3: closed-loop launches too)
-        if (KIND != SCG_QUAD_1D && !ro.step_outputs && (h.cfg & SpecCfg<KIND>::MASK) == SpecCfg<KIND>::VAL)   // this kind's family switches compiled in (SpecCfg)
+        if (KIND != SCG_QUAD_1D && !ro.step_outputs && e->spec_enabled && (h.cfg & SpecCfg<KIND>::MASK) == SpecCfg<KIND>::VAL) {   // this kind's family switches compiled in (SpecCfg)
+            e->last_spec = 1;
             launch_rollout_v<KIND, real, ATT, true, F32, (F32 && KIND != SCG_QUAD_1D), (F32 && KIND != SCG_QUAD_1D)>(e, h, cold, b, ro, blocks, st);
-        else launch_rollout_v<KIND, real, ATT, true, F32, false, (F32 && KIND != SCG_QUAD_1D)>(e, h, cold, b, ro, blocks, st);
+        } else launch_rollout_v<KIND, real, ATT, true, F32, false, (F32 && KIND != SCG_QUAD_1D)>(e, h, cold, b, ro, blocks, st);
     }
     else if (e->lean) launch_rollout_v<KIND, real, ATT, true, false, false>(e, h, cold, b, ro, blocks, st);
     else launch_rollout_v<KIND, real, ATT, false, false, false>(e, h, cold, b, ro, blocks, st);
@@ -121,7 +124,7 @@ int launch_rollout(scg_env* e, const Roll<real>& ro, cudaStream_t st) {
     const unsigned blocks = unsigned((b.n + ENV_BLOCK - 1) / ENV_BLOCK);
     const Cold<real>* cold = static_cast<const Cold<real>*>(e->cold_dev);
     const int att = e->cfg.attitude_mode;
-    e->last_tlog = 0;
+    e->last_tlog = 0; e->last_spec = 0;
     if constexpr (KIND == SCG_QUAD_3D && sizeof(real) == 4) {
         if (ro.log_out && e->queue_mode != 1 && launch_rollout_tlog_3d_f(e, ro, st)) {   // staged (TMA) trajectory log
             e->launches += 1;

@@ -37,7 +37,8 @@ static bool encode(CUtensorMap* m, void* base, uint64_t n, uint64_t rows, uint32
 template <int ATT, bool DS>
 static void launch_att(scg_env* e, const Hot<float>& h, const Cold<float>* cold, const Buf<float>& b, const Roll<float>& ro,
                        const LogMaps& maps, unsigned blocks, cudaStream_t st) {
-    if ((h.cfg & CFG_SPEC_MASK) == CFG_SPEC_VAL) k_rollout_tlog<ATT, DS, true><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro, maps);
+    e->last_spec = (e->spec_enabled && (h.cfg & CFG_SPEC_MASK) == CFG_SPEC_VAL) ? 1 : 0;
+    if (e->last_spec) k_rollout_tlog<ATT, DS, true><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro, maps);
     else k_rollout_tlog<ATT, DS, false><<<blocks, ENV_BLOCK, 0, st>>>(h, cold, b, ro, maps);
 }
 

@@ -194,6 +194,15 @@ class BatchedEnvBase:
         """True when the last fused rollout wrote its trajectory log through the TMA unit (scg_last_rollout_tlog)."""
         return bool(self.lib.scg_last_rollout_tlog(self._h))
 
+    @property
+    def last_rollout_spec(self):
+        """True when the last fused rollout ran a SPEC instantiation (the scenario switches of its family compiled in)."""
+        return bool(self.lib.scg_last_rollout_spec(self._h))
+
+    def set_spec_enabled(self, enabled):
+        """Keep this env's launches on the non-SPEC kernels (``False``): same results; parity tests and A/B measurements."""
+        L.check(self.lib.scg_set_spec_enabled(self._h, int(bool(enabled))))
+
     def set_injection(self, channel, k, tensor):
         """Feed pre-drawn noise for disturbance ``k`` of ``channel`` ([dim, N]); None = Philox."""
         ch = {"observation": L.CH_OBSERVATION, "action": L.CH_ACTION, "dynamics": L.CH_DYNAMICS}[channel]
