@@ -347,3 +347,28 @@ def test_tma_staged_log_equals_plain_log(variant, n, k, stride):
     c.rollout(_actions(4099, 8), log_out=torch.empty(8, 16, 4099, device="cuda"))
     assert not c.last_rollout_tlog
     a.close(); b.close(); c.close()
+
+
+def test_stats_read_folds_the_replicas():
+    """The device accumulators are SCG_STAT_REPLICAS copies of the statistics vector (a warp adds to copy `warp index mod 64`);
+    scg_stats_read returns their totals -- equal to the facade's own fold, with every warp-group copy in use, and zeroed by
+    scg_stats_reset."""
+    import ctypes as C
+    from safe_control_gym_b200 import _lib as L
+    n, k = 64 * 200 + 40, 70
+    env = _quad(n, attitude="fast_intrinsic")
+    env.reset()
+    env.rollout(_actions(n, k, std=0.01))
+    for t in range(3):
+        env.step(_actions(n, 1, std=0.01)[0])
+    out = (C.c_double * L.STATS_LEN)()
+    L.check(env.lib.scg_stats_read(env._h, out, env._stream()))
+    torch.cuda.synchronize()
+    want = env.stats_vector().cpu().numpy()
+    assert np.array_equal(np.array(out[:]), want)
+    assert want[L.STAT_NAMES.index("env_steps")] == n * (k + 3)
+    assert int((env.buf_stats[:, L.STAT_NAMES.index("env_steps")] > 0).sum()) == L.STAT_REPLICAS   # every replica took its share
+    L.check(env.lib.scg_stats_reset(env._h, env._stream()))
+    torch.cuda.synchronize()
+    assert float(env.buf_stats.abs().sum()) == 0.0
+    env.close()
