@@ -59,10 +59,10 @@ static bool launch_queued(scg_env* e, K kernel, bool plain, const int64_t n, int
     return true;
 }
 
-template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN, bool SPEC, bool DS = false>
+template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN, int SPEC, bool DS = false>
 static void launch_rollout_v(scg_env* e, const Hot<real>& h, const Cold<real>* cold, const Buf<real>& b, const Roll<real>& ro,
                              unsigned blocks, cudaStream_t st) {
-    if constexpr (LEAN && sizeof(real) == 4) {
+    if constexpr (LEAN && sizeof(real) == 4 && SPEC != 2) {   // (SPEC 2: launches with per-step outputs are never queued)
         Roll<real> rq = ro;
         unsigned grid = 0;
         if (!ro.step_outputs && launch_queued(e, k_rollout<KIND, real, ATT, LEAN, PLAIN, SPEC, true, DS>, PLAIN && !DS, b.n, ro.k_steps, &rq.q_chunk,
@@ -101,20 +101,21 @@ static void launch_rollout_att(scg_env* e, const Hot<real>& h, const Cold<real>*
     constexpr bool F32 = sizeof(real) == 4;
     e->last_spec = 0;
     if (e->lean && e->plain && !ro.use_pid && F32) {
-        if (KIND == SCG_QUAD_3D && !ro.step_outputs && e->spec_enabled && (h.cfg & CFG_SPEC_MASK) == CFG_SPEC_VAL) {
-            e->last_spec = 1;
-            launch_rollout_v<KIND, real, ATT, true, F32, (F32 && KIND == SCG_QUAD_3D)>(e, h, cold, b, ro, blocks, st);
-        } else launch_rollout_v<KIND, real, ATT, true, F32, false>(e, h, cold, b, ro, blocks, st);
+        if (KIND == SCG_QUAD_3D && e->spec_enabled && (h.cfg & CFG_SPEC_MASK) == CFG_SPEC_VAL) {
+            e->last_spec = ro.step_outputs ? 2 : 1;
+            if (ro.step_outputs) launch_rollout_v<KIND, real, ATT, true, F32, ((F32 && KIND == SCG_QUAD_3D) ? 2 : 0)>(e, h, cold, b, ro, blocks, st);
+            else launch_rollout_v<KIND, real, ATT, true, F32, ((F32 && KIND == SCG_QUAD_3D) ? 1 : 0)>(e, h, cold, b, ro, blocks, st);
+        } else launch_rollout_v<KIND, real, ATT, true, F32, 0>(e, h, cold, b, ro, blocks, st);
     }
     else if (e->lean && F32 && KIND != SCG_QUAD_1D && (KIND == SCG_QUAD_3D || !ro.use_pid) && ds_kernel_ok(h) &&
              !(KIND == SCG_QUAD_3D && h.dyn_uses_episode_inertia)) {   // (quad_type 3: closed-loop launches too)
         if (KIND != SCG_QUAD_1D && !ro.step_outputs && e->spec_enabled && (h.cfg & SpecCfg<KIND>::MASK) == SpecCfg<KIND>::VAL) {   // this kind's family switches compiled in (SpecCfg)
             e->last_spec = 1;
-            launch_rollout_v<KIND, real, ATT, true, F32, (F32 && KIND != SCG_QUAD_1D), (F32 && KIND != SCG_QUAD_1D)>(e, h, cold, b, ro, blocks, st);
-        } else launch_rollout_v<KIND, real, ATT, true, F32, false, (F32 && KIND != SCG_QUAD_1D)>(e, h, cold, b, ro, blocks, st);
+            launch_rollout_v<KIND, real, ATT, true, F32, ((F32 && KIND != SCG_QUAD_1D) ? 1 : 0), (F32 && KIND != SCG_QUAD_1D)>(e, h, cold, b, ro, blocks, st);
+        } else launch_rollout_v<KIND, real, ATT, true, F32, 0, (F32 && KIND != SCG_QUAD_1D)>(e, h, cold, b, ro, blocks, st);
     }
-    else if (e->lean) launch_rollout_v<KIND, real, ATT, true, false, false>(e, h, cold, b, ro, blocks, st);
-    else launch_rollout_v<KIND, real, ATT, false, false, false>(e, h, cold, b, ro, blocks, st);
+    else if (e->lean) launch_rollout_v<KIND, real, ATT, true, false, 0>(e, h, cold, b, ro, blocks, st);
+    else launch_rollout_v<KIND, real, ATT, false, false, 0>(e, h, cold, b, ro, blocks, st);
 }
 
 template <int KIND, typename real>

@@ -1138,7 +1138,9 @@ k_reset(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold
 constexpr int SPARE_CADENCE = SCG_SPARE_CADENCE;   // control steps between the warp-wide spare refills (power of two)
 constexpr int ACC_LD = ENV_BLOCK + 1;   // column ENV_BLOCK is the scratch column of out-of-range lanes
 constexpr int N_ACC = 11;   // episodes, return, length, truncated, completed, violated episodes, violation steps, (mse: double column), env steps, gates, collisions
-template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN, bool SPEC, bool TLOG = false, bool DS = false>
+// SPEC: 0 none; 1 the kind's family (SpecCfg) for fused launches without per-step outputs; 2 (quad_type 3 PLAIN only) the same family
+// for launches WITH per-step outputs -- the host-driven scg_step (9.73 -> 9.12 us per step at 65,536 envs).
+template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN, int SPEC, bool TLOG = false, bool DS = false>
 SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ cold, const Buf<real>& b, const Roll<real>& ro,
                            const int64_t i, const int k0, const int k1, float* const ep_acc, double* const mse_acc, real* const sp,
                            const LogMaps* const lg_maps = nullptr, float* const lg_warp = nullptr, real* const pm = nullptr) {
@@ -1187,9 +1189,10 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
     Motors<real> mot;
     // the uniform switches of the loop in one word (see CFG_*)
     const uint32_t cfg_rt = h.cfg | (ro.step_outputs ? (CFG_FULL_STATE | CFG_STEP_OUTPUTS) : 0u);
-    const uint32_t cfg = SPEC ? ((cfg_rt & ~SpecCfg<KIND>::MASK) | SpecCfg<KIND>::VAL) : cfg_rt;
+    const uint32_t cfg = SPEC == 1 ? ((cfg_rt & ~SpecCfg<KIND>::MASK) | SpecCfg<KIND>::VAL)
+                       : SPEC == 2 ? ((cfg_rt & ~SpecCfg<KIND>::MASK) | SpecCfg<KIND>::VAL | CFG_FULL_STATE | CFG_STEP_OUTPUTS) : cfg_rt;
     const bool full = (cfg & CFG_FULL_STATE) != 0u;
-    real* const c_out = SPEC ? nullptr : ((ro.step_outputs && valid) ? b.c_values : nullptr);
+    real* const c_out = SPEC == 1 ? nullptr : ((ro.step_outputs && valid) ? b.c_values : nullptr);
     // software prefetch of the next action (one 16-byte load per 3D env per step)
     real raw[NU], nxt[NU];
     // uniform: actions from the on-device PID (scg_pid.cuh); its memory rides in the shared-memory column pm[j * ENV_BLOCK]
@@ -1333,7 +1336,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
                     real tl[NX];
 #pragma unroll
                     for (int d = 0; d < NX; ++d) tl[d] = sk[d];
-                    write_obs_sel<KIND, real, (!SPEC || KIND == SCG_CARTPOLE)>(h, cold, b.dist_offset, b.terminal_obs, tl, e.t - 1, uint32_t(e.t), key,
+                    write_obs_sel<KIND, real, (SPEC != 1 || KIND == SCG_CARTPOLE)>(h, cold, b.dist_offset, b.terminal_obs, tl, e.t - 1, uint32_t(e.t), key,
                                                                               (cfg & CFG_RESEED) ? 0u : uint32_t(e.resets - 1), n, ii);
                 }
                 if constexpr (!LEAN) {
@@ -1440,7 +1443,7 @@ SCG_DEV void rollout_range(const Hot<real>& h, const Cold<real>* __restrict__ co
         real fl[NX];
 #pragma unroll
         for (int d = 0; d < NX; ++d) fl[d] = st[d];
-        write_obs_sel<KIND, real, (!SPEC || KIND == SCG_CARTPOLE)>(h, cold, b.dist_offset, b.obs, fl, fresh ? 0 : e.t - 1, fresh ? 0u : uint32_t(e.t), key, ep, n, ii);
+        write_obs_sel<KIND, real, (SPEC != 1 || KIND == SCG_CARTPOLE)>(h, cold, b.dist_offset, b.obs, fl, fresh ? 0 : e.t - 1, fresh ? 0u : uint32_t(e.t), key, ep, n, ii);
     }
     b.reward[ii] = reward; b.done[ii] = done ? 1 : 0; b.info[ii] = uint8_t(info);
     if (b.mse) b.mse[ii] = mse;
@@ -1500,8 +1503,8 @@ SCG_DEV void st_release_gpu(int32_t* p, int32_t v) { asm volatile("st.release.gp
 // four-warp ones set the makespan; through the queue every scheduler hosts four warps, the ~14 % that wait for a range
 // sleep, and a scheduler that runs ahead simply takes more ranges (same result: the split into ranges is invisible, see
 // rollout_range).
-template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN = false, bool SPEC = false, bool QUEUE = false, bool DS = false>
-__global__ void __launch_bounds__(ENV_BLOCK, sizeof(real) == 4 ? (DS ? SCG_DS_BLOCKS : (SPEC ? SCG_BLOCKS_PER_SM : 8)) : 1)
+template <int KIND, typename real, int ATT, bool LEAN, bool PLAIN = false, int SPEC = 0, bool QUEUE = false, bool DS = false>
+__global__ void __launch_bounds__(ENV_BLOCK, sizeof(real) == 4 ? (DS ? SCG_DS_BLOCKS : (SPEC == 1 ? SCG_BLOCKS_PER_SM : 8)) : 1)
 k_rollout(const __grid_constant__ Hot<real> h, const Cold<real>* __restrict__ cold, const Buf<real> b, const Roll<real> ro) {
     if constexpr (!QUEUE) {
         if (ro.pdl) {   // uniform; scg_inst.cuh: launch_rollout_v.  Nothing above this line reads batch memory.

@@ -47,6 +47,13 @@ def test_spec_kernels_equal_the_generic_ones(cid):
         assert torch.equal(ra, rb) and torch.equal(da, db)
         for name in ("state", "ctrl_step", "episode", "flags", "obs", "ep_return", "ep_length", "inertia", "dist_offset"):
             assert torch.equal(getattr(a, "buf_" + name), getattr(b, "buf_" + name)), (cid, queue, name)
+    if cid == "2":   # the host-driven step has its own instantiation of the family (SPEC = 2: per-step outputs compiled in)
+        for t in range(40):
+            oa, rwa, dna, ia = a.step(A[t]); ob, rwb, dnb, ib = b.step(A[t])
+            assert int(a.lib.scg_last_rollout_spec(a._h)) == 2 and int(b.lib.scg_last_rollout_spec(b._h)) == 0
+            assert torch.equal(oa, ob) and torch.equal(rwa, rwb) and torch.equal(dna, dnb)
+            for name in ("info", "c_values", "mse", "terminal_obs", "env_state", "state", "flags"):
+                assert torch.equal(getattr(a, "buf_" + name), getattr(b, "buf_" + name)), (t, name)
     sa, sb = a.stats(), b.stats()
     assert sa == sb and sa["episodes"] > 0
     if cid == "5":   # the logged form (TMA store) too
