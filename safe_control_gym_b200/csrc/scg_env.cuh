@@ -526,8 +526,9 @@ SCG_DEV void pose_offsets(const RandP<real>& rp, uint32_t stream, uint32_t idx, 
 }
 
 // ground plane against the drone's collision cylinder: its support along -z
-template <typename real> SCG_DEV bool ground_contact(real pz, real r8) {
-    const real support = Geo<real>::drone_hl * m_abs(r8) + Geo<real>::drone_r * m_sqrt(m_max(real(0), real(1) - r8 * r8));
+template <typename real, bool FAST = false> SCG_DEV bool ground_contact(real pz, real r8) {
+    const real s2 = m_max(real(0), real(1) - r8 * r8);
+    const real support = Geo<real>::drone_hl * m_abs(r8) + Geo<real>::drone_r * (FAST ? sqrt_fast(s2) : m_sqrt(s2));   // (FAST: MUFU.SQRT, no slow-path call in the loop)
     return pz - support < real(0);
 }
 

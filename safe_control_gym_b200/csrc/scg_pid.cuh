@@ -40,12 +40,16 @@ SCG_DEV void pid_action(const PidP<real>& P, const real (&pos)[3], const real (&
     }
     tt[2] += P.gravity;
     const real scalar = m_max(real(0), (tt[0] * R[2] + tt[1] * R[5]) + tt[2] * R[8]);
-    const real thrust = (m_sqrt(scalar * P.inv_4kf) - P.pwm_const) * P.inv_pwm_scale;
-    const real inv_n = real(1) / m_sqrt((tt[0] * tt[0] + tt[1] * tt[1]) + tt[2] * tt[2]);
+    // fp32 fast attitude modes: MUFU square root / reciprocal square root (a few ulp, like the integrator's own fast map)
+    constexpr bool FASTM = sizeof(real) == 4 && ATT != SCG_ATT_ROUNDTRIP;
+    const real thrust = ((FASTM ? sqrt_fast(scalar * P.inv_4kf) : m_sqrt(scalar * P.inv_4kf)) - P.pwm_const) * P.inv_pwm_scale;
+    const real n2 = (tt[0] * tt[0] + tt[1] * tt[1]) + tt[2] * tt[2];
+    const real inv_n = FASTM ? m_rsqrt(n2) : real(1) / m_sqrt(n2);
     const real z[3] = {tt[0] * inv_n, tt[1] * inv_n, tt[2] * inv_n};
     // target yaw 0: x_c = (1, 0, 0); y = z x x_c / |.|, x = y x z; M = [x y z] (columns)
     real y[3] = {real(0), z[2], -z[1]};
-    const real inv_y = real(1) / m_sqrt(y[1] * y[1] + y[2] * y[2]);
+    const real y2 = y[1] * y[1] + y[2] * y[2];
+    const real inv_y = FASTM ? m_rsqrt(y2) : real(1) / m_sqrt(y2);
     y[1] *= inv_y; y[2] *= inv_y;
     const real x[3] = {y[1] * z[2] - y[2] * z[1], y[2] * z[0] - y[0] * z[2], y[0] * z[1] - y[1] * z[0]};
     const real M[9] = {x[0], y[0], z[0], x[1], y[1], z[1], x[2], y[2], z[2]};

@@ -855,7 +855,7 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
         if (cfg & CFG_GATE_GEOMETRY) {   // extension: the contact scan and the gate rays on the integrated pose
             real r8;
             if constexpr (PAIRED) r8 = e.R8; else r8 = e.a3.R[8];
-            collided = ground_contact<real>(st[4], r8);
+            collided = ground_contact<real, FASTMATH>(st[4], r8);
             // first broad phase, inline on constant-bank operands (Hot::geo): is the drone near ANY gate / obstacle axis?
             bool near = false;
             const f32x2 P = pk2(float(st[0]), float(st[2]));
