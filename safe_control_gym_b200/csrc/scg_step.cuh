@@ -950,7 +950,9 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
 #pragma unroll
             for (int j = 0; j < NU; ++j) { const real er = pre[j] - h.u_goal[j]; dact += h.rew_act_weight[j] * er * er; }
             reward = -(dist + dact);
-            if (cfg & CFG_REW_EXP) reward = m_exp(reward);
+            if (cfg & CFG_REW_EXP) {   // fp32 fast modes: MUFU.EX2 (|err| ~ 2 ulp of a value in (0, 1]); literal modes: expf / exp
+                if constexpr (FASTMATH) reward = __expf(float(reward)); else reward = m_exp(reward);
+            }
         } else if (cfg & CFG_COST_QUAD) {
             real lx = real(0), lu = real(0);
             if (PLAIN || !(cfg & CFG_QR_DENSE)) {
