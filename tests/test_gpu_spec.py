@@ -55,7 +55,12 @@ def test_spec_kernels_equal_the_generic_ones(cid):
             for name in ("info", "c_values", "mse", "terminal_obs", "env_state", "state", "flags"):
                 assert torch.equal(getattr(a, "buf_" + name), getattr(b, "buf_" + name)), (t, name)
     sa, sb = a.stats(), b.stats()
-    assert sa == sb and sa["episodes"] > 0
+    assert sa["episodes"] > 0
+    for key in sa:   # counts are exact; the two fp64 sums are formed by atomics in launch order (last bits may differ)
+        if key in ("return", "mse"):
+            assert abs(sa[key] - sb[key]) <= 1e-9 * max(1.0, abs(sb[key])), key
+        else:
+            assert sa[key] == sb[key], key
     if cid == "5":   # the logged form (TMA store) too
         la, lb = torch.empty(16, 16, n, device="cuda"), torch.empty(16, 16, n, device="cuda")
         a.set_rollout_queue(-1); b.set_rollout_queue(-1)
