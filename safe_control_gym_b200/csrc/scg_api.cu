@@ -204,16 +204,17 @@ static int build_params(const scg_config& c, int nx, int nu, Hot<real>& h, Cold<
             return double(INFINITY);
         };
         k.gate_broad2 = real(broad2(c.gate_rand)); k.obstacle_broad2 = real(broad2(c.obstacle_rand));
-        // the inline copy of the same test (Hot::geo): fp32, radius widened by 1e-4 relative so that it never rejects what the scan accepts
+        // the inline copy of the same test (Hot::geo_*): fp32, radius widened by 2e-4 relative so that it never rejects what the scan accepts
         h.geo_n = 0;
-        for (int g = 0; g < c.n_gates; ++g, ++h.geo_n) {
-            h.geo_neg[h.geo_n][0] = -float(c.gates[g][0]); h.geo_neg[h.geo_n][1] = -float(c.gates[g][1]);
-            h.geo_r2[h.geo_n] = float(broad2(c.gate_rand) * 1.0002 + 1e-6);
-        }
-        for (int g = 0; g < c.n_obstacles; ++g, ++h.geo_n) {
-            h.geo_neg[h.geo_n][0] = -float(c.obstacles[g][0]); h.geo_neg[h.geo_n][1] = -float(c.obstacles[g][1]);
-            h.geo_r2[h.geo_n] = float(broad2(c.obstacle_rand) * 1.0002 + 1e-6);
-        }
+        for (int q = 0; q < (SCG_MAX_GATES + SCG_MAX_OBSTACLES) / 2; ++q)
+            for (int w = 0; w < 2; ++w) { h.geo_negx[q][w] = -1e18f; h.geo_negy[q][w] = -1e18f; h.geo_r2[q][w] = 0.f; }   // padding: never near
+        auto put = [&](double x, double y, double r2) {
+            h.geo_negx[h.geo_n >> 1][h.geo_n & 1] = -float(x); h.geo_negy[h.geo_n >> 1][h.geo_n & 1] = -float(y);
+            h.geo_r2[h.geo_n >> 1][h.geo_n & 1] = float(r2 * 1.0002 + 1e-6);
+            ++h.geo_n;
+        };
+        for (int g = 0; g < c.n_gates; ++g) put(c.gates[g][0], c.gates[g][1], broad2(c.gate_rand));
+        for (int g = 0; g < c.n_obstacles; ++g) put(c.obstacles[g][0], c.obstacles[g][1], broad2(c.obstacle_rand));
     }
     k.n_obstacles = c.n_obstacles;
     h.seed = c.seed; h.env_id_base_lo = uint32_t(c.env_id_base & 0xFFFFFFFFll);

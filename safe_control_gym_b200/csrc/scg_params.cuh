@@ -99,8 +99,9 @@ template <typename real> struct Hot {
     int32_t aero;
     real aero_drag[3], aero_gnd_coeff, aero_prop_radius, aero_h_clip, aero_prop_xy[4][2];
     int32_t geo_n;
-    alignas(8) float geo_neg[SCG_MAX_GATES + SCG_MAX_OBSTACLES][2];   // (-x, -y): one packed add per object
-    float geo_r2[SCG_MAX_GATES + SCG_MAX_OBSTACLES];
+    // two objects per packed operation: (-x_2j, -x_2j+1), (-y_2j, -y_2j+1), (r2_2j, r2_2j+1); an odd count is padded with an object at infinity
+    alignas(8) float geo_negx[(SCG_MAX_GATES + SCG_MAX_OBSTACLES) / 2][2], geo_negy[(SCG_MAX_GATES + SCG_MAX_OBSTACLES) / 2][2];
+    float geo_r2[(SCG_MAX_GATES + SCG_MAX_OBSTACLES) / 2][2];
     // the uniform switches the control-step loop tests, packed (CFG_*): one constant-bank word feeds all of
     // them, where a separate field per switch costs a dependent load -> compare -> branch chain each
     uint32_t cfg;

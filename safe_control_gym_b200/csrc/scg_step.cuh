@@ -858,13 +858,13 @@ SCG_DEV void step_env(const Hot<real>& h, const Cold<real>* __restrict__ cold, c
             collided = ground_contact<real, FASTMATH>(st[4], r8);
             // first broad phase, inline on constant-bank operands (Hot::geo): is the drone near ANY gate / obstacle axis?
             bool near = false;
-            const f32x2 P = pk2(float(st[0]), float(st[2]));
+            const f32x2 PX = bc2(float(st[0])), PY = bc2(float(st[2]));
 #pragma unroll
-            for (int j = 0; j < SCG_MAX_GATES + SCG_MAX_OBSTACLES; ++j) {
-                if (j >= h.geo_n) break;   // uniform
-                const f32x2 D = add2(P, *reinterpret_cast<const f32x2*>(h.geo_neg[j]));
-                const f32x2 S = mul2(D, D);
-                near |= lo2(S) + hi2(S) <= h.geo_r2[j];
+            for (int j = 0; j < (SCG_MAX_GATES + SCG_MAX_OBSTACLES) / 2; ++j) {   // two objects per packed operation
+                if (2 * j >= h.geo_n) break;   // uniform
+                const f32x2 DX = add2(PX, *reinterpret_cast<const f32x2*>(h.geo_negx[j])), DY = add2(PY, *reinterpret_cast<const f32x2*>(h.geo_negy[j]));
+                const f32x2 S = fma2(DX, DX, mul2(DY, DY));
+                near |= (lo2(S) <= h.geo_r2[j][0]) | (hi2(S) <= h.geo_r2[j][1]);
             }
             if (near) {   // rare: the whole rotation matrix (the gate rays work in the body frame) and the exact scan, out of line
                 Att3<real> c = e.a3;
